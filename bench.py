@@ -1,0 +1,360 @@
+#!/usr/bin/env python
+"""bench.py — MCTS simulations/s of the self-play search hot path (BASELINE.json metric) on N B200s.
+
+A "step" is one pass of the hot path over one batch: T concurrent searches (initial inference + num_simulations x
+{tree step, recurrent inference} + statistics) on synthetic observations of the workload's shape, random-init weights.
+  value : whole-job sims/s with the observations already resident in HBM (device time, CUDA events, max over ranks)
+  e2e   : same metric through the public C-ABI call with HOST buffers (H2D of observations + D2H of results inside)
+  roofline     : the residual-tower kernels (tensor bound): F_rec x states/s vs the measured bf16 peak
+  roofline_tree: the tree kernels alone (HBM bound; network stubbed by the SE evaluator)
+  cpu_baseline : the reference's own CPU path (oracle/_ref/ref_driver bench) on this box's host cores, bounded sample
+`--impl reference` times only that CPU path and prints the same line shape.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "muzero-cpp_b200"))
+
+METRIC = "mcts_sims_per_s"
+UNIT = "sims/s"
+WORKLOADS = {  # BASELINE.json configs that fit one GPU; configs[1] is the headline
+    "c4d": dict(desc="Connect4 example, 50 sims/move, ResNet tower 128ch x 4+4+4 blocks, 1024 concurrent games per GPU", trees=1024),
+    "c4r": dict(desc="Connect4, README/shipped tower 64ch x 3 blocks, 50 sims, 1024 concurrent games per GPU", trees=1024),
+    "reanalyze": dict(desc="Connect4 reanalyze: batched re-search of 4096 replay positions per GPU, 50 sims", trees=4096, preset="c4d"),
+    "ale": dict(desc="ALE/Pong-shaped synthetic 96x96 stacked frames, downsample ResNet, 50 sims, 18 actions, 1024 games per GPU", trees=1024),
+    "ttt": dict(desc="TicTacToe, 25 sims/move (reference CPU-runnable case)", trees=1024),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d["bf16_tflops_sustained"], source="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.samples, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            tok = [t.strip() for t in s.split(",")]
+            if len(tok) < 7:
+                continue
+            try:
+                sm.append(float(tok[0])); mx = float(tok[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, tok[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm))
+
+
+def run_reference_cpu(game, seconds_target, sims):
+    """The reference's own CPU path on this box's host cores (oracle/_ref/ref_driver bench: unmodified MCTS::run +
+    VPRNetEvaluator + DeviceManager + VPRNetModel on libtorch CPU, --devices=cpu,cpu semantics).  Bounded sample."""
+    drv = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+    cores = os.cpu_count() or 1
+    if not os.path.exists(drv):
+        return None
+    actors = max(4, min(cores, 64))
+    # calibrate: one move per actor, then scale the number of moves to the time target
+    best = None
+    for moves in (1,):
+        out = subprocess.run([drv, "bench", "game=" + game, "sims=%d" % sims, "actors=%d" % actors, "batch=%d" % actors,
+                              "moves=%d" % moves, "devices=2"], capture_output=True, text=True, timeout=1200)
+        if out.returncode != 0:
+            return dict(error=out.stderr[-300:])
+        best = json.loads(out.stdout.strip().splitlines()[-1])
+    moves = int(max(1, min(50, seconds_target / max(best["seconds"], 1e-3))))
+    if moves > 1:
+        out = subprocess.run([drv, "bench", "game=" + game, "sims=%d" % sims, "actors=%d" % actors, "batch=%d" % actors,
+                              "moves=%d" % moves, "devices=2"], capture_output=True, text=True, timeout=1800)
+        if out.returncode == 0:
+            best = json.loads(out.stdout.strip().splitlines()[-1])
+    best["cores"] = cores
+    return best
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c4d", choices=sorted(WORKLOADS))
+    ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "fp32"])
+    ap.add_argument("--trees", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    wl = WORKLOADS[args.workload]
+    preset_name = wl.get("preset", args.workload)
+
+    import mzb200
+    cfg0 = mzb200.preset(preset_name)
+    sims = cfg0.num_simulations
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        t0 = time.time()
+        vals = []
+        for _ in range(max(1, args.warmup) - 1 + 0):
+            pass
+        res = None
+        for _ in range(max(1, min(args.steps, 3))):
+            res = run_reference_cpu(preset_name, args.cpu_seconds, sims)
+            if res is None or "error" in res:
+                break
+            vals.append(res["sims_per_s"])
+        if not vals:
+            # the oracle port always exists: time the C/torch-CPU restatement instead
+            res = run_port_cpu(preset_name, args.cpu_seconds, sims)
+            vals = [res["sims_per_s"]]
+            kind = "port"
+        else:
+            kind = "reference"
+        v = sum(vals) / len(vals)
+        line = dict(metric=METRIC, value=v, unit=UNIT, n_gpus=args.gpus, steps=len(vals), warmup=0,
+                    ms_per_step=1000.0 * res["seconds"], higher_is_better=True, scaling="weak", vs_baseline=None,
+                    dtype="f32", data="synthetic", impl="reference",
+                    config=dict(workload=wl["desc"], sims_per_move=sims),
+                    cpu_baseline=dict(value=v, unit=UNIT, cores=res.get("cores", os.cpu_count()), kind=kind,
+                                      sample="%d actor threads x %d moves x %d sims, evaluator batch %d, libtorch CPU (%s torch threads)" % (
+                                          res.get("actors", 0), int(res.get("sims", 0) / max(1, res.get("actors", 1)) / sims), sims,
+                                          res.get("batch", 0), res.get("torch_threads", "?"))),
+                    e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                    wall_s=time.time() - t0)
+        print(json.dumps(line))
+        return 0
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from mzb200.weights import random_weights, recurrent_flops
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    T = args.trees or wl["trees"]
+    precision = {"bf16": mzb200.BF16, "fp32": mzb200.FP32_CHECK}.get(args.precision)
+    eng = None
+    if precision is None:
+        try:
+            eng = mzb200.Engine(mzb200.preset(preset_name, max_trees=T, precision=mzb200.BF16, seed=1000 * rank), local_rank)
+            precision = mzb200.BF16
+        except mzb200.MzbError as e:
+            if "not available" not in str(e):
+                raise
+            precision = mzb200.FP32_CHECK
+    cfg = mzb200.preset(preset_name, max_trees=T, precision=precision, seed=1000 * rank)
+    if eng is None:
+        eng = mzb200.Engine(cfg, local_rank)
+    # weights: rank 0 draws them, every other rank receives them with ONE ncclBroadcast of the packed blob
+    W = random_weights(cfg, seed=0 if rank == 0 else 1 + rank)
+    eng.load_weights(W)
+    sync_ms = None
+    if world > 1:
+        uid = [mzb200.Engine.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        eng.nccl_init(uid[0], rank, world)
+        torch.cuda.synchronize()
+        t0 = time.time()
+        eng.broadcast_weights(0)
+        sync_ms = 1000 * (time.time() - t0)
+        sums = [None] * world
+        dist.all_gather_object(sums, eng.weights_checksum())
+        assert len(set(sums)) == 1, "weight broadcast left replicas different"
+
+    A = cfg.num_actions
+    flat = eng.shapes.initial_flat_size
+    rng = np.random.default_rng(rank)
+    obs_host = torch.from_numpy(rng.random((T, flat), dtype=np.float32)).pin_memory()
+    obs_dev = obs_host.cuda()
+    masks = np.full(T, (1 << A) - 1, np.uint32)
+    to_play = (np.arange(T) % cfg.num_players).astype(np.int32)
+    noise = np.ones(T, np.uint8)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        dev_ms, t0 = 0.0, time.time()
+        launches = 0
+        for _ in range(steps):
+            fn()
+            tm = eng.last_search_timing()
+            dev_ms += tm["total_ms"]
+            launches += tm["kernel_launches"]
+        barrier()
+        wall_ms = 1000 * (time.time() - t0)
+        if world > 1:
+            t = torch.tensor([dev_ms, wall_ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dev_ms, wall_ms = float(t[0]), float(t[1])
+        return dev_ms, wall_ms, launches
+
+    run_dev = lambda: eng.run(None, masks, to_play, noise, device_obs_ptr=obs_dev.data_ptr())
+    run_host = lambda: eng.run(obs_host.numpy(), masks, to_play, noise)
+    for _ in range(args.warmup):
+        run_dev()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    dev_ms, wall_ms, launches = timed(run_dev, args.steps)
+    clocks = sampler.stop()
+    for _ in range(1):
+        run_host()
+    e2e_dev_ms, e2e_wall_ms, _ = timed(run_host, args.steps)
+    total_sims = world * T * sims * args.steps
+    value = total_sims / (dev_ms / 1000.0)
+    e2e_value = total_sims / (e2e_wall_ms / 1000.0)   # host clock: includes H2D, D2H and host-side noise generation
+
+    # roofline of the dominant kernels: the residual towers of recurrent_inference (tensor bound), measured live
+    pk = peaks()
+    frec = recurrent_flops(cfg)
+    rec_ms, rec_launches = eng.bench_recurrent(T, 5)
+    states_per_s = T / (rec_ms / 1000.0)
+    achieved_tf = frec * states_per_s / 1e12
+    roofline = dict(bound="tensor", achieved=achieved_tf, peak=pk["tf_sustained"], unit="TFLOP/s",
+                    frac=achieved_tf / pk["tf_sustained"], traffic=None, peak_source=pk["source"] + " (sustained bf16)",
+                    kernel="recurrent_inference towers", flops_per_state=frec, states_per_s=states_per_s,
+                    launches_per_pass=rec_launches)
+    if world > 1:
+        t = torch.tensor([states_per_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        roofline["states_per_s_all_gpus"] = float(t[0])
+
+    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
+                ms_per_step=dev_ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
+                dtype="bf16" if precision == mzb200.BF16 else "f32", data="synthetic",
+                config=dict(workload=wl["desc"], trees_per_gpu=T, sims_per_move=sims, weights="random-init",
+                            l2="working set (node pool %.2f GB per GPU) exceeds the 126 MB L2; no explicit flush" % (eng.get_shapes().node_pool_bytes / 1e9),
+                            timing="CUDA events around each search on the engine's stream; max over ranks"),
+                wall_ms_per_step=wall_ms / args.steps, clocks=clocks,
+                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=int(T * flat * 4 + T * (4 + 4 + 1)),
+                         d2h_bytes_per_step=int(T * (8 + 4 + 4 + A * (4 + 4 + 8 + 8))), ms_per_step=e2e_wall_ms / args.steps,
+                         device_ms_per_step=e2e_dev_ms / args.steps),
+                gpu_launches=int(launches), roofline=roofline, recurrent_states_per_s=states_per_s)
+    if sync_ms is not None:
+        line["weight_sync_ms"] = sync_ms
+    eng.close()
+
+    if rank == 0 and world == 1:
+        # tree kernels alone (HBM bound): same search with the network stubbed by the SE evaluator
+        scfg = mzb200.preset(preset_name, max_trees=T, evaluator=mzb200.EVAL_SYNTHETIC)
+        seng = mzb200.Engine(scfg, local_rank)
+        keys = (np.arange(T) + 1).astype(np.float32)
+        for _ in range(3):
+            seng.run(keys, masks, to_play, noise)
+        ms = 0.0
+        for _ in range(5):
+            seng.run(keys, masks, to_play, noise)
+            ms += seng.last_search_timing()["sim_loop_ms"]
+        sims_s = 5 * T * sims / (ms / 1000.0)
+        S_h = 4 * eng.shapes.recurrent_flat_size
+        d = 4
+        b_sim = 2 * S_h + d * 28 * A + 32 * A + 36 * (d + 1) + (4 + 16 + 4 * A)
+        line["roofline_tree"] = dict(bound="hbm", achieved=b_sim * sims_s / 1e9, peak=pk["hbm"], unit="GB/s",
+                                     frac=b_sim * sims_s / 1e9 / pk["hbm"], traffic=None, bytes_per_sim=b_sim,
+                                     sims_per_s=sims_s, kernel="tree_step + SE stub (hidden-state move)")
+        seng.close()
+        if not args.no_cpu_baseline:
+            res = run_reference_cpu(preset_name, args.cpu_seconds, sims)
+            if res and "error" not in res:
+                line["cpu_baseline"] = dict(value=res["sims_per_s"], unit=UNIT, cores=res["cores"], kind="reference",
+                                            sample="%d actor threads x %d sims total, evaluator batch %d, 2 libtorch-CPU model replicas, %s torch threads" % (
+                                                res["actors"], res["sims"], res["batch"], res["torch_threads"]))
+            else:
+                res = run_port_cpu(preset_name, args.cpu_seconds, sims)
+                line["cpu_baseline"] = dict(value=res["sims_per_s"], unit=UNIT, cores=1, kind="port", sample=res["sample"])
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def run_port_cpu(game, seconds_target, sims):
+    """Fallback CPU baseline when oracle/_ref is absent: the oracle port (C search + torch-CPU network), 1 thread."""
+    import numpy as np
+    import mzb200
+    from mzb200.weights import random_weights
+    from oracle import oracle_py as O
+    from oracle import vprnet_oracle as V
+    cfg = mzb200.preset(game)
+    W = random_weights(cfg, 0)
+    net = V.VPRNetOracle(V.preset(game), W)
+    ocfg = O.make_config(num_players=cfg.num_players, num_simulations=sims, num_actions=cfg.num_actions,
+                         lower=cfg.value_lowerbound, upper=cfg.value_upperbound)
+    rng = np.random.default_rng(0)
+    c, h, w = cfg.observation_shape
+    flat = (c * (cfg.stacked_observations + 1) + cfg.stacked_observations * cfg.action_channels) * h * w
+    t0 = time.time()
+    moves = 0
+    while time.time() - t0 < seconds_target:
+        hidden = {}
+
+        def ev(parent, action, new_node):
+            if parent < 0:
+                o = net.initial_inference(rng.random((1, flat), dtype=np.float32))
+            else:
+                o = net.recurrent_inference(hidden[parent], [action])
+            hidden[new_node] = o["hidden"]
+            return float(o["value"][0]), float(o["reward"][0]), [float(x) for x in o["policy"][0]]
+        m = O.mcts_create(ocfg, moves)
+        O.mcts_run(m, list(range(cfg.num_actions)), 0, True, ev)
+        O.mcts_destroy(m)
+        moves += 1
+    sec = time.time() - t0
+    return dict(sims_per_s=moves * sims / sec, seconds=sec, sample="%d moves x %d sims, 1 thread, oracle port" % (moves, sims), cores=1)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

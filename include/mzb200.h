@@ -1,0 +1,168 @@
+/* mzb200.h — C ABI of libmzb200.so, the B200-native replacement for the self-play search hot path of
+ * tuero/muzero-cpp (lock-step batched MCTS + the initial/recurrent inference calls it drives).
+ *
+ * Plain C: pointers and sizes only, no torch / libtorch / C++ types.  Every entry point names the reference
+ * interface it replaces (paths relative to the reference repository root).  All functions return 0 on success
+ * and a negative mzb_status otherwise; mzb_last_error() gives the message (thread-local).  The reference has
+ * no error codes of its own (assert / std::exit / c10::Error); the C++ facade turns a failure into an abort.
+ *
+ * Threading: an engine is bound to one CUDA device and is driven by one host thread at a time (the reference's
+ * MCTS objects are thread-confined too, self_play.cpp:228-238); use one engine per GPU / per rank.
+ */
+#ifndef MZB200_H_
+#define MZB200_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MZB_MAX_ACTIONS 32
+#define MZB_MAX_HEAD_LAYERS 8
+
+typedef enum { MZB_OK = 0, MZB_ERR_INVALID = -1, MZB_ERR_CUDA = -2, MZB_ERR_STATE = -3, MZB_ERR_NCCL = -4 } mzb_status;
+
+/* arithmetic mode of the network towers */
+typedef enum {
+    MZB_FP32_CHECK = 0, /* plain fp32 CUDA-core kernels: <= 1e-4 abs vs libtorch fp32 (north star) */
+    MZB_BF16 = 1        /* tcgen05 implicit-GEMM towers, bf16 operands / fp32 accumulate: <= 2e-2 rel */
+} mzb_precision;
+
+/* what stands behind Evaluator::{Initial,Recurrent}Inference (muzero-cpp/vprnet_evaluator.h:35-41) */
+typedef enum {
+    MZB_EVAL_NETWORK = 0,   /* the VPRNet towers (vprnet.cpp / models.cpp / model_layers.cpp) */
+    MZB_EVAL_SYNTHETIC = 1  /* deterministic hash evaluator "SE": pins the tree kernels bit-exactly and measures them
+                               alone (the stub still moves one hidden state parent->child per simulation) */
+} mzb_evaluator;
+
+/* POD mirror of muzero_config::MuZeroConfig + MuZeroNetworkConfig (muzero-cpp/config.h:15-117), restricted to the
+ * fields the hot path reads.  Field names follow the reference. */
+typedef struct {
+    /* Game (config.h:52-66) */
+    int32_t observation_c, observation_h, observation_w; /* observation_shape */
+    int32_t num_actions;                                 /* action_space = {0..num_actions-1} */
+    int32_t action_channels;
+    int32_t num_players;                                 /* 1 or 2 (mcts.cpp:30) */
+    int32_t stacked_observations;
+    double value_upperbound, value_lowerbound;           /* "unknown" = (lowest, max) sentinels, types.h:77-78 */
+    /* categorical transform (config.h:69-73) */
+    double min_reward, max_reward, min_value, max_value;
+    int32_t use_contractive_mapping;
+    /* search (config.h:83-93) */
+    int32_t num_simulations;
+    double discount, dirichlet_alpha, dirichlet_epsilon, pb_c_base, pb_c_init;
+    int32_t seed;                                        /* tree slot i is seeded seed + i (self_play.cpp:232) */
+    /* network_config (config.h:15-31) */
+    int32_t downsample, normalize_hidden_states;
+    int32_t resnet_channels, representation_blocks, dynamics_blocks, prediction_blocks;
+    int32_t reward_reduced_channels, policy_reduced_channels, value_reduced_channels;
+    int32_t n_reward_head_layers, n_policy_head_layers, n_value_head_layers;
+    int32_t reward_head_layers[MZB_MAX_HEAD_LAYERS], policy_head_layers[MZB_MAX_HEAD_LAYERS],
+        value_head_layers[MZB_MAX_HEAD_LAYERS];
+    /* action_representation_recurrent (types.h:43, vprnet.cpp:143) pre-evaluated once per action:
+     * [num_actions][action_channels * enc_h * enc_w] floats; NULL = the examples' constant plane action/num_actions */
+    const float* action_planes;
+    /* engine */
+    int32_t max_trees;    /* concurrent tree slots resident on this GPU */
+    int32_t precision;    /* mzb_precision */
+    int32_t evaluator;    /* mzb_evaluator */
+    double se_value_lo, se_value_hi, se_reward_lo, se_reward_hi; /* SE output ranges (evaluator == SYNTHETIC) */
+} mzb_config;
+
+typedef struct mzb_engine mzb_engine;
+
+/* One named fp32 tensor of the reference module archive (checkpoint-<step>.pt), e.g.
+ * "dynamics_network.dynamics_resnet_body.0.resnet_0_conv1.weight", "...resnet_0_bn1.running_var". */
+typedef struct {
+    const char* name;
+    const float* data;
+    int32_t ndim;
+    int64_t dims[4];
+} mzb_tensor_desc;
+
+/* SoA result of a batch of searches = T x types::MCTSReturn (muzero-cpp/types.h:70-76).  Caller-owned host arrays;
+ * any pointer may be NULL to skip that output.  Rows are padded to num_actions. */
+typedef struct {
+    double* root_value;               /* [T] */
+    int32_t* max_tree_depth;          /* [T] */
+    int32_t* n_children;              /* [T] number of legal root actions L */
+    int32_t* child_actions;           /* [T][A] first L valid, in the FINAL SHUFFLED child order (mcts.cpp:187) */
+    int32_t* child_visits;            /* [T][A] integer visit counts, same order */
+    double* children_relative_visit;  /* [T][A] visits / sum (mcts.cpp:192-194) */
+    double* emperical_policy;         /* [T][A] dense, indexed by action id (mcts.cpp:196-199) */
+} mzb_search_result;
+
+const char* mzb_last_error(void);
+const char* mzb_version(void);
+
+/* Replaces: VPRNetModel::VPRNetModel (vprnet.cpp:30-50) + DeviceManager::AddDevice (device_manager.h:36-39) +
+ * MCTS::MCTS (mcts.cpp:17-31) for max_trees tree slots.  device = CUDA ordinal. */
+int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out);
+void mzb_engine_destroy(mzb_engine* e);
+
+/* Replaces: VPRNetModel::LoadCheckpoint (vprnet.cpp:66-74): takes the module's named fp32 tensors (78 params + 60
+ * buffers for the shipped Connect4 net), folds eval-mode BN (eps 1e-4) and packs them for the kernels. */
+int mzb_load_weights(mzb_engine* e, const mzb_tensor_desc* tensors, int n_tensors);
+
+/* Replaces: the disk round trip SaveCheckpoint -> LoadCheckpoint of learner.cpp:93-101 / muzero.cpp:142-148.
+ * One ncclBroadcast of the packed weight blob from `root` to all ranks.  id = 128-byte ncclUniqueId. */
+int mzb_nccl_unique_id(char id_out[128]);
+int mzb_nccl_init(mzb_engine* e, const char id[128], int rank, int world_size);
+int mzb_broadcast_weights(mzb_engine* e, int root);
+/* checksum (FNV-1a over the packed blob, read back from the device) to verify a broadcast */
+int mzb_weights_checksum(mzb_engine* e, uint64_t* out);
+
+/* Replaces: VPRNetModel::InitialInference (vprnet.cpp:77-129).  Host pointers, exactly the reference's batch API:
+ * obs [B][Cin*H*W] -> value[B], reward[B] (== 0), policy[B][A] (softmax), hidden[B][C*h*w] (NCHW order, fp32). */
+int mzb_initial_inference(mzb_engine* e, const float* obs, int batch, double* value, double* reward, double* policy,
+                          float* hidden);
+/* Replaces: VPRNetModel::RecurrentInference (vprnet.cpp:131-189).  hidden [B][C*h*w] NCHW, action [B]. */
+int mzb_recurrent_inference(mzb_engine* e, const float* hidden, const int32_t* action, int batch, double* value,
+                            double* reward, double* policy, float* hidden_out);
+/* recurrent_inference states/s with device-resident inputs (BASELINE metric M2): runs `iters` passes over an
+ * internal batch of `batch` random hidden states and reports the mean device time per pass (CUDA events). */
+int mzb_bench_recurrent(mzb_engine* e, int batch, int iters, float* ms_per_pass, int* launches_per_pass);
+
+/* Replaces: MCTS::MCTS's rng_(seed) (mcts.cpp:26) for tree slots [first, first+n). */
+int mzb_search_seed(mzb_engine* e, int first_slot, int n, const int32_t* seeds);
+
+/* Replaces: T concurrent MCTS::run calls (mcts.cpp:34-87; callers self_play.cpp:130,208), tree slot t <- row t.
+ * obs [T][Cin*H*W] host (SYNTHETIC evaluator: obs row = one float, the position key), legal_mask[T] bit a = action a
+ * legal, to_play[T], add_noise[T].  Blocks until all T searches finished. */
+int mzb_search_batch(mzb_engine* e, const float* obs, const uint32_t* legal_mask, const int32_t* to_play,
+                     const uint8_t* add_noise, int n_trees, mzb_search_result* out);
+/* Same search with observations already resident in HBM (device pointer, engine layout = row-major fp32). */
+int mzb_search_batch_device_obs(mzb_engine* e, const float* d_obs, const uint32_t* legal_mask, const int32_t* to_play,
+                                const uint8_t* add_noise, int n_trees, mzb_search_result* out);
+/* device time (CUDA events) of the last search, split as far as the engine can tell */
+typedef struct {
+    float total_ms, root_ms, sim_loop_ms;
+    int64_t kernel_launches;  /* kernels launched (graph nodes included) */
+    int64_t simulations;      /* T * num_simulations */
+} mzb_search_timing;
+int mzb_last_search_timing(mzb_engine* e, mzb_search_timing* out);
+
+/* Parity hooks.  Enable before a search; afterwards read, per tree, the expansion trace ("tree indices": node i+1
+ * was expanded by simulation i under (parent node, action)) and the network outputs each node was expanded with
+ * (node 0 = root) so the oracle can replay "identical network outputs". */
+int mzb_search_set_recording(mzb_engine* e, int enabled);
+int mzb_search_get_trace(mzb_engine* e, int n_trees, int32_t* parent /*[T][n]*/, int32_t* action /*[T][n]*/);
+int mzb_search_get_records(mzb_engine* e, int n_trees, double* value /*[T][n+1]*/, double* reward /*[T][n+1]*/,
+                           double* policy /*[T][n+1][A]*/);
+
+/* derived shapes (VPRNetModel ctor, vprnet.cpp:41-46; ValueEncoder::get_support_size, util.cpp:91-102) */
+typedef struct {
+    int32_t initial_channels, initial_flat_size; /* Cin, Cin*H*W */
+    int32_t enc_c, enc_h, enc_w, recurrent_flat_size;
+    int32_t value_support_size, reward_support_size;
+    double value_step, value_min, reward_step, reward_min; /* ValueEncoder step_size_/min_value_ after h() */
+    int64_t weight_blob_bytes;
+    int64_t node_pool_bytes;
+} mzb_shapes;
+int mzb_get_shapes(mzb_engine* e, mzb_shapes* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MZB200_H_ */

@@ -1,0 +1,261 @@
+// engine.cu — the engine object behind the C ABI (include/mzb200.h): owns the trees, the node pool, the network
+// backend and the lock-step search loop.  Host C++ only drives launches; no libtorch anywhere.
+//
+// Replaces, for its GPU: MCTS objects (mcts.cpp:17-31) for max_trees slots, VPRNetEvaluator's batching queues
+// (vprnet_evaluator.cpp:105-178: lock-step cohorts need no queue, promise or 1 ms deadline), DeviceManager's
+// model loan (device_manager.h:68-80: one resident model per engine), VPRNetModel's inference entry points.
+#include <dlfcn.h>
+
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <memory>
+#include <numeric>
+#include <random>
+
+#include "engine.h"
+
+namespace mzb {
+int ensure_pinned(mzb_engine* e, size_t bytes) {
+    if (bytes <= e->h_pin_bytes) return MZB_OK;
+    if (e->h_pin) cudaFreeHost(e->h_pin);
+    e->h_pin = nullptr;
+    e->h_pin_bytes = 0;
+    MZB_CUDA(cudaMallocHost(&e->h_pin, bytes));
+    e->h_pin_bytes = bytes;
+    return MZB_OK;
+}
+}  // namespace mzb
+
+using namespace mzb;
+
+namespace {
+
+int alloc_trees(mzb_engine* e) {
+    const mzb_config& c = e->cfg;
+    const int T = c.max_trees, A = c.num_actions, n = c.num_simulations;
+    TreeDev& td = e->td;
+    memset(&td, 0, sizeof(td));
+    td.T = T; td.A = A; td.n_sims = n; td.players = c.num_players;
+    td.slots_per_tree = 1 + A + n * A;
+    const size_t S = (size_t)T * td.slots_per_tree;
+    MZB_CUDA(e->meta.alloc(S * sizeof(int4)));
+    MZB_CUDA(e->prior.alloc(S * sizeof(double)));
+    MZB_CUDA(e->value_sum.alloc(S * sizeof(double)));
+    MZB_CUDA(e->reward.alloc(S * sizeof(double)));
+    MZB_CUDA(e->mm_min.alloc(T * sizeof(double)));
+    MZB_CUDA(e->mm_max.alloc(T * sizeof(double)));
+    MZB_CUDA(e->root_to_play.alloc(T * sizeof(int)));
+    MZB_CUDA(e->n_legal.alloc(T * sizeof(int)));
+    MZB_CUDA(e->n_slots.alloc(T * sizeof(int)));
+    MZB_CUDA(e->max_depth.alloc(T * sizeof(int)));
+    MZB_CUDA(e->mt.alloc((size_t)T * 624 * sizeof(uint32_t)));
+    MZB_CUDA(e->mt_idx.alloc(T * sizeof(int)));
+    MZB_CUDA(e->path_slot.alloc((size_t)T * (n + 2) * sizeof(int)));
+    MZB_CUDA(e->path_len.alloc(T * sizeof(int)));
+    MZB_CUDA(e->in_slot.alloc(T * sizeof(int)));
+    MZB_CUDA(e->out_slot.alloc(T * sizeof(int)));
+    MZB_CUDA(e->action.alloc(T * sizeof(int)));
+    MZB_CUDA(e->value.alloc(T * sizeof(double)));
+    MZB_CUDA(e->reward_out.alloc(T * sizeof(double)));
+    MZB_CUDA(e->policy.alloc((size_t)T * A * sizeof(double)));
+    MZB_CUDA(e->pbc_table.alloc((n + 2) * sizeof(double)));
+    td.meta = e->meta.as<int4>(); td.prior = e->prior.as<double>(); td.value_sum = e->value_sum.as<double>();
+    td.reward = e->reward.as<double>(); td.mm_min = e->mm_min.as<double>(); td.mm_max = e->mm_max.as<double>();
+    td.root_to_play = e->root_to_play.as<int>(); td.n_legal = e->n_legal.as<int>(); td.n_slots = e->n_slots.as<int>();
+    td.max_depth = e->max_depth.as<int>(); td.mt = e->mt.as<uint32_t>(); td.mt_idx = e->mt_idx.as<int>();
+    td.path_slot = e->path_slot.as<int>(); td.path_len = e->path_len.as<int>();
+    td.in_slot = e->in_slot.as<int>(); td.out_slot = e->out_slot.as<int>(); td.action = e->action.as<int>();
+    td.value = e->value.as<double>(); td.reward_out = e->reward_out.as<double>(); td.policy = e->policy.as<double>();
+    td.discount = c.discount;
+    td.init_min = c.value_lowerbound;   // MinMaxStats(minimum = value_lowerbound, maximum = value_upperbound), mcts.cpp:25
+    td.init_max = c.value_upperbound;
+    td.dirichlet_epsilon = c.dirichlet_epsilon;
+    // pb_c table: std::log is glibc's on the reference side, so evaluate it on the host with the same libm
+    std::vector<double> tab(n + 2);
+    for (int N = 0; N < n + 2; ++N) tab[N] = std::log((N + c.pb_c_base + 1) / c.pb_c_base) + c.pb_c_init;  // mcts.cpp:129
+    MZB_CUDA(cudaMemcpy(e->pbc_table.p, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice));
+    td.pbc_table = e->pbc_table.as<double>();
+    // inputs / results
+    MZB_CUDA(e->d_legal.alloc(T * sizeof(uint32_t)));
+    MZB_CUDA(e->d_to_play.alloc(T * sizeof(int)));
+    MZB_CUDA(e->d_add_noise.alloc(T));
+    MZB_CUDA(e->d_noise.alloc((size_t)T * A * sizeof(double)));
+    MZB_CUDA(e->d_root_slots.alloc(T * sizeof(int)));
+    MZB_CUDA(e->d_iota.alloc((size_t)2 * T * sizeof(int)));
+    MZB_CUDA(e->r_root_value.alloc(T * sizeof(double)));
+    MZB_CUDA(e->r_depth.alloc(T * sizeof(int)));
+    MZB_CUDA(e->r_nchild.alloc(T * sizeof(int)));
+    MZB_CUDA(e->r_actions.alloc((size_t)T * A * sizeof(int)));
+    MZB_CUDA(e->r_visits.alloc((size_t)T * A * sizeof(int)));
+    MZB_CUDA(e->r_rel.alloc((size_t)T * A * sizeof(double)));
+    MZB_CUDA(e->r_policy.alloc((size_t)T * A * sizeof(double)));
+    std::vector<int> roots(T), iota(2 * T);
+    for (int t = 0; t < T; ++t) roots[t] = t * (n + 1);
+    for (int i = 0; i < 2 * T; ++i) iota[i] = i;
+    MZB_CUDA(cudaMemcpy(e->d_root_slots.p, roots.data(), T * sizeof(int), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(e->d_iota.p, iota.data(), 2 * T * sizeof(int), cudaMemcpyHostToDevice));
+    // seeds: slot i <- seed + i
+    std::vector<int> seeds(T);
+    for (int t = 0; t < T; ++t) seeds[t] = c.seed + t;
+    MZB_CUDA(cudaMemcpy(e->d_to_play.p, seeds.data(), T * sizeof(int), cudaMemcpyHostToDevice));
+    launch_mt_seed(td.mt, td.mt_idx, e->d_to_play.as<int>(), 0, T, e->stream);
+    MZB_CUDA(cudaStreamSynchronize(e->stream));
+    return MZB_OK;
+}
+
+int set_recording_buffers(mzb_engine* e, bool on) {
+    TreeDev& td = e->td;
+    if (on) {
+        const size_t T = td.T, n = td.n_sims, A = td.A;
+        if (!e->trace_parent.p) {
+            MZB_CUDA(e->trace_parent.alloc(T * n * sizeof(int)));
+            MZB_CUDA(e->trace_action.alloc(T * n * sizeof(int)));
+            MZB_CUDA(e->rec_value.alloc(T * (n + 1) * sizeof(double)));
+            MZB_CUDA(e->rec_reward.alloc(T * (n + 1) * sizeof(double)));
+            MZB_CUDA(e->rec_policy.alloc(T * (n + 1) * A * sizeof(double)));
+        }
+        td.trace_parent = e->trace_parent.as<int>(); td.trace_action = e->trace_action.as<int>();
+        td.rec_value = e->rec_value.as<double>(); td.rec_reward = e->rec_reward.as<double>();
+        td.rec_policy = e->rec_policy.as<double>();
+    } else {
+        td.trace_parent = td.trace_action = nullptr;
+        td.rec_value = td.rec_reward = td.rec_policy = nullptr;
+    }
+    e->recording = on;
+    return MZB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* mzb_last_error(void) { return mzb::get_error(); }
+const char* mzb_version(void) { return "mzb200 0.1 (sm_100a)"; }
+
+int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out) {
+    MZB_REQUIRE(config && out, "null argument");
+    MZB_REQUIRE(config->max_trees >= 1, "max_trees must be >= 1");
+    MZB_REQUIRE(config->num_simulations >= 0, "num_simulations must be >= 0");
+    std::unique_ptr<mzb_engine> e(new mzb_engine());
+    e->cfg = *config;
+    e->device = device;
+    memset(&e->timing, 0, sizeof(e->timing));
+    memset(&e->se, 0, sizeof(e->se));
+    int rc = derive_dims(e->cfg, &e->dims, &e->venc, &e->renc);
+    if (rc) return rc;
+    if (config->action_planes) {
+        size_t n = (size_t)e->dims.A * e->dims.ach * e->dims.hw();
+        e->action_planes.assign(config->action_planes, config->action_planes + n);
+        e->cfg.action_planes = e->action_planes.data();
+    }
+    int ndev = 0;
+    MZB_CUDA(cudaGetDeviceCount(&ndev));
+    MZB_REQUIRE(device >= 0 && device < ndev, "CUDA device %d not present (%d devices)", device, ndev);
+    MZB_CUDA(cudaSetDevice(device));
+    MZB_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    MZB_CUDA(cudaStreamCreateWithFlags(&e->aux, cudaStreamNonBlocking));
+    MZB_CUDA(cudaEventCreate(&e->ev_start));
+    MZB_CUDA(cudaEventCreate(&e->ev_root));
+    MZB_CUDA(cudaEventCreate(&e->ev_end));
+    MZB_CUDA(cudaEventCreateWithFlags(&e->ev_aux, cudaEventDisableTiming));
+    rc = alloc_trees(e.get());
+    if (rc) return rc;
+    const int T = e->cfg.max_trees, n = e->cfg.num_simulations;
+    if (e->cfg.evaluator == MZB_EVAL_SYNTHETIC) {
+        e->se.slot_floats = e->dims.hidden_size();
+        e->se.vlo = e->cfg.se_value_lo; e->se.vhi = e->cfg.se_value_hi;
+        e->se.rlo = e->cfg.se_reward_lo; e->se.rhi = e->cfg.se_reward_hi;
+        MZB_CUDA(e->se_cid.alloc((size_t)T * (n + 1) * sizeof(uint32_t)));
+        MZB_CUDA(e->se_pool.alloc((size_t)T * (n + 1) * e->se.slot_floats * sizeof(float)));
+        e->se.node_cid = e->se_cid.as<uint32_t>();
+        e->se.pool = e->se_pool.as<float>();
+        MZB_CUDA(e->d_obs.alloc((size_t)T * sizeof(float)));
+    } else {
+        e->net.reset(e->cfg.precision == MZB_BF16 ? make_bf16_backend() : make_fp32_backend());
+        MZB_REQUIRE(e->net != nullptr, "precision mode %d is not available in this build", e->cfg.precision);
+        MZB_CUDA(e->d_obs.alloc((size_t)T * e->dims.initial_flat() * sizeof(float)));
+    }
+    *out = e.release();
+    return MZB_OK;
+}
+
+void mzb_engine_destroy(mzb_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    cudaDeviceSynchronize();
+    if (e->h_pin) cudaFreeHost(e->h_pin);
+    if (e->ev_start) cudaEventDestroy(e->ev_start);
+    if (e->ev_root) cudaEventDestroy(e->ev_root);
+    if (e->ev_end) cudaEventDestroy(e->ev_end);
+    if (e->ev_aux) cudaEventDestroy(e->ev_aux);
+    e->net.reset();
+    if (e->stream) cudaStreamDestroy(e->stream);
+    if (e->aux) cudaStreamDestroy(e->aux);
+    delete e;
+}
+
+int mzb_get_shapes(mzb_engine* e, mzb_shapes* o) {
+    MZB_REQUIRE(e && o, "null argument");
+    memset(o, 0, sizeof(*o));
+    o->initial_channels = e->dims.cin; o->initial_flat_size = e->dims.initial_flat();
+    o->enc_c = e->dims.C; o->enc_h = e->dims.h; o->enc_w = e->dims.w; o->recurrent_flat_size = e->dims.hidden_size();
+    o->value_support_size = e->dims.Sv; o->reward_support_size = e->dims.Sr;
+    o->value_step = e->venc.step; o->value_min = e->venc.min_value;
+    o->reward_step = e->renc.step; o->reward_min = e->renc.min_value;
+    o->weight_blob_bytes = e->net ? (int64_t)e->net->blob_bytes() : 0;
+    o->node_pool_bytes = e->net ? (int64_t)e->net->pool_bytes() : (int64_t)e->se_pool.bytes;
+    return MZB_OK;
+}
+
+int mzb_load_weights(mzb_engine* e, const mzb_tensor_desc* tensors, int n_tensors) {
+    MZB_REQUIRE(e && tensors && n_tensors > 0, "null argument");
+    MZB_REQUIRE(e->net != nullptr, "engine was created with the synthetic evaluator; it has no network");
+    MZB_CUDA(cudaSetDevice(e->device));
+    TensorMap tm;
+    for (int i = 0; i < n_tensors; ++i) {
+        MZB_REQUIRE(tensors[i].name && tensors[i].data && tensors[i].ndim >= 0 && tensors[i].ndim <= 4, "bad tensor descriptor %d", i);
+        std::vector<int64_t> dims(tensors[i].dims, tensors[i].dims + tensors[i].ndim);
+        tm[tensors[i].name] = std::make_pair(tensors[i].data, dims);
+    }
+    int rc = build_plan(e->cfg, tm, &e->plan);
+    if (rc) return rc;
+    MZB_CUDA(cudaStreamSynchronize(e->stream));
+    rc = e->net->upload(e->plan);
+    if (rc) return rc;
+    if (!e->weights_loaded) {
+        rc = e->net->alloc_pool((size_t)e->cfg.max_trees * (e->cfg.num_simulations + 1) + 2 * (size_t)e->cfg.max_trees, e->cfg.max_trees);
+        if (rc) return rc;
+    }
+    e->weights_loaded = true;
+    return MZB_OK;
+}
+
+int mzb_weights_checksum(mzb_engine* e, uint64_t* out) {
+    MZB_REQUIRE(e && out && e->net && e->weights_loaded, "no weights loaded");
+    MZB_CUDA(cudaSetDevice(e->device));
+    std::vector<uint8_t> h(e->net->blob_bytes());
+    MZB_CUDA(cudaMemcpy(h.data(), e->net->blob_ptr(), h.size(), cudaMemcpyDeviceToHost));
+    uint64_t x = 1469598103934665603ULL;
+    for (uint8_t b : h) { x ^= b; x *= 1099511628211ULL; }
+    *out = x;
+    return MZB_OK;
+}
+
+int mzb_search_seed(mzb_engine* e, int first_slot, int n, const int32_t* seeds) {
+    MZB_REQUIRE(e && seeds && first_slot >= 0 && n >= 0 && first_slot + n <= e->cfg.max_trees, "bad slot range");
+    MZB_CUDA(cudaSetDevice(e->device));
+    MZB_CUDA(cudaMemcpy(e->d_to_play.p, seeds, n * sizeof(int), cudaMemcpyHostToDevice));
+    launch_mt_seed(e->td.mt, e->td.mt_idx, e->d_to_play.as<int>(), first_slot, n, e->stream);
+    MZB_CUDA(cudaGetLastError());
+    MZB_CUDA(cudaStreamSynchronize(e->stream));
+    return MZB_OK;
+}
+
+int mzb_search_set_recording(mzb_engine* e, int enabled) {
+    MZB_REQUIRE(e, "null argument");
+    MZB_CUDA(cudaSetDevice(e->device));
+    return set_recording_buffers(e, enabled != 0);
+}
+
+}  // extern "C"

@@ -1,0 +1,74 @@
+// engine.h — the engine object behind the C ABI (include/mzb200.h).
+#pragma once
+#include <memory>
+#include <vector>
+
+#include "net_backend.h"
+#include "tree.h"
+
+namespace mzb {
+
+// URBG view over a raw mt19937 state with the exact interface std::mt19937 shows to libstdc++'s distributions
+// (result_type = uint_fast32_t, min 0, max 2^32-1), so std::gamma_distribution consumes it identically.
+struct HostMt {
+    typedef uint_fast32_t result_type;
+    uint32_t* mt;
+    int* idx;
+    static constexpr result_type min() { return 0; }
+    static constexpr result_type max() { return 0xffffffffUL; }
+    result_type operator()() {
+        if (*idx >= 624) {
+            for (int k = 0; k < 624; ++k) {
+                uint32_t y = (mt[k] & 0x80000000u) | (mt[(k + 1) % 624] & 0x7fffffffu);
+                mt[k] = mt[(k + 397) % 624] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+            }
+            *idx = 0;
+        }
+        uint32_t y = mt[(*idx)++];
+        y ^= y >> 11; y ^= (y << 7) & 0x9d2c5680u; y ^= (y << 15) & 0xefc60000u; y ^= y >> 18;
+        return y;
+    }
+};
+
+}  // namespace mzb
+
+using namespace mzb;
+
+struct mzb_engine {
+    mzb_config cfg;
+    int device = 0;
+    NetDims dims;
+    EncoderConsts venc, renc;
+    NetPlan plan;
+    std::unique_ptr<NetBackend> net;
+    bool weights_loaded = false;
+    std::vector<float> action_planes;   // owned copy of cfg.action_planes
+    cudaStream_t stream = nullptr, aux = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_root = nullptr, ev_end = nullptr, ev_aux = nullptr;
+    // trees
+    TreeDev td;
+    DevBuf meta, prior, value_sum, reward, mm_min, mm_max, root_to_play, n_legal, n_slots, max_depth, mt, mt_idx,
+        path_slot, path_len, in_slot, out_slot, action, value, reward_out, policy, pbc_table;
+    DevBuf trace_parent, trace_action, rec_value, rec_reward, rec_policy;
+    bool recording = false;
+    // search inputs / outputs on the device
+    DevBuf d_obs, d_legal, d_to_play, d_add_noise, d_noise, d_root_slots, d_iota;
+    DevBuf r_root_value, r_depth, r_nchild, r_actions, r_visits, r_rel, r_policy;
+    // SE stub
+    SEDev se;
+    DevBuf se_cid, se_pool;
+    // pinned host staging
+    void* h_pin = nullptr;
+    size_t h_pin_bytes = 0;
+    // compat-path scratch
+    DevBuf c_hidden_in, c_hidden_out, c_action;
+    mzb_search_timing timing;
+    // nccl (dlopen'ed)
+    void* nccl_lib = nullptr;
+    void* nccl_comm = nullptr;
+};
+
+
+namespace mzb {
+int ensure_pinned(mzb_engine* e, size_t bytes);
+}

@@ -1,0 +1,312 @@
+// engine_search.cu — the lock-step batched search (T x MCTS::run, mcts.cpp:34-87) and the batch inference entry
+// points of the C ABI.  One host thread enqueues everything on one stream; the only host work inside a search is
+// the Dirichlet noise (std::gamma_distribution on the slots' own mt19937 streams, util.cpp:28-43), overlapped with
+// the initial inference.
+#include <cstring>
+#include <numeric>
+#include <random>
+
+#include "engine.h"
+
+using namespace mzb;
+
+namespace {
+
+// util::sample_dirichlet (util.cpp:28-43) on a tree slot's RNG stream
+void sample_dirichlet(HostMt& rng, double alpha, int n, double* out) {
+    std::gamma_distribution<double> gamma_dist(alpha, 1.0);
+    for (int i = 0; i < n; ++i) out[i] = gamma_dist(rng);
+    double sum = std::reduce(out, out + n);
+    for (int i = 0; i < n; ++i) out[i] /= sum;
+}
+
+int popcount32(uint32_t x) { return __builtin_popcount(x); }
+
+NetOutputs tree_outputs(mzb_engine* e) {
+    NetOutputs o;
+    o.value = e->td.value; o.reward = e->td.reward_out; o.policy = e->td.policy;
+    return o;
+}
+
+// d_obs: device rows.  Everything else host.
+int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_t* legal_mask, const int32_t* to_play,
+                const uint8_t* add_noise, int T, mzb_search_result* out) {
+    const mzb_config& c = e->cfg;
+    const int A = c.num_actions, n = c.num_simulations;
+    TreeDev& td = e->td;
+    const bool synthetic = c.evaluator == MZB_EVAL_SYNTHETIC;
+    const uint32_t full = (A >= 32) ? 0xffffffffu : ((1u << A) - 1u);
+    bool any_noise = false;
+    for (int t = 0; t < T; ++t) {
+        MZB_REQUIRE((legal_mask[t] & full) != 0 && (legal_mask[t] & ~full) == 0, "tree %d: legal_mask must select 1..A actions (mcts.cpp:37)", t);
+        MZB_REQUIRE(to_play[t] >= 0 && to_play[t] < c.num_players, "tree %d: to_play out of range", t);
+        any_noise = any_noise || add_noise[t];
+    }
+    cudaStream_t s = e->stream;
+    int64_t launches = 0;
+    MZB_CUDA(cudaEventRecord(e->ev_start, s));
+    // ---- root: initial inference (async) ----
+    if (synthetic) {
+        launch_se_initial(td, e->se, T, d_obs, obs_stride, s);
+        ++launches;
+    } else {
+        int rc = e->net->initial(d_obs, T, e->d_root_slots.as<int>(), tree_outputs(e), s);
+        if (rc) return rc;
+        launches += e->net->launches_initial();
+    }
+    // ---- host side, overlapped: per-tree inputs and Dirichlet noise ----
+    size_t pin_need = (size_t)T * (sizeof(uint32_t) + sizeof(int) + 1 + (size_t)A * sizeof(double) + 624 * sizeof(uint32_t) + sizeof(int)) + 256;
+    int rc = ensure_pinned(e, pin_need);
+    if (rc) return rc;
+    uint8_t* pin = (uint8_t*)e->h_pin;
+    double* h_noise = (double*)pin; pin += (size_t)T * A * sizeof(double);
+    uint32_t* h_mt = (uint32_t*)pin; pin += (size_t)T * 624 * sizeof(uint32_t);
+    uint32_t* h_legal = (uint32_t*)pin; pin += (size_t)T * sizeof(uint32_t);
+    int* h_to_play = (int*)pin; pin += (size_t)T * sizeof(int);
+    int* h_idx = (int*)pin; pin += (size_t)T * sizeof(int);
+    uint8_t* h_add = pin;
+    memcpy(h_legal, legal_mask, T * sizeof(uint32_t));
+    memcpy(h_to_play, to_play, T * sizeof(int));
+    memcpy(h_add, add_noise, T);
+    cudaStream_t ax = e->aux;
+    MZB_CUDA(cudaMemcpyAsync(e->d_legal.p, h_legal, T * sizeof(uint32_t), cudaMemcpyHostToDevice, ax));
+    MZB_CUDA(cudaMemcpyAsync(e->d_to_play.p, h_to_play, T * sizeof(int), cudaMemcpyHostToDevice, ax));
+    MZB_CUDA(cudaMemcpyAsync(e->d_add_noise.p, h_add, T, cudaMemcpyHostToDevice, ax));
+    if (any_noise) {
+        MZB_CUDA(cudaMemcpyAsync(h_mt, td.mt, (size_t)T * 624 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ax));
+        MZB_CUDA(cudaMemcpyAsync(h_idx, td.mt_idx, T * sizeof(int), cudaMemcpyDeviceToHost, ax));
+        MZB_CUDA(cudaStreamSynchronize(ax));
+        for (int t = 0; t < T; ++t) {
+            if (!add_noise[t]) continue;
+            HostMt rng{h_mt + (size_t)t * 624, h_idx + t};
+            sample_dirichlet(rng, c.dirichlet_alpha, popcount32(legal_mask[t]), h_noise + (size_t)t * A);
+        }
+        MZB_CUDA(cudaMemcpyAsync(td.mt, h_mt, (size_t)T * 624 * sizeof(uint32_t), cudaMemcpyHostToDevice, ax));
+        MZB_CUDA(cudaMemcpyAsync(td.mt_idx, h_idx, T * sizeof(int), cudaMemcpyHostToDevice, ax));
+        MZB_CUDA(cudaMemcpyAsync(e->d_noise.p, h_noise, (size_t)T * A * sizeof(double), cudaMemcpyHostToDevice, ax));
+    }
+    MZB_CUDA(cudaEventRecord(e->ev_aux, ax));
+    MZB_CUDA(cudaStreamWaitEvent(s, e->ev_aux, 0));
+    launch_tree_root(td, T, e->d_legal.as<uint32_t>(), e->d_to_play.as<int>(), e->d_add_noise.as<uint8_t>(), e->d_noise.as<double>(), s);
+    ++launches;
+    MZB_CUDA(cudaEventRecord(e->ev_root, s));
+    // ---- simulation loop: tree step <-> recurrent inference, lock-step over all trees (mcts.cpp:52-79) ----
+    for (int sim = 0; sim <= n; ++sim) {
+        launch_tree_step(td, T, sim, s);
+        ++launches;
+        if (sim == n) break;
+        if (synthetic) {
+            launch_se_recurrent(td, e->se, T, s);
+            ++launches;
+        } else {
+            rc = e->net->recurrent(T, td.in_slot, td.action, td.out_slot, tree_outputs(e), s);
+            if (rc) return rc;
+            launches += e->net->launches_recurrent();
+        }
+    }
+    ResultDev r;
+    r.root_value = e->r_root_value.as<double>(); r.max_tree_depth = e->r_depth.as<int>(); r.n_children = e->r_nchild.as<int>();
+    r.child_actions = e->r_actions.as<int>(); r.child_visits = e->r_visits.as<int>();
+    r.relative_visit = e->r_rel.as<double>(); r.emperical_policy = e->r_policy.as<double>();
+    launch_tree_stats(td, T, r, s);
+    ++launches;
+    MZB_CUDA(cudaGetLastError());
+    if (out) {
+        if (out->root_value) MZB_CUDA(cudaMemcpyAsync(out->root_value, r.root_value, T * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (out->max_tree_depth) MZB_CUDA(cudaMemcpyAsync(out->max_tree_depth, r.max_tree_depth, T * sizeof(int), cudaMemcpyDeviceToHost, s));
+        if (out->n_children) MZB_CUDA(cudaMemcpyAsync(out->n_children, r.n_children, T * sizeof(int), cudaMemcpyDeviceToHost, s));
+        if (out->child_actions) MZB_CUDA(cudaMemcpyAsync(out->child_actions, r.child_actions, (size_t)T * A * sizeof(int), cudaMemcpyDeviceToHost, s));
+        if (out->child_visits) MZB_CUDA(cudaMemcpyAsync(out->child_visits, r.child_visits, (size_t)T * A * sizeof(int), cudaMemcpyDeviceToHost, s));
+        if (out->children_relative_visit) MZB_CUDA(cudaMemcpyAsync(out->children_relative_visit, r.relative_visit, (size_t)T * A * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (out->emperical_policy) MZB_CUDA(cudaMemcpyAsync(out->emperical_policy, r.emperical_policy, (size_t)T * A * sizeof(double), cudaMemcpyDeviceToHost, s));
+    }
+    MZB_CUDA(cudaEventRecord(e->ev_end, s));
+    MZB_CUDA(cudaStreamSynchronize(s));
+    MZB_CUDA(cudaGetLastError());
+    float total = 0.f, root = 0.f;
+    MZB_CUDA(cudaEventElapsedTime(&total, e->ev_start, e->ev_end));
+    MZB_CUDA(cudaEventElapsedTime(&root, e->ev_start, e->ev_root));
+    e->timing.total_ms = total; e->timing.root_ms = root; e->timing.sim_loop_ms = total - root;
+    e->timing.kernel_launches = launches;
+    e->timing.simulations = (int64_t)T * n;
+    return MZB_OK;
+}
+
+int check_search_args(mzb_engine* e, const void* obs, const uint32_t* legal_mask, const int32_t* to_play, const uint8_t* add_noise, int T) {
+    MZB_REQUIRE(e && obs && legal_mask && to_play && add_noise, "null argument");
+    MZB_REQUIRE(T >= 1 && T <= e->cfg.max_trees, "n_trees %d outside [1, max_trees=%d]", T, e->cfg.max_trees);
+    MZB_REQUIRE(e->cfg.evaluator == MZB_EVAL_SYNTHETIC || e->weights_loaded, "weights not loaded (mzb_load_weights)");
+    return MZB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mzb_search_batch(mzb_engine* e, const float* obs, const uint32_t* legal_mask, const int32_t* to_play,
+                     const uint8_t* add_noise, int n_trees, mzb_search_result* out) {
+    int rc = check_search_args(e, obs, legal_mask, to_play, add_noise, n_trees);
+    if (rc) return rc;
+    MZB_CUDA(cudaSetDevice(e->device));
+    const int stride = (e->cfg.evaluator == MZB_EVAL_SYNTHETIC) ? 1 : e->dims.initial_flat();
+    // host -> device copy of the observations (pageable or pinned caller memory) on the search stream
+    MZB_CUDA(cudaMemcpyAsync(e->d_obs.p, obs, (size_t)n_trees * stride * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    return search_impl(e, e->d_obs.as<float>(), stride, legal_mask, to_play, add_noise, n_trees, out);
+}
+
+int mzb_search_batch_device_obs(mzb_engine* e, const float* d_obs, const uint32_t* legal_mask, const int32_t* to_play,
+                                const uint8_t* add_noise, int n_trees, mzb_search_result* out) {
+    int rc = check_search_args(e, d_obs, legal_mask, to_play, add_noise, n_trees);
+    if (rc) return rc;
+    MZB_CUDA(cudaSetDevice(e->device));
+    const int stride = (e->cfg.evaluator == MZB_EVAL_SYNTHETIC) ? 1 : e->dims.initial_flat();
+    return search_impl(e, d_obs, stride, legal_mask, to_play, add_noise, n_trees, out);
+}
+
+int mzb_last_search_timing(mzb_engine* e, mzb_search_timing* out) {
+    MZB_REQUIRE(e && out, "null argument");
+    *out = e->timing;
+    return MZB_OK;
+}
+
+int mzb_search_get_trace(mzb_engine* e, int T, int32_t* parent, int32_t* action) {
+    MZB_REQUIRE(e && parent && action, "null argument");
+    MZB_REQUIRE(e->recording && e->trace_parent.p, "recording is not enabled (mzb_search_set_recording)");
+    MZB_REQUIRE(T >= 1 && T <= e->cfg.max_trees, "bad n_trees");
+    MZB_CUDA(cudaSetDevice(e->device));
+    const size_t n = e->cfg.num_simulations;
+    MZB_CUDA(cudaMemcpy(parent, e->trace_parent.p, T * n * sizeof(int), cudaMemcpyDeviceToHost));
+    MZB_CUDA(cudaMemcpy(action, e->trace_action.p, T * n * sizeof(int), cudaMemcpyDeviceToHost));
+    return MZB_OK;
+}
+
+int mzb_search_get_records(mzb_engine* e, int T, double* value, double* reward, double* policy) {
+    MZB_REQUIRE(e && value && reward && policy, "null argument");
+    MZB_REQUIRE(e->recording && e->rec_value.p, "recording is not enabled (mzb_search_set_recording)");
+    MZB_REQUIRE(T >= 1 && T <= e->cfg.max_trees, "bad n_trees");
+    MZB_CUDA(cudaSetDevice(e->device));
+    const size_t n1 = e->cfg.num_simulations + 1, A = e->cfg.num_actions;
+    MZB_CUDA(cudaMemcpy(value, e->rec_value.p, T * n1 * sizeof(double), cudaMemcpyDeviceToHost));
+    MZB_CUDA(cudaMemcpy(reward, e->rec_reward.p, T * n1 * sizeof(double), cudaMemcpyDeviceToHost));
+    MZB_CUDA(cudaMemcpy(policy, e->rec_policy.p, T * n1 * A * sizeof(double), cudaMemcpyDeviceToHost));
+    return MZB_OK;
+}
+
+// ------------------------------------------------------------------ VPRNetModel batch API (host pointers)
+static int infer_common(mzb_engine* e, int batch) {
+    MZB_REQUIRE(e, "null argument");
+    MZB_REQUIRE(e->net && e->weights_loaded, "weights not loaded (mzb_load_weights)");
+    MZB_REQUIRE(batch >= 1, "empty batch");
+    MZB_CUDA(cudaSetDevice(e->device));
+    return MZB_OK;
+}
+
+int mzb_initial_inference(mzb_engine* e, const float* obs, int batch, double* value, double* reward, double* policy, float* hidden) {
+    int rc = infer_common(e, batch);
+    if (rc) return rc;
+    MZB_REQUIRE(obs, "null observations");
+    const int T = e->cfg.max_trees, A = e->cfg.num_actions, flat = e->dims.initial_flat(), S = e->dims.hidden_size();
+    const int scratch0 = T * (e->cfg.num_simulations + 1);   // compat-path pool slots live behind the trees' slots
+    cudaStream_t s = e->stream;
+    if (!e->c_hidden_out.p) MZB_CUDA(e->c_hidden_out.alloc((size_t)T * S * sizeof(float)));
+    for (int b0 = 0; b0 < batch; b0 += T) {
+        const int B = (batch - b0 < T) ? batch - b0 : T;
+        MZB_CUDA(cudaMemcpyAsync(e->d_obs.p, obs + (size_t)b0 * flat, (size_t)B * flat * sizeof(float), cudaMemcpyHostToDevice, s));
+        const int* out_slots = e->d_iota.as<int>();   // iota values 0..2T-1; offset by scratch0 through a shifted copy below
+        (void)out_slots;
+        // slots scratch0 + [0, B): reuse d_in_slot storage as the index array
+        std::vector<int> idx(B);
+        for (int i = 0; i < B; ++i) idx[i] = scratch0 + i;
+        MZB_CUDA(cudaMemcpyAsync(e->in_slot.p, idx.data(), B * sizeof(int), cudaMemcpyHostToDevice, s));
+        MZB_CUDA(cudaStreamSynchronize(s));
+        rc = e->net->initial(e->d_obs.as<float>(), B, e->in_slot.as<int>(), tree_outputs(e), s);
+        if (rc) return rc;
+        if (hidden) {
+            rc = e->net->export_hidden(e->c_hidden_out.as<float>(), B, e->in_slot.as<int>(), s);
+            if (rc) return rc;
+            MZB_CUDA(cudaMemcpyAsync(hidden + (size_t)b0 * S, e->c_hidden_out.p, (size_t)B * S * sizeof(float), cudaMemcpyDeviceToHost, s));
+        }
+        if (value) MZB_CUDA(cudaMemcpyAsync(value + b0, e->td.value, B * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (reward) MZB_CUDA(cudaMemcpyAsync(reward + b0, e->td.reward_out, B * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (policy) MZB_CUDA(cudaMemcpyAsync(policy + (size_t)b0 * A, e->td.policy, (size_t)B * A * sizeof(double), cudaMemcpyDeviceToHost, s));
+        MZB_CUDA(cudaStreamSynchronize(s));
+    }
+    return MZB_OK;
+}
+
+int mzb_recurrent_inference(mzb_engine* e, const float* hidden, const int32_t* action, int batch, double* value,
+                            double* reward, double* policy, float* hidden_out) {
+    int rc = infer_common(e, batch);
+    if (rc) return rc;
+    MZB_REQUIRE(hidden && action, "null inputs");
+    const int T = e->cfg.max_trees, A = e->cfg.num_actions, S = e->dims.hidden_size();
+    for (int i = 0; i < batch; ++i) MZB_REQUIRE(action[i] >= 0 && action[i] < A, "action %d of sample %d outside the action space", action[i], i);
+    const int scratch0 = T * (e->cfg.num_simulations + 1);
+    cudaStream_t s = e->stream;
+    if (!e->c_hidden_in.p) MZB_CUDA(e->c_hidden_in.alloc((size_t)T * S * sizeof(float)));
+    if (!e->c_hidden_out.p) MZB_CUDA(e->c_hidden_out.alloc((size_t)T * S * sizeof(float)));
+    for (int b0 = 0; b0 < batch; b0 += T) {
+        const int B = (batch - b0 < T) ? batch - b0 : T;
+        std::vector<int> idx(2 * B);
+        for (int i = 0; i < B; ++i) { idx[i] = scratch0 + i; idx[B + i] = scratch0 + T + i; }
+        MZB_CUDA(cudaMemcpyAsync(e->in_slot.p, idx.data(), B * sizeof(int), cudaMemcpyHostToDevice, s));
+        MZB_CUDA(cudaMemcpyAsync(e->out_slot.p, idx.data() + B, B * sizeof(int), cudaMemcpyHostToDevice, s));
+        MZB_CUDA(cudaMemcpyAsync(e->action.p, action + b0, B * sizeof(int), cudaMemcpyHostToDevice, s));
+        MZB_CUDA(cudaMemcpyAsync(e->c_hidden_in.p, hidden + (size_t)b0 * S, (size_t)B * S * sizeof(float), cudaMemcpyHostToDevice, s));
+        MZB_CUDA(cudaStreamSynchronize(s));
+        rc = e->net->import_hidden(e->c_hidden_in.as<float>(), B, e->in_slot.as<int>(), s);
+        if (rc) return rc;
+        rc = e->net->recurrent(B, e->in_slot.as<int>(), e->action.as<int>(), e->out_slot.as<int>(), tree_outputs(e), s);
+        if (rc) return rc;
+        if (hidden_out) {
+            rc = e->net->export_hidden(e->c_hidden_out.as<float>(), B, e->out_slot.as<int>(), s);
+            if (rc) return rc;
+            MZB_CUDA(cudaMemcpyAsync(hidden_out + (size_t)b0 * S, e->c_hidden_out.p, (size_t)B * S * sizeof(float), cudaMemcpyDeviceToHost, s));
+        }
+        if (value) MZB_CUDA(cudaMemcpyAsync(value + b0, e->td.value, B * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (reward) MZB_CUDA(cudaMemcpyAsync(reward + b0, e->td.reward_out, B * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (policy) MZB_CUDA(cudaMemcpyAsync(policy + (size_t)b0 * A, e->td.policy, (size_t)B * A * sizeof(double), cudaMemcpyDeviceToHost, s));
+        MZB_CUDA(cudaStreamSynchronize(s));
+    }
+    return MZB_OK;
+}
+
+int mzb_bench_recurrent(mzb_engine* e, int batch, int iters, float* ms_per_pass, int* launches_per_pass) {
+    int rc = infer_common(e, batch);
+    if (rc) return rc;
+    const int T = e->cfg.max_trees, A = e->cfg.num_actions, S = e->dims.hidden_size();
+    MZB_REQUIRE(batch <= T && iters >= 1, "batch above max_trees or iters < 1");
+    const int scratch0 = T * (e->cfg.num_simulations + 1);
+    cudaStream_t s = e->stream;
+    // device-resident inputs: pseudo-random hidden states in [0,1) and actions, imported once
+    if (!e->c_hidden_in.p) MZB_CUDA(e->c_hidden_in.alloc((size_t)T * S * sizeof(float)));
+    std::vector<float> h((size_t)batch * S);
+    uint32_t x = 12345u;
+    for (auto& v : h) { x = x * 1664525u + 1013904223u; v = (float)(x >> 8) / 16777216.0f; }
+    std::vector<int> idx(2 * batch), act(batch);
+    for (int i = 0; i < batch; ++i) { idx[i] = scratch0 + i; idx[batch + i] = scratch0 + T + i; act[i] = i % A; }
+    MZB_CUDA(cudaMemcpy(e->c_hidden_in.p, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(e->in_slot.p, idx.data(), batch * sizeof(int), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(e->out_slot.p, idx.data() + batch, batch * sizeof(int), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(e->action.p, act.data(), batch * sizeof(int), cudaMemcpyHostToDevice));
+    rc = e->net->import_hidden(e->c_hidden_in.as<float>(), batch, e->in_slot.as<int>(), s);
+    if (rc) return rc;
+    for (int w = 0; w < 3; ++w) {
+        rc = e->net->recurrent(batch, e->in_slot.as<int>(), e->action.as<int>(), e->out_slot.as<int>(), tree_outputs(e), s);
+        if (rc) return rc;
+    }
+    MZB_CUDA(cudaEventRecord(e->ev_start, s));
+    for (int i = 0; i < iters; ++i) {
+        rc = e->net->recurrent(batch, e->in_slot.as<int>(), e->action.as<int>(), e->out_slot.as<int>(), tree_outputs(e), s);
+        if (rc) return rc;
+    }
+    MZB_CUDA(cudaEventRecord(e->ev_end, s));
+    MZB_CUDA(cudaStreamSynchronize(s));
+    float ms = 0.f;
+    MZB_CUDA(cudaEventElapsedTime(&ms, e->ev_start, e->ev_end));
+    if (ms_per_pass) *ms_per_pass = ms / iters;
+    if (launches_per_pass) *launches_per_pass = e->net->launches_recurrent();
+    return MZB_OK;
+}
+
+}  // extern "C"

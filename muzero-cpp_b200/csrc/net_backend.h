@@ -1,0 +1,47 @@
+// net_backend.h — device-side executor interface of the VPRNet towers.
+// Two implementations: Fp32Backend (net_fp32.cu, check mode) and Bf16Backend (net_bf16.cu, tcgen05).
+// Hidden states never leave HBM: both read the parent state from, and write the child state into, a
+// pool of fixed-size slots ("node pool"), addressed by slot index arrays living on the device.
+#pragma once
+#include "common.h"
+#include "net_plan.h"
+
+namespace mzb {
+
+// where the heads leave their results (device SoA, fp64 like VPRNetModel::InferenceOutputs, vprnet.h:64-69)
+struct NetOutputs {
+    double* value = nullptr;   // [B]
+    double* reward = nullptr;  // [B]
+    double* policy = nullptr;  // [B][A]
+};
+
+class NetBackend {
+public:
+    virtual ~NetBackend() {}
+    virtual const char* name() const = 0;
+    // upload folded weights; (re)callable for weight sync
+    virtual int upload(const NetPlan& plan) = 0;
+    // packed device weight blob (one contiguous allocation) for NCCL broadcast / checksum
+    virtual void* blob_ptr() = 0;
+    virtual size_t blob_bytes() const = 0;
+    // node pool
+    virtual int alloc_pool(size_t n_slots, int max_batch) = 0;
+    virtual size_t pool_bytes() const = 0;
+    virtual size_t slot_bytes() const = 0;
+    // NCHW fp32 rows <-> pool slots (C-ABI compatibility path)
+    virtual int import_hidden(const float* d_nchw, int B, const int* d_slot, cudaStream_t s) = 0;
+    virtual int export_hidden(float* d_nchw, int B, const int* d_slot, cudaStream_t s) = 0;
+    // VPRNetModel::InitialInference (vprnet.cpp:77-129): obs rows NCHW fp32 on device -> hidden into out slots
+    virtual int initial(const float* d_obs, int B, const int* d_out_slot, const NetOutputs& out, cudaStream_t s) = 0;
+    // VPRNetModel::RecurrentInference (vprnet.cpp:131-189): parent slots + actions -> child slots
+    virtual int recurrent(int B, const int* d_in_slot, const int* d_action, const int* d_out_slot,
+                          const NetOutputs& out, cudaStream_t s) = 0;
+    // kernels launched by one initial()/recurrent() call (for gpu_launches accounting)
+    virtual int launches_initial() const = 0;
+    virtual int launches_recurrent() const = 0;
+};
+
+NetBackend* make_fp32_backend();
+NetBackend* make_bf16_backend();
+
+}  // namespace mzb

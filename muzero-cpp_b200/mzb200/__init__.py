@@ -1,0 +1,427 @@
+"""mzb200 — Python host mirror of the reference interface for the self-play search hot path, over the C ABI of
+libmzb200.so (include/mzb200.h).  ctypes only: no torch on the product path.
+
+Names follow the reference: MuZeroConfig / MuZeroNetworkConfig fields (muzero-cpp/config.h:15-117), MCTSReturn
+(types.h:70-76), VPRNetModel.InitialInference / RecurrentInference (vprnet.h:71-100), MCTS.run (mcts.h:133-136) —
+batched: every call takes T trees / B samples at once.  The library must be present: there is no CPU fallback."""
+import ctypes as C
+import os
+from dataclasses import dataclass, field
+from typing import List, Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libmzb200.so")
+
+MAX_ACTIONS = 32
+MAX_HEAD_LAYERS = 8
+FP32_CHECK, BF16 = 0, 1
+EVAL_NETWORK, EVAL_SYNTHETIC = 0, 1
+INF_D = float(np.finfo(np.float64).max)    # types::INF_D  (types.h:78)
+NINF_D = -float(np.finfo(np.float64).max)  # types::NINF_D (types.h:77)
+
+
+class MzbError(RuntimeError):
+    pass
+
+
+class _CConfig(C.Structure):
+    _fields_ = [
+        ("observation_c", C.c_int32), ("observation_h", C.c_int32), ("observation_w", C.c_int32),
+        ("num_actions", C.c_int32), ("action_channels", C.c_int32), ("num_players", C.c_int32),
+        ("stacked_observations", C.c_int32),
+        ("value_upperbound", C.c_double), ("value_lowerbound", C.c_double),
+        ("min_reward", C.c_double), ("max_reward", C.c_double), ("min_value", C.c_double), ("max_value", C.c_double),
+        ("use_contractive_mapping", C.c_int32),
+        ("num_simulations", C.c_int32),
+        ("discount", C.c_double), ("dirichlet_alpha", C.c_double), ("dirichlet_epsilon", C.c_double),
+        ("pb_c_base", C.c_double), ("pb_c_init", C.c_double),
+        ("seed", C.c_int32),
+        ("downsample", C.c_int32), ("normalize_hidden_states", C.c_int32),
+        ("resnet_channels", C.c_int32), ("representation_blocks", C.c_int32), ("dynamics_blocks", C.c_int32),
+        ("prediction_blocks", C.c_int32),
+        ("reward_reduced_channels", C.c_int32), ("policy_reduced_channels", C.c_int32),
+        ("value_reduced_channels", C.c_int32),
+        ("n_reward_head_layers", C.c_int32), ("n_policy_head_layers", C.c_int32), ("n_value_head_layers", C.c_int32),
+        ("reward_head_layers", C.c_int32 * MAX_HEAD_LAYERS), ("policy_head_layers", C.c_int32 * MAX_HEAD_LAYERS),
+        ("value_head_layers", C.c_int32 * MAX_HEAD_LAYERS),
+        ("action_planes", C.POINTER(C.c_float)),
+        ("max_trees", C.c_int32), ("precision", C.c_int32), ("evaluator", C.c_int32),
+        ("se_value_lo", C.c_double), ("se_value_hi", C.c_double), ("se_reward_lo", C.c_double),
+        ("se_reward_hi", C.c_double),
+    ]
+
+
+class _CTensorDesc(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("data", C.POINTER(C.c_float)), ("ndim", C.c_int32), ("dims", C.c_int64 * 4)]
+
+
+class _CSearchResult(C.Structure):
+    _fields_ = [("root_value", C.POINTER(C.c_double)), ("max_tree_depth", C.POINTER(C.c_int32)),
+                ("n_children", C.POINTER(C.c_int32)), ("child_actions", C.POINTER(C.c_int32)),
+                ("child_visits", C.POINTER(C.c_int32)), ("children_relative_visit", C.POINTER(C.c_double)),
+                ("emperical_policy", C.POINTER(C.c_double))]
+
+
+class _CSearchTiming(C.Structure):
+    _fields_ = [("total_ms", C.c_float), ("root_ms", C.c_float), ("sim_loop_ms", C.c_float),
+                ("kernel_launches", C.c_int64), ("simulations", C.c_int64)]
+
+
+class _CShapes(C.Structure):
+    _fields_ = [("initial_channels", C.c_int32), ("initial_flat_size", C.c_int32), ("enc_c", C.c_int32),
+                ("enc_h", C.c_int32), ("enc_w", C.c_int32), ("recurrent_flat_size", C.c_int32),
+                ("value_support_size", C.c_int32), ("reward_support_size", C.c_int32),
+                ("value_step", C.c_double), ("value_min", C.c_double), ("reward_step", C.c_double),
+                ("reward_min", C.c_double), ("weight_blob_bytes", C.c_int64), ("node_pool_bytes", C.c_int64)]
+
+
+@dataclass
+class MuZeroNetworkConfig:  # config.h:15-31
+    downsample: bool = False
+    normalize_hidden_states: bool = True
+    resnet_channels: int = 128
+    representation_blocks: int = 4
+    dynamics_blocks: int = 4
+    prediction_blocks: int = 4
+    reward_reduced_channels: int = 16
+    policy_reduced_channels: int = 16
+    value_reduced_channels: int = 16
+    reward_head_layers: List[int] = field(default_factory=lambda: [64])
+    policy_head_layers: List[int] = field(default_factory=lambda: [64])
+    value_head_layers: List[int] = field(default_factory=lambda: [64])
+
+
+@dataclass
+class MuZeroConfig:  # config.h:33-117 (hot-path fields) + engine knobs
+    observation_shape: tuple = (3, 6, 7)
+    num_actions: int = 7                 # action_space = range(num_actions)
+    action_channels: int = 1
+    num_players: int = 2
+    stacked_observations: int = 0
+    value_upperbound: float = NINF_D
+    value_lowerbound: float = INF_D
+    min_reward: float = -300.0
+    max_reward: float = 300.0
+    min_value: float = -300.0
+    max_value: float = 300.0
+    use_contractive_mapping: bool = True
+    num_simulations: int = 50
+    discount: float = 0.997
+    dirichlet_alpha: float = 0.3
+    dirichlet_epsilon: float = 0.25
+    pb_c_base: float = 19652.0
+    pb_c_init: float = 1.25
+    seed: int = 0
+    network_config: MuZeroNetworkConfig = field(default_factory=MuZeroNetworkConfig)
+    action_planes: Optional[np.ndarray] = None   # action_representation_recurrent pre-evaluated [A][ach*h*w]
+    # engine
+    max_trees: int = 1024
+    precision: int = FP32_CHECK
+    evaluator: int = EVAL_NETWORK
+    se_ranges: tuple = (-1.0, 1.0, -0.5, 0.5)
+
+
+@dataclass
+class MCTSReturn:  # T x types::MCTSReturn (types.h:70-76), SoA
+    root_value: np.ndarray
+    max_tree_depth: np.ndarray
+    n_children: np.ndarray
+    child_actions: np.ndarray
+    child_visits: np.ndarray
+    children_relative_visit: np.ndarray
+    emperical_policy: np.ndarray
+
+
+@dataclass
+class InferenceOutputs:  # B x VPRNetModel::InferenceOutputs (vprnet.h:64-69), SoA
+    value: np.ndarray
+    reward: np.ndarray
+    policy: np.ndarray
+    encoded_state: np.ndarray
+
+
+_lib = None
+
+EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_destroy", "mzb_load_weights",
+           "mzb_nccl_unique_id", "mzb_nccl_init", "mzb_broadcast_weights", "mzb_weights_checksum",
+           "mzb_initial_inference", "mzb_recurrent_inference", "mzb_bench_recurrent", "mzb_search_seed",
+           "mzb_search_batch", "mzb_search_batch_device_obs", "mzb_last_search_timing", "mzb_search_set_recording",
+           "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes"]
+
+
+def load_library(path=None):
+    """dlopen libmzb200.so.  Fails loudly when the CUDA extension is missing: there is no fallback path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise MzbError("libmzb200.so not found at %s — build it (python __graft_entry__.py / muzero-cpp_b200/build.py)" % path)
+    lib = C.CDLL(path)
+    lib.mzb_last_error.restype = C.c_char_p
+    lib.mzb_version.restype = C.c_char_p
+    lib.mzb_engine_create.argtypes = [C.POINTER(_CConfig), C.c_int, C.POINTER(C.c_void_p)]
+    lib.mzb_engine_destroy.argtypes = [C.c_void_p]
+    lib.mzb_engine_destroy.restype = None
+    lib.mzb_load_weights.argtypes = [C.c_void_p, C.POINTER(_CTensorDesc), C.c_int]
+    lib.mzb_nccl_unique_id.argtypes = [C.c_char_p]
+    lib.mzb_nccl_init.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int]
+    lib.mzb_broadcast_weights.argtypes = [C.c_void_p, C.c_int]
+    lib.mzb_weights_checksum.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+    dp, fp, ip = C.POINTER(C.c_double), C.POINTER(C.c_float), C.POINTER(C.c_int32)
+    lib.mzb_initial_inference.argtypes = [C.c_void_p, fp, C.c_int, dp, dp, dp, fp]
+    lib.mzb_recurrent_inference.argtypes = [C.c_void_p, fp, ip, C.c_int, dp, dp, dp, fp]
+    lib.mzb_bench_recurrent.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int)]
+    lib.mzb_search_seed.argtypes = [C.c_void_p, C.c_int, C.c_int, ip]
+    lib.mzb_search_batch.argtypes = [C.c_void_p, fp, C.POINTER(C.c_uint32), ip, C.POINTER(C.c_uint8), C.c_int,
+                                     C.POINTER(_CSearchResult)]
+    lib.mzb_search_batch_device_obs.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), ip,
+                                                C.POINTER(C.c_uint8), C.c_int, C.POINTER(_CSearchResult)]
+    lib.mzb_last_search_timing.argtypes = [C.c_void_p, C.POINTER(_CSearchTiming)]
+    lib.mzb_search_set_recording.argtypes = [C.c_void_p, C.c_int]
+    lib.mzb_search_get_trace.argtypes = [C.c_void_p, C.c_int, ip, ip]
+    lib.mzb_search_get_records.argtypes = [C.c_void_p, C.c_int, dp, dp, dp]
+    lib.mzb_get_shapes.argtypes = [C.c_void_p, C.POINTER(_CShapes)]
+    _lib = lib
+    return lib
+
+
+def _ptr(a, ct):
+    return a.ctypes.data_as(C.POINTER(ct))
+
+
+class Engine:
+    """One engine per GPU: T tree slots (each with its own std::mt19937 stream, seed + slot), the node pool and the
+    network.  Stands where the reference has N x MCTS + VPRNetEvaluator + DeviceManager + VPRNetModel."""
+
+    def __init__(self, config: MuZeroConfig, device: int = 0):
+        self.lib = load_library()
+        self.config = config
+        nc = config.network_config
+        cc = _CConfig()
+        cc.observation_c, cc.observation_h, cc.observation_w = config.observation_shape
+        cc.num_actions = config.num_actions
+        cc.action_channels = config.action_channels
+        cc.num_players = config.num_players
+        cc.stacked_observations = config.stacked_observations
+        cc.value_upperbound, cc.value_lowerbound = config.value_upperbound, config.value_lowerbound
+        cc.min_reward, cc.max_reward = config.min_reward, config.max_reward
+        cc.min_value, cc.max_value = config.min_value, config.max_value
+        cc.use_contractive_mapping = int(config.use_contractive_mapping)
+        cc.num_simulations = config.num_simulations
+        cc.discount, cc.dirichlet_alpha, cc.dirichlet_epsilon = config.discount, config.dirichlet_alpha, config.dirichlet_epsilon
+        cc.pb_c_base, cc.pb_c_init = config.pb_c_base, config.pb_c_init
+        cc.seed = config.seed
+        cc.downsample = int(nc.downsample)
+        cc.normalize_hidden_states = int(nc.normalize_hidden_states)
+        cc.resnet_channels = nc.resnet_channels
+        cc.representation_blocks, cc.dynamics_blocks, cc.prediction_blocks = nc.representation_blocks, nc.dynamics_blocks, nc.prediction_blocks
+        cc.reward_reduced_channels, cc.policy_reduced_channels, cc.value_reduced_channels = nc.reward_reduced_channels, nc.policy_reduced_channels, nc.value_reduced_channels
+        for name in ("reward", "policy", "value"):
+            layers = list(getattr(nc, name + "_head_layers"))
+            if len(layers) > MAX_HEAD_LAYERS:
+                raise MzbError("too many head layers")
+            setattr(cc, "n_%s_head_layers" % name, len(layers))
+            arr = getattr(cc, name + "_head_layers")
+            for i, v in enumerate(layers):
+                arr[i] = v
+        self._planes = None
+        if config.action_planes is not None:
+            self._planes = np.ascontiguousarray(config.action_planes, dtype=np.float32)
+            cc.action_planes = _ptr(self._planes, C.c_float)
+        cc.max_trees, cc.precision, cc.evaluator = config.max_trees, config.precision, config.evaluator
+        cc.se_value_lo, cc.se_value_hi, cc.se_reward_lo, cc.se_reward_hi = config.se_ranges
+        self._h = C.c_void_p()
+        self._check(self.lib.mzb_engine_create(C.byref(cc), device, C.byref(self._h)))
+        sh = _CShapes()
+        self._check(self.lib.mzb_get_shapes(self._h, C.byref(sh)))
+        self.shapes = sh
+
+    def _check(self, rc):
+        if rc != 0:
+            raise MzbError("mzb200 error %d: %s" % (rc, self.lib.mzb_last_error().decode()))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self.lib.mzb_engine_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def get_shapes(self):
+        sh = _CShapes()
+        self._check(self.lib.mzb_get_shapes(self._h, C.byref(sh)))
+        return sh
+
+    # VPRNetModel::LoadCheckpoint (vprnet.cpp:66-74): named fp32 tensors of the module archive
+    def load_weights(self, tensors: dict):
+        keep = []
+        descs = (_CTensorDesc * len(tensors))()
+        for i, (name, arr) in enumerate(tensors.items()):
+            a = np.ascontiguousarray(arr, dtype=np.float32)
+            keep.append(a)
+            descs[i].name = name.encode()
+            descs[i].data = _ptr(a, C.c_float)
+            descs[i].ndim = a.ndim
+            for k in range(a.ndim):
+                descs[i].dims[k] = a.shape[k]
+        self._check(self.lib.mzb_load_weights(self._h, descs, len(tensors)))
+
+    def weights_checksum(self):
+        out = C.c_uint64()
+        self._check(self.lib.mzb_weights_checksum(self._h, C.byref(out)))
+        return out.value
+
+    # learner.cpp:93-101 weight sync
+    @staticmethod
+    def nccl_unique_id():
+        lib = load_library()
+        buf = C.create_string_buffer(128)
+        rc = lib.mzb_nccl_unique_id(buf)
+        if rc != 0:
+            raise MzbError(lib.mzb_last_error().decode())
+        return buf.raw
+
+    def nccl_init(self, uid: bytes, rank: int, world_size: int):
+        self._check(self.lib.mzb_nccl_init(self._h, uid, rank, world_size))
+
+    def broadcast_weights(self, root: int = 0):
+        self._check(self.lib.mzb_broadcast_weights(self._h, root))
+
+    # VPRNetModel::InitialInference (vprnet.cpp:77-129)
+    def initial_inference(self, stacked_observations) -> InferenceOutputs:
+        obs = np.ascontiguousarray(stacked_observations, dtype=np.float32).reshape(-1, self.shapes.initial_flat_size)
+        B, A = obs.shape[0], self.config.num_actions
+        v = np.empty(B, np.float64); r = np.empty(B, np.float64); p = np.empty((B, A), np.float64)
+        h = np.empty((B, self.shapes.recurrent_flat_size), np.float32)
+        self._check(self.lib.mzb_initial_inference(self._h, _ptr(obs, C.c_float), B, _ptr(v, C.c_double),
+                                                   _ptr(r, C.c_double), _ptr(p, C.c_double), _ptr(h, C.c_float)))
+        return InferenceOutputs(v, r, p, h)
+
+    # VPRNetModel::RecurrentInference (vprnet.cpp:131-189)
+    def recurrent_inference(self, encoded_state, action) -> InferenceOutputs:
+        hid = np.ascontiguousarray(encoded_state, dtype=np.float32).reshape(-1, self.shapes.recurrent_flat_size)
+        act = np.ascontiguousarray(action, dtype=np.int32).reshape(-1)
+        B, A = hid.shape[0], self.config.num_actions
+        if act.shape[0] != B:
+            raise MzbError("action batch differs from hidden batch")
+        v = np.empty(B, np.float64); r = np.empty(B, np.float64); p = np.empty((B, A), np.float64)
+        h = np.empty((B, self.shapes.recurrent_flat_size), np.float32)
+        self._check(self.lib.mzb_recurrent_inference(self._h, _ptr(hid, C.c_float), _ptr(act, C.c_int32), B,
+                                                     _ptr(v, C.c_double), _ptr(r, C.c_double), _ptr(p, C.c_double),
+                                                     _ptr(h, C.c_float)))
+        return InferenceOutputs(v, r, p, h)
+
+    def bench_recurrent(self, batch, iters):
+        ms = C.c_float(); nl = C.c_int()
+        self._check(self.lib.mzb_bench_recurrent(self._h, batch, iters, C.byref(ms), C.byref(nl)))
+        return ms.value, nl.value
+
+    # MCTS::MCTS rng_(seed) (mcts.cpp:26)
+    def seed_slots(self, seeds, first_slot=0):
+        s = np.ascontiguousarray(seeds, dtype=np.int32)
+        self._check(self.lib.mzb_search_seed(self._h, first_slot, s.shape[0], _ptr(s, C.c_int32)))
+
+    # T x MCTS::run (mcts.cpp:34-87)
+    def run(self, stacked_observations, legal_mask, to_play, add_exploration_noise, device_obs_ptr=None) -> MCTSReturn:
+        legal = np.ascontiguousarray(legal_mask, dtype=np.uint32).reshape(-1)
+        T, A = legal.shape[0], self.config.num_actions
+        tp = np.ascontiguousarray(to_play, dtype=np.int32).reshape(-1)
+        noise = np.ascontiguousarray(add_exploration_noise, dtype=np.uint8).reshape(-1)
+        if tp.shape[0] != T or noise.shape[0] != T:
+            raise MzbError("per-tree inputs disagree on the number of trees")
+        res = MCTSReturn(np.empty(T, np.float64), np.empty(T, np.int32), np.empty(T, np.int32),
+                         np.empty((T, A), np.int32), np.empty((T, A), np.int32), np.empty((T, A), np.float64),
+                         np.empty((T, A), np.float64))
+        cr = _CSearchResult(_ptr(res.root_value, C.c_double), _ptr(res.max_tree_depth, C.c_int32),
+                            _ptr(res.n_children, C.c_int32), _ptr(res.child_actions, C.c_int32),
+                            _ptr(res.child_visits, C.c_int32), _ptr(res.children_relative_visit, C.c_double),
+                            _ptr(res.emperical_policy, C.c_double))
+        if device_obs_ptr is not None:
+            self._check(self.lib.mzb_search_batch_device_obs(self._h, C.c_void_p(device_obs_ptr), _ptr(legal, C.c_uint32),
+                                                             _ptr(tp, C.c_int32), _ptr(noise, C.c_uint8), T, C.byref(cr)))
+        else:
+            width = 1 if self.config.evaluator == EVAL_SYNTHETIC else self.shapes.initial_flat_size
+            obs = np.ascontiguousarray(stacked_observations, dtype=np.float32).reshape(T, width)
+            self._check(self.lib.mzb_search_batch(self._h, _ptr(obs, C.c_float), _ptr(legal, C.c_uint32),
+                                                  _ptr(tp, C.c_int32), _ptr(noise, C.c_uint8), T, C.byref(cr)))
+        return res
+
+    def last_search_timing(self):
+        t = _CSearchTiming()
+        self._check(self.lib.mzb_last_search_timing(self._h, C.byref(t)))
+        return dict(total_ms=t.total_ms, root_ms=t.root_ms, sim_loop_ms=t.sim_loop_ms,
+                    kernel_launches=t.kernel_launches, simulations=t.simulations)
+
+    def set_recording(self, enabled=True):
+        self._check(self.lib.mzb_search_set_recording(self._h, int(enabled)))
+
+    def get_trace(self, n_trees):
+        n = self.config.num_simulations
+        parent = np.empty((n_trees, n), np.int32); action = np.empty((n_trees, n), np.int32)
+        self._check(self.lib.mzb_search_get_trace(self._h, n_trees, _ptr(parent, C.c_int32), _ptr(action, C.c_int32)))
+        return parent, action
+
+    def get_records(self, n_trees):
+        n1, A = self.config.num_simulations + 1, self.config.num_actions
+        v = np.empty((n_trees, n1), np.float64); r = np.empty((n_trees, n1), np.float64)
+        p = np.empty((n_trees, n1, A), np.float64)
+        self._check(self.lib.mzb_search_get_records(self._h, n_trees, _ptr(v, C.c_double), _ptr(r, C.c_double), _ptr(p, C.c_double)))
+        return v, r, p
+
+
+def legal_mask_from_actions(legal_actions, num_actions):
+    """legal action lists (AbstractGame::legal_actions, abstract_game.h) -> bit masks.  Children are created in
+    ascending action order, which is the order every shipped game reports them in."""
+    out = np.zeros(len(legal_actions), np.uint32)
+    for i, acts in enumerate(legal_actions):
+        m = 0
+        for a in acts:
+            if a < 0 or a >= num_actions:
+                raise MzbError("action outside the action space")
+            m |= 1 << a
+        out[i] = m
+    return out
+
+
+# game presets = the shapes of BASELINE.json's configs
+def preset(name, **over):
+    nc = MuZeroNetworkConfig()
+    kw = {}
+    if name in ("c4d", "c4r", "ttt"):
+        kw = dict(observation_shape=(3, 6, 7) if name != "ttt" else (3, 3, 3), num_actions=7 if name != "ttt" else 9,
+                  num_players=2, value_upperbound=10.0, value_lowerbound=-10.0, min_reward=-10.0, max_reward=10.0,
+                  min_value=-10.0, max_value=10.0)
+        if name == "c4r":
+            nc = MuZeroNetworkConfig(resnet_channels=64, representation_blocks=3, dynamics_blocks=3, prediction_blocks=3)
+        if name == "ttt":
+            kw["num_simulations"] = 25
+    elif name == "ale":
+        nc = MuZeroNetworkConfig(downsample=True, reward_reduced_channels=64, policy_reduced_channels=64,
+                                 value_reduced_channels=64, reward_head_layers=[64, 64], policy_head_layers=[64, 64],
+                                 value_head_layers=[64, 64])
+        kw = dict(observation_shape=(1, 96, 96), num_actions=18, num_players=1, stacked_observations=6,
+                  min_value=-21.0, max_value=21.0, min_reward=-1.0, max_reward=1.0)
+    elif name == "tiny":
+        nc = MuZeroNetworkConfig(resnet_channels=16, representation_blocks=1, dynamics_blocks=1, prediction_blocks=2,
+                                 reward_reduced_channels=4, policy_reduced_channels=2, value_reduced_channels=3,
+                                 reward_head_layers=[8], policy_head_layers=[8, 6], value_head_layers=[])
+        kw = dict(observation_shape=(2, 3, 4), num_actions=5, num_players=2, stacked_observations=1,
+                  value_upperbound=5.0, value_lowerbound=-5.0, min_reward=-3.0, max_reward=3.0, min_value=-5.0, max_value=5.0)
+    elif name == "tinyds":
+        nc = MuZeroNetworkConfig(downsample=True, resnet_channels=16, representation_blocks=1, dynamics_blocks=1,
+                                 prediction_blocks=1, reward_reduced_channels=4, policy_reduced_channels=4,
+                                 value_reduced_channels=4, reward_head_layers=[8], policy_head_layers=[8], value_head_layers=[8])
+        kw = dict(observation_shape=(1, 32, 24), num_actions=6, num_players=1, stacked_observations=2,
+                  min_value=-21.0, max_value=21.0, min_reward=-1.0, max_reward=1.0)
+    else:
+        raise MzbError("unknown preset " + name)
+    kw["network_config"] = nc
+    kw.update(over)
+    return MuZeroConfig(**kw)

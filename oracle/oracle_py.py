@@ -206,3 +206,43 @@ def mzbt_save(path, tensors):
             f.write(struct.pack("<I", len(nb)) + nb + struct.pack("<II", _DT_INV[arr.dtype], arr.ndim))
             f.write(struct.pack("<%dq" % arr.ndim, *arr.shape))
             f.write(arr.tobytes())
+
+
+# ---------------------------------------------------------------- custom evaluators (Python callbacks)
+class EvalOut(C.Structure):
+    _fields_ = [("value", C.c_double), ("reward", C.c_double), ("policy", C.c_double * MAX_A)]
+
+
+EVAL_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(EvalOut))
+
+
+def mcts_create(cfg, seed):
+    return lib().mzo_mcts_create(C.byref(cfg), seed)
+
+
+def mcts_destroy(m):
+    lib().mzo_mcts_destroy(m)
+
+
+def mcts_run(m, legal, to_play, noise, eval_py):
+    """eval_py(parent_node, action, new_node) -> (value, reward, policy list); parent_node < 0 = initial inference."""
+    l = lib()
+    l.mzo_mcts_run.argtypes = [C.POINTER(MCTS), C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, EVAL_FN, C.c_void_p,
+                               C.POINTER(Result), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    cfg = m.contents.cfg
+
+    def cb(ctx, parent, action, new_node, out):
+        v, r, p = eval_py(parent, action, new_node)
+        out.contents.value = v
+        out.contents.reward = r
+        for i, x in enumerate(p):
+            out.contents.policy[i] = x
+
+    fn = EVAL_FN(cb)
+    n = cfg.num_simulations
+    res = Result()
+    tp = (C.c_int32 * max(n, 1))()
+    ta = (C.c_int32 * max(n, 1))()
+    arr = (C.c_int32 * len(legal))(*legal)
+    l.mzo_mcts_run(m, arr, len(legal), to_play, int(noise), fn, None, C.byref(res), tp, ta)
+    return result_to_dict(res, cfg.num_actions, tp[:n], ta[:n])

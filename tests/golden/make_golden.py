@@ -1,0 +1,69 @@
+"""Regenerate the golden fixtures from the UNMODIFIED reference (oracle/_ref/ref_driver, built from
+/root/reference by oracle/ref_build/Makefile).  Run in the build container only:
+
+    make -C oracle/ref_build && python tests/golden/make_golden.py
+
+Outputs (committed):
+  mcts_se.json    MCTS::run results + expansion traces for the SE synthetic evaluator over several configs
+  net_tiny.mzbt   weights / inputs / outputs of VPRNetModel::{Initial,Recurrent}Inference, plain head
+  net_tinyds.mzbt same for the downsample head
+  encoder.json    ValueEncoder support sizes and decode known answers
+"""
+import json
+import os
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+from oracle import oracle_py as O  # noqa: E402
+
+# (name, ref_driver args, oracle config kwargs, trees, runs, legal_mode, noise, seed)
+MCTS_CASES = [
+    ("c4_default", ["game=c4d"], dict(), 8, 2, 0, 1, 0),
+    ("c4_legal_subsets", ["game=c4d"], dict(), 8, 2, 1, 1, 11),
+    ("c4_no_noise", ["game=c4d"], dict(), 4, 2, 1, 0, 3),
+    ("ttt_25", ["game=ttt", "sims=25"], dict(num_actions=9, num_simulations=25), 8, 2, 1, 1, 0),
+    ("ale_like_1p_unbounded", ["game=tinyds", "actions=18", "unbounded"],
+     dict(num_actions=18, num_players=1, lower="INF", upper="NINF"), 4, 2, 0, 1, 5),
+    ("ref_test_config", ["game=c4d", "actions=6", "sims=10", "pb_c_base=1", "pb_c_init=0", "discount=0.5", "lower=0", "upper=1"],
+     dict(num_actions=6, num_simulations=10, pb_c_base=1.0, pb_c_init=0.0, discount=0.5, lower=0.0, upper=1.0), 4, 2, 1, 1, 0),
+    ("deep_4_actions_200", ["game=c4d", "actions=4", "sims=200"], dict(num_actions=4, num_simulations=200), 2, 1, 0, 1, 2),
+    ("even_actions_2", ["game=c4d", "actions=2", "sims=30"], dict(num_actions=2, num_simulations=30), 4, 1, 0, 1, 9),
+]
+
+
+def main():
+    assert O.have_ref(), "build oracle/_ref first (make -C oracle/ref_build)"
+    cases = []
+    for name, rargs, okw, T, runs, legal_mode, noise, seed in MCTS_CASES:
+        txt = O.run_ref("mcts", *rargs, "trees=%d" % T, "runs=%d" % runs, "legal_mode=%d" % legal_mode,
+                        "noise=%d" % noise, "seed=%d" % seed)
+        res = O.parse_ref_mcts(txt)
+        for r in res:
+            r["root_value"] = float(r["root_value"]).hex()
+            r["relvisits"] = [float(x).hex() for x in r["relvisits"]]
+            r["policy"] = [float(x).hex() for x in r["policy"]]
+        cases.append(dict(name=name, config=okw, trees=T, runs=runs, legal_mode=legal_mode, noise=noise, seed=seed, results=res))
+    with open(os.path.join(HERE, "mcts_se.json"), "w") as f:
+        json.dump(cases, f)
+    O.run_ref("net", "game=tiny", "batch=3", "seed=3", "out=" + os.path.join(HERE, "net_tiny.mzbt"))
+    O.run_ref("net", "game=tinyds", "batch=2", "seed=4", "out=" + os.path.join(HERE, "net_tinyds.mzbt"))
+    enc = []
+    for lo, hi, extra in [(-10, 10, []), (-22, 22, []), (-1, 1, []), (-21, 21, []), (-300, 300, []), (-5, 7, ["no_contractive"])]:
+        txt = O.run_ref("encoder", "min=%g" % lo, "max=%g" % hi, "rows=6", "seed=1", *extra)
+        lines = txt.strip().splitlines()
+        support = int(lines[0].split()[1])
+        rows = []
+        for ln in lines[1:]:
+            tok = ln.split()
+            arrow = tok.index("->")
+            rows.append(dict(logits=tok[1:arrow], decoded=tok[arrow + 1]))
+        enc.append(dict(min=lo, max=hi, contractive=not extra, support=support, rows=rows))
+    with open(os.path.join(HERE, "encoder.json"), "w") as f:
+        json.dump(enc, f)
+    print("golden fixtures written to", HERE)
+
+
+if __name__ == "__main__":
+    main()

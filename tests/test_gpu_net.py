@@ -1,0 +1,129 @@
+"""GPU parity, part 2: the VPRNet towers through the C ABI (mzb_initial_inference / mzb_recurrent_inference =
+VPRNetModel::{Initial,Recurrent}Inference, vprnet.cpp:77-189) against the pinned fp32 oracle.
+Tolerances are the north star's: <= 1e-4 absolute in fp32 check mode, <= 2e-2 relative in bf16 mode."""
+import os
+
+import numpy as np
+import pytest
+
+import helpers as H
+from oracle import oracle_py as O
+from oracle import vprnet_oracle as V
+
+pytestmark = pytest.mark.gpu
+
+FP32_ATOL = 1e-4   # north star: fp32 check mode vs libtorch fp32
+BF16_RTOL = 2e-2   # north star: bf16 mode, relative (to the output's scale)
+
+
+def _engine(game, T, precision, **over):
+    import mzb200
+    cfg = mzb200.preset(game, max_trees=T, precision=precision, **over)
+    return mzb200.Engine(cfg, 0)
+
+
+def _check(got, want, precision, what):
+    if precision == 0:
+        np.testing.assert_allclose(got, want, rtol=0, atol=FP32_ATOL, err_msg=what)
+    else:
+        scale = max(1.0, float(np.abs(want).max()))
+        err = float(np.abs(got - want).max())
+        assert err <= BF16_RTOL * scale, "%s: max err %g above %g" % (what, err, BF16_RTOL * scale)
+
+
+def _run_chain(eng, net, obs, a1, a2, precision, tag):
+    g0 = eng.initial_inference(obs)
+    o0 = net.initial_inference(obs)
+    for k in ("value", "reward", "policy"):
+        _check(getattr(g0, k), o0[k], precision, "%s init %s" % (tag, k))
+    _check(g0.encoded_state, o0["hidden"], precision, tag + " init hidden")
+    # feed the ORACLE's hidden state so each step is compared on identical inputs
+    g1 = eng.recurrent_inference(o0["hidden"], a1)
+    o1 = net.recurrent_inference(o0["hidden"], a1)
+    for k in ("value", "reward", "policy"):
+        _check(getattr(g1, k), o1[k], precision, "%s rec1 %s" % (tag, k))
+    _check(g1.encoded_state, o1["hidden"], precision, tag + " rec1 hidden")
+    g2 = eng.recurrent_inference(o1["hidden"], a2)
+    o2 = net.recurrent_inference(o1["hidden"], a2)
+    for k in ("value", "reward", "policy"):
+        _check(getattr(g2, k), o2[k], precision, "%s rec2 %s" % (tag, k))
+    _check(g2.encoded_state, o2["hidden"], precision, tag + " rec2 hidden")
+    assert np.allclose(g1.policy.sum(axis=1), 1.0, atol=1e-5)
+
+
+@pytest.mark.parametrize("game", ["tiny", "tinyds"])
+def test_fp32_matches_reference_golden(game, golden_dir):
+    """weights, inputs and outputs produced by the unmodified reference's VPRNetModel (tests/golden/make_golden.py)"""
+    d = O.mzbt_load(os.path.join(golden_dir, "net_%s.mzbt" % game))
+    W = {k[2:]: v for k, v in d.items() if k.startswith("w.")}
+    eng = _engine(game, 8, 0)
+    eng.load_weights(W)
+    g0 = eng.initial_inference(d["in.obs"])
+    for k, attr in (("value", "value"), ("reward", "reward"), ("policy", "policy"), ("hidden", "encoded_state")):
+        np.testing.assert_allclose(getattr(g0, attr), d["init." + k], rtol=0, atol=FP32_ATOL, err_msg="init " + k)
+    g1 = eng.recurrent_inference(d["init.hidden"], d["in.a1"])
+    for k, attr in (("value", "value"), ("reward", "reward"), ("policy", "policy"), ("hidden", "encoded_state")):
+        np.testing.assert_allclose(getattr(g1, attr), d["rec1." + k], rtol=0, atol=FP32_ATOL, err_msg="rec1 " + k)
+    g2 = eng.recurrent_inference(d["rec1.hidden"], d["in.a2"])
+    for k, attr in (("value", "value"), ("reward", "reward"), ("policy", "policy"), ("hidden", "encoded_state")):
+        np.testing.assert_allclose(getattr(g2, attr), d["rec2." + k], rtol=0, atol=FP32_ATOL, err_msg="rec2 " + k)
+    eng.close()
+
+
+@pytest.mark.parametrize("game,B", [("c4r", 9), ("ttt", 5), ("c4d", 4)])
+def test_fp32_matches_oracle_random_weights(game, B):
+    ncfg = V.preset(game)
+    W = H.random_weights(ncfg, seed=7)
+    net = V.VPRNetOracle(ncfg, W)
+    eng = _engine(game, 16, 0)
+    eng.load_weights(W)
+    rng = np.random.default_rng(1)
+    obs = rng.random((B, ncfg.in_channels * ncfg.obs_shape[1] * ncfg.obs_shape[2]), dtype=np.float32)
+    a1 = rng.integers(0, ncfg.num_actions, B).astype(np.int32)
+    a2 = rng.integers(0, ncfg.num_actions, B).astype(np.int32)
+    _run_chain(eng, net, obs, a1, a2, 0, game)
+    sh = eng.get_shapes()
+    assert sh.value_support_size == net.value_encoder.support_size
+    assert abs(sh.value_step - net.value_encoder.step_size) < 1e-12
+    eng.close()
+
+
+def test_fp32_batch_larger_than_slots_and_errors():
+    import mzb200
+    ncfg = V.preset("tiny")
+    W = H.random_weights(ncfg, seed=2)
+    net = V.VPRNetOracle(ncfg, W)
+    eng = _engine("tiny", 4, 0)
+    with pytest.raises(mzb200.MzbError):   # weights not loaded yet: must fail loudly, not fall back
+        eng.initial_inference(np.zeros((1, ncfg.in_channels * 12), np.float32))
+    with pytest.raises(mzb200.MzbError):   # missing tensor
+        eng.load_weights({k: v for k, v in W.items() if "reward_conv" not in k})
+    eng.load_weights(W)
+    rng = np.random.default_rng(0)
+    obs = rng.random((11, ncfg.in_channels * 12), dtype=np.float32)   # 11 samples through 4 slots: chunked
+    g = eng.initial_inference(obs)
+    o = net.initial_inference(obs)
+    np.testing.assert_allclose(g.value, o["value"], atol=FP32_ATOL)
+    np.testing.assert_allclose(g.encoded_state, o["hidden"], atol=FP32_ATOL)
+    with pytest.raises(mzb200.MzbError):
+        eng.recurrent_inference(o["hidden"], np.full(11, 99, np.int32))
+    eng.close()
+
+
+def test_custom_action_planes():
+    """action_representation_recurrent (vprnet.cpp:143) is a user function: arbitrary planes via the per-action table"""
+    ncfg = V.preset("tiny")
+    W = H.random_weights(ncfg, seed=5)
+    rng = np.random.default_rng(3)
+    planes = rng.random((ncfg.num_actions, 12), dtype=np.float32)
+    net = V.VPRNetOracle(ncfg, W)
+    eng = _engine("tiny", 8, 0, action_planes=planes)
+    eng.load_weights(W)
+    hid = rng.random((6, 16 * 12), dtype=np.float32)
+    act = rng.integers(0, ncfg.num_actions, 6).astype(np.int32)
+    g = eng.recurrent_inference(hid, act)
+    o = net.recurrent_inference(hid, act, action_plane_fn=lambda a: planes[a])
+    np.testing.assert_allclose(g.value, o["value"], atol=FP32_ATOL)
+    np.testing.assert_allclose(g.reward, o["reward"], atol=FP32_ATOL)
+    np.testing.assert_allclose(g.encoded_state, o["hidden"], atol=FP32_ATOL)
+    eng.close()

@@ -45,11 +45,11 @@ __global__ void __launch_bounds__(128) head_kernel(const T* __restrict__ x, cons
     const int n0 = hd.red * hd.hw;
     for (int o = warp; o < n0; o += 4) {
         int r = o / hd.hw, p = o - r * hd.hw;
-        float acc = 0.f;
-        for (int c = lane; c < hd.C; c += 32) acc += hd.w1[r * hd.C + c] * xs[p * hd.C + c];
+        double acc = 0.0;   // fp64 accumulation: the heads are tiny and feed the error-amplifying decode
+        for (int c = lane; c < hd.C; c += 32) acc += (double)(hd.w1[r * hd.C + c] * xs[p * hd.C + c]);
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
-        if (lane == 0) bufA[o] = acc + hd.b1[r];
+        if (lane == 0) bufA[o] = (float)(acc + (double)hd.b1[r]);
     }
     __syncthreads();
     float* cur = bufA;
@@ -59,12 +59,12 @@ __global__ void __launch_bounds__(128) head_kernel(const T* __restrict__ x, cons
         const float* W = hd.W[l];
         const float* bias = hd.b[l];
         for (int j = warp; j < nout; j += 4) {
-            float acc = 0.f;
-            for (int i = lane; i < nin; i += 32) acc += W[(long)j * nin + i] * cur[i];
+            double dacc = 0.0;
+            for (int i = lane; i < nin; i += 32) dacc += (double)(W[(long)j * nin + i] * cur[i]);
 #pragma unroll
-            for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+            for (int off = 16; off > 0; off >>= 1) dacc += __shfl_xor_sync(0xffffffffu, dacc, off);
             if (lane == 0) {
-                acc += bias[j];
+                float acc = (float)(dacc + (double)bias[j]);
                 if (l < hd.n_layers - 1) acc = fmaxf(acc, 0.f);
                 nxt[j] = acc;
             }

@@ -1,5 +1,276 @@
-// net_bf16.cu — placeholder until the tcgen05 towers land (next milestone).
-#include "net_backend.h"
+// net_bf16.cu — MZB_BF16 backend: the residual towers as implicit-GEMM tcgen05 kernels (bf16 operands, fp32
+// accumulation in tensor memory), activations stored in bf16 NHWC.  Replaces conv3x3+BN+ReLU(+residual) of
+// ResidualHead / ResidualBlock (model_layers.cpp:70-109) for every layer whose shape fits the tensor path; the few
+// that do not (3-channel representation head, strided downsample convs) run on the direct kernels of net_direct.cuh.
+//
+// Formulation (per CTA = G whole games):   D[cout, pixel] = sum_{tap, cin} Wf[cout, tap, cin] * X[pixel + shift(tap), cin]
+//   * A operand  = BN-folded weights, bf16, pre-packed on the host as ready-made shared-memory images of
+//                  [64 K][128 cout] blocks; streamed by 1-D bulk async copies (UBLKCP) through a ring of stages.
+//   * B operand  = the CTA's activations, loaded ONCE from HBM/L2 into a zero-padded pixel layout: every game owns
+//                  P = (H+1)*(W+1) rows: one zero row of W+1 pixels, then H rows of W real pixels + 1 zero pixel.  In this
+//                  layout a 3x3 tap is a constant row shift dy*(W+1)+dx, so the nine taps are nine shared-memory
+//                  matrix descriptors over the same resident tile: no im2col copy, no re-read of activations.
+//                  No-swizzle K-major core matrices ([K chunk of 8][row][8 elems]) make a row shift a 16-byte offset.
+//   * D          = 128 TMEM lanes (cout) x N columns (padded pixels), fp32.
+//   * epilogue   = tcgen05.ld, + bias (+ per-action table) (+ residual), ReLU, bf16 store of the real pixels only.
+// Roles: warp 0 streams weights, warp 1 allocates TMEM and issues the MMAs (one thread), warps 2-5 run the epilogue.
+#include <cuda_bf16.h>
+
+#include "net_direct.cuh"
+#include "umma.cuh"
+
 namespace mzb {
-NetBackend* make_bf16_backend() { return nullptr; }
+namespace {
+
+using bf16 = __nv_bfloat16;
+using namespace umma;
+
+constexpr int UM = 128;                 // MMA M = cout rows (zero-padded)
+constexpr int KB = 64;                  // K elements per weight stage
+constexpr int STAGE_BYTES = KB * UM * 2;  // 16 KB
+constexpr int NSTAGE = 3;
+constexpr int UMMA_THREADS = 192;
+constexpr int TMEM_COLS = 256;
+
+struct UmmaGeom {
+    int H, W, P, G, N, HALO, R;   // rows per game, games per tile, MMA N, halo rows, total rows of the resident tile
+};
+
+struct UmmaArgs {
+    const bf16* in; const int* in_slot; long in_stride;
+    bf16* out; const int* out_slot; long out_stride;
+    const bf16* res; const int* res_slot; long res_stride;
+    const bf16* wpack;          // [9 * C/64][8][128][8]
+    const float* bias;          // [cout]
+    const float* act_table;     // [A][HW][cout] or null
+    const int* action;
+    int B, C, cout, relu;
+    UmmaGeom g;
+};
+
+__host__ __device__ inline size_t umma_x_bytes(int C, int R) { return (((size_t)(C / 8) * R * 16) + 127) / 128 * 128; }
+inline size_t umma_smem_bytes(int C, const UmmaGeom& g) {
+    return umma_x_bytes(C, g.R) + (size_t)NSTAGE * STAGE_BYTES + 128 /*barriers + tmem ptr*/ + (size_t)g.N * 4 + 128;
 }
+
+__global__ void __launch_bounds__(UMMA_THREADS, 2) umma_conv3_kernel(UmmaArgs a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const UmmaGeom g = a.g;
+    const int KC = a.C >> 3;                 // 16-byte K chunks per pixel
+    const int KB_PER_TAP = a.C / KB;
+    const int NKB = 9 * KB_PER_TAP;
+    uint8_t* X = smem;
+    uint8_t* stages = X + umma_x_bytes(a.C, g.R);
+    uint64_t* full = reinterpret_cast<uint64_t*>(stages + NSTAGE * STAGE_BYTES);
+    uint64_t* empty = full + NSTAGE;
+    uint64_t* accum = empty + NSTAGE;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(accum + 1);
+    int* colinfo = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(full) + 128);
+    const int game0 = blockIdx.x * g.G;
+    const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(a.wpack);
+
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        mbar_init(accum, 1);
+        fence_mbar_init();
+        // first ring fill: weights do not depend on the activations, start streaming immediately
+        for (int kb = 0; kb < NSTAGE && kb < NKB; ++kb) {
+            mbar_expect_tx(&full[kb], STAGE_BYTES);
+            bulk_g2s(stages + kb * STAGE_BYTES, wsrc + (size_t)kb * STAGE_BYTES, STAGE_BYTES, &full[kb]);
+        }
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr, TMEM_COLS);
+
+    // column -> (game, pixel) map of the padded layout; -1 = padding row / absent game
+    for (int q = tid; q < g.N; q += UMMA_THREADS) {
+        int info = -1;
+        const int gi = q / g.P, rem = q - gi * g.P;
+        const int yy = rem / (g.W + 1), xx = rem - yy * (g.W + 1);
+        if (gi < g.G && yy >= 1 && xx < g.W && game0 + gi < a.B) info = (gi << 16) | ((yy - 1) * g.W + xx);
+        colinfo[q] = info;
+    }
+    // resident activation tile: [K chunk][row][8 x bf16], zero padded
+    for (int idx = tid; idx < KC * g.R; idx += UMMA_THREADS) {
+        const int kc = idx % KC, r = idx / KC;
+        const int q = r - g.HALO;
+        uint8_t* dst = X + ((size_t)kc * g.R + r) * 16;
+        const bf16* src = nullptr;
+        if (q >= 0 && q < g.G * g.P) {
+            const int gi = q / g.P, rem = q - gi * g.P;
+            const int yy = rem / (g.W + 1), xx = rem - yy * (g.W + 1);
+            const int game = game0 + gi;
+            if (yy >= 1 && xx < g.W && game < a.B)
+                src = a.in + (long)(a.in_slot ? a.in_slot[game] : game) * a.in_stride + ((long)((yy - 1) * g.W + xx) * a.C + kc * 8);
+        }
+        if (src) cp_async16(dst, src);
+        else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    cp_async_wait_all();
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {   // ===== weight producer: remaining K blocks =====
+            for (int kb = NSTAGE; kb < NKB; ++kb) {
+                const int s = kb % NSTAGE;
+                mbar_wait(&empty[s], ((kb / NSTAGE) - 1) & 1);
+                mbar_expect_tx(&full[s], STAGE_BYTES);
+                bulk_g2s(stages + s * STAGE_BYTES, wsrc + (size_t)kb * STAGE_BYTES, STAGE_BYTES, &full[s]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {   // ===== MMA issuer =====
+            const uint32_t idesc = idesc_bf16_f32(UM, (uint32_t)g.N);
+            const uint32_t x_addr = smem_u32(X);
+            const uint32_t st_addr = smem_u32(stages);
+            const uint32_t lbo_b = (uint32_t)g.R * 16u;
+            for (int kb = 0; kb < NKB; ++kb) {
+                const int s = kb % NSTAGE;
+                mbar_wait(&full[s], (kb / NSTAGE) & 1);
+                tc_fence_after();
+                const int tap = kb / KB_PER_TAP, cc = kb - tap * KB_PER_TAP;
+                const int shift = (tap / 3 - 1) * (g.W + 1) + (tap % 3 - 1);
+#pragma unroll
+                for (int kk = 0; kk < KB / 16; ++kk) {
+                    const uint64_t da = smem_desc_kmajor_noswizzle(st_addr + s * STAGE_BYTES + kk * 2 * (UM * 16), UM * 16, 128);
+                    const uint64_t db = smem_desc_kmajor_noswizzle(
+                        x_addr + (uint32_t)(((cc * 8 + kk * 2) * g.R + g.HALO + shift) * 16), lbo_b, 128);
+                    mma_bf16(tmem, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+                }
+                mma_commit(&empty[s]);   // frees the weight stage once these MMAs have read it
+            }
+            mma_commit(accum);
+        }
+    } else {
+        // ===== epilogue: TMEM -> registers -> global (bf16, real pixels only) =====
+        mbar_wait(accum, 0);
+        tc_fence_after();
+        const int lane_base = 32 * (warp & 3);     // a warp may only touch its own TMEM lane quarter
+        const int co = lane_base + lane;
+        const bool co_ok = co < a.cout;
+        const float bias = co_ok ? a.bias[co] : 0.f;
+        const int HW = g.H * g.W;
+        for (int c0 = 0; c0 < g.N; c0 += 16) {
+            uint32_t v[16];
+            tmem_ld16(tmem + ((uint32_t)lane_base << 16) + (uint32_t)c0, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const int info = colinfo[c0 + j];
+                if (info < 0 || !co_ok) continue;
+                const int game = game0 + (info >> 16), pix = info & 0xffff;
+                float x = __uint_as_float(v[j]) + bias;
+                if (a.act_table) x += a.act_table[((long)a.action[game] * HW + pix) * a.cout + co];
+                if (a.res) x += __bfloat162float(a.res[(long)(a.res_slot ? a.res_slot[game] : game) * a.res_stride + (long)pix * a.cout + co]);
+                if (a.relu) x = fmaxf(x, 0.f);
+                a.out[(long)(a.out_slot ? a.out_slot[game] : game) * a.out_stride + (long)pix * a.cout + co] = __float2bfloat16(x);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem, TMEM_COLS);
+}
+
+}  // namespace
+
+namespace {
+
+// geometry of the padded resident tile for an H x W board; returns false when the shape does not fit the tensor path
+bool make_geom(int H, int W, int C, UmmaGeom* g) {
+    g->H = H; g->W = W;
+    g->P = (H + 1) * (W + 1);
+    if (g->P > 256) return false;
+    g->G = 256 / g->P;
+    g->N = (g->G * g->P + 15) / 16 * 16;
+    g->HALO = W + 2;
+    g->R = g->HALO + g->N + g->HALO;
+    if ((g->R & 1) == 0) g->R += 1;   // odd row count: the 16-byte staging stores of one pixel hit 8 distinct bank groups
+    // two CTAs per SM must fit (their prologue / epilogue overlap each other's MMA phase)
+    return umma_smem_bytes(C, *g) <= 113 * 1024;
+}
+
+class Bf16Backend : public direct::DirectBackend<bf16> {
+public:
+    const char* name() const override { return "bf16-tcgen05"; }
+
+protected:
+    struct Packed { bool ok = false; size_t off = 0; UmmaGeom g; };
+
+    bool eligible(const Conv3Host& c, UmmaGeom* g) const {
+        if (c.stride != 1 || c.cin % KB != 0 || c.cout > UM || c.cout % 8 != 0) return false;
+        if (c.in_h != c.out_h || c.in_w != c.out_w) return false;
+        return make_geom(c.in_h, c.in_w, c.cin, g);
+    }
+
+    // bf16 weight images: per 64-wide K block a ready-made smem tile [8 K-chunks][128 cout rows][8 elems]
+    int pack_extra(const NetPlan& plan, std::vector<uint8_t>* extra) override {
+        const Tower* tw[3] = {&plan.representation, &plan.dynamics, &plan.prediction};
+        extra->clear();
+        for (int t = 0; t < 3; ++t) {
+            packed_[t].assign(tw[t]->convs.size(), Packed());
+            for (size_t i = 0; i < tw[t]->convs.size(); ++i) {
+                const Conv3Host& c = tw[t]->convs[i];
+                Packed p;
+                if (!eligible(c, &p.g)) continue;
+                p.ok = true;
+                while (extra->size() % 128) extra->push_back(0);
+                p.off = extra->size();
+                const int kb_per_tap = c.cin / KB;
+                const size_t bytes = (size_t)9 * kb_per_tap * STAGE_BYTES;
+                extra->resize(extra->size() + bytes, 0);
+                bf16* dst = reinterpret_cast<bf16*>(extra->data() + p.off);
+                for (int tap = 0; tap < 9; ++tap)
+                    for (int cc = 0; cc < kb_per_tap; ++cc)
+                        for (int kc = 0; kc < 8; ++kc)
+                            for (int row = 0; row < UM; ++row)
+                                for (int e = 0; e < 8; ++e) {
+                                    const int k = cc * KB + kc * 8 + e;
+                                    const float v = row < c.cout ? c.w[((size_t)row * 9 + tap) * c.cin + k] : 0.f;
+                                    dst[(((size_t)(tap * kb_per_tap + cc) * 8 + kc) * UM + row) * 8 + e] = __float2bfloat16(v);
+                                }
+                packed_[t][i] = p;
+            }
+        }
+        if (!attr_set_) {
+            MZB_CUDA(cudaFuncSetAttribute(umma_conv3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
+            attr_set_ = true;
+        }
+        return MZB_OK;
+    }
+
+    int fast_conv(const direct::ConvCall<bf16>& call, cudaStream_t s) override {
+        const direct::ConvDev& c = *call.conv;
+        const Packed& p = packed_[c.tower][c.index];
+        if (!p.ok) return 0;
+        const float* base = blob_.as<float>();
+        UmmaArgs a;
+        a.in = call.in; a.in_slot = call.in_slot; a.in_stride = call.in_stride;
+        a.out = call.out; a.out_slot = call.out_slot; a.out_stride = call.out_stride;
+        a.res = call.res; a.res_slot = call.res_slot; a.res_stride = call.res_stride;
+        a.wpack = reinterpret_cast<const bf16*>(reinterpret_cast<const uint8_t*>(blob_.p) + fp32_bytes_ + p.off);
+        a.bias = base + c.bias_off;
+        a.act_table = c.has_table ? base + c.table_off : nullptr;
+        a.action = call.action;
+        a.B = call.B; a.C = c.cin; a.cout = c.cout; a.relu = c.relu;
+        a.g = p.g;
+        const int tiles = (call.B + p.g.G - 1) / p.g.G;
+        umma_conv3_kernel<<<tiles, UMMA_THREADS, umma_smem_bytes(c.cin, p.g), s>>>(a);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("umma_conv3_kernel launch failed: %s", cudaGetErrorString(e)); return MZB_ERR_CUDA; }
+        return 1;
+    }
+
+    std::vector<Packed> packed_[3];
+    bool attr_set_ = false;
+};
+
+}  // namespace
+
+NetBackend* make_bf16_backend() { return new Bf16Backend(); }
+
+}  // namespace mzb

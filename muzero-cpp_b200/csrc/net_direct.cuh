@@ -274,6 +274,7 @@ public:
         renc_ = plan.reward_enc;
         // backend-specific extra weights (e.g. bf16 tensor-core packing) are appended to the same blob so that one
         // broadcast moves everything
+        while (blob.size() % 32) blob.push_back(0.f);   // extras start 128-byte aligned (bulk copies need 16)
         std::vector<uint8_t> extra;
         int rc = pack_extra(plan, &extra);
         if (rc) return rc;

@@ -127,3 +127,33 @@ def test_custom_action_planes():
     np.testing.assert_allclose(g.reward, o["reward"], atol=FP32_ATOL)
     np.testing.assert_allclose(g.encoded_state, o["hidden"], atol=FP32_ATOL)
     eng.close()
+
+
+# ---------------------------------------------------------------- bf16 tcgen05 mode
+@pytest.mark.parametrize("game,B", [("c4d", 13), ("c4r", 9), ("ttt", 37)])
+def test_bf16_matches_oracle_random_weights(game, B):
+    """north star: bf16 mode within 2e-2 relative of the libtorch fp32 model on the same random-init weights"""
+    ncfg = V.preset(game)
+    W = H.random_weights(ncfg, seed=7)
+    net = V.VPRNetOracle(ncfg, W)
+    eng = _engine(game, 64, 1)
+    eng.load_weights(W)
+    rng = np.random.default_rng(1)
+    obs = rng.random((B, ncfg.in_channels * ncfg.obs_shape[1] * ncfg.obs_shape[2]), dtype=np.float32)
+    a1 = rng.integers(0, ncfg.num_actions, B).astype(np.int32)
+    a2 = rng.integers(0, ncfg.num_actions, B).astype(np.int32)
+    _run_chain(eng, net, obs, a1, a2, 1, game + " bf16")
+    eng.close()
+
+
+def test_bf16_odd_shapes_use_direct_kernels():
+    """channel counts the tensor path cannot take (16) still run in bf16 storage on the direct kernels"""
+    ncfg = V.preset("tiny")
+    W = H.random_weights(ncfg, seed=3)
+    net = V.VPRNetOracle(ncfg, W)
+    eng = _engine("tiny", 8, 1)
+    eng.load_weights(W)
+    rng = np.random.default_rng(2)
+    obs = rng.random((6, ncfg.in_channels * 12), dtype=np.float32)
+    _run_chain(eng, net, obs, np.arange(6, dtype=np.int32) % 5, np.arange(6, dtype=np.int32)[::-1] % 5, 1, "tiny bf16")
+    eng.close()

@@ -16,6 +16,8 @@
 // Roles: warp 0 streams weights, warp 1 allocates TMEM and issues the MMAs (one thread), warps 2-5 run the epilogue.
 #include <cuda_bf16.h>
 
+#include <cstdlib>
+
 #include "net_direct.cuh"
 #include "umma.cuh"
 
@@ -46,11 +48,12 @@ struct UmmaArgs {
     const int* action;
     int B, C, cout, relu;
     UmmaGeom g;
+    long long* dbg;             // optional per-CTA phase clocks {start, tile staged, accumulator ready, done}
 };
 
 __host__ __device__ inline size_t umma_x_bytes(int C, int R) { return (((size_t)(C / 8) * R * 16) + 127) / 128 * 128; }
 inline size_t umma_smem_bytes(int C, const UmmaGeom& g) {
-    return umma_x_bytes(C, g.R) + (size_t)NSTAGE * STAGE_BYTES + 128 /*barriers + tmem ptr*/ + (size_t)g.N * 4 + 128;
+    return umma_x_bytes(C, g.R) + (size_t)NSTAGE * STAGE_BYTES + 128 /*barriers + tmem ptr*/ + (size_t)(256 /*colinfo*/ + 256 /*pixinfo*/ + 4 * 64 /*per-game offsets*/) * 4 + 128;
 }
 
 __global__ void __launch_bounds__(UMMA_THREADS, 2) umma_conv3_kernel(UmmaArgs a) {
@@ -66,8 +69,15 @@ __global__ void __launch_bounds__(UMMA_THREADS, 2) umma_conv3_kernel(UmmaArgs a)
     uint64_t* empty = full + NSTAGE;
     uint64_t* accum = empty + NSTAGE;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(accum + 1);
-    int* colinfo = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(full) + 128);
+    int* colinfo = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(full) + 128);   // [256] padded column -> (game << 16 | pixel) or -1
+    int* pixinfo = colinfo + 256;                                                    // [256] real pixel (compact) -> same code
+    int* g_in = pixinfo + 256;      // [64] per-game pool slot / buffer index of the input
+    int* g_res = g_in + 64;         // residual
+    int* g_out = g_res + 64;        // output
+    int* g_act = g_out + 64;        // action
     const int game0 = blockIdx.x * g.G;
+    const int HW = g.H * g.W;
+    if (a.dbg && tid == 0) a.dbg[blockIdx.x * 8 + 0] = clock64();
     const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(a.wpack);
 
     if (tid == 0) {
@@ -82,29 +92,38 @@ __global__ void __launch_bounds__(UMMA_THREADS, 2) umma_conv3_kernel(UmmaArgs a)
     }
     if (warp == 1) tmem_alloc(tmem_ptr, TMEM_COLS);
 
-    // column -> (game, pixel) map of the padded layout; -1 = padding row / absent game
-    for (int q = tid; q < g.N; q += UMMA_THREADS) {
+    // per-game indirections and the column -> (game, pixel) map: loaded once, so the staging and store loops below
+    // carry no dependent global loads and no divisions
+    if (tid < g.G) {
+        const int game = game0 + tid;
+        const bool on = game < a.B;
+        g_in[tid] = on ? (a.in_slot ? a.in_slot[game] : game) : 0;
+        g_res[tid] = on ? (a.res_slot ? a.res_slot[game] : game) : 0;
+        g_out[tid] = on ? (a.out_slot ? a.out_slot[game] : game) : 0;
+        g_act[tid] = (on && a.action) ? a.action[game] : 0;
+    }
+    for (int q = tid; q < 256; q += UMMA_THREADS) {
         int info = -1;
         const int gi = q / g.P, rem = q - gi * g.P;
         const int yy = rem / (g.W + 1), xx = rem - yy * (g.W + 1);
-        if (gi < g.G && yy >= 1 && xx < g.W && game0 + gi < a.B) info = (gi << 16) | ((yy - 1) * g.W + xx);
+        if (q < g.N && gi < g.G && yy >= 1 && xx < g.W && game0 + gi < a.B) info = (gi << 16) | ((yy - 1) * g.W + xx);
         colinfo[q] = info;
+        const int pg = q / HW;
+        pixinfo[q] = (pg < g.G && game0 + pg < a.B) ? ((pg << 16) | (q - pg * HW)) : -1;
     }
-    // resident activation tile: [K chunk][row][8 x bf16], zero padded
-    for (int idx = tid; idx < KC * g.R; idx += UMMA_THREADS) {
-        const int kc = idx % KC, r = idx / KC;
-        const int q = r - g.HALO;
-        uint8_t* dst = X + ((size_t)kc * g.R + r) * 16;
-        const bf16* src = nullptr;
-        if (q >= 0 && q < g.G * g.P) {
-            const int gi = q / g.P, rem = q - gi * g.P;
-            const int yy = rem / (g.W + 1), xx = rem - yy * (g.W + 1);
-            const int game = game0 + gi;
-            if (yy >= 1 && xx < g.W && game < a.B)
-                src = a.in + (long)(a.in_slot ? a.in_slot[game] : game) * a.in_stride + ((long)((yy - 1) * g.W + xx) * a.C + kc * 8);
+    __syncthreads();
+    // resident activation tile: [K chunk][row][8 x bf16], zero padded.  thread <-> fixed K chunk, rows stride by 192/KC
+    {
+        const int kc = tid % KC, r0 = tid / KC, rstep = UMMA_THREADS / KC;
+        for (int r = r0; r < g.R; r += rstep) {
+            const int q = r - g.HALO;
+            uint8_t* dst = X + ((size_t)kc * g.R + r) * 16;
+            const int info = (q >= 0 && q < 256) ? colinfo[q] : -1;
+            if (info >= 0)
+                cp_async16(dst, a.in + (long)g_in[info >> 16] * a.in_stride + ((long)(info & 0xffff) * a.C + kc * 8));
+            else
+                *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
         }
-        if (src) cp_async16(dst, src);
-        else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
     }
     cp_async_wait_all();
     fence_proxy_async_smem();
@@ -112,6 +131,7 @@ __global__ void __launch_bounds__(UMMA_THREADS, 2) umma_conv3_kernel(UmmaArgs a)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_ptr;
+    if (a.dbg && tid == 0) a.dbg[blockIdx.x * 8 + 1] = clock64();
 
     if (warp == 0) {
         if (lane == 0) {   // ===== weight producer: remaining K blocks =====
@@ -144,16 +164,20 @@ __global__ void __launch_bounds__(UMMA_THREADS, 2) umma_conv3_kernel(UmmaArgs a)
                 mma_commit(&empty[s]);   // frees the weight stage once these MMAs have read it
             }
             mma_commit(accum);
+            if (a.dbg) a.dbg[blockIdx.x * 8 + 6] = clock64();
         }
     } else {
-        // ===== epilogue: TMEM -> registers -> global (bf16, real pixels only) =====
+        // ===== epilogue, phase 1: TMEM -> registers -> fp32 staging tile in shared memory =====
+        // All MMAs have completed when `accum` fires, so the activation tile and the weight ring are dead: their
+        // space becomes S[real pixel][cout] (fp32), written conflict-free (lane <-> consecutive cout).
         mbar_wait(accum, 0);
         tc_fence_after();
+        if (a.dbg && tid == 64) a.dbg[blockIdx.x * 8 + 2] = clock64();
         const int lane_base = 32 * (warp & 3);     // a warp may only touch its own TMEM lane quarter
         const int co = lane_base + lane;
         const bool co_ok = co < a.cout;
         const float bias = co_ok ? a.bias[co] : 0.f;
-        const int HW = g.H * g.W;
+        float* S = reinterpret_cast<float*>(smem);
         for (int c0 = 0; c0 < g.N; c0 += 16) {
             uint32_t v[16];
             tmem_ld16(tmem + ((uint32_t)lane_base << 16) + (uint32_t)c0, v);
@@ -161,19 +185,65 @@ __global__ void __launch_bounds__(UMMA_THREADS, 2) umma_conv3_kernel(UmmaArgs a)
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
                 const int info = colinfo[c0 + j];
-                if (info < 0 || !co_ok) continue;
-                const int game = game0 + (info >> 16), pix = info & 0xffff;
-                float x = __uint_as_float(v[j]) + bias;
-                if (a.act_table) x += a.act_table[((long)a.action[game] * HW + pix) * a.cout + co];
-                if (a.res) x += __bfloat162float(a.res[(long)(a.res_slot ? a.res_slot[game] : game) * a.res_stride + (long)pix * a.cout + co]);
-                if (a.relu) x = fmaxf(x, 0.f);
-                a.out[(long)(a.out_slot ? a.out_slot[game] : game) * a.out_stride + (long)pix * a.cout + co] = __float2bfloat16(x);
+                if (info >= 0 && co_ok) S[((info >> 16) * HW + (info & 0xffff)) * a.cout + co] = __uint_as_float(v[j]) + bias;
             }
         }
+        if (a.dbg && tid == 64) a.dbg[blockIdx.x * 8 + 4] = clock64();
     }
     tc_fence_before();
     __syncthreads();
+    if (a.dbg && tid == 0) a.dbg[blockIdx.x * 8 + 5] = clock64();
     if (warp == 1) tmem_dealloc(tmem, TMEM_COLS);
+    // ===== epilogue, phase 2 (all warps): coalesced 16-byte residual loads / bf16 stores, 8 independent items in flight =====
+    {
+        const float* S = reinterpret_cast<const float*>(smem);
+        const int CH = a.cout >> 3;                       // 16-byte chunks per pixel; 192 % CH == 0 for cout in {64, 128}
+        const int ch = tid % CH, p0 = tid / CH, pstep = UMMA_THREADS / CH;
+        const int npix = g.G * HW;
+        const bf16* __restrict__ res = a.res;
+        bf16* __restrict__ out = a.out;
+        const float* __restrict__ table = a.act_table;
+        constexpr int U = 8;
+        for (int pb = p0; pb < npix; pb += pstep * U) {
+            uint4 rv[U]; float4 t0[U], t1[U]; int info[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int pixc = pb + u * pstep;
+                info[u] = pixc < npix ? pixinfo[pixc] : -1;
+                rv[u] = make_uint4(0u, 0u, 0u, 0u);
+                t0[u] = make_float4(0.f, 0.f, 0.f, 0.f); t1[u] = t0[u];
+                if (info[u] >= 0) {
+                    const int gi = info[u] >> 16, pix = info[u] & 0xffff;
+                    if (res) rv[u] = *reinterpret_cast<const uint4*>(res + (long)g_res[gi] * a.res_stride + (long)pix * a.cout + ch * 8);
+                    if (table) {
+                        const float* tp = table + ((long)g_act[gi] * HW + pix) * a.cout + ch * 8;
+                        t0[u] = *reinterpret_cast<const float4*>(tp);
+                        t1[u] = *reinterpret_cast<const float4*>(tp + 4);
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (info[u] < 0) continue;
+                const int pixc = pb + u * pstep;
+                const int gi = info[u] >> 16, pix = info[u] & 0xffff;
+                const float4 s0 = *reinterpret_cast<const float4*>(S + pixc * a.cout + ch * 8);
+                const float4 s1 = *reinterpret_cast<const float4*>(S + pixc * a.cout + ch * 8 + 4);
+                float x[8] = {s0.x + t0[u].x, s0.y + t0[u].y, s0.z + t0[u].z, s0.w + t0[u].w,
+                              s1.x + t1[u].x, s1.y + t1[u].y, s1.z + t1[u].z, s1.w + t1[u].w};
+                const bf16* r8 = reinterpret_cast<const bf16*>(&rv[u]);
+                uint4 ov;
+                bf16* o8 = reinterpret_cast<bf16*>(&ov);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    float v = x[e] + __bfloat162float(r8[e]);
+                    o8[e] = __float2bfloat16(a.relu ? fmaxf(v, 0.f) : v);
+                }
+                *reinterpret_cast<uint4*>(out + (long)g_out[gi] * a.out_stride + (long)pix * a.cout + ch * 8) = ov;
+            }
+        }
+    }
+    if (a.dbg && tid == 0) a.dbg[blockIdx.x * 8 + 3] = clock64();
 }
 
 }  // namespace
@@ -203,8 +273,10 @@ protected:
 
     bool eligible(const Conv3Host& c, UmmaGeom* g) const {
         if (c.stride != 1 || c.cin % KB != 0 || c.cout > UM || c.cout % 8 != 0) return false;
+        if (UMMA_THREADS % (c.cin / 8) != 0 || UMMA_THREADS % (c.cout / 8) != 0) return false;
         if (c.in_h != c.out_h || c.in_w != c.out_w) return false;
-        return make_geom(c.in_h, c.in_w, c.cin, g);
+        if (!make_geom(c.in_h, c.in_w, c.cin, g)) return false;
+        return (size_t)g->G * c.in_h * c.in_w * c.cout * 4 <= umma_x_bytes(c.cin, g->R) + (size_t)NSTAGE * STAGE_BYTES;
     }
 
     // bf16 weight images: per 64-wide K block a ready-made smem tile [8 K-chunks][128 cout rows][8 elems]
@@ -259,13 +331,35 @@ protected:
         a.B = call.B; a.C = c.cin; a.cout = c.cout; a.relu = c.relu;
         a.g = p.g;
         const int tiles = (call.B + p.g.G - 1) / p.g.G;
+        static const bool debug = getenv("MZB_UMMA_DEBUG") != nullptr;
+        a.dbg = nullptr;
+        if (debug) {
+            if (dbg_.bytes < (size_t)tiles * 8 * sizeof(long long)) MZB_CUDA(dbg_.alloc((size_t)tiles * 8 * sizeof(long long)));
+            a.dbg = dbg_.as<long long>();
+        }
         umma_conv3_kernel<<<tiles, UMMA_THREADS, umma_smem_bytes(c.cin, p.g), s>>>(a);
+        if (debug) {
+            MZB_CUDA(cudaStreamSynchronize(s));
+            std::vector<long long> h((size_t)tiles * 8);
+            MZB_CUDA(cudaMemcpy(h.data(), dbg_.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+            double st = 0, issue = 0, mma = 0, p1 = 0, sync = 0, p2 = 0;
+            long long t0 = h[0], t1 = h[3];
+            for (int i = 0; i < tiles; ++i) {
+                const long long* d = &h[(size_t)i * 8];
+                st += d[1] - d[0]; issue += d[6] - d[1]; mma += d[2] - d[1]; p1 += d[4] - d[2]; sync += d[5] - d[4]; p2 += d[3] - d[5];
+                if (d[0] < t0) t0 = d[0];
+                if (d[3] > t1) t1 = d[3];
+            }
+            fprintf(stderr, "[umma] tower %d conv %d tiles %d N %d (cycles/CTA avg): stage %.0f | mma issue %.0f, accum ready %.0f | tmem->smem %.0f | barrier %.0f | store %.0f | kernel span %lld\n",
+                    c.tower, c.index, tiles, p.g.N, st / tiles, issue / tiles, mma / tiles, p1 / tiles, sync / tiles, p2 / tiles, t1 - t0);
+        }
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("umma_conv3_kernel launch failed: %s", cudaGetErrorString(e)); return MZB_ERR_CUDA; }
         return 1;
     }
 
     std::vector<Packed> packed_[3];
+    DevBuf dbg_;
     bool attr_set_ = false;
 };
 

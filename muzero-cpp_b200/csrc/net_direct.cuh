@@ -264,9 +264,10 @@ public:
                 hoff_[h].W[l] = blob.size(); blob.insert(blob.end(), hh[h]->W[l].begin(), hh[h]->W[l].end());
                 hoff_[h].b[l] = blob.size(); blob.insert(blob.end(), hh[h]->b[l].begin(), hh[h]->b[l].end());
             }
-            int mw = 0;
-            for (size_t i = 0; i < hh[h]->sizes.size(); ++i) mw = hh[h]->sizes[i] > mw ? hh[h]->sizes[i] : mw;
-            head_maxw_[h] = mw;
+            int mw2 = 1;
+            for (size_t i = 1; i < hh[h]->sizes.size(); ++i) mw2 = hh[h]->sizes[i] > mw2 ? hh[h]->sizes[i] : mw2;
+            head_maxw_[h] = hh[h]->sizes[0];
+            head_maxw2_[h] = mw2;
         }
         heads_[0].out_kind = 1; heads_[1].out_kind = 0; heads_[2].out_kind = 1;
         heads_[0].step = (float)plan.reward_enc.step; heads_[0].min_value = (float)plan.reward_enc.min_value; heads_[0].contractive = plan.reward_enc.contractive;
@@ -383,7 +384,7 @@ protected:
     virtual int fast_conv(const ConvCall<T>&, cudaStream_t) { return 0; }
 
     static int conv_smem(int stride) { int PW = TILE * stride + 2; return (CK * PW * PW + 9 * CK * TC) * (int)sizeof(float); }
-    int head_smem(int h) const { return (heads_[h].hw * heads_[h].C + 2 * head_maxw_[h]) * (int)sizeof(float); }
+    int head_smem(int h) const { return (int)head_smem_bytes(heads_[h], head_maxw_[h], head_maxw2_[h]); }
 
     int launch_conv(const ConvDev& c, int B, const T* in, const int* in_slot, long in_stride, T* out,
                     const T* res, const int* res_slot, long res_stride, const int* action, cudaStream_t s) {
@@ -468,7 +469,7 @@ protected:
     }
 
     int run_head(int h, const T* x, const int* slots, long stride, int B, double* out, int out_stride, cudaStream_t s) {
-        head_kernel<T><<<B, 128, head_smem(h), s>>>(x, slots, stride, heads_[h], out, out_stride, head_maxw_[h]);
+        head_kernel<T><<<(B + HEAD_GS - 1) / HEAD_GS, HEAD_THREADS, head_smem(h), s>>>(x, slots, stride, B, heads_[h], out, out_stride, head_maxw_[h], head_maxw2_[h]);
         ++launches_;
         MZB_CUDA(cudaGetLastError());
         return MZB_OK;
@@ -491,7 +492,7 @@ protected:
     int max_act_[3] = {0, 0, 0};
     HeadDev heads_[3];
     HeadOff hoff_[3];
-    int head_maxw_[3] = {0, 0, 0};
+    int head_maxw_[3] = {0, 0, 0}, head_maxw2_[3] = {0, 0, 0};
     EncoderConsts renc_;
     DevBuf blob_, pool_, bufA_, bufB_, bufC_;
     size_t fp32_bytes_ = 0;

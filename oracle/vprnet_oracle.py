@@ -170,6 +170,7 @@ class VPRNetOracle:
                            F.conv2d(obs, W[head + ".representation_resnet_head_conv.weight"], None, 1, 1)))
         for i in range(c.rep_blocks):
             x = _resblock(W, "representation_network.representation_layers.%d" % i, i, x)
+        self._raw = x
         return normalize_hidden_state(x) if c.normalize else x
 
     def dynamics(self, h, act):  # models.cpp:105-117,231-240
@@ -182,6 +183,7 @@ class VPRNetOracle:
         r = F.conv2d(x, W["dynamics_network.dynamics_reward_conv.weight"], W["dynamics_network.dynamics_reward_conv.bias"])
         r = r.reshape(r.shape[0], -1)
         r = _mlp(W, "dynamics_network.dynamics_reward_mlp.dynamics_reward_mlp", len(c.reward_layers) + 1, r)
+        self._raw = x
         return (normalize_hidden_state(x) if c.normalize else x), r
 
     def prediction(self, x):  # models.cpp:153-166
@@ -200,7 +202,8 @@ class VPRNetOracle:
         policy = torch.softmax(policy_logits, -1).to(torch.float64)
         return dict(value=value.numpy(), reward=reward.numpy(), policy=policy.numpy(),
                     hidden=hidden.reshape(hidden.shape[0], -1).numpy(), value_logits=value_logits.numpy(),
-                    reward_logits=reward_logits.numpy(), policy_logits=policy_logits.numpy())
+                    reward_logits=reward_logits.numpy(), policy_logits=policy_logits.numpy(),
+                    hidden_raw=self._raw.reshape(hidden.shape[0], -1).numpy())
 
     @torch.no_grad()
     def initial_inference(self, obs_flat):  # vprnet.cpp:77-129, models.cpp:248-258

@@ -16,9 +16,14 @@
 // Roles: warp 0 streams weights, warp 1 allocates TMEM and issues the MMAs (one thread), warps 2-5 run the epilogue.
 #include <cuda_bf16.h>
 
+#include <algorithm>
 #include <cstdlib>
+#include <memory>
+
+#include <map>
 
 #include "net_direct.cuh"
+#include "tower_fused.cuh"
 #include "umma.cuh"
 
 namespace mzb {
@@ -312,8 +317,365 @@ protected:
             MZB_CUDA(cudaFuncSetAttribute(umma_conv3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
             attr_set_ = true;
         }
+        return pack_fused(plan, extra);
+    }
+
+    // ------------------------------------------------------------------ whole-chain fusion (tower_fused.cuh)
+    struct FusedChain {
+        bool ok = false;
+        fused::FusedArgs args;     // template: per-call pointers are filled in at launch
+        int gmax = 0;
+        size_t smem = 0;
+    };
+    struct TileTab { DevBuf first, count; int n_tiles = 0; };
+
+    static bool tower_fusable(const Tower& tw, bool leading_conv, int C, int H, int W) {
+        size_t i = 0;
+        if (leading_conv) {
+            if (tw.steps.empty() || tw.steps[0].kind != TowerStep::CONV) return false;
+            i = 1;
+        }
+        for (; i < tw.steps.size(); ++i) if (tw.steps[i].kind != TowerStep::BLOCK) return false;
+        for (size_t k = 0; k < tw.convs.size(); ++k) {
+            const Conv3Host& c = tw.convs[k];
+            if (c.stride != 1 || c.cin != C || c.cout != C || c.in_h != H || c.in_w != W || c.out_h != H || c.out_w != W) return false;
+        }
+        return true;
+    }
+
+    // 1x1 head convolutions as single-tap weight stages: [C/64][8 K chunks][128 rows][8], rows = stacked head channels
+    size_t pack_conv1(const HeadHost* const* hh, int nh, int C, std::vector<uint8_t>* extra, size_t* bias_rel) {
+        while (extra->size() % 128) extra->push_back(0);
+        const size_t off = extra->size();
+        const int kbs = C / KB;
+        extra->resize(off + (size_t)kbs * STAGE_BYTES, 0);
+        bf16* dst = reinterpret_cast<bf16*>(extra->data() + off);
+        std::vector<float> bias(128, 0.f);
+        int row0 = 0;
+        for (int h = 0; h < nh; ++h) {
+            for (int r = 0; r < hh[h]->red; ++r) {
+                bias[row0 + r] = hh[h]->b1[r];
+                for (int k = 0; k < C; ++k) {
+                    const int cc = k / KB, kc = (k % KB) / 8, e = k % 8;
+                    dst[(((size_t)cc * 8 + kc) * UM + row0 + r) * 8 + e] = __float2bfloat16(hh[h]->w1[(size_t)r * C + k]);
+                }
+            }
+            row0 += hh[h]->red;
+        }
+        // (resize may have moved the buffer: dst is not used past this point)
+        *bias_rel = extra->size();
+        const uint8_t* bp = reinterpret_cast<const uint8_t*>(bias.data());
+        extra->insert(extra->end(), bp, bp + 128 * sizeof(float));
+        return off;
+    }
+
+    int pack_fused(const NetPlan& plan, std::vector<uint8_t>* extra) {
+        fused_rec_ = FusedChain(); fused_init_ = FusedChain();
+        fused_final_ = false;
+        tiles_.clear();
+        static const bool disabled = getenv("MZB_NO_FUSED") != nullptr;
+        if (disabled) return MZB_OK;
+        const NetDims& d = plan.dims;
+        const int C = d.C, H = d.h, W = d.w;
+        if (C % KB != 0 || C > UM) return MZB_OK;
+        const int P = ((H + 1) * (W + 1) + 7) / 8 * 8;
+        if (P > 256) return MZB_OK;
+        const HeadHost* hr[1] = {&plan.reward_head};
+        const HeadHost* hpv[2] = {&plan.policy_head, &plan.value_head};
+        if (plan.reward_head.red > UM || plan.policy_head.red + plan.value_head.red > UM) return MZB_OK;
+        for (const HeadHost* h : {&plan.reward_head, &plan.policy_head, &plan.value_head}) {
+            if ((int)h->W.size() > fused::MLP_MAX_LAYERS) return MZB_OK;
+            for (size_t i = 1; i < h->sizes.size(); ++i) if (h->sizes[i] > 256) return MZB_OK;
+        }
+        const bool dyn_ok = tower_fusable(plan.dynamics, true, C, H, W) && packed_[1].size() == plan.dynamics.convs.size();
+        const bool pred_ok = tower_fusable(plan.prediction, false, C, H, W);
+        if (!dyn_ok || !pred_ok) return MZB_OK;
+        for (int t = 1; t < 3; ++t) for (const Packed& p : packed_[t]) if (!p.ok) return MZB_OK;
+        // geometry
+        const int gmax = std::min(256 / P, fused::F_MAX_G);
+        const int nmax = (gmax * P + 15) / 16 * 16;
+        const int halo = W + 2;
+        int R = halo + nmax + halo;
+        if ((R & 1) == 0) ++R;
+        const int x_bytes = (int)((((size_t)(C / 8) * R * 16) + 127) / 128 * 128);
+        const size_t smem = fused::fused_smem_bytes(x_bytes);
+        if (smem > 227 * 1024) return MZB_OK;
+        // extra weights
+        conv1_rel_[0] = pack_conv1(hr, 1, C, extra, &conv1_bias_rel_[0]);
+        conv1_rel_[1] = pack_conv1(hpv, 2, C, extra, &conv1_bias_rel_[1]);
+        const HeadHost* hh[3] = {&plan.reward_head, &plan.policy_head, &plan.value_head};
+        for (int h = 0; h < 3; ++h) {   // first MLP layer transposed [in][out] for coalesced reads
+            while (extra->size() % 16) extra->push_back(0);
+            w0t_rel_[h] = extra->size();
+            const int n0 = hh[h]->sizes[0], n1 = hh[h]->sizes[1];
+            std::vector<float> wt((size_t)n0 * n1);
+            for (int j = 0; j < n1; ++j) for (int i = 0; i < n0; ++i) wt[(size_t)i * n1 + j] = hh[h]->W[0][(size_t)j * n0 + i];
+            const uint8_t* bp = reinterpret_cast<const uint8_t*>(wt.data());
+            extra->insert(extra->end(), bp, bp + wt.size() * sizeof(float));
+        }
+        fused::FusedArgs base;
+        memset(&base, 0, sizeof(base));
+        base.C = C; base.H = H; base.W = W; base.P = P; base.HALO = halo; base.R = R; base.HW = H * W; base.x_bytes = x_bytes;
+        base.normalize = plan.normalize ? 1 : 0;
+        base.red_rows[0] = plan.reward_head.red; base.red_rows[1] = plan.policy_head.red; base.red_rows[2] = plan.value_head.red;
+        fused_rec_.args = base; fused_rec_.gmax = gmax; fused_rec_.smem = smem;
+        fused_rec_.ok = true;    // phases are laid out by finalize_fused() once the blob offsets are known
+        // the representation head conv (index 0) has its own input channel count and stays on the direct kernel
+        fused_init_.args = base; fused_init_.gmax = gmax; fused_init_.smem = smem;
+        fused_init_.ok = rep_init_fusable(plan, C, H, W);
+        MZB_CUDA(cudaFuncSetAttribute(fused::tower_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MZB_CUDA(cudaFuncSetAttribute(fused::mlp_heads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         return MZB_OK;
     }
+
+    bool rep_init_fusable(const NetPlan& plan, int C, int H, int W) const {
+        const Tower& tw = plan.representation;
+        if (tw.steps.empty() || tw.steps[0].kind != TowerStep::CONV || tw.steps[0].conv0 != 0) return false;
+        for (size_t i = 1; i < tw.steps.size(); ++i) if (tw.steps[i].kind != TowerStep::BLOCK) return false;
+        const Conv3Host& c0 = tw.convs[0];
+        if (c0.cout != C || c0.out_h != H || c0.out_w != W) return false;
+        for (size_t k = 1; k < tw.convs.size(); ++k) {
+            const Conv3Host& c = tw.convs[k];
+            if (c.stride != 1 || c.cin != C || c.cout != C || c.in_h != H || c.in_w != W) return false;
+            if (!packed_[0][k].ok) return false;
+        }
+        return true;
+    }
+
+    void add_conv_phase(fused::FusedArgs* fa, int tower, int index, int flags) {
+        const direct::ConvDev& c = convs_[tower][index];
+        fused::Phase& ph = fa->ph[fa->n_phases++];
+        memset(&ph, 0, sizeof(ph));
+        ph.w_off = (uint32_t)(fp32_bytes_ + packed_[tower][index].off);
+        ph.taps = 9; ph.nkb = 9 * (c.cin / KB);
+        ph.bias_off = (int)(c.bias_off * sizeof(float));
+        ph.table_off = c.has_table ? (int)(c.table_off * sizeof(float)) : -1;
+        ph.flags = flags | (c.relu ? fused::PH_RELU : 0) | (c.has_table ? fused::PH_TABLE : 0);
+    }
+    void add_blocks(fused::FusedArgs* fa, int tower, size_t first_step) {
+        for (size_t i = first_step; i < steps_[tower].size(); ++i) {
+            add_conv_phase(fa, tower, steps_[tower][i].conv0, fused::PH_WRITE_X);
+            add_conv_phase(fa, tower, steps_[tower][i].conv1, fused::PH_WRITE_X | fused::PH_ACC_R2 | fused::PH_STASH);
+        }
+    }
+    void add_conv1_phase(fused::FusedArgs* fa, int which, int flags, int C) {
+        fused::Phase& ph = fa->ph[fa->n_phases++];
+        memset(&ph, 0, sizeof(ph));
+        ph.bias_off = -1; ph.table_off = -1;
+        ph.flags = flags;
+        if (which >= 0) {
+            ph.w_off = (uint32_t)(fp32_bytes_ + conv1_rel_[which]);
+            ph.taps = 1; ph.nkb = C / KB;
+            ph.bias_off = (int)(fp32_bytes_ + conv1_bias_rel_[which]);
+            ph.flags |= fused::PH_RED;
+            if (which == 0) { ph.red_head0 = 0; ph.red_n0 = fa->red_rows[0]; ph.red_head1 = 0; ph.red_n1 = 0; }
+            else { ph.red_head0 = 1; ph.red_n0 = fa->red_rows[1]; ph.red_head1 = 2; ph.red_n1 = fa->red_rows[2]; }
+        }
+    }
+
+    int finalize_fused() {
+        if (fused_final_) return MZB_OK;
+        fused_final_ = true;
+        if (!fused_rec_.ok) return MZB_OK;
+        const int C = plan_dims_.C, hw = plan_dims_.hw();
+        int dev = 0;
+        MZB_CUDA(cudaGetDevice(&dev));
+        MZB_CUDA(cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, dev));
+        size_t phases_rec = 1 + 2 * (steps_[1].size() - 1) + 1 + 2 * steps_[2].size() + 1;
+        if (phases_rec > (size_t)fused::F_MAX_PHASES) { fused_rec_.ok = false; fused_init_.ok = false; return MZB_OK; }
+        {   // recurrent: dynamics head, dynamics blocks, reward conv1x1 + normalise, prediction blocks, policy/value conv1x1
+            fused::FusedArgs* fa = &fused_rec_.args;
+            fa->n_phases = 0; fa->preload = 0;
+            add_conv_phase(fa, 1, steps_[1][0].conv0, fused::PH_WRITE_X | fused::PH_STASH);
+            add_blocks(fa, 1, 1);
+            add_conv1_phase(fa, 0, fused::PH_NORM, C);
+            add_blocks(fa, 2, 0);
+            add_conv1_phase(fa, 1, 0, C);
+        }
+        size_t phases_init = 2 * (steps_[0].size() - 1) + 1 + 2 * steps_[2].size() + 1;
+        if (fused_init_.ok && phases_init > (size_t)fused::F_MAX_PHASES) fused_init_.ok = false;
+        if (fused_init_.ok) {   // initial: (head conv on the direct kernel), representation blocks, normalise, prediction, heads
+            fused::FusedArgs* fa = &fused_init_.args;
+            fa->n_phases = 0; fa->preload = 1;
+            add_blocks(fa, 0, 1);
+            add_conv1_phase(fa, -1, fused::PH_NORM, C);
+            add_blocks(fa, 2, 0);
+            add_conv1_phase(fa, 1, 0, C);
+        }
+        // reduced head inputs and MLP descriptors
+        for (int h = 0; h < 3; ++h) MZB_CUDA(red_[h].alloc((size_t)max_batch_ * heads_[h].red * hw * sizeof(float)));
+        const uint8_t* blob = reinterpret_cast<const uint8_t*>(blob_.p);
+        memset(&mlp_, 0, sizeof(mlp_));
+        for (int h = 0; h < 3; ++h) {
+            fused::MlpHead& m = mlp_.h[h];
+            m.x = red_[h].as<float>();
+            m.w0t = reinterpret_cast<const float*>(blob + fp32_bytes_ + w0t_rel_[h]);
+            m.n_layers = heads_[h].n_layers;
+            for (int l = 0; l <= m.n_layers; ++l) m.sizes[l] = heads_[h].sizes[l];
+            for (int l = 0; l < m.n_layers; ++l) { m.W[l] = heads_[h].W[l]; m.b[l] = heads_[h].b[l]; }
+            m.out_kind = heads_[h].out_kind; m.step = heads_[h].step; m.min_value = heads_[h].min_value; m.contractive = heads_[h].contractive;
+        }
+        int n0max = 0;
+        for (int h = 0; h < 3; ++h) n0max = std::max(n0max, heads_[h].sizes[0]);
+        mlp_mg_ = 16;
+        while (mlp_mg_ > 4 && (size_t)mlp_mg_ * (n0max + 512) * sizeof(float) > 150 * 1024) mlp_mg_ /= 2;
+        if ((size_t)mlp_mg_ * (n0max + 512) * sizeof(float) > 160 * 1024) { fused_rec_.ok = false; fused_init_.ok = false; }
+        return MZB_OK;
+    }
+
+    // balanced tiles: every SM gets ceil-or-floor(B / SMs) games, cut into as few tiles of <= gmax games as possible,
+    // emitted wave by wave (the hardware scheduler hands out CTAs in index order)
+    int tiles_for(int B, int gmax, const TileTab** out) {
+        auto it = tiles_.find(B);
+        if (it == tiles_.end()) {
+            std::vector<int> first, count;
+            const int S = n_sm_ > 0 ? n_sm_ : 148;
+            const int per = (B + S - 1) / S;
+            const int waves = (per + gmax - 1) / gmax;
+            std::vector<int> left(S), next(S);
+            int g = 0;
+            for (int k = 0; k < S; ++k) { left[k] = B / S + (k < B % S ? 1 : 0); next[k] = g; g += left[k]; }
+            for (int w = 0; w < waves; ++w)
+                for (int k = 0; k < S; ++k) {
+                    if (left[k] <= 0) continue;
+                    const int part = std::min(gmax, (left[k] + (waves - w) - 1) / (waves - w));
+                    first.push_back(next[k]); count.push_back(part);
+                    next[k] += part; left[k] -= part;
+                }
+            std::unique_ptr<TileTab> tt(new TileTab());
+            tt->n_tiles = (int)first.size();
+            MZB_CUDA(tt->first.alloc(first.size() * sizeof(int)));
+            MZB_CUDA(tt->count.alloc(count.size() * sizeof(int)));
+            MZB_CUDA(cudaMemcpy(tt->first.p, first.data(), first.size() * sizeof(int), cudaMemcpyHostToDevice));
+            MZB_CUDA(cudaMemcpy(tt->count.p, count.data(), count.size() * sizeof(int), cudaMemcpyHostToDevice));
+            it = tiles_.emplace(B, std::move(tt)).first;
+        }
+        *out = it->second.get();
+        return MZB_OK;
+    }
+
+    int launch_fused(FusedChain& ch, int B, const bf16* in, const int* in_slot, long in_stride, const int* out_slot,
+                     const int* action, cudaStream_t s) {
+        const TileTab* tt = nullptr;
+        int rc = tiles_for(B, ch.gmax, &tt);
+        if (rc) return rc;
+        fused::FusedArgs a = ch.args;
+        a.in = in; a.in_slot = in_slot; a.in_stride = in_stride;
+        a.pool = pool_.as<bf16>(); a.out_slot = out_slot; a.pool_stride = (long)slot_elems_;
+        a.action = action;
+        a.blob = reinterpret_cast<const uint8_t*>(blob_.p);
+        for (int h = 0; h < 3; ++h) a.red[h] = red_[h].as<float>();
+        a.tile_first = tt->first.as<int>(); a.tile_count = tt->count.as<int>();
+        if (!dbg_host_) {
+            MZB_CUDA(cudaHostAlloc((void**)&dbg_host_, 16 * sizeof(int), cudaHostAllocMapped));
+            memset(dbg_host_, 0, 16 * sizeof(int));
+            MZB_CUDA(cudaHostGetDevicePointer((void**)&dbg_dev_, dbg_host_, 0));
+        }
+        a.dbg = dbg_dev_;
+        static const bool timing = getenv("MZB_FUSED_TIMING") != nullptr;
+        a.tim = nullptr;
+        if (timing) {
+            const size_t need = (size_t)tt->n_tiles * fused::F_MAX_PHASES * 4 * sizeof(long long);
+            if (tim_.bytes < need) MZB_CUDA(tim_.alloc(need));
+            MZB_CUDA(cudaMemsetAsync(tim_.p, 0, need, s));
+            a.tim = tim_.as<long long>();
+        }
+        fused::tower_fused_kernel<<<tt->n_tiles, fused::F_THREADS, ch.smem, s>>>(a);
+        MZB_CUDA(cudaGetLastError());
+        if (timing) {
+            MZB_CUDA(cudaStreamSynchronize(s));
+            std::vector<long long> h((size_t)tt->n_tiles * fused::F_MAX_PHASES * 4);
+            MZB_CUDA(cudaMemcpy(h.data(), tim_.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+            fprintf(stderr, "[fused] %d tiles, %d phases; per phase avg cycles over tiles: wait(prev epi done -> mma start) | mma issue | mma start -> accum full | epilogue\n", tt->n_tiles, a.n_phases);
+            for (int p = 0; p < a.n_phases; ++p) {
+                double issue = 0, full = 0, epi = 0, gap = 0;
+                for (int t = 0; t < tt->n_tiles; ++t) {
+                    const long long* d = &h[((size_t)t * fused::F_MAX_PHASES + p) * 4];
+                    issue += d[1] - d[0]; full += d[2] - d[0]; epi += d[3] - d[2];
+                    if (p > 0) gap += d[0] - h[((size_t)t * fused::F_MAX_PHASES + p - 1) * 4 + 3];
+                }
+                const int n = tt->n_tiles;
+                fprintf(stderr, "[fused]  phase %2d nkb %3d flags %3d: gap %7.0f | issue %7.0f | full %7.0f | epi %7.0f\n", p, a.ph[p].nkb, a.ph[p].flags, gap / n, issue / n, full / n, epi / n);
+            }
+            const long long* d0 = &h[0];
+            fprintf(stderr, "[fused]  tile 0 span %lld cycles\n", h[((size_t)(a.n_phases - 1)) * 4 + 3] - d0[0]);
+        }
+        static const bool sync_debug = getenv("MZB_FUSED_SYNC") != nullptr;
+        if (sync_debug) {
+            cudaError_t e = cudaStreamSynchronize(s);
+            if (e != cudaSuccess) {
+                set_error("tower_fused_kernel failed: %s; barrier diagnostics {code %d (1 empty, 2 act_ready, 3 full, 4 accum_full), block %d, parity %d, aux %d}",
+                          cudaGetErrorString(e), dbg_host_[0], dbg_host_[1], dbg_host_[2], dbg_host_[3]);
+                return MZB_ERR_CUDA;
+            }
+        }
+        return MZB_OK;
+    }
+    int launch_mlp(int B, int first_head, const NetOutputs& out, cudaStream_t s) {
+        fused::MlpArgs m;
+        memset(&m, 0, sizeof(m));
+        double* outs[3] = {out.reward, out.policy, out.value};
+        const int strides[3] = {1, plan_dims_.A, 1};
+        int n = 0, n0max = 0;
+        for (int h = first_head; h < 3; ++h) {
+            m.h[n] = mlp_.h[h]; m.h[n].out = outs[h]; m.h[n].out_stride = strides[h];
+            n0max = std::max(n0max, m.h[n].sizes[0]);
+            ++n;
+        }
+        m.n_heads = n; m.B = B; m.mg = mlp_mg_;
+        const size_t smem = (size_t)mlp_mg_ * (n0max + 512) * sizeof(float);
+        dim3 grid((B + mlp_mg_ - 1) / mlp_mg_, n);
+        fused::mlp_heads_kernel<<<grid, fused::MLP_THREADS, smem, s>>>(m);
+        MZB_CUDA(cudaGetLastError());
+        return MZB_OK;
+    }
+
+public:
+    int recurrent(int B, const int* d_in_slot, const int* d_action, const int* d_out_slot, const NetOutputs& out, cudaStream_t s) override {
+        MZB_REQUIRE(uploaded_, "weights not loaded (mzb_load_weights)");
+        int rc = finalize_fused();
+        if (rc) return rc;
+        if (!fused_rec_.ok) return direct::DirectBackend<bf16>::recurrent(B, d_in_slot, d_action, d_out_slot, out, s);
+        MZB_REQUIRE(B <= max_batch_, "batch %d above engine capacity %d", B, max_batch_);
+        rc = launch_fused(fused_rec_, B, pool_.as<bf16>(), d_in_slot, (long)slot_elems_, d_out_slot, d_action, s);
+        if (rc) return rc;
+        rc = launch_mlp(B, 0, out, s);
+        if (rc) return rc;
+        launches_recurrent_ = 2;
+        return MZB_OK;
+    }
+    int initial(const float* d_obs, int B, const int* d_out_slot, const NetOutputs& out, cudaStream_t s) override {
+        MZB_REQUIRE(uploaded_, "weights not loaded (mzb_load_weights)");
+        int rc = finalize_fused();
+        if (rc) return rc;
+        if (!fused_init_.ok) return direct::DirectBackend<bf16>::initial(d_obs, B, d_out_slot, out, s);
+        MZB_REQUIRE(B <= max_batch_, "batch %d above engine capacity %d", B, max_batch_);
+        const NetDims& d = plan_dims_;
+        long total = (long)B * d.initial_flat();
+        direct::nchw_to_nhwc_kernel<bf16><<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_obs, bufA_.as<bf16>(), nullptr, (long)d.initial_flat(), B, d.cin, d.in_h * d.in_w);
+        launches_ = 1;
+        rc = launch_conv(convs_[0][0], B, bufA_.as<bf16>(), nullptr, (long)d.initial_flat(), bufB_.as<bf16>(), nullptr, nullptr, 0, nullptr, s);
+        if (rc) return rc;
+        rc = launch_fused(fused_init_, B, bufB_.as<bf16>(), nullptr, (long)slot_elems_, d_out_slot, nullptr, s);
+        if (rc) return rc;
+        rc = launch_mlp(B, 1, out, s);
+        if (rc) return rc;
+        initial_reward_kernel<<<(B + 127) / 128, 128, 0, s>>>(out.reward, B, renc_.support, (float)renc_.step, (float)renc_.min_value, renc_.contractive);
+        MZB_CUDA(cudaGetLastError());
+        launches_initial_ = launches_ + 3;
+        return MZB_OK;
+    }
+
+protected:
+    FusedChain fused_rec_, fused_init_;
+    bool fused_final_ = false;
+    size_t conv1_rel_[2] = {0, 0}, conv1_bias_rel_[2] = {0, 0}, w0t_rel_[3] = {0, 0, 0};
+    DevBuf red_[3];
+    fused::MlpArgs mlp_;
+    int mlp_mg_ = 16, n_sm_ = 0;
+    int* dbg_host_ = nullptr; int* dbg_dev_ = nullptr;
+    DevBuf tim_;
+    std::map<int, std::unique_ptr<TileTab>> tiles_;
 
     int fast_conv(const direct::ConvCall<bf16>& call, cudaStream_t s) override {
         const direct::ConvDev& c = *call.conv;

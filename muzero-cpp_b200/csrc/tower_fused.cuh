@@ -1,0 +1,440 @@
+// tower_fused.cuh — the whole residual tower chain of one inference call as ONE tcgen05 kernel.
+//
+// Replaces, in MZB_BF16 mode, the per-layer launches of MuzeroNetworkImpl::recurrent_inference / initial_inference
+// (models.cpp:222-265): DynamicsNetwork head + blocks (models.cpp:105-117), reward conv1x1, normalize_hidden_state
+// (models.cpp:16-26), PredictionNetwork blocks + policy/value conv1x1 (models.cpp:153-166); ResidualBlock =
+// relu(bn2(conv2(relu(bn1(conv1 x)))) + x) (model_layers.cpp:70-88), eval-mode BN folded on the host.
+//
+// One CTA owns a tile of G whole games for the entire chain; nothing but the parent hidden state (in) and the child
+// hidden state + the reduced head inputs (out) touches HBM:
+//   * shared memory holds ONE activation buffer X, bf16, zero-padded pixel rows (every game = P rows: a zero row of
+//     W+1 pixels, then H rows of W pixels + 1 zero pixel, padded to a multiple of 8) in K-major no-swizzle core-matrix
+//     order [K chunk of 8 channels][row][16 B].  A 3x3 tap is a constant row shift, so the nine taps are nine
+//     descriptors over the same resident tile (no im2col, no re-read).  Layer outputs overwrite X in place.
+//   * tensor memory holds two fp32 accumulator regions of N <= 256 columns (column = padded pixel row, lane = output
+//     channel): R1 for convolutions that start from zero, R2 for the second convolution of a residual block, which
+//     accumulates ON TOP OF the block input kept there in fp32 — the skip connection never leaves TMEM and is never
+//     rounded to bf16.
+//   * BN-folded bf16 weights stream from L2 through a ring of 16 KB stages (64 K x 128 cout images pre-packed on the
+//     host) with 1-D bulk async copies; the producer runs ahead across layer boundaries.
+//   * per phase: [MMA issuer: 9 taps x C/64 stages x 4 tcgen05.mma] -> accumulator-full barrier -> [8 epilogue warps:
+//     tcgen05.ld, + bias (+ per-action table), ReLU, bf16 store into X, fp32 tcgen05.st of the block input into R2]
+//     -> activations-ready barrier -> next phase.  The 1x1 head convolutions are extra single-tap phases whose rows go
+//     to a small fp32 buffer (channel-major flatten, models.cpp:114,161-162); the per-(game, channel) min-max
+//     normalisation is a pure per-thread reduction because a thread owns one channel and its columns are pixels.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "umma.cuh"
+
+namespace mzb {
+namespace fused {
+
+using bf16 = __nv_bfloat16;
+using namespace umma;
+
+constexpr int F_THREADS = 320;        // warp 0: weight producer, warp 1: MMA issuer + TMEM owner, warps 2-9: epilogue
+constexpr int F_EPI_WARPS = 8;
+constexpr int F_NSTAGE = 8;
+constexpr int F_STAGE_BYTES = 64 * 128 * 2;   // 64 K x 128 cout, bf16
+constexpr int F_TMEM_COLS = 512;
+constexpr int F_R2_COL = 256;
+constexpr int F_MAX_PHASES = 40;
+constexpr int F_MAX_G = 16;
+
+enum : int {
+    PH_RELU = 1,      // ReLU in the epilogue
+    PH_ACC_R2 = 2,    // accumulate into R2 on top of the block input stored there (second conv of a residual block)
+    PH_STASH = 4,     // keep the epilogue result in R2 (fp32) as the next block's skip input
+    PH_TABLE = 8,     // add the per-action table (dynamics head: contribution of the action planes)
+    PH_WRITE_X = 16,  // store the epilogue result into X (bf16)
+    PH_RED = 32,      // 1x1 head convolution: rows of R1 -> red[] buffers (no activation)
+    PH_NORM = 64,     // normalize_hidden_state on R2 -> X, node pool slot, R2
+};
+
+struct Phase {
+    uint32_t w_off;        // byte offset of this phase's weight stages in the packed blob
+    int nkb;               // 64-wide K stages (taps * C / 64); 0 = no tensor work
+    int taps;              // 9 (3x3) or 1 (1x1)
+    int bias_off;          // byte offset of the fp32 bias vector, -1 = none
+    int table_off;         // byte offset of the fp32 [A][HW][C] table (PH_TABLE)
+    int flags;
+    int red_head0, red_n0, red_head1, red_n1;   // PH_RED: rows [0,n0) -> red[head0], rows [n0, n0+n1) -> red[head1]
+};
+
+struct FusedArgs {
+    const bf16* in; const int* in_slot; long in_stride;       // chain input, NHWC bf16 per game
+    bf16* pool; const int* out_slot; long pool_stride;        // PH_NORM destination (node pool)
+    const int* action;                                        // PH_TABLE
+    const uint8_t* blob;                                      // weights: fp32 section + packed bf16 stages
+    float* red[3];                                            // [B][red_h * HW] fp32 per head (reward, policy, value)
+    int red_rows[3];
+    const int* tile_first; const int* tile_count;             // tile -> first game, number of games
+    int C, H, W, P, HALO, R, HW, x_bytes;
+    int n_phases, preload, normalize;
+    int* dbg;                                                 // host-mapped diagnostics (barrier time-outs), may be null
+    long long* tim;                                           // optional [tile][phase][4] clocks: mma start, mma issued, accum full, epilogue done
+    Phase ph[F_MAX_PHASES];
+};
+
+inline size_t fused_smem_bytes(int x_bytes) { return (size_t)x_bytes + (size_t)F_NSTAGE * F_STAGE_BYTES + 256 + 1024 + 3 * F_MAX_G * 4 + 128; }
+
+// explicit shared-space accesses (32-bit shared addresses: no generic-pointer conversion per access)
+__device__ __forceinline__ void sts_u16(uint32_t addr, unsigned short v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(v) : "memory"); }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
+    unsigned short v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void lds_v4(uint32_t addr, int* p) {
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(p[0]), "=r"(p[1]), "=r"(p[2]), "=r"(p[3]) : "r"(addr) : "memory");
+}
+
+__global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_constant__ FusedArgs a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int game0 = a.tile_first[blockIdx.x], G = a.tile_count[blockIdx.x];
+    const int P = a.P, R = a.R, HALO = a.HALO, C = a.C, KC = C >> 3, HW = a.HW, W1 = a.W + 1;
+    const int N = (G * P + 15) & ~15;
+    uint8_t* X = smem;
+    uint8_t* stages = X + a.x_bytes;
+    uint64_t* full = reinterpret_cast<uint64_t*>(stages + F_NSTAGE * F_STAGE_BYTES);
+    uint64_t* empty = full + F_NSTAGE;
+    uint64_t* accum_full = empty + F_NSTAGE;
+    uint64_t* act_ready = accum_full + 1;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(act_ready + 1);
+    int* pixtab = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(full) + 256);   // [P] row within a game -> pixel or -1
+    int* g_in = pixtab + 256;
+    int* g_out = g_in + F_MAX_G;
+    int* g_act = g_out + F_MAX_G;
+
+    if (tid == 0) {
+        for (int s = 0; s < F_NSTAGE; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        mbar_init(accum_full, 1);
+        mbar_init(act_ready, F_EPI_WARPS);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr, F_TMEM_COLS);
+    if (tid < G) {
+        const int game = game0 + tid;
+        g_in[tid] = a.in_slot ? a.in_slot[game] : game;
+        g_out[tid] = a.out_slot ? a.out_slot[game] : game;
+        g_act[tid] = a.action ? a.action[game] : 0;
+    }
+    for (int r = tid; r < 256; r += F_THREADS) {
+        const int yy = r / W1, xx = r - yy * W1;
+        pixtab[r] = (r < P && yy >= 1 && yy <= a.H && xx < a.W) ? (yy - 1) * a.W + xx : -1;
+    }
+    __syncthreads();
+    // ---- chain input -> X (zero padded), 16 bytes = 8 channels of one pixel per request ----
+    {
+        const int kc = tid % KC, r0 = tid / KC, rstep = F_THREADS / KC;
+        const int rows = G * P;
+        for (int r = r0; r < R; r += rstep) {
+            uint8_t* dst = X + ((size_t)kc * R + r) * 16;
+            const int q = r - HALO;
+            int pix = -1, gi = 0;
+            if (q >= 0 && q < rows) { gi = q / P; pix = pixtab[q - gi * P]; }
+            if (pix >= 0)
+                cp_async16(dst, a.in + (long)g_in[gi] * a.in_stride + ((long)pix * C + kc * 8));
+            else
+                *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+        }
+    }
+    cp_async_wait_all();
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {   // ===== weight producer: every stage of every phase, in order, as far ahead as the ring allows =====
+            uint32_t it = 0;
+            for (int p = 0; p < a.n_phases; ++p) {
+                const uint8_t* src = a.blob + a.ph[p].w_off;
+                const int nkb = a.ph[p].nkb;
+                for (int kb = 0; kb < nkb; ++kb, ++it, src += F_STAGE_BYTES) {
+                    const uint32_t s = it % F_NSTAGE;
+                    if (it >= F_NSTAGE) mbar_wait_dbg(&empty[s], ((it / F_NSTAGE) - 1) & 1, a.dbg, 1, (int)it);
+                    mbar_expect_tx(&full[s], F_STAGE_BYTES);
+                    bulk_g2s(stages + s * F_STAGE_BYTES, src, F_STAGE_BYTES, &full[s]);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {   // ===== MMA issuer =====
+            const uint32_t idesc = idesc_bf16_f32(128u, (uint32_t)N);
+            const uint32_t x_addr = smem_u32(X), st_addr = smem_u32(stages);
+            const uint32_t lbo_b = (uint32_t)R * 16u;
+            uint32_t it = 0, ar = 0;
+            for (int p = 0; p < a.n_phases; ++p) {
+                if (p > 0 || a.preload) { mbar_wait_dbg(act_ready, ar & 1, a.dbg, 2, p); ++ar; tc_fence_after(); }
+                if (a.tim) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 0] = clock64();
+                const int nkb = a.ph[p].nkb, taps = a.ph[p].taps;
+                const bool onto = (a.ph[p].flags & PH_ACC_R2) != 0;
+                const uint32_t d_tmem = tmem + (onto ? (uint32_t)F_R2_COL : 0u);
+                const int kpt = taps > 0 ? nkb / taps : 1;
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const uint32_t s = it % F_NSTAGE;
+                    mbar_wait_dbg(&full[s], (it / F_NSTAGE) & 1, a.dbg, 3, (int)it);
+                    tc_fence_after();
+                    const int tap = (taps == 9) ? kb / kpt : 4;
+                    const int cc = kb - (taps == 9 ? tap * kpt : 0);
+                    const int shift = (tap / 3 - 1) * W1 + (tap % 3 - 1);
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        const uint64_t da = smem_desc_kmajor_noswizzle(st_addr + s * F_STAGE_BYTES + kk * 2 * (128 * 16), 128 * 16, 128);
+                        const uint64_t db = smem_desc_kmajor_noswizzle(x_addr + (uint32_t)(((cc * 8 + kk * 2) * R + HALO + shift) * 16), lbo_b, 128);
+                        mma_bf16(d_tmem, da, db, idesc, (onto || (kb | kk) != 0) ? 1u : 0u);
+                    }
+                    mma_commit(&empty[s]);
+                }
+                if (nkb > 0) mma_commit(accum_full); else mbar_arrive(accum_full);
+                if (a.tim) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 1] = clock64();
+            }
+        }
+    } else {
+        // ===== epilogue warps: lane quarter q (hardware rule: warp id % 4), games of parity hsel =====
+        // Every TMEM access below is a warp-collective: all control flow around it is warp-uniform, lanes are only
+        // predicated on their stores.  The pixel map of a chunk is fetched BEFORE its stores (two 16-byte shared loads),
+        // so the eight bf16 stores of a chunk issue back to back instead of alternating with dependent table look-ups.
+        const int q = warp & 3, hsel = (warp - 2) >> 2;
+        const int ch = 32 * q + lane;
+        const bool ch_ok = ch < C;
+        const uint32_t t_lane = tmem + ((uint32_t)(32 * q) << 16);
+        const uint32_t xs = smem_u32(X) + (uint32_t)(((ch >> 3) * R + HALO) * 16 + (ch & 7) * 2);   // + row * 16
+        const uint32_t pt = smem_u32(pixtab);
+        if (a.preload) {   // the chain starts with a residual block: its skip input = the chain input, fp32 into R2
+            for (int g = hsel; g < G; g += 2) {
+                const int cbase = g * P;
+                for (int c0 = 0; c0 < P; c0 += 8) {
+                    int pix[8];
+                    lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
+                    uint32_t v[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        uint32_t raw = 0;
+                        if (pix[j] >= 0 && ch_ok) raw = lds_u16(xs + (uint32_t)(cbase + c0 + j) * 16);
+                        v[j] = raw << 16;   // bf16 -> fp32 bit pattern
+                    }
+                    tmem_st8(t_lane + F_R2_COL + cbase + c0, v);
+                }
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(act_ready);
+        }
+        for (int p = 0; p < a.n_phases; ++p) {
+            const Phase& ph = a.ph[p];
+            const int flags = ph.flags;
+            mbar_wait_dbg(accum_full, p & 1, a.dbg, 4, p);
+            tc_fence_after();
+            if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 2] = clock64();
+            if (flags & PH_RED) {
+                const int nred = ph.red_n0 + ph.red_n1;
+                if (32 * q < nred) {   // warp-uniform; lanes beyond nred only skip the stores
+                    const bool row_ok = ch < nred;
+                    const int head = ch < ph.red_n0 ? ph.red_head0 : ph.red_head1;
+                    const int rr = ch < ph.red_n0 ? ch : ch - ph.red_n0;
+                    const float bias = row_ok ? reinterpret_cast<const float*>(a.blob + ph.bias_off)[ch] : 0.f;
+                    float* dst0 = a.red[head] + (long)rr * HW;
+                    const long gstride = (long)a.red_rows[head] * HW;
+                    for (int g = hsel; g < G; g += 2) {
+                        float* dst = dst0 + (long)(game0 + g) * gstride;
+                        const int cbase = g * P;
+                        for (int c0 = 0; c0 < P; c0 += 8) {
+                            int pix[8];
+                            lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
+                            uint32_t v[8];
+                            tmem_ld8(t_lane + cbase + c0, v);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (pix[j] >= 0 && row_ok) dst[pix[j]] = __uint_as_float(v[j]) + bias;
+                        }
+                    }
+                }
+            }
+            if (flags & PH_NORM) {
+                for (int g = hsel; g < G; g += 2) {
+                    const int cbase = g * P;
+                    float mn = 3.402823466e38f, mx = -3.402823466e38f;
+                    if (a.normalize) {
+                        for (int c0 = 0; c0 < P; c0 += 8) {
+                            int pix[8];
+                            lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
+                            uint32_t v[8];
+                            tmem_ld8(t_lane + F_R2_COL + cbase + c0, v);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (pix[j] >= 0) { const float x = __uint_as_float(v[j]); mn = fminf(mn, x); mx = fmaxf(mx, x); }
+                        }
+                    }
+                    float scale = mx - mn;
+                    if (scale < 1e-5f) scale = 1e-5f;
+                    if (!a.normalize) { mn = 0.f; scale = 1.f; }
+                    bf16* pdst = a.pool + (long)g_out[g] * a.pool_stride + ch;
+                    for (int c0 = 0; c0 < P; c0 += 8) {
+                        int pix[8];
+                        lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
+                        uint32_t v[8];
+                        tmem_ld8(t_lane + F_R2_COL + cbase + c0, v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float y = (__uint_as_float(v[j]) - mn) / scale;
+                            v[j] = __float_as_uint(y);
+                            if (pix[j] >= 0 && ch_ok) {
+                                const bf16 yb = __float2bfloat16(y);
+                                sts_u16(xs + (uint32_t)(cbase + c0 + j) * 16, __bfloat16_as_ushort(yb));
+                                pdst[(long)pix[j] * C] = yb;
+                            }
+                        }
+                        tmem_st8(t_lane + F_R2_COL + cbase + c0, v);
+                    }
+                }
+                tmem_st_wait();
+            }
+            if (!(flags & (PH_RED | PH_NORM))) {
+                const uint32_t src_col = (flags & PH_ACC_R2) ? (uint32_t)F_R2_COL : 0u;
+                const float bias = (ph.bias_off >= 0 && ch_ok) ? reinterpret_cast<const float*>(a.blob + ph.bias_off)[ch] : 0.f;
+                const bool relu = (flags & PH_RELU) != 0, stash = (flags & PH_STASH) != 0, wx = (flags & PH_WRITE_X) != 0 && ch_ok;
+                const float* table = (flags & PH_TABLE) ? reinterpret_cast<const float*>(a.blob + ph.table_off) : nullptr;
+                for (int g = hsel; g < G; g += 2) {
+                    const int cbase = g * P;
+                    const float* tg = (table && ch_ok) ? table + (long)g_act[g] * HW * C + ch : nullptr;
+                    for (int c0 = 0; c0 < P; c0 += 8) {
+                        int pix[8];
+                        lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
+                        uint32_t v[8];
+                        tmem_ld8(t_lane + src_col + cbase + c0, v);
+                        float tv[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) tv[j] = (tg && pix[j] >= 0) ? tg[(long)pix[j] * C] : 0.f;
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float y = __uint_as_float(v[j]) + bias + tv[j];
+                            if (relu) y = fmaxf(y, 0.f);
+                            v[j] = __float_as_uint(y);
+                            if (wx && pix[j] >= 0) sts_u16(xs + (uint32_t)(cbase + c0 + j) * 16, __bfloat16_as_ushort(__float2bfloat16(y)));
+                        }
+                        if (stash) tmem_st8(t_lane + F_R2_COL + cbase + c0, v);
+                    }
+                }
+                if (stash) tmem_st_wait();
+            }
+            fence_proxy_async_smem();   // generic-proxy stores into X -> visible to the tensor core's operand reads
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(act_ready);
+            if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem, F_TMEM_COLS);
+}
+
+// ------------------------------------------------------------------ head MLPs on the reduced activations
+// red[head] : [B][n0] fp32, flatten order r*HW + p (models.cpp:114,161-162)  ->  MLP (model_layers.cpp:46-65)  ->
+// policy softmax (vprnet.cpp:118-119,178-179) or support-to-scalar (ValueEncoder::decode, util.cpp:80-87).
+constexpr int MLP_THREADS = 256;
+constexpr int MLP_MAX_LAYERS = 6;
+struct MlpHead {
+    const float* x;            // [B][n0]
+    const float* w0t;          // first layer transposed: [n0][n1]
+    const float* W[MLP_MAX_LAYERS];   // later layers [out][in] (W[0] unused)
+    const float* b[MLP_MAX_LAYERS];
+    int sizes[MLP_MAX_LAYERS + 1];
+    int n_layers;
+    int out_kind;              // 0 = softmax policy, 1 = support -> scalar
+    float step, min_value; int contractive;
+    double* out; int out_stride;
+};
+struct MlpArgs { MlpHead h[3]; int n_heads, B, mg; };
+
+__global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_constant__ MlpArgs a) {
+    extern __shared__ float msm[];
+    const MlpHead& hd = a.h[blockIdx.y];
+    const int tid = threadIdx.x;
+    const int b0 = blockIdx.x * a.mg;
+    const int nb = min(a.mg, a.B - b0);
+    const int n0 = hd.sizes[0], n1 = hd.sizes[1];
+    float* xs = msm;                     // [mg][n0]
+    float* bufA = xs + a.mg * n0;        // [mg][256]
+    float* bufB = bufA + a.mg * 256;     // [mg][256]
+    for (int i = tid; i < nb * n0; i += MLP_THREADS) xs[i] = hd.x[(long)b0 * n0 + i];
+    __syncthreads();
+    // layer 0: thread <-> (output j, group of games); weights read once per CTA, coalesced over j
+    {
+        const int groups = MLP_THREADS / n1;           // n1 <= 256
+        const int j = tid % n1, gq = tid / n1;
+        if (gq < groups) {
+            for (int gb = gq * 4; gb < nb; gb += groups * 4) {
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+                const float* x0 = xs + gb * n0;
+                const int cnt = min(4, nb - gb);
+#pragma unroll 8
+                for (int i = 0; i < n0; ++i) {
+                    const float w = hd.w0t[(long)i * n1 + j];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) acc[k] += w * x0[(k < cnt ? k : 0) * n0 + i];
+                }
+                for (int k = 0; k < cnt; ++k) {
+                    float v = acc[k] + hd.b[0][j];
+                    if (hd.n_layers > 1) v = fmaxf(v, 0.f);
+                    bufA[(gb + k) * 256 + j] = v;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    float* cur = bufA; float* nxt = bufB;
+    for (int l = 1; l < hd.n_layers; ++l) {
+        const int nin = hd.sizes[l], nout = hd.sizes[l + 1];
+        for (int o = tid; o < nb * nout; o += MLP_THREADS) {
+            const int g = o / nout, j = o - g * nout;
+            const float* wr = hd.W[l] + (long)j * nin;
+            const float* xr = cur + g * 256;
+            float acc = 0.f;
+            for (int i = 0; i < nin; ++i) acc += wr[i] * xr[i];
+            acc += hd.b[l][j];
+            if (l < hd.n_layers - 1) acc = fmaxf(acc, 0.f);
+            nxt[g * 256 + j] = acc;
+        }
+        __syncthreads();
+        float* t = cur; cur = nxt; nxt = t;
+    }
+    if (tid < nb) {
+        const int b = b0 + tid;
+        const float* lg = cur + tid * 256;
+        float* ex = nxt + tid * 256;
+        const int n = hd.sizes[hd.n_layers];
+        float mx = lg[0];
+        for (int i = 1; i < n; ++i) mx = fmaxf(mx, lg[i]);
+        float sum = 0.f;
+        for (int i = 0; i < n; ++i) { const float e = expf(lg[i] - mx); ex[i] = e; sum += e; }
+        if (hd.out_kind == 0) {
+            for (int i = 0; i < n; ++i) hd.out[(long)b * hd.out_stride + i] = (double)(ex[i] / sum);
+        } else {
+            float ev = 0.f;
+            for (int i = 0; i < n; ++i) ev += (float)i * (ex[i] / sum);
+            float v = ev * hd.step + hd.min_value;
+            if (hd.contractive) {
+                const float eps = 0.001f;
+                const float s = (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f);
+                const float inner = sqrtf(1.f + (4.f * eps) * (fabsf(v) + 1.f + eps)) - 1.f;
+                const float qq = inner / (2.f * eps);
+                v = s * (qq * qq - 1.f);
+            }
+            hd.out[(long)b * hd.out_stride] = (double)v;
+        }
+    }
+}
+
+}  // namespace fused
+}  // namespace mzb

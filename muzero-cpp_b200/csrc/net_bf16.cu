@@ -572,6 +572,8 @@ protected:
             MZB_CUDA(cudaHostGetDevicePointer((void**)&dbg_dev_, dbg_host_, 0));
         }
         a.dbg = dbg_dev_;
+        static const int dbg_flags = getenv("MZB_FUSED_DBGFLAGS") ? atoi(getenv("MZB_FUSED_DBGFLAGS")) : 0;
+        a.dbg_flags = dbg_flags;
         static const bool timing = getenv("MZB_FUSED_TIMING") != nullptr;
         a.tim = nullptr;
         if (timing) {

@@ -35,8 +35,9 @@ using namespace umma;
 
 constexpr int F_THREADS = 320;        // warp 0: weight producer, warp 1: MMA issuer + TMEM owner, warps 2-9: epilogue
 constexpr int F_EPI_WARPS = 8;
-constexpr int F_NSTAGE = 8;
-constexpr int F_STAGE_BYTES = 64 * 128 * 2;   // 64 K x 128 cout, bf16
+constexpr int F_NSTAGE = 4;                   // ring slots of two 64-K weight images each
+constexpr int F_KB_BYTES = 64 * 128 * 2;      // one weight image: 64 K x 128 cout, bf16 (16 KB)
+constexpr int F_STAGE_BYTES = 2 * F_KB_BYTES; // a ring slot = 128 K: halves the issuer's wait/commit overhead per MMA
 constexpr int F_TMEM_COLS = 512;
 constexpr int F_R2_COL = 256;
 constexpr int F_MAX_PHASES = 40;
@@ -72,18 +73,29 @@ struct FusedArgs {
     const int* tile_first; const int* tile_count;             // tile -> first game, number of games
     int C, H, W, P, HALO, R, HW, x_bytes;
     int n_phases, preload, normalize;
+    int dbg_flags;                                            // experiments: bit 0 = all taps unshifted (timing only, wrong results)
     int* dbg;                                                 // host-mapped diagnostics (barrier time-outs), may be null
     long long* tim;                                           // optional [tile][phase][4] clocks: mma start, mma issued, accum full, epilogue done
     Phase ph[F_MAX_PHASES];
 };
 
-inline size_t fused_smem_bytes(int x_bytes) { return (size_t)x_bytes + (size_t)F_NSTAGE * F_STAGE_BYTES + 256 + 1024 + 3 * F_MAX_G * 4 + 128; }
+inline size_t fused_smem_bytes(int x_bytes) { return (size_t)x_bytes + (size_t)F_NSTAGE * F_STAGE_BYTES + 256 + 1024 + 3 * F_MAX_G * 4 + 32 + 128; }
 
 // explicit shared-space accesses (32-bit shared addresses: no generic-pointer conversion per access)
 __device__ __forceinline__ void sts_u16(uint32_t addr, unsigned short v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(v) : "memory"); }
 __device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
     unsigned short v;
     asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint4 lds_v4u(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
     return v;
 }
 __device__ __forceinline__ void lds_v4(uint32_t addr, int* p) {
@@ -107,6 +119,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
     int* g_in = pixtab + 256;
     int* g_out = g_in + F_MAX_G;
     int* g_act = g_out + F_MAX_G;
+    uint32_t* pixmask = reinterpret_cast<uint32_t*>(g_act + F_MAX_G);   // [8] bit r = row r of a game is a real pixel
 
     if (tid == 0) {
         for (int s = 0; s < F_NSTAGE; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
@@ -124,6 +137,14 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
     for (int r = tid; r < 256; r += F_THREADS) {
         const int yy = r / W1, xx = r - yy * W1;
         pixtab[r] = (r < P && yy >= 1 && yy <= a.H && xx < a.W) ? (yy - 1) * a.W + xx : -1;
+    }
+    if (tid < 8) {
+        uint32_t m = 0;
+        for (int j = 0; j < 32; ++j) {
+            const int r = tid * 32 + j, yy = r / W1, xx = r - yy * W1;
+            if (r < P && yy >= 1 && yy <= a.H && xx < a.W) m |= 1u << j;
+        }
+        pixmask[tid] = m;
     }
     __syncthreads();
     // ---- chain input -> X (zero padded), 16 bytes = 8 channels of one pixel per request ----
@@ -154,19 +175,25 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             for (int p = 0; p < a.n_phases; ++p) {
                 const uint8_t* src = a.blob + a.ph[p].w_off;
                 const int nkb = a.ph[p].nkb;
-                for (int kb = 0; kb < nkb; ++kb, ++it, src += F_STAGE_BYTES) {
+                for (int kb = 0; kb < nkb; kb += 2, ++it) {
                     const uint32_t s = it % F_NSTAGE;
+                    const uint32_t bytes = (uint32_t)min(2, nkb - kb) * F_KB_BYTES;
                     if (it >= F_NSTAGE) mbar_wait_dbg(&empty[s], ((it / F_NSTAGE) - 1) & 1, a.dbg, 1, (int)it);
-                    mbar_expect_tx(&full[s], F_STAGE_BYTES);
-                    bulk_g2s(stages + s * F_STAGE_BYTES, src, F_STAGE_BYTES, &full[s]);
+                    mbar_expect_tx(&full[s], bytes);
+                    bulk_g2s(stages + s * F_STAGE_BYTES, src, bytes, &full[s]);
+                    src += bytes;
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {   // ===== MMA issuer =====
             const uint32_t idesc = idesc_bf16_f32(128u, (uint32_t)N);
-            const uint32_t x_addr = smem_u32(X), st_addr = smem_u32(stages);
-            const uint32_t lbo_b = (uint32_t)R * 16u;
+            // descriptors: everything but the 14-bit start-address field is constant, so the loop only adds to the low words
+            const uint64_t da0 = smem_desc_kmajor_noswizzle(smem_u32(stages), 128 * 16, 128);
+            const uint64_t db0 = smem_desc_kmajor_noswizzle(smem_u32(X) + (uint32_t)HALO * 16u, (uint32_t)R * 16u, 128);
+            const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32);
+            const uint32_t a_lo0 = (uint32_t)da0, b_lo0 = (uint32_t)db0;
+            const uint32_t kk_b = 2u * (uint32_t)R;          // two 8-channel chunks per K = 16 step, in 16-byte units
             uint32_t it = 0, ar = 0;
             for (int p = 0; p < a.n_phases; ++p) {
                 if (p > 0 || a.preload) { mbar_wait_dbg(act_ready, ar & 1, a.dbg, 2, p); ++ar; tc_fence_after(); }
@@ -175,18 +202,26 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 const bool onto = (a.ph[p].flags & PH_ACC_R2) != 0;
                 const uint32_t d_tmem = tmem + (onto ? (uint32_t)F_R2_COL : 0u);
                 const int kpt = taps > 0 ? nkb / taps : 1;
-                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                int tap = (taps == 9) ? 0 : 4, cc = 0;
+                uint32_t b_tap = b_lo0 + (uint32_t)((tap / 3 - 1) * W1 + (tap % 3 - 1));
+                for (int kb = 0; kb < nkb; ++it) {
                     const uint32_t s = it % F_NSTAGE;
+                    const int n = min(2, nkb - kb);
+                    const uint32_t a_lo = a_lo0 + s * (F_STAGE_BYTES >> 4);
                     mbar_wait_dbg(&full[s], (it / F_NSTAGE) & 1, a.dbg, 3, (int)it);
                     tc_fence_after();
-                    const int tap = (taps == 9) ? kb / kpt : 4;
-                    const int cc = kb - (taps == 9 ? tap * kpt : 0);
-                    const int shift = (tap / 3 - 1) * W1 + (tap % 3 - 1);
 #pragma unroll
-                    for (int kk = 0; kk < 4; ++kk) {
-                        const uint64_t da = smem_desc_kmajor_noswizzle(st_addr + s * F_STAGE_BYTES + kk * 2 * (128 * 16), 128 * 16, 128);
-                        const uint64_t db = smem_desc_kmajor_noswizzle(x_addr + (uint32_t)(((cc * 8 + kk * 2) * R + HALO + shift) * 16), lbo_b, 128);
-                        mma_bf16(d_tmem, da, db, idesc, (onto || (kb | kk) != 0) ? 1u : 0u);
+                    for (int h = 0; h < 2; ++h) {
+                        if (h < n) {
+                            const uint32_t ah = a_lo + h * (F_KB_BYTES >> 4);
+                            const uint32_t b_lo = b_tap + (uint32_t)(cc * 8 * R);
+                            mma_bf16_lohi_rt(d_tmem, ah, a_hi, b_lo, b_hi, idesc, (onto || kb != 0) ? 1u : 0u);
+                            mma_bf16_lohi<1>(d_tmem, ah + 256u, a_hi, b_lo + kk_b, b_hi, idesc);
+                            mma_bf16_lohi<1>(d_tmem, ah + 512u, a_hi, b_lo + 2u * kk_b, b_hi, idesc);
+                            mma_bf16_lohi<1>(d_tmem, ah + 768u, a_hi, b_lo + 3u * kk_b, b_hi, idesc);
+                            ++kb;
+                            if (++cc == kpt) { cc = 0; ++tap; b_tap = b_lo0 + (uint32_t)((tap / 3 - 1) * W1 + (tap % 3 - 1)); }
+                        }
                     }
                     mma_commit(&empty[s]);
                 }
@@ -204,7 +239,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
         const bool ch_ok = ch < C;
         const uint32_t t_lane = tmem + ((uint32_t)(32 * q) << 16);
         const uint32_t xs = smem_u32(X) + (uint32_t)(((ch >> 3) * R + HALO) * 16 + (ch & 7) * 2);   // + row * 16
-        const uint32_t pt = smem_u32(pixtab);
+        const uint32_t pt = smem_u32(pixtab), pm = smem_u32(pixmask);
         if (a.preload) {   // the chain starts with a residual block: its skip input = the chain input, fp32 into R2
             for (int g = hsel; g < G; g += 2) {
                 const int cbase = g * P;
@@ -258,42 +293,45 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 }
             }
             if (flags & PH_NORM) {
+                // normalize_hidden_state (models.cpp:16-26): a thread owns one channel, its columns are the pixels
                 for (int g = hsel; g < G; g += 2) {
                     const int cbase = g * P;
                     float mn = 3.402823466e38f, mx = -3.402823466e38f;
                     if (a.normalize) {
-                        for (int c0 = 0; c0 < P; c0 += 8) {
-                            int pix[8];
-                            lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
-                            uint32_t v[8];
-                            tmem_ld8(t_lane + F_R2_COL + cbase + c0, v);
+                        for (int c0 = 0; c0 < P; c0 += 32) {
+                            const bool two = P - c0 > 16;
+                            uint32_t v[32];
+                            tmem_ld16(t_lane + F_R2_COL + cbase + c0, v);
+                            if (two) tmem_ld16(t_lane + F_R2_COL + cbase + c0 + 16, v + 16);
+                            const uint32_t m = lds_u32(pm + (c0 >> 5) * 4);
                             tmem_ld_wait();
 #pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                if (pix[j] >= 0) { const float x = __uint_as_float(v[j]); mn = fminf(mn, x); mx = fmaxf(mx, x); }
+                            for (int j = 0; j < 32; ++j)
+                                if ((j < 16 || two) && ((m >> j) & 1u)) { const float x = __uint_as_float(v[j]); mn = fminf(mn, x); mx = fmaxf(mx, x); }
                         }
                     }
                     float scale = mx - mn;
                     if (scale < 1e-5f) scale = 1e-5f;
                     if (!a.normalize) { mn = 0.f; scale = 1.f; }
-                    bf16* pdst = a.pool + (long)g_out[g] * a.pool_stride + ch;
-                    for (int c0 = 0; c0 < P; c0 += 8) {
-                        int pix[8];
-                        lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
-                        uint32_t v[8];
-                        tmem_ld8(t_lane + F_R2_COL + cbase + c0, v);
+                    const float inv = 1.0f / scale;
+                    for (int c0 = 0; c0 < P; c0 += 32) {
+                        const bool two = P - c0 > 16;
+                        uint32_t v[32];
+                        tmem_ld16(t_lane + F_R2_COL + cbase + c0, v);
+                        if (two) tmem_ld16(t_lane + F_R2_COL + cbase + c0 + 16, v + 16);
+                        const uint32_t m = lds_u32(pm + (c0 >> 5) * 4);
                         tmem_ld_wait();
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float y = (__uint_as_float(v[j]) - mn) / scale;
-                            v[j] = __float_as_uint(y);
-                            if (pix[j] >= 0 && ch_ok) {
-                                const bf16 yb = __float2bfloat16(y);
-                                sts_u16(xs + (uint32_t)(cbase + c0 + j) * 16, __bfloat16_as_ushort(yb));
-                                pdst[(long)pix[j] * C] = yb;
+                        for (int j = 0; j < 32; ++j) {
+                            if (j < 16 || two) {
+                                const float y = (__uint_as_float(v[j]) - mn) * inv;   // reciprocal multiply: IEEE division costs 10x here; 1 ulp, far inside the bf16 tolerance
+                                v[j] = __float_as_uint(y);
+                                if (ch_ok && ((m >> j) & 1u)) sts_u16(xs + (uint32_t)(cbase + c0 + j) * 16, __bfloat16_as_ushort(__float2bfloat16(y)));
                             }
                         }
-                        tmem_st8(t_lane + F_R2_COL + cbase + c0, v);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (c0 + 8 * k < P) tmem_st8(t_lane + F_R2_COL + cbase + c0 + 8 * k, v + 8 * k);
                     }
                 }
                 tmem_st_wait();
@@ -302,27 +340,55 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 const uint32_t src_col = (flags & PH_ACC_R2) ? (uint32_t)F_R2_COL : 0u;
                 const float bias = (ph.bias_off >= 0 && ch_ok) ? reinterpret_cast<const float*>(a.blob + ph.bias_off)[ch] : 0.f;
                 const bool relu = (flags & PH_RELU) != 0, stash = (flags & PH_STASH) != 0, wx = (flags & PH_WRITE_X) != 0 && ch_ok;
-                const float* table = (flags & PH_TABLE) ? reinterpret_cast<const float*>(a.blob + ph.table_off) : nullptr;
-                for (int g = hsel; g < G; g += 2) {
-                    const int cbase = g * P;
-                    const float* tg = (table && ch_ok) ? table + (long)g_act[g] * HW * C + ch : nullptr;
-                    for (int c0 = 0; c0 < P; c0 += 8) {
-                        int pix[8];
-                        lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
-                        uint32_t v[8];
-                        tmem_ld8(t_lane + src_col + cbase + c0, v);
-                        float tv[8];
+                if (flags & PH_TABLE) {   // dynamics head: + per-action table (needs the pixel index: 8-column chunks)
+                    const float* table = reinterpret_cast<const float*>(a.blob + ph.table_off);
+                    for (int g = hsel; g < G; g += 2) {
+                        const int cbase = g * P;
+                        const float* tg = ch_ok ? table + (long)g_act[g] * HW * C + ch : nullptr;
+                        for (int c0 = 0; c0 < P; c0 += 8) {
+                            int pix[8];
+                            lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
+                            uint32_t v[8];
+                            tmem_ld8(t_lane + src_col + cbase + c0, v);
+                            float tv[8];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) tv[j] = (tg && pix[j] >= 0) ? tg[(long)pix[j] * C] : 0.f;
-                        tmem_ld_wait();
+                            for (int j = 0; j < 8; ++j) tv[j] = (tg && pix[j] >= 0) ? tg[(long)pix[j] * C] : 0.f;
+                            tmem_ld_wait();
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            float y = __uint_as_float(v[j]) + bias + tv[j];
-                            if (relu) y = fmaxf(y, 0.f);
-                            v[j] = __float_as_uint(y);
-                            if (wx && pix[j] >= 0) sts_u16(xs + (uint32_t)(cbase + c0 + j) * 16, __bfloat16_as_ushort(__float2bfloat16(y)));
+                            for (int j = 0; j < 8; ++j) {
+                                float y = __uint_as_float(v[j]) + bias + tv[j];
+                                if (relu) y = fmaxf(y, 0.f);
+                                v[j] = __float_as_uint(y);
+                                if (wx && pix[j] >= 0) sts_u16(xs + (uint32_t)(cbase + c0 + j) * 16, __bfloat16_as_ushort(__float2bfloat16(y)));
+                            }
+                            if (stash) tmem_st8(t_lane + F_R2_COL + cbase + c0, v);
                         }
-                        if (stash) tmem_st8(t_lane + F_R2_COL + cbase + c0, v);
+                    }
+                } else {
+                    for (int g = hsel; g < G; g += 2) {
+                        const int cbase = g * P;
+                        for (int c0 = 0; c0 < P; c0 += 32) {
+                            const bool two = P - c0 > 16;
+                            uint32_t v[32];
+                            tmem_ld16(t_lane + src_col + cbase + c0, v);
+                            if (two) tmem_ld16(t_lane + src_col + cbase + c0 + 16, v + 16);
+                            const uint32_t m = lds_u32(pm + (c0 >> 5) * 4);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                if (j < 16 || two) {
+                                    float y = __uint_as_float(v[j]) + bias;
+                                    if (relu) y = fmaxf(y, 0.f);
+                                    v[j] = __float_as_uint(y);
+                                    if (wx && ((m >> j) & 1u)) sts_u16(xs + (uint32_t)(cbase + c0 + j) * 16, __bfloat16_as_ushort(__float2bfloat16(y)));
+                                }
+                            }
+                            if (stash) {
+#pragma unroll
+                                for (int k = 0; k < 4; ++k)
+                                    if (c0 + 8 * k < P) tmem_st8(t_lane + F_R2_COL + cbase + c0 + 8 * k, v + 8 * k);
+                            }
+                        }
                     }
                 }
                 if (stash) tmem_st_wait();
@@ -331,6 +397,22 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(act_ready);
+            if (flags & PH_NORM) {
+                // child hidden state -> node pool, straight from X (bf16, already normalised): 16-byte coalesced stores,
+                // overlapped with the next phase's MMAs (which only read X)
+                asm volatile("bar.sync 1, 256;" ::: "memory");   // every epilogue warp has finished writing X
+                const int et = tid - 64;
+                const int kc = et % KC, rsub = et / KC, rstep = 256 / KC;   // a thread keeps its 8-channel chunk; rows stride
+                const uint32_t xk = smem_u32(X) + (uint32_t)((kc * R + HALO) * 16);
+                for (int g = 0; g < G; ++g) {
+                    bf16* pg = a.pool + (long)g_out[g] * a.pool_stride + kc * 8;
+                    for (int r = rsub; r < P; r += rstep) {
+                        const int pix = pixtab[r];
+                        if (pix >= 0) *reinterpret_cast<uint4*>(pg + (long)pix * C) = lds_v4u(xk + (uint32_t)(g * P + r) * 16);
+                    }
+                }
+                asm volatile("bar.sync 1, 256;" ::: "memory");   // nobody overwrites X (next epilogue) before the copy is done
+            }
             if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();
         }
     }

@@ -369,6 +369,36 @@ protected:
         return off;
     }
 
+    // first MLP layer of 1 or 2 heads as tensor-core weight images: rows = stacked hidden units, K = concatenated head
+    // inputs (block structure: a head's rows are zero outside its own K range), K padded to a multiple of 64
+    size_t pack_mlp0(const HeadHost* const* hh, int nh, std::vector<uint8_t>* extra, size_t* bias_rel, int* nkb_out) {
+        int ktot = 0;
+        for (int h = 0; h < nh; ++h) ktot += hh[h]->sizes[0];
+        const int nkb = (ktot + KB - 1) / KB;
+        while (extra->size() % 128) extra->push_back(0);
+        const size_t off = extra->size();
+        extra->resize(off + (size_t)nkb * STAGE_BYTES, 0);
+        bf16* dst = reinterpret_cast<bf16*>(extra->data() + off);
+        std::vector<float> bias(128, 0.f);
+        int row0 = 0, k0 = 0;
+        for (int h = 0; h < nh; ++h) {
+            const int n0 = hh[h]->sizes[0], n1 = hh[h]->sizes[1];
+            for (int j = 0; j < n1; ++j) {
+                bias[row0 + j] = hh[h]->b[0][j];
+                for (int i = 0; i < n0; ++i) {
+                    const int k = k0 + i, cc = k / KB, kc = (k % KB) / 8, e = k % 8;
+                    dst[(((size_t)cc * 8 + kc) * UM + row0 + j) * 8 + e] = __float2bfloat16(hh[h]->W[0][(size_t)j * n0 + i]);
+                }
+            }
+            row0 += n1; k0 += n0;
+        }
+        *bias_rel = extra->size();
+        const uint8_t* bp = reinterpret_cast<const uint8_t*>(bias.data());
+        extra->insert(extra->end(), bp, bp + 128 * sizeof(float));
+        *nkb_out = nkb;
+        return off;
+    }
+
     int pack_fused(const NetPlan& plan, std::vector<uint8_t>* extra) {
         fused_rec_ = FusedChain(); fused_init_ = FusedChain();
         fused_final_ = false;
@@ -398,8 +428,22 @@ protected:
         int R = halo + nmax + halo;
         if ((R & 1) == 0) ++R;
         const int x_bytes = (int)((((size_t)(C / 8) * R * 16) + 127) / 128 * 128);
-        const size_t smem = fused::fused_smem_bytes(x_bytes);
-        if (smem > 227 * 1024) return MZB_OK;
+        if (fused::fused_smem_bytes(x_bytes, 0) > 227 * 1024) return MZB_OK;
+        // in-kernel head MLPs (first layer on the tensor core): needs <= 8 games per tile, stacked widths <= 128
+        const HeadHost& hR = plan.reward_head; const HeadHost& hP = plan.policy_head; const HeadHost& hV = plan.value_head;
+        int z_bytes = 0;
+        {
+            bool ok = gmax <= 8 && hP.W.size() == hV.W.size() && hR.sizes[1] <= UM;
+            for (size_t l = 1; ok && l < hP.sizes.size(); ++l) ok = hP.sizes[l] + hV.sizes[l] <= UM;
+            for (size_t l = 1; ok && l < hR.sizes.size(); ++l) ok = hR.sizes[l] <= UM;
+            static const bool no_z = getenv("MZB_NO_INKERNEL_MLP") != nullptr;
+            if (ok && !no_z) {
+                const int kr = (hR.sizes[0] + KB - 1) / KB * KB, kpv = (hP.sizes[0] + hV.sizes[0] + KB - 1) / KB * KB;
+                z_bytes = std::max(kr, kpv) / 8 * 128;
+                if (fused::fused_smem_bytes(x_bytes, z_bytes) > 227 * 1024) z_bytes = 0;
+            }
+        }
+        const size_t smem = fused::fused_smem_bytes(x_bytes, z_bytes);
         // extra weights
         conv1_rel_[0] = pack_conv1(hr, 1, C, extra, &conv1_bias_rel_[0]);
         conv1_rel_[1] = pack_conv1(hpv, 2, C, extra, &conv1_bias_rel_[1]);
@@ -413,8 +457,15 @@ protected:
             const uint8_t* bp = reinterpret_cast<const uint8_t*>(wt.data());
             extra->insert(extra->end(), bp, bp + wt.size() * sizeof(float));
         }
+        if (z_bytes) {
+            const HeadHost* r1[1] = {&hR};
+            const HeadHost* pv2[2] = {&hP, &hV};
+            mlp0_rel_[0] = pack_mlp0(r1, 1, extra, &mlp0_bias_rel_[0], &mlp0_nkb_[0]);
+            mlp0_rel_[1] = pack_mlp0(pv2, 2, extra, &mlp0_bias_rel_[1], &mlp0_nkb_[1]);
+        }
         fused::FusedArgs base;
         memset(&base, 0, sizeof(base));
+        base.z_bytes = z_bytes;
         base.C = C; base.H = H; base.W = W; base.P = P; base.HALO = halo; base.R = R; base.HW = H * W; base.x_bytes = x_bytes;
         base.normalize = plan.normalize ? 1 : 0;
         base.red_rows[0] = plan.reward_head.red; base.red_rows[1] = plan.policy_head.red; base.red_rows[2] = plan.value_head.red;
@@ -470,7 +521,20 @@ protected:
             ph.flags |= fused::PH_RED;
             if (which == 0) { ph.red_head0 = 0; ph.red_n0 = fa->red_rows[0]; ph.red_head1 = 0; ph.red_n1 = 0; }
             else { ph.red_head0 = 1; ph.red_n0 = fa->red_rows[1]; ph.red_head1 = 2; ph.red_n1 = fa->red_rows[2]; }
+            ph.z_k0 = 0; ph.z_k1 = heads_[ph.red_head0].sizes[0];
         }
+    }
+    void add_mlp_phase(fused::FusedArgs* fa, int which) {
+        if (!fa->z_bytes) return;
+        fused::Phase& ph = fa->ph[fa->n_phases++];
+        memset(&ph, 0, sizeof(ph));
+        ph.table_off = -1;
+        ph.flags = fused::PH_MLP;
+        ph.w_off = (uint32_t)(fp32_bytes_ + mlp0_rel_[which]);
+        ph.taps = 1; ph.nkb = mlp0_nkb_[which];
+        ph.bias_off = (int)(fp32_bytes_ + mlp0_bias_rel_[which]);
+        if (which == 0) { ph.red_head0 = 0; ph.red_n0 = heads_[0].sizes[1]; ph.red_head1 = 0; ph.red_n1 = 0; }
+        else { ph.red_head0 = 1; ph.red_n0 = heads_[1].sizes[1]; ph.red_head1 = 2; ph.red_n1 = heads_[2].sizes[1]; }
     }
 
     int finalize_fused() {
@@ -481,7 +545,7 @@ protected:
         int dev = 0;
         MZB_CUDA(cudaGetDevice(&dev));
         MZB_CUDA(cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, dev));
-        size_t phases_rec = 1 + 2 * (steps_[1].size() - 1) + 1 + 2 * steps_[2].size() + 1;
+        size_t phases_rec = 1 + 2 * (steps_[1].size() - 1) + 1 + 2 * steps_[2].size() + 1 + 2;
         if (phases_rec > (size_t)fused::F_MAX_PHASES) { fused_rec_.ok = false; fused_init_.ok = false; return MZB_OK; }
         {   // recurrent: dynamics head, dynamics blocks, reward conv1x1 + normalise, prediction blocks, policy/value conv1x1
             fused::FusedArgs* fa = &fused_rec_.args;
@@ -489,10 +553,12 @@ protected:
             add_conv_phase(fa, 1, steps_[1][0].conv0, fused::PH_WRITE_X | fused::PH_STASH);
             add_blocks(fa, 1, 1);
             add_conv1_phase(fa, 0, fused::PH_NORM, C);
+            add_mlp_phase(fa, 0);
             add_blocks(fa, 2, 0);
             add_conv1_phase(fa, 1, 0, C);
+            add_mlp_phase(fa, 1);
         }
-        size_t phases_init = 2 * (steps_[0].size() - 1) + 1 + 2 * steps_[2].size() + 1;
+        size_t phases_init = 2 * (steps_[0].size() - 1) + 1 + 2 * steps_[2].size() + 1 + 1;
         if (fused_init_.ok && phases_init > (size_t)fused::F_MAX_PHASES) fused_init_.ok = false;
         if (fused_init_.ok) {   // initial: (head conv on the direct kernel), representation blocks, normalise, prediction, heads
             fused::FusedArgs* fa = &fused_init_.args;
@@ -501,6 +567,7 @@ protected:
             add_conv1_phase(fa, -1, fused::PH_NORM, C);
             add_blocks(fa, 2, 0);
             add_conv1_phase(fa, 1, 0, C);
+            add_mlp_phase(fa, 1);
         }
         // reduced head inputs and MLP descriptors
         for (int h = 0; h < 3; ++h) MZB_CUDA(red_[h].alloc((size_t)max_batch_ * heads_[h].red * hw * sizeof(float)));
@@ -518,8 +585,7 @@ protected:
         int n0max = 0;
         for (int h = 0; h < 3; ++h) n0max = std::max(n0max, heads_[h].sizes[0]);
         mlp_mg_ = 16;
-        while (mlp_mg_ > 4 && (size_t)mlp_mg_ * (n0max + 512) * sizeof(float) > 150 * 1024) mlp_mg_ /= 2;
-        if ((size_t)mlp_mg_ * (n0max + 512) * sizeof(float) > 160 * 1024) { fused_rec_.ok = false; fused_init_.ok = false; }
+        (void)n0max;
         return MZB_OK;
     }
 
@@ -555,7 +621,7 @@ protected:
     }
 
     int launch_fused(FusedChain& ch, int B, const bf16* in, const int* in_slot, long in_stride, const int* out_slot,
-                     const int* action, cudaStream_t s) {
+                     const int* action, const NetOutputs& out, cudaStream_t s) {
         const TileTab* tt = nullptr;
         int rc = tiles_for(B, ch.gmax, &tt);
         if (rc) return rc;
@@ -565,6 +631,18 @@ protected:
         a.action = action;
         a.blob = reinterpret_cast<const uint8_t*>(blob_.p);
         for (int h = 0; h < 3; ++h) a.red[h] = red_[h].as<float>();
+        if (a.z_bytes) {
+            double* outs[3] = {out.reward, out.policy, out.value};
+            const int strides[3] = {1, plan_dims_.A, 1};
+            for (int h = 0; h < 3; ++h) {
+                fused::HeadTail& t = a.head[h];
+                t.n_layers = heads_[h].n_layers;
+                for (int l = 0; l <= t.n_layers; ++l) t.sizes[l] = heads_[h].sizes[l];
+                for (int l = 0; l < t.n_layers; ++l) { t.W[l] = heads_[h].W[l]; t.b[l] = heads_[h].b[l]; }
+                t.out_kind = heads_[h].out_kind; t.step = heads_[h].step; t.min_value = heads_[h].min_value; t.contractive = heads_[h].contractive;
+                t.out = outs[h]; t.out_stride = strides[h];
+            }
+        }
         a.tile_first = tt->first.as<int>(); a.tile_count = tt->count.as<int>();
         if (!dbg_host_) {
             MZB_CUDA(cudaHostAlloc((void**)&dbg_host_, 16 * sizeof(int), cudaHostAllocMapped));
@@ -625,7 +703,8 @@ protected:
             ++n;
         }
         m.n_heads = n; m.B = B; m.mg = mlp_mg_;
-        const size_t smem = (size_t)mlp_mg_ * (n0max + 512) * sizeof(float);
+        const size_t smem = ((size_t)mlp_mg_ * 512 + 16 * (fused::MLP_KT + 4) + fused::MLP_KT * 64) * sizeof(float);
+        (void)n0max;
         dim3 grid((B + mlp_mg_ - 1) / mlp_mg_, n);
         fused::mlp_heads_kernel<<<grid, fused::MLP_THREADS, smem, s>>>(m);
         MZB_CUDA(cudaGetLastError());
@@ -639,11 +718,14 @@ public:
         if (rc) return rc;
         if (!fused_rec_.ok) return direct::DirectBackend<bf16>::recurrent(B, d_in_slot, d_action, d_out_slot, out, s);
         MZB_REQUIRE(B <= max_batch_, "batch %d above engine capacity %d", B, max_batch_);
-        rc = launch_fused(fused_rec_, B, pool_.as<bf16>(), d_in_slot, (long)slot_elems_, d_out_slot, d_action, s);
+        rc = launch_fused(fused_rec_, B, pool_.as<bf16>(), d_in_slot, (long)slot_elems_, d_out_slot, d_action, out, s);
         if (rc) return rc;
-        rc = launch_mlp(B, 0, out, s);
-        if (rc) return rc;
-        launches_recurrent_ = 2;
+        launches_recurrent_ = 1;
+        if (!fused_rec_.args.z_bytes) {
+            rc = launch_mlp(B, 0, out, s);
+            if (rc) return rc;
+            launches_recurrent_ = 2;
+        }
         return MZB_OK;
     }
     int initial(const float* d_obs, int B, const int* d_out_slot, const NetOutputs& out, cudaStream_t s) override {
@@ -658,10 +740,12 @@ public:
         launches_ = 1;
         rc = launch_conv(convs_[0][0], B, bufA_.as<bf16>(), nullptr, (long)d.initial_flat(), bufB_.as<bf16>(), nullptr, nullptr, 0, nullptr, s);
         if (rc) return rc;
-        rc = launch_fused(fused_init_, B, bufB_.as<bf16>(), nullptr, (long)slot_elems_, d_out_slot, nullptr, s);
+        rc = launch_fused(fused_init_, B, bufB_.as<bf16>(), nullptr, (long)slot_elems_, d_out_slot, nullptr, out, s);
         if (rc) return rc;
-        rc = launch_mlp(B, 1, out, s);
-        if (rc) return rc;
+        if (!fused_init_.args.z_bytes) {
+            rc = launch_mlp(B, 1, out, s);
+            if (rc) return rc;
+        }
         initial_reward_kernel<<<(B + 127) / 128, 128, 0, s>>>(out.reward, B, renc_.support, (float)renc_.step, (float)renc_.min_value, renc_.contractive);
         MZB_CUDA(cudaGetLastError());
         launches_initial_ = launches_ + 3;
@@ -672,6 +756,8 @@ protected:
     FusedChain fused_rec_, fused_init_;
     bool fused_final_ = false;
     size_t conv1_rel_[2] = {0, 0}, conv1_bias_rel_[2] = {0, 0}, w0t_rel_[3] = {0, 0, 0};
+    size_t mlp0_rel_[2] = {0, 0}, mlp0_bias_rel_[2] = {0, 0};
+    int mlp0_nkb_[2] = {0, 0};
     DevBuf red_[3];
     fused::MlpArgs mlp_;
     int mlp_mg_ = 16, n_sm_ = 0;

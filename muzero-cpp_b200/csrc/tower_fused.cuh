@@ -51,6 +51,7 @@ enum : int {
     PH_WRITE_X = 16,  // store the epilogue result into X (bf16)
     PH_RED = 32,      // 1x1 head convolution: rows of R1 -> red[] buffers (no activation)
     PH_NORM = 64,     // normalize_hidden_state on R2 -> X, node pool slot, R2
+    PH_MLP = 128,     // head MLPs: first layer on the tensor core (A = stacked W0 images, B = Z), later layers + output transform on CUDA cores
 };
 
 struct Phase {
@@ -61,6 +62,19 @@ struct Phase {
     int table_off;         // byte offset of the fp32 [A][HW][C] table (PH_TABLE)
     int flags;
     int red_head0, red_n0, red_head1, red_n1;   // PH_RED: rows [0,n0) -> red[head0], rows [n0, n0+n1) -> red[head1]
+                                                // PH_MLP: hidden rows [0,n0) belong to head0, [n0, n0+n1) to head1 (n1 = 0: one head)
+    int z_k0, z_k1;                             // PH_RED with Z: first K index of head0 / head1 inside Z
+};
+
+// one head's MLP tail (layers >= 1) and output transform, for the in-kernel path
+struct HeadTail {
+    const float* W[6];     // [out][in] per layer (W[0] unused: layer 0 runs on the tensor core)
+    const float* b[6];
+    int sizes[7];
+    int n_layers;
+    int out_kind;          // 0 = softmax policy, 1 = support -> scalar
+    float step, min_value; int contractive;
+    double* out; int out_stride;
 };
 
 struct FusedArgs {
@@ -76,10 +90,15 @@ struct FusedArgs {
     int dbg_flags;                                            // experiments: bit 0 = all taps unshifted (timing only, wrong results)
     int* dbg;                                                 // host-mapped diagnostics (barrier time-outs), may be null
     long long* tim;                                           // optional [tile][phase][4] clocks: mma start, mma issued, accum full, epilogue done
+    int z_bytes;                                              // > 0: head inputs stay in shared memory (Z) and the MLPs run in-kernel
+    HeadTail head[3];
     Phase ph[F_MAX_PHASES];
 };
 
-inline size_t fused_smem_bytes(int x_bytes) { return (size_t)x_bytes + (size_t)F_NSTAGE * F_STAGE_BYTES + 256 + 1024 + 3 * F_MAX_G * 4 + 32 + 128; }
+constexpr int F_HS_BYTES = 2 * 8 * 128 * 4;   // two ping-pong buffers [8 games][128 stacked units] fp32 for the MLP tails
+inline size_t fused_smem_bytes(int x_bytes, int z_bytes) {
+    return (size_t)x_bytes + (size_t)F_NSTAGE * F_STAGE_BYTES + 256 + 1024 + 3 * F_MAX_G * 4 + 32 + 128 + (z_bytes ? (size_t)z_bytes + F_HS_BYTES + 128 : 0);
+}
 
 // explicit shared-space accesses (32-bit shared addresses: no generic-pointer conversion per access)
 __device__ __forceinline__ void sts_u16(uint32_t addr, unsigned short v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(v) : "memory"); }
@@ -120,6 +139,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
     int* g_out = g_in + F_MAX_G;
     int* g_act = g_out + F_MAX_G;
     uint32_t* pixmask = reinterpret_cast<uint32_t*>(g_act + F_MAX_G);   // [8] bit r = row r of a game is a real pixel
+    uint8_t* Z = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(pixmask + 8) + 127) & ~(uintptr_t)127);   // [K/8][8 games][16 B] bf16 head inputs
+    float* Hs = reinterpret_cast<float*>(Z + a.z_bytes);
 
     if (tid == 0) {
         for (int s = 0; s < F_NSTAGE; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
@@ -146,6 +167,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
         }
         pixmask[tid] = m;
     }
+    for (int i = tid; i < a.z_bytes / 16; i += F_THREADS) reinterpret_cast<uint4*>(Z)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
     // ---- chain input -> X (zero padded), 16 bytes = 8 channels of one pixel per request ----
     {
@@ -187,13 +209,13 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
         }
     } else if (warp == 1) {
         if (lane == 0) {   // ===== MMA issuer =====
-            const uint32_t idesc = idesc_bf16_f32(128u, (uint32_t)N);
+            const uint32_t idescN = idesc_bf16_f32(128u, (uint32_t)N), idesc16 = idesc_bf16_f32(128u, 16u);
             // descriptors: everything but the 14-bit start-address field is constant, so the loop only adds to the low words
             const uint64_t da0 = smem_desc_kmajor_noswizzle(smem_u32(stages), 128 * 16, 128);
             const uint64_t db0 = smem_desc_kmajor_noswizzle(smem_u32(X) + (uint32_t)HALO * 16u, (uint32_t)R * 16u, 128);
-            const uint32_t a_hi = (uint32_t)(da0 >> 32), b_hi = (uint32_t)(db0 >> 32);
-            const uint32_t a_lo0 = (uint32_t)da0, b_lo0 = (uint32_t)db0;
-            const uint32_t kk_b = 2u * (uint32_t)R;          // two 8-channel chunks per K = 16 step, in 16-byte units
+            const uint64_t dz0 = smem_desc_kmajor_noswizzle(smem_u32(Z), 128, 0);
+            const uint32_t a_hi = (uint32_t)(da0 >> 32), x_hi = (uint32_t)(db0 >> 32), z_hi = (uint32_t)(dz0 >> 32);
+            const uint32_t a_lo0 = (uint32_t)da0, b_lo0 = (uint32_t)db0, z_lo0 = (uint32_t)dz0;
             uint32_t it = 0, ar = 0;
             for (int p = 0; p < a.n_phases; ++p) {
                 if (p > 0 || a.preload) { mbar_wait_dbg(act_ready, ar & 1, a.dbg, 2, p); ++ar; tc_fence_after(); }
@@ -203,7 +225,12 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 const uint32_t d_tmem = tmem + (onto ? (uint32_t)F_R2_COL : 0u);
                 const int kpt = taps > 0 ? nkb / taps : 1;
                 int tap = (taps == 9) ? 0 : 4, cc = 0;
-                uint32_t b_tap = b_lo0 + (uint32_t)((tap / 3 - 1) * W1 + (tap % 3 - 1));
+                const bool mlp = (a.ph[p].flags & PH_MLP) != 0;   // B = Z: 8 rows per K chunk (rows 8-15 alias them: SBO 0), N = 16
+                const uint32_t idesc = mlp ? idesc16 : idescN;
+                const uint32_t b_hi = mlp ? z_hi : x_hi;
+                const uint32_t kk_b = mlp ? 16u : 2u * (uint32_t)R;    // two 8-element K chunks per MMA, in 16-byte units
+                const uint32_t cc_b = mlp ? 64u : 8u * (uint32_t)R;    // eight K chunks per weight image
+                uint32_t b_tap = mlp ? z_lo0 : b_lo0 + (uint32_t)((tap / 3 - 1) * W1 + (tap % 3 - 1));
                 for (int kb = 0; kb < nkb; ++it) {
                     const uint32_t s = it % F_NSTAGE;
                     const int n = min(2, nkb - kb);
@@ -214,13 +241,13 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                     for (int h = 0; h < 2; ++h) {
                         if (h < n) {
                             const uint32_t ah = a_lo + h * (F_KB_BYTES >> 4);
-                            const uint32_t b_lo = b_tap + (uint32_t)(cc * 8 * R);
+                            const uint32_t b_lo = b_tap + (uint32_t)cc * cc_b;
                             mma_bf16_lohi_rt(d_tmem, ah, a_hi, b_lo, b_hi, idesc, (onto || kb != 0) ? 1u : 0u);
                             mma_bf16_lohi<1>(d_tmem, ah + 256u, a_hi, b_lo + kk_b, b_hi, idesc);
                             mma_bf16_lohi<1>(d_tmem, ah + 512u, a_hi, b_lo + 2u * kk_b, b_hi, idesc);
                             mma_bf16_lohi<1>(d_tmem, ah + 768u, a_hi, b_lo + 3u * kk_b, b_hi, idesc);
                             ++kb;
-                            if (++cc == kpt) { cc = 0; ++tap; b_tap = b_lo0 + (uint32_t)((tap / 3 - 1) * W1 + (tap % 3 - 1)); }
+                            if (++cc == kpt && !mlp) { cc = 0; ++tap; b_tap = b_lo0 + (uint32_t)((tap / 3 - 1) * W1 + (tap % 3 - 1)); }
                         }
                     }
                     mma_commit(&empty[s]);
@@ -276,6 +303,9 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                     const float bias = row_ok ? reinterpret_cast<const float*>(a.blob + ph.bias_off)[ch] : 0.f;
                     float* dst0 = a.red[head] + (long)rr * HW;
                     const long gstride = (long)a.red_rows[head] * HW;
+                    // in-kernel heads: Z[k / 8][game][k % 8] bf16, k = head offset + row * HW + pixel (channel-major flatten)
+                    const int zk0 = (ch < ph.red_n0 ? ph.z_k0 : ph.z_k1) + rr * HW;
+                    const uint32_t zs = smem_u32(Z);
                     for (int g = hsel; g < G; g += 2) {
                         float* dst = dst0 + (long)(game0 + g) * gstride;
                         const int cbase = g * P;
@@ -286,8 +316,17 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                             tmem_ld8(t_lane + cbase + c0, v);
                             tmem_ld_wait();
 #pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                if (pix[j] >= 0 && row_ok) dst[pix[j]] = __uint_as_float(v[j]) + bias;
+                            for (int j = 0; j < 8; ++j) {
+                                if (pix[j] >= 0 && row_ok) {
+                                    const float y = __uint_as_float(v[j]) + bias;
+                                    if (a.z_bytes) {
+                                        const int k = zk0 + pix[j];
+                                        sts_u16(zs + (uint32_t)((k >> 3) * 128 + g * 16 + (k & 7) * 2), __bfloat16_as_ushort(__float2bfloat16(y)));
+                                    } else {
+                                        dst[pix[j]] = y;
+                                    }
+                                }
+                            }
                         }
                     }
                 }
@@ -336,7 +375,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 }
                 tmem_st_wait();
             }
-            if (!(flags & (PH_RED | PH_NORM))) {
+            if (!(flags & (PH_RED | PH_NORM | PH_MLP))) {
                 const uint32_t src_col = (flags & PH_ACC_R2) ? (uint32_t)F_R2_COL : 0u;
                 const float bias = (ph.bias_off >= 0 && ch_ok) ? reinterpret_cast<const float*>(a.blob + ph.bias_off)[ch] : 0.f;
                 const bool relu = (flags & PH_RELU) != 0, stash = (flags & PH_STASH) != 0, wx = (flags & PH_WRITE_X) != 0 && ch_ok;
@@ -393,10 +432,86 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 }
                 if (stash) tmem_st_wait();
             }
-            fence_proxy_async_smem();   // generic-proxy stores into X -> visible to the tensor core's operand reads
+            if (flags & PH_MLP) {
+                // first MLP layer came off the tensor core: lane = stacked hidden unit, column = game.  bias + ReLU -> Hs
+                if (hsel == 0) {
+                    uint32_t v[8];
+                    tmem_ld8(t_lane, v);
+                    tmem_ld_wait();
+                    if (ch < ph.red_n0 + ph.red_n1) {
+                        const HeadTail& hd = a.head[ch < ph.red_n0 ? ph.red_head0 : ph.red_head1];
+                        const float b0 = reinterpret_cast<const float*>(a.blob + ph.bias_off)[ch];
+                        const bool relu0 = hd.n_layers > 1;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float y = __uint_as_float(v[j]) + b0;
+                            if (relu0) y = fmaxf(y, 0.f);
+                            Hs[j * 128 + ch] = y;
+                        }
+                    }
+                }
+            }
+            fence_proxy_async_smem();   // generic-proxy stores into X / Z -> visible to the tensor core's operand reads
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(act_ready);
+            if (flags & PH_MLP) {
+                // remaining layers (model_layers.cpp:46-65) and the output transform on CUDA cores, overlapped with the next
+                // phase's MMAs: policy softmax (vprnet.cpp:118-119,178-179) / ValueEncoder::decode (util.cpp:80-87)
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                const int et = tid - 64;
+                const int nh = ph.red_n1 > 0 ? 2 : 1;
+                float* cur = Hs;
+                float* nxt = Hs + 8 * 128;
+                const int n_layers = a.head[ph.red_head0].n_layers;
+                for (int l = 1; l < n_layers; ++l) {
+                    for (int hh = 0; hh < nh; ++hh) {
+                        const HeadTail& hd = a.head[hh ? ph.red_head1 : ph.red_head0];
+                        const int nin = hd.sizes[l], nout = hd.sizes[l + 1];
+                        const int ibase = hh ? a.head[ph.red_head0].sizes[l] : 0, obase = hh ? a.head[ph.red_head0].sizes[l + 1] : 0;
+                        const float* __restrict__ Wl = hd.W[l];
+                        for (int i = et; i < G * nout; i += 256) {
+                            const int g = i / nout, o = i - g * nout;
+                            const float* wr = Wl + (long)o * nin;
+                            const float* xr = cur + g * 128 + ibase;
+                            float acc = hd.b[l][o];
+#pragma unroll 8
+                            for (int k = 0; k < nin; ++k) acc += wr[k] * xr[k];
+                            if (l < n_layers - 1) acc = fmaxf(acc, 0.f);
+                            nxt[g * 128 + obase + o] = acc;
+                        }
+                    }
+                    asm volatile("bar.sync 1, 256;" ::: "memory");
+                    float* t = cur; cur = nxt; nxt = t;
+                }
+                if (et < G * nh) {
+                    const int g = et / nh, hh = et - g * nh;
+                    const HeadTail& hd = a.head[hh ? ph.red_head1 : ph.red_head0];
+                    const int n = hd.sizes[n_layers];
+                    const float* lg = cur + g * 128 + (hh ? a.head[ph.red_head0].sizes[n_layers] : 0);
+                    float mx = lg[0];
+                    for (int i = 1; i < n; ++i) mx = fmaxf(mx, lg[i]);
+                    float sum = 0.f;
+                    for (int i = 0; i < n; ++i) sum += expf(lg[i] - mx);
+                    const long b = game0 + g;
+                    if (hd.out_kind == 0) {
+                        for (int i = 0; i < n; ++i) hd.out[b * hd.out_stride + i] = (double)(expf(lg[i] - mx) / sum);
+                    } else {
+                        float ev = 0.f;
+                        for (int i = 0; i < n; ++i) ev += (float)i * (expf(lg[i] - mx) / sum);
+                        float v = ev * hd.step + hd.min_value;
+                        if (hd.contractive) {
+                            const float eps = 0.001f;
+                            const float sg = (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f);
+                            const float inner = sqrtf(1.f + (4.f * eps) * (fabsf(v) + 1.f + eps)) - 1.f;
+                            const float qq = inner / (2.f * eps);
+                            v = sg * (qq * qq - 1.f);
+                        }
+                        hd.out[b * hd.out_stride] = (double)v;
+                    }
+                }
+                asm volatile("bar.sync 1, 256;" ::: "memory");   // Hs is free again
+            }
             if (flags & PH_NORM) {
                 // child hidden state -> node pool, straight from X (bf16, already normalised): 16-byte coalesced stores,
                 // overlapped with the next phase's MMAs (which only read X)
@@ -439,6 +554,10 @@ struct MlpHead {
 };
 struct MlpArgs { MlpHead h[3]; int n_heads, B, mg; };
 
+constexpr int MLP_KT = 32;    // K tile of the first layer
+
+// One CTA = mg (<= 16) games of one head.  First layer (the only sizeable one: n0 = red*HW inputs) as a shared-memory
+// tiled SGEMM: x tile [mg][KT] and transposed-weight tile [KT][n1] staged per K step, thread = (output j, 4 games).
 __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_constant__ MlpArgs a) {
     extern __shared__ float msm[];
     const MlpHead& hd = a.h[blockIdx.y];
@@ -446,33 +565,52 @@ __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_con
     const int b0 = blockIdx.x * a.mg;
     const int nb = min(a.mg, a.B - b0);
     const int n0 = hd.sizes[0], n1 = hd.sizes[1];
-    float* xs = msm;                     // [mg][n0]
-    float* bufA = xs + a.mg * n0;        // [mg][256]
-    float* bufB = bufA + a.mg * 256;     // [mg][256]
-    for (int i = tid; i < nb * n0; i += MLP_THREADS) xs[i] = hd.x[(long)b0 * n0 + i];
-    __syncthreads();
-    // layer 0: thread <-> (output j, group of games); weights read once per CTA, coalesced over j
+    float* bufA = msm;                    // [mg][256]
+    float* bufB = bufA + a.mg * 256;      // [mg][256]
+    float* xs = bufB + a.mg * 256;        // [16][KT + 4]
+    float* ws = xs + 16 * (MLP_KT + 4);   // [KT][n1]
     {
-        const int groups = MLP_THREADS / n1;           // n1 <= 256
-        const int j = tid % n1, gq = tid / n1;
-        if (gq < groups) {
-            for (int gb = gq * 4; gb < nb; gb += groups * 4) {
-                float acc[4] = {0.f, 0.f, 0.f, 0.f};
-                const float* x0 = xs + gb * n0;
-                const int cnt = min(4, nb - gb);
-#pragma unroll 8
-                for (int i = 0; i < n0; ++i) {
-                    const float w = hd.w0t[(long)i * n1 + j];
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) acc[k] += w * x0[(k < cnt ? k : 0) * n0 + i];
+        const int groups = MLP_THREADS / 64;                 // 4 groups of 64 threads: group <-> 4 games
+        const int tx = tid & 63, ty = tid >> 6;
+        for (int j0 = 0; j0 < n1; j0 += 64) {
+            const int j = j0 + tx;
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            for (int k0 = 0; k0 < n0; k0 += MLP_KT) {
+                const int kt = min(MLP_KT, n0 - k0);
+                __syncthreads();
+                for (int i = tid; i < 16 * MLP_KT; i += MLP_THREADS) {
+                    const int g = i / MLP_KT, k = i - g * MLP_KT;
+                    xs[g * (MLP_KT + 4) + k] = (g < nb && k < kt) ? hd.x[(long)(b0 + g) * n0 + k0 + k] : 0.f;
                 }
-                for (int k = 0; k < cnt; ++k) {
-                    float v = acc[k] + hd.b[0][j];
-                    if (hd.n_layers > 1) v = fmaxf(v, 0.f);
-                    bufA[(gb + k) * 256 + j] = v;
+                for (int i = tid; i < MLP_KT * 64; i += MLP_THREADS) {
+                    const int k = i >> 6, jj = i & 63;
+                    ws[i] = (k < kt && j0 + jj < n1) ? hd.w0t[(long)(k0 + k) * n1 + j0 + jj] : 0.f;
+                }
+                __syncthreads();
+                const float* xr = xs + (ty * 4) * (MLP_KT + 4);
+#pragma unroll
+                for (int k = 0; k < MLP_KT; k += 4) {
+                    const float w0 = ws[(k + 0) * 64 + tx], w1 = ws[(k + 1) * 64 + tx], w2 = ws[(k + 2) * 64 + tx], w3 = ws[(k + 3) * 64 + tx];
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        const float4 x = *reinterpret_cast<const float4*>(xr + g * (MLP_KT + 4) + k);
+                        acc[g] += w0 * x.x + w1 * x.y + w2 * x.z + w3 * x.w;
+                    }
+                }
+            }
+            if (j < n1) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const int gg = ty * 4 + g;
+                    if (gg < nb) {
+                        float v = acc[g] + hd.b[0][j];
+                        if (hd.n_layers > 1) v = fmaxf(v, 0.f);
+                        bufA[gg * 256 + j] = v;
+                    }
                 }
             }
         }
+        (void)groups;
     }
     __syncthreads();
     float* cur = bufA; float* nxt = bufB;

@@ -33,8 +33,10 @@ namespace fused {
 using bf16 = __nv_bfloat16;
 using namespace umma;
 
-constexpr int F_THREADS = 320;        // warp 0: weight producer, warp 1: MMA issuer + TMEM owner, warps 2-9: epilogue
-constexpr int F_EPI_WARPS = 8;
+constexpr int F_EPI_WARPS = 8;        // 2 per TMEM lane quarter (16 measured no faster: the epilogue is issue-bound); a warp owns games g = e (mod 2)
+constexpr int F_EPI_THREADS = 32 * F_EPI_WARPS;
+constexpr int F_EPI_SPLIT = F_EPI_WARPS / 4;
+constexpr int F_THREADS = 64 + F_EPI_THREADS;   // warp 0: weight producer, warp 1: MMA issuer + TMEM owner, the rest: epilogue
 constexpr int F_NSTAGE = 4;                   // ring slots of two 64-K weight images each
 constexpr int F_KB_BYTES = 64 * 128 * 2;      // one weight image: 64 K x 128 cout, bf16 (16 KB)
 constexpr int F_STAGE_BYTES = 2 * F_KB_BYTES; // a ring slot = 128 K: halves the issuer's wait/commit overhead per MMA
@@ -119,6 +121,38 @@ __device__ __forceinline__ uint4 lds_v4u(uint32_t addr) {
 }
 __device__ __forceinline__ void lds_v4(uint32_t addr, int* p) {
     asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(p[0]), "=r"(p[1]), "=r"(p[2]), "=r"(p[3]) : "r"(addr) : "memory");
+}
+
+// Two adjacent accumulator columns (rows J, J+1 of the chunk) of one lane: + bias, optional ReLU, one packed bf16x2
+// conversion, predicated 2-byte stores into X (bit J / J+1 of m = the row is a real pixel).  Hand-scheduled PTX: the
+// epilogue is instruction-issue bound (measured: 16 warps no faster than 8), so instructions per element is the metric.
+template <int J, bool RELU>
+__device__ __forceinline__ void epi_pair(uint32_t& v0, uint32_t& v1, float bias, uint32_t m, uint32_t xa) {
+    float y0 = __uint_as_float(v0) + bias, y1 = __uint_as_float(v1) + bias;
+    if (RELU) { y0 = fmaxf(y0, 0.f); y1 = fmaxf(y1, 0.f); }
+    v0 = __float_as_uint(y0); v1 = __float_as_uint(y1);
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 pk, t0, t1;\n\t"
+        ".reg .b16 lo, hi;\n\t"
+        ".reg .pred p0, p1;\n\t"
+        "cvt.rn.bf16x2.f32 pk, %1, %0;\n\t"
+        "mov.b32 {lo, hi}, pk;\n\t"
+        "and.b32 t0, %2, %4;\n\t"
+        "and.b32 t1, %2, %5;\n\t"
+        "setp.ne.u32 p0, t0, 0;\n\t"
+        "setp.ne.u32 p1, t1, 0;\n\t"
+        "@p0 st.shared.u16 [%3 + %6], lo;\n\t"
+        "@p1 st.shared.u16 [%3 + %7], hi;\n\t"
+        "}" ::"f"(y0), "f"(y1), "r"(m), "r"(xa), "n"(1u << J), "n"(2u << J), "n"(J * 16), "n"(J * 16 + 16)
+        : "memory");
+}
+template <bool RELU>
+__device__ __forceinline__ void epi_store16(uint32_t* v, float bias, uint32_t m, uint32_t xa) {
+    epi_pair<0, RELU>(v[0], v[1], bias, m, xa);   epi_pair<2, RELU>(v[2], v[3], bias, m, xa);
+    epi_pair<4, RELU>(v[4], v[5], bias, m, xa);   epi_pair<6, RELU>(v[6], v[7], bias, m, xa);
+    epi_pair<8, RELU>(v[8], v[9], bias, m, xa);   epi_pair<10, RELU>(v[10], v[11], bias, m, xa);
+    epi_pair<12, RELU>(v[12], v[13], bias, m, xa); epi_pair<14, RELU>(v[14], v[15], bias, m, xa);
 }
 
 __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_constant__ FusedArgs a) {
@@ -261,14 +295,14 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
         // Every TMEM access below is a warp-collective: all control flow around it is warp-uniform, lanes are only
         // predicated on their stores.  The pixel map of a chunk is fetched BEFORE its stores (two 16-byte shared loads),
         // so the eight bf16 stores of a chunk issue back to back instead of alternating with dependent table look-ups.
-        const int q = warp & 3, hsel = (warp - 2) >> 2;
+        const int q = warp & 3, hsel = (warp - 2) >> 2;   // hsel in [0, F_EPI_SPLIT)
         const int ch = 32 * q + lane;
         const bool ch_ok = ch < C;
         const uint32_t t_lane = tmem + ((uint32_t)(32 * q) << 16);
         const uint32_t xs = smem_u32(X) + (uint32_t)(((ch >> 3) * R + HALO) * 16 + (ch & 7) * 2);   // + row * 16
         const uint32_t pt = smem_u32(pixtab), pm = smem_u32(pixmask);
         if (a.preload) {   // the chain starts with a residual block: its skip input = the chain input, fp32 into R2
-            for (int g = hsel; g < G; g += 2) {
+            for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                 const int cbase = g * P;
                 for (int c0 = 0; c0 < P; c0 += 8) {
                     int pix[8];
@@ -291,6 +325,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
         for (int p = 0; p < a.n_phases; ++p) {
             const Phase& ph = a.ph[p];
             const int flags = ph.flags;
+            // the per-channel bias is fetched BEFORE waiting for the accumulator: its L2 latency hides behind the MMAs
+            const float bias_pf = (ph.bias_off >= 0) ? __ldg(reinterpret_cast<const float*>(a.blob + ph.bias_off) + ch) : 0.f;
             mbar_wait_dbg(accum_full, p & 1, a.dbg, 4, p);
             tc_fence_after();
             if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 2] = clock64();
@@ -300,13 +336,13 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                     const bool row_ok = ch < nred;
                     const int head = ch < ph.red_n0 ? ph.red_head0 : ph.red_head1;
                     const int rr = ch < ph.red_n0 ? ch : ch - ph.red_n0;
-                    const float bias = row_ok ? reinterpret_cast<const float*>(a.blob + ph.bias_off)[ch] : 0.f;
+                    const float bias = row_ok ? bias_pf : 0.f;
                     float* dst0 = a.red[head] + (long)rr * HW;
                     const long gstride = (long)a.red_rows[head] * HW;
                     // in-kernel heads: Z[k / 8][game][k % 8] bf16, k = head offset + row * HW + pixel (channel-major flatten)
                     const int zk0 = (ch < ph.red_n0 ? ph.z_k0 : ph.z_k1) + rr * HW;
                     const uint32_t zs = smem_u32(Z);
-                    for (int g = hsel; g < G; g += 2) {
+                    for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                         float* dst = dst0 + (long)(game0 + g) * gstride;
                         const int cbase = g * P;
                         for (int c0 = 0; c0 < P; c0 += 8) {
@@ -333,7 +369,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             }
             if (flags & PH_NORM) {
                 // normalize_hidden_state (models.cpp:16-26): a thread owns one channel, its columns are the pixels
-                for (int g = hsel; g < G; g += 2) {
+                for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                     const int cbase = g * P;
                     float mn = 3.402823466e38f, mx = -3.402823466e38f;
                     if (a.normalize) {
@@ -377,11 +413,11 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             }
             if (!(flags & (PH_RED | PH_NORM | PH_MLP))) {
                 const uint32_t src_col = (flags & PH_ACC_R2) ? (uint32_t)F_R2_COL : 0u;
-                const float bias = (ph.bias_off >= 0 && ch_ok) ? reinterpret_cast<const float*>(a.blob + ph.bias_off)[ch] : 0.f;
+                const float bias = ch_ok ? bias_pf : 0.f;
                 const bool relu = (flags & PH_RELU) != 0, stash = (flags & PH_STASH) != 0, wx = (flags & PH_WRITE_X) != 0 && ch_ok;
                 if (flags & PH_TABLE) {   // dynamics head: + per-action table (needs the pixel index: 8-column chunks)
                     const float* table = reinterpret_cast<const float*>(a.blob + ph.table_off);
-                    for (int g = hsel; g < G; g += 2) {
+                    for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                         const int cbase = g * P;
                         const float* tg = ch_ok ? table + (long)g_act[g] * HW * C + ch : nullptr;
                         for (int c0 = 0; c0 < P; c0 += 8) {
@@ -404,7 +440,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                         }
                     }
                 } else {
-                    for (int g = hsel; g < G; g += 2) {
+                    for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                         const int cbase = g * P;
                         for (int c0 = 0; c0 < P; c0 += 32) {
                             const bool two = P - c0 > 16;
@@ -413,15 +449,10 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                             if (two) tmem_ld16(t_lane + src_col + cbase + c0 + 16, v + 16);
                             const uint32_t m = lds_u32(pm + (c0 >> 5) * 4);
                             tmem_ld_wait();
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) {
-                                if (j < 16 || two) {
-                                    float y = __uint_as_float(v[j]) + bias;
-                                    if (relu) y = fmaxf(y, 0.f);
-                                    v[j] = __float_as_uint(y);
-                                    if (wx && ((m >> j) & 1u)) sts_u16(xs + (uint32_t)(cbase + c0 + j) * 16, __bfloat16_as_ushort(__float2bfloat16(y)));
-                                }
-                            }
+                            const uint32_t mw = wx ? m : 0u;
+                            const uint32_t xa = xs + (uint32_t)(cbase + c0) * 16;
+                            if (relu) { epi_store16<true>(v, bias, mw, xa); if (two) epi_store16<true>(v + 16, bias, mw >> 16, xa + 256); }
+                            else { epi_store16<false>(v, bias, mw, xa); if (two) epi_store16<false>(v + 16, bias, mw >> 16, xa + 256); }
                             if (stash) {
 #pragma unroll
                                 for (int k = 0; k < 4; ++k)
@@ -440,7 +471,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                     tmem_ld_wait();
                     if (ch < ph.red_n0 + ph.red_n1) {
                         const HeadTail& hd = a.head[ch < ph.red_n0 ? ph.red_head0 : ph.red_head1];
-                        const float b0 = reinterpret_cast<const float*>(a.blob + ph.bias_off)[ch];
+                        const float b0 = bias_pf;
                         const bool relu0 = hd.n_layers > 1;
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
@@ -458,7 +489,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             if (flags & PH_MLP) {
                 // remaining layers (model_layers.cpp:46-65) and the output transform on CUDA cores, overlapped with the next
                 // phase's MMAs: policy softmax (vprnet.cpp:118-119,178-179) / ValueEncoder::decode (util.cpp:80-87)
-                asm volatile("bar.sync 1, 256;" ::: "memory");
+                asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");
                 const int et = tid - 64;
                 const int nh = ph.red_n1 > 0 ? 2 : 1;
                 float* cur = Hs;
@@ -470,7 +501,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                         const int nin = hd.sizes[l], nout = hd.sizes[l + 1];
                         const int ibase = hh ? a.head[ph.red_head0].sizes[l] : 0, obase = hh ? a.head[ph.red_head0].sizes[l + 1] : 0;
                         const float* __restrict__ Wl = hd.W[l];
-                        for (int i = et; i < G * nout; i += 256) {
+                        for (int i = et; i < G * nout; i += F_EPI_THREADS) {
                             const int g = i / nout, o = i - g * nout;
                             const float* wr = Wl + (long)o * nin;
                             const float* xr = cur + g * 128 + ibase;
@@ -481,7 +512,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                             nxt[g * 128 + obase + o] = acc;
                         }
                     }
-                    asm volatile("bar.sync 1, 256;" ::: "memory");
+                    asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");
                     float* t = cur; cur = nxt; nxt = t;
                 }
                 if (et < G * nh) {
@@ -510,14 +541,14 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                         hd.out[b * hd.out_stride] = (double)v;
                     }
                 }
-                asm volatile("bar.sync 1, 256;" ::: "memory");   // Hs is free again
+                asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");   // Hs is free again
             }
             if (flags & PH_NORM) {
                 // child hidden state -> node pool, straight from X (bf16, already normalised): 16-byte coalesced stores,
                 // overlapped with the next phase's MMAs (which only read X)
-                asm volatile("bar.sync 1, 256;" ::: "memory");   // every epilogue warp has finished writing X
+                asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");   // every epilogue warp has finished writing X
                 const int et = tid - 64;
-                const int kc = et % KC, rsub = et / KC, rstep = 256 / KC;   // a thread keeps its 8-channel chunk; rows stride
+                const int kc = et % KC, rsub = et / KC, rstep = F_EPI_THREADS / KC;   // a thread keeps its 8-channel chunk; rows stride
                 const uint32_t xk = smem_u32(X) + (uint32_t)((kc * R + HALO) * 16);
                 for (int g = 0; g < G; ++g) {
                     bf16* pg = a.pool + (long)g_out[g] * a.pool_stride + kc * 8;
@@ -526,7 +557,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                         if (pix >= 0) *reinterpret_cast<uint4*>(pg + (long)pix * C) = lds_v4u(xk + (uint32_t)(g * P + r) * 16);
                     }
                 }
-                asm volatile("bar.sync 1, 256;" ::: "memory");   // nobody overwrites X (next epilogue) before the copy is done
+                asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");   // nobody overwrites X (next epilogue) before the copy is done
             }
             if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();
         }

@@ -354,10 +354,12 @@ protected:
         int row0 = 0;
         for (int h = 0; h < nh; ++h) {
             for (int r = 0; r < hh[h]->red; ++r) {
-                bias[row0 + r] = hh[h]->b1[r];
+                const int sr = row0 + r;                         // stacked row
+                const int lane = sr;
+                bias[sr] = hh[h]->b1[r];
                 for (int k = 0; k < C; ++k) {
                     const int cc = k / KB, kc = (k % KB) / 8, e = k % 8;
-                    dst[(((size_t)cc * 8 + kc) * UM + row0 + r) * 8 + e] = __float2bfloat16(hh[h]->w1[(size_t)r * C + k]);
+                    dst[(((size_t)cc * 8 + kc) * UM + lane) * 8 + e] = __float2bfloat16(hh[h]->w1[(size_t)r * C + k]);
                 }
             }
             row0 += hh[h]->red;
@@ -371,26 +373,32 @@ protected:
 
     // first MLP layer of 1 or 2 heads as tensor-core weight images: rows = stacked hidden units, K = concatenated head
     // inputs (block structure: a head's rows are zero outside its own K range), K padded to a multiple of 64
-    size_t pack_mlp0(const HeadHost* const* hh, int nh, std::vector<uint8_t>* extra, size_t* bias_rel, int* nkb_out) {
-        int ktot = 0;
-        for (int h = 0; h < nh; ++h) ktot += hh[h]->sizes[0];
+    size_t pack_mlp0(const HeadHost* const* hh, int nh, int rp, int P, int H, int W, std::vector<uint8_t>* extra, size_t* bias_rel, int* nkb_out) {
+        // K order of Z: k = padded pixel row c * rp + reduced channel r (tower_fused.cuh, PH_RED); the reference's flatten
+        // index is r * HW + pixel (models.cpp:114,161-162).  Pad rows and channels >= red get zero weights.
+        const int ktot = P * rp;
         const int nkb = (ktot + KB - 1) / KB;
         while (extra->size() % 128) extra->push_back(0);
         const size_t off = extra->size();
         extra->resize(off + (size_t)nkb * STAGE_BYTES, 0);
         bf16* dst = reinterpret_cast<bf16*>(extra->data() + off);
         std::vector<float> bias(128, 0.f);
-        int row0 = 0, k0 = 0;
+        int row0 = 0;
         for (int h = 0; h < nh; ++h) {
-            const int n0 = hh[h]->sizes[0], n1 = hh[h]->sizes[1];
+            const int n0 = hh[h]->sizes[0], n1 = hh[h]->sizes[1], red = hh[h]->red, hw = hh[h]->hw;
             for (int j = 0; j < n1; ++j) {
                 bias[row0 + j] = hh[h]->b[0][j];
-                for (int i = 0; i < n0; ++i) {
-                    const int k = k0 + i, cc = k / KB, kc = (k % KB) / 8, e = k % 8;
-                    dst[(((size_t)cc * 8 + kc) * UM + row0 + j) * 8 + e] = __float2bfloat16(hh[h]->W[0][(size_t)j * n0 + i]);
+                for (int c = 0; c < P; ++c) {
+                    const int yy = c / (W + 1), xx = c % (W + 1);
+                    if (yy < 1 || yy > H || xx >= W) continue;
+                    const int pix = (yy - 1) * W + xx;
+                    for (int r = 0; r < red; ++r) {
+                        const int k = c * rp + r, cc = k / KB, kc = (k % KB) / 8, e = k % 8;
+                        dst[(((size_t)cc * 8 + kc) * UM + row0 + j) * 8 + e] = __float2bfloat16(hh[h]->W[0][(size_t)j * n0 + (size_t)r * hw + pix]);
+                    }
                 }
             }
-            row0 += n1; k0 += n0;
+            row0 += n1;
         }
         *bias_rel = extra->size();
         const uint8_t* bp = reinterpret_cast<const uint8_t*>(bias.data());
@@ -431,15 +439,15 @@ protected:
         if (fused::fused_smem_bytes(x_bytes, 0) > 227 * 1024) return MZB_OK;
         // in-kernel head MLPs (first layer on the tensor core): needs <= 8 games per tile, stacked widths <= 128
         const HeadHost& hR = plan.reward_head; const HeadHost& hP = plan.policy_head; const HeadHost& hV = plan.value_head;
-        int z_bytes = 0;
+        int z_bytes = 0, z_rp = 0;
         {
             bool ok = gmax <= 8 && hP.W.size() == hV.W.size() && hR.sizes[1] <= UM;
             for (size_t l = 1; ok && l < hP.sizes.size(); ++l) ok = hP.sizes[l] + hV.sizes[l] <= UM;
             for (size_t l = 1; ok && l < hR.sizes.size(); ++l) ok = hR.sizes[l] <= UM;
             static const bool no_z = getenv("MZB_NO_INKERNEL_MLP") != nullptr;
             if (ok && !no_z) {
-                const int kr = (hR.sizes[0] + KB - 1) / KB * KB, kpv = (hP.sizes[0] + hV.sizes[0] + KB - 1) / KB * KB;
-                z_bytes = std::max(kr, kpv) / 8 * 128;
+                z_rp = (std::max(hR.red, std::max(hP.red, hV.red)) + 7) / 8 * 8;
+                z_bytes = (P * z_rp + KB - 1) / KB * KB / 8 * 256;   // [K / 8][16 rows][16 B]
                 if (fused::fused_smem_bytes(x_bytes, z_bytes) > 227 * 1024) z_bytes = 0;
             }
         }
@@ -460,12 +468,12 @@ protected:
         if (z_bytes) {
             const HeadHost* r1[1] = {&hR};
             const HeadHost* pv2[2] = {&hP, &hV};
-            mlp0_rel_[0] = pack_mlp0(r1, 1, extra, &mlp0_bias_rel_[0], &mlp0_nkb_[0]);
-            mlp0_rel_[1] = pack_mlp0(pv2, 2, extra, &mlp0_bias_rel_[1], &mlp0_nkb_[1]);
+            mlp0_rel_[0] = pack_mlp0(r1, 1, z_rp, P, H, W, extra, &mlp0_bias_rel_[0], &mlp0_nkb_[0]);
+            mlp0_rel_[1] = pack_mlp0(pv2, 2, z_rp, P, H, W, extra, &mlp0_bias_rel_[1], &mlp0_nkb_[1]);
         }
         fused::FusedArgs base;
         memset(&base, 0, sizeof(base));
-        base.z_bytes = z_bytes;
+        base.z_bytes = z_bytes; base.z_rp = z_rp;
         base.C = C; base.H = H; base.W = W; base.P = P; base.HALO = halo; base.R = R; base.HW = H * W; base.x_bytes = x_bytes;
         base.normalize = plan.normalize ? 1 : 0;
         base.red_rows[0] = plan.reward_head.red; base.red_rows[1] = plan.policy_head.red; base.red_rows[2] = plan.value_head.red;

@@ -93,6 +93,7 @@ struct FusedArgs {
     int* dbg;                                                 // host-mapped diagnostics (barrier time-outs), may be null
     long long* tim;                                           // optional [tile][phase][4] clocks: mma start, mma issued, accum full, epilogue done
     int z_bytes;                                              // > 0: head inputs stay in shared memory (Z) and the MLPs run in-kernel
+    int z_rp;                                                 // channels per padded pixel row in Z's K order (multiple of 8)
     HeadTail head[3];
     Phase ph[F_MAX_PHASES];
 };
@@ -247,7 +248,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             // descriptors: everything but the 14-bit start-address field is constant, so the loop only adds to the low words
             const uint64_t da0 = smem_desc_kmajor_noswizzle(smem_u32(stages), 128 * 16, 128);
             const uint64_t db0 = smem_desc_kmajor_noswizzle(smem_u32(X) + (uint32_t)HALO * 16u, (uint32_t)R * 16u, 128);
-            const uint64_t dz0 = smem_desc_kmajor_noswizzle(smem_u32(Z), 128, 0);
+            const uint64_t dz0 = smem_desc_kmajor_noswizzle(smem_u32(Z), 256, 128);
             const uint32_t a_hi = (uint32_t)(da0 >> 32), x_hi = (uint32_t)(db0 >> 32), z_hi = (uint32_t)(dz0 >> 32);
             const uint32_t a_lo0 = (uint32_t)da0, b_lo0 = (uint32_t)db0, z_lo0 = (uint32_t)dz0;
             uint32_t it = 0, ar = 0;
@@ -259,11 +260,11 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 const uint32_t d_tmem = tmem + (onto ? (uint32_t)F_R2_COL : 0u);
                 const int kpt = taps > 0 ? nkb / taps : 1;
                 int tap = (taps == 9) ? 0 : 4, cc = 0;
-                const bool mlp = (a.ph[p].flags & PH_MLP) != 0;   // B = Z: 8 rows per K chunk (rows 8-15 alias them: SBO 0), N = 16
+                const bool mlp = (a.ph[p].flags & PH_MLP) != 0;   // B = Z: 16 rows per K chunk (head0's games, head1's games), N = 16
                 const uint32_t idesc = mlp ? idesc16 : idescN;
                 const uint32_t b_hi = mlp ? z_hi : x_hi;
-                const uint32_t kk_b = mlp ? 16u : 2u * (uint32_t)R;    // two 8-element K chunks per MMA, in 16-byte units
-                const uint32_t cc_b = mlp ? 64u : 8u * (uint32_t)R;    // eight K chunks per weight image
+                const uint32_t kk_b = mlp ? 32u : 2u * (uint32_t)R;    // two 8-element K chunks per MMA, in 16-byte units
+                const uint32_t cc_b = mlp ? 128u : 8u * (uint32_t)R;    // eight K chunks per weight image
                 uint32_t b_tap = mlp ? z_lo0 : b_lo0 + (uint32_t)((tap / 3 - 1) * W1 + (tap % 3 - 1));
                 for (int kb = 0; kb < nkb; ++it) {
                     const uint32_t s = it % F_NSTAGE;
@@ -331,37 +332,48 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             tc_fence_after();
             if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 2] = clock64();
             if (flags & PH_RED) {
+                // 1x1 head convolution: lane = stacked reduced channel (head0's rows, then head1's), column = padded pixel row
                 const int nred = ph.red_n0 + ph.red_n1;
                 if (32 * q < nred) {   // warp-uniform; lanes beyond nred only skip the stores
                     const bool row_ok = ch < nred;
-                    const int head = ch < ph.red_n0 ? ph.red_head0 : ph.red_head1;
-                    const int rr = ch < ph.red_n0 ? ch : ch - ph.red_n0;
+                    const bool second = ch >= ph.red_n0;
+                    const int rr = second ? ch - ph.red_n0 : ch;
                     const float bias = row_ok ? bias_pf : 0.f;
-                    float* dst0 = a.red[head] + (long)rr * HW;
-                    const long gstride = (long)a.red_rows[head] * HW;
-                    // in-kernel heads: Z[k / 8][game][k % 8] bf16, k = head offset + row * HW + pixel (channel-major flatten)
-                    const int zk0 = (ch < ph.red_n0 ? ph.z_k0 : ph.z_k1) + rr * HW;
-                    const uint32_t zs = smem_u32(Z);
-                    for (int g = hsel; g < G; g += F_EPI_SPLIT) {
-                        float* dst = dst0 + (long)(game0 + g) * gstride;
-                        const int cbase = g * P;
-                        for (int c0 = 0; c0 < P; c0 += 8) {
-                            int pix[8];
-                            lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
-                            uint32_t v[8];
-                            tmem_ld8(t_lane + cbase + c0, v);
-                            tmem_ld_wait();
+                    if (a.z_bytes) {
+                        // in-kernel heads.  Z is the B operand of the first MLP layer: [K / 8][16 rows][8] bf16, rows 0-7 = head0's
+                        // games, rows 8-15 = head1's; K index = column * z_rp + channel (pad columns are stored too: their
+                        // weights are zero), so a lane's stores are an affine function of the column — no pixel look-up
+                        const uint32_t zl = smem_u32(Z) + (second ? 128u : 0u) + (uint32_t)((rr >> 3) * 256 + (rr & 7) * 2);
+                        const uint32_t cstride = (uint32_t)(a.z_rp >> 3) * 256u;
+                        for (int g = hsel; g < G; g += F_EPI_SPLIT) {
+                            const int cbase = g * P;
+                            for (int c0 = 0; c0 < P; c0 += 16) {
+                                uint32_t v[16];
+                                tmem_ld16(t_lane + cbase + c0, v);
+                                tmem_ld_wait();
+                                const uint32_t za = zl + (uint32_t)g * 16u + (uint32_t)c0 * cstride;
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                if (pix[j] >= 0 && row_ok) {
-                                    const float y = __uint_as_float(v[j]) + bias;
-                                    if (a.z_bytes) {
-                                        const int k = zk0 + pix[j];
-                                        sts_u16(zs + (uint32_t)((k >> 3) * 128 + g * 16 + (k & 7) * 2), __bfloat16_as_ushort(__float2bfloat16(y)));
-                                    } else {
-                                        dst[pix[j]] = y;
-                                    }
-                                }
+                                for (int j = 0; j < 16; ++j)
+                                    if (row_ok && c0 + j < P)
+                                        sts_u16(za + (uint32_t)j * cstride, __bfloat16_as_ushort(__float2bfloat16(__uint_as_float(v[j]) + bias)));
+                            }
+                        }
+                    } else {
+                        const int head = second ? ph.red_head1 : ph.red_head0;
+                        float* dst0 = a.red[head] + (long)rr * HW;
+                        const long gstride = (long)a.red_rows[head] * HW;
+                        for (int g = hsel; g < G; g += F_EPI_SPLIT) {
+                            float* dst = dst0 + (long)(game0 + g) * gstride;
+                            const int cbase = g * P;
+                            for (int c0 = 0; c0 < P; c0 += 8) {
+                                int pix[8];
+                                lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
+                                uint32_t v[8];
+                                tmem_ld8(t_lane + cbase + c0, v);
+                                tmem_ld_wait();
+#pragma unroll
+                                for (int j = 0; j < 8; ++j)
+                                    if (pix[j] >= 0 && row_ok) dst[pix[j]] = __uint_as_float(v[j]) + bias;
                             }
                         }
                     }
@@ -466,16 +478,17 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             if (flags & PH_MLP) {
                 // first MLP layer came off the tensor core: lane = stacked hidden unit, column = game.  bias + ReLU -> Hs
                 if (hsel == 0) {
-                    uint32_t v[8];
-                    tmem_ld8(t_lane, v);
+                    uint32_t v[16];   // columns 0-7: head0's games, 8-15: head1's games (Z rows 8-15)
+                    tmem_ld16(t_lane, v);
                     tmem_ld_wait();
                     if (ch < ph.red_n0 + ph.red_n1) {
-                        const HeadTail& hd = a.head[ch < ph.red_n0 ? ph.red_head0 : ph.red_head1];
+                        const bool second = ch >= ph.red_n0;
+                        const HeadTail& hd = a.head[second ? ph.red_head1 : ph.red_head0];
                         const float b0 = bias_pf;
                         const bool relu0 = hd.n_layers > 1;
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
-                            float y = __uint_as_float(v[j]) + b0;
+                            float y = __uint_as_float(second ? v[8 + j] : v[j]) + b0;
                             if (relu0) y = fmaxf(y, 0.f);
                             Hs[j * 128 + ch] = y;
                         }
@@ -501,15 +514,26 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                         const int nin = hd.sizes[l], nout = hd.sizes[l + 1];
                         const int ibase = hh ? a.head[ph.red_head0].sizes[l] : 0, obase = hh ? a.head[ph.red_head0].sizes[l + 1] : 0;
                         const float* __restrict__ Wl = hd.W[l];
-                        for (int i = et; i < G * nout; i += F_EPI_THREADS) {
-                            const int g = i / nout, o = i - g * nout;
+                        // four threads per output: the weight rows come from L2, so the loads of a dot product must
+                        // be issued together rather than chained
+                        for (int base = 0; base < G * nout; base += F_EPI_THREADS / 4) {   // warp-uniform trip count
+                            const int i = base + (et >> 2), part = et & 3;
+                            const bool on = i < G * nout;
+                            const int g = on ? i / nout : 0, o = on ? i - g * nout : 0;
                             const float* wr = Wl + (long)o * nin;
                             const float* xr = cur + g * 128 + ibase;
-                            float acc = hd.b[l][o];
+                            float acc = 0.f;
+                            if (on) {
 #pragma unroll 8
-                            for (int k = 0; k < nin; ++k) acc += wr[k] * xr[k];
-                            if (l < n_layers - 1) acc = fmaxf(acc, 0.f);
-                            nxt[g * 128 + obase + o] = acc;
+                                for (int k = part; k < nin; k += 4) acc += __ldg(wr + k) * xr[k];
+                            }
+                            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+                            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+                            if (on && part == 0) {
+                                acc += hd.b[l][o];
+                                if (l < n_layers - 1) acc = fmaxf(acc, 0.f);
+                                nxt[g * 128 + obase + o] = acc;
+                            }
                         }
                     }
                     asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");

@@ -135,6 +135,11 @@ int mzb_search_batch(mzb_engine* e, const float* obs, const uint32_t* legal_mask
 /* Same search with observations already resident in HBM (device pointer, engine layout = row-major fp32). */
 int mzb_search_batch_device_obs(mzb_engine* e, const float* d_obs, const uint32_t* legal_mask, const int32_t* to_play,
                                 const uint8_t* add_noise, int n_trees, mzb_search_result* out);
+/* Same search for an arbitrary subset of tree slots: row i uses (and advances) the RNG stream of slot slots[i]
+ * (distinct, in [0, max_trees)).  This is what the blocking one-tree MCTS::run facade (include/mzb200_facade.hpp)
+ * batches through: actors whose games finished simply stop submitting their slot. */
+int mzb_search_batch_slots(mzb_engine* e, const float* obs, const int32_t* slots, const uint32_t* legal_mask,
+                           const int32_t* to_play, const uint8_t* add_noise, int n_trees, mzb_search_result* out);
 /* device time (CUDA events) of the last search, split as far as the engine can tell */
 typedef struct {
     float total_ms, root_ms, sim_loop_ms;

@@ -53,6 +53,7 @@ struct mzb_engine {
     bool recording = false;
     // search inputs / outputs on the device
     DevBuf d_obs, d_legal, d_to_play, d_add_noise, d_noise, d_root_slots, d_iota;
+    DevBuf d_slots, mt_rows, mt_idx_rows;   // mzb_search_batch_slots: slot list and compact RNG rows
     DevBuf r_root_value, r_depth, r_nchild, r_actions, r_visits, r_rel, r_policy;
     // SE stub
     SEDev se;

@@ -396,6 +396,15 @@ __global__ void mt_seed_kernel(uint32_t* mt, int* idx, const int* seeds, int fir
     idx[first_slot + i] = 624;
 }
 
+__global__ void mt_move_kernel(uint32_t* home, int* idx_home, uint32_t* rows, int* idx_rows, const int* slots, int n, int dir) {
+    const int i = blockIdx.x;
+    if (i >= n) return;
+    uint32_t* h = home + (long)slots[i] * 624;
+    uint32_t* r = rows + (long)i * 624;
+    for (int k = threadIdx.x; k < 624; k += blockDim.x) { if (dir == 0) r[k] = h[k]; else h[k] = r[k]; }
+    if (threadIdx.x == 0) { if (dir == 0) idx_rows[i] = idx_home[slots[i]]; else idx_home[slots[i]] = idx_rows[i]; }
+}
+
 inline unsigned warps_grid(int n_trees, int block) { return (unsigned)(((long)n_trees * 32 + block - 1) / block); }
 
 }  // namespace
@@ -415,6 +424,10 @@ void launch_se_initial(const TreeDev& td, const SEDev& se, int n_trees, const fl
 }
 void launch_se_recurrent(const TreeDev& td, const SEDev& se, int n_trees, cudaStream_t s) {
     se_recurrent_kernel<<<warps_grid(n_trees, 128), 128, 0, s>>>(td, se, n_trees);
+}
+void launch_mt_move(uint32_t* d_mt_home, int* d_idx_home, uint32_t* d_mt_rows, int* d_idx_rows, const int* d_slots, int n,
+                    int dir, cudaStream_t s) {
+    mt_move_kernel<<<n, 128, 0, s>>>(d_mt_home, d_idx_home, d_mt_rows, d_idx_rows, d_slots, n, dir);
 }
 void launch_mt_seed(uint32_t* d_mt, int* d_idx, const int* d_seeds, int first_slot, int n, cudaStream_t s) {
     mt_seed_kernel<<<(n + 127) / 128, 128, 0, s>>>(d_mt, d_idx, d_seeds, first_slot, n);

@@ -146,7 +146,7 @@ _lib = None
 
 EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_destroy", "mzb_load_weights",
            "mzb_nccl_unique_id", "mzb_nccl_init", "mzb_broadcast_weights", "mzb_weights_checksum",
-           "mzb_initial_inference", "mzb_recurrent_inference", "mzb_bench_recurrent", "mzb_search_seed",
+           "mzb_initial_inference", "mzb_recurrent_inference", "mzb_bench_recurrent", "mzb_search_seed", "mzb_search_batch_slots",
            "mzb_search_batch", "mzb_search_batch_device_obs", "mzb_last_search_timing", "mzb_search_set_recording",
            "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes"]
 
@@ -177,6 +177,8 @@ def load_library(path=None):
     lib.mzb_search_seed.argtypes = [C.c_void_p, C.c_int, C.c_int, ip]
     lib.mzb_search_batch.argtypes = [C.c_void_p, fp, C.POINTER(C.c_uint32), ip, C.POINTER(C.c_uint8), C.c_int,
                                      C.POINTER(_CSearchResult)]
+    lib.mzb_search_batch_slots.argtypes = [C.c_void_p, fp, ip, C.POINTER(C.c_uint32), ip, C.POINTER(C.c_uint8), C.c_int,
+                                           C.POINTER(_CSearchResult)]
     lib.mzb_search_batch_device_obs.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), ip,
                                                 C.POINTER(C.c_uint8), C.c_int, C.POINTER(_CSearchResult)]
     lib.mzb_last_search_timing.argtypes = [C.c_void_p, C.POINTER(_CSearchTiming)]
@@ -329,7 +331,7 @@ class Engine:
         self._check(self.lib.mzb_search_seed(self._h, first_slot, s.shape[0], _ptr(s, C.c_int32)))
 
     # T x MCTS::run (mcts.cpp:34-87)
-    def run(self, stacked_observations, legal_mask, to_play, add_exploration_noise, device_obs_ptr=None) -> MCTSReturn:
+    def run(self, stacked_observations, legal_mask, to_play, add_exploration_noise, device_obs_ptr=None, slots=None) -> MCTSReturn:
         legal = np.ascontiguousarray(legal_mask, dtype=np.uint32).reshape(-1)
         T, A = legal.shape[0], self.config.num_actions
         tp = np.ascontiguousarray(to_play, dtype=np.int32).reshape(-1)
@@ -343,7 +345,15 @@ class Engine:
                             _ptr(res.n_children, C.c_int32), _ptr(res.child_actions, C.c_int32),
                             _ptr(res.child_visits, C.c_int32), _ptr(res.children_relative_visit, C.c_double),
                             _ptr(res.emperical_policy, C.c_double))
-        if device_obs_ptr is not None:
+        if slots is not None:
+            sl = np.ascontiguousarray(slots, dtype=np.int32).reshape(-1)
+            if sl.shape[0] != T:
+                raise MzbError("slot list disagrees on the number of trees")
+            width = 1 if self.config.evaluator == EVAL_SYNTHETIC else self.shapes.initial_flat_size
+            obs = np.ascontiguousarray(stacked_observations, dtype=np.float32).reshape(T, width)
+            self._check(self.lib.mzb_search_batch_slots(self._h, _ptr(obs, C.c_float), _ptr(sl, C.c_int32), _ptr(legal, C.c_uint32),
+                                                        _ptr(tp, C.c_int32), _ptr(noise, C.c_uint8), T, C.byref(cr)))
+        elif device_obs_ptr is not None:
             self._check(self.lib.mzb_search_batch_device_obs(self._h, C.c_void_p(device_obs_ptr), _ptr(legal, C.c_uint32),
                                                              _ptr(tp, C.c_int32), _ptr(noise, C.c_uint8), T, C.byref(cr)))
         else:

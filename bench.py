@@ -42,14 +42,41 @@ def peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
 
 
+def ncu_traffic(workload, trees):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed ncu --set full
+    summary (profiles/); None when no capture exists for this workload and cohort size."""
+    p = os.path.join(ROOT, "profiles", "tower_fused_traffic.json")
+    try:
+        with open(p) as f:
+            d = json.load(f)
+        return d.get("%s_T%d" % (workload, trees), {}).get("dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md clocks line).  NVML in a
+    thread every 5 ms (a 50-simulation search lasts ~17 ms, shorter than one `nvidia-smi -lms` period); falls back to
+    the nvidia-smi loop when the NVML binding is missing."""
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    BITS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index):
-        self.index, self.samples, self.proc = index, [], None
+        self.index, self.samples, self.proc, self.nvml, self.stop_flag = index, [], None, None, False
+        self.sm, self.mx, self.reasons = [], None, set()
 
     def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -58,11 +85,29 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        n = self.nvml
+        while not self.stop_flag:
+            try:
+                self.sm.append(float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM)))
+                r = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.BITS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.005)
+
     def _read(self):
         for line in self.proc.stdout:
             self.samples.append(line.strip())
 
     def stop(self):
+        if self.nvml:
+            self.stop_flag = True
+            self.thread.join(timeout=1)
+            sm = sorted(self.sm)
+            return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=self.mx, reasons=sorted(self.reasons), samples=len(sm), source="nvml")
         if not self.proc:
             return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
         self.proc.terminate()
@@ -84,7 +129,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(n)
         sm.sort()
-        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm))
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm), source="nvidia-smi")
 
 
 def run_reference_cpu(game, seconds_target, sims):
@@ -116,7 +161,7 @@ def run_reference_cpu(game, seconds_target, sims):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c4d", choices=sorted(WORKLOADS))
@@ -259,12 +304,16 @@ def main():
     # roofline of the dominant kernels: the residual towers of recurrent_inference (tensor bound), measured live
     pk = peaks()
     frec = recurrent_flops(cfg)
-    rec_ms, rec_launches = eng.bench_recurrent(T, 5)
+    rec_passes = 50   # ~15 ms of back-to-back launches, as long as one search step: a sustained, not a burst, measurement
+    rec_ms, rec_launches = eng.bench_recurrent(T, rec_passes)
     states_per_s = T / (rec_ms / 1000.0)
     achieved_tf = frec * states_per_s / 1e12
     roofline = dict(bound="tensor", achieved=achieved_tf, peak=pk["tf_sustained"], unit="TFLOP/s",
-                    frac=achieved_tf / pk["tf_sustained"], traffic=None, peak_source=pk["source"] + " (sustained bf16)",
-                    kernel="recurrent_inference towers", flops_per_state=frec, states_per_s=states_per_s,
+                    frac=achieved_tf / pk["tf_sustained"], traffic=ncu_traffic(args.workload, T),
+                    peak_source=pk["source"] + " (sustained bf16; %d back-to-back launches)" % rec_passes,
+                    frac_of_burst_peak=achieved_tf / pk["tf_burst"],
+                    kernel="tower_fused_kernel (one launch = recurrent_inference of all trees)" if rec_launches == 1 else "recurrent_inference towers",
+                    flops_per_state=frec, flops_per_launch=frec * T, launch_ms=rec_ms, states_per_s=states_per_s,
                     launches_per_pass=rec_launches)
     if world > 1:
         t = torch.tensor([states_per_s], device="cuda", dtype=torch.float64)

@@ -327,7 +327,7 @@ protected:
         int gmax = 0;
         size_t smem = 0;
     };
-    struct TileTab { DevBuf first, count; int n_tiles = 0; };
+    struct TileTab { DevBuf first, count; std::vector<int> h_count; int n_tiles = 0; };
 
     static bool tower_fusable(const Tower& tw, bool leading_conv, int C, int H, int W) {
         size_t i = 0;
@@ -577,6 +577,8 @@ protected:
             add_conv1_phase(fa, 1, 0, C);
             add_mlp_phase(fa, 1);
         }
+        for (fused::FusedArgs* fa : {&fused_rec_.args, &fused_init_.args})
+            for (int p = 0; p < fa->n_phases; ++p) fused::derive_issue_fields(fa->ph[p], fa->R, fa->W);
         // reduced head inputs and MLP descriptors
         for (int h = 0; h < 3; ++h) MZB_CUDA(red_[h].alloc((size_t)max_batch_ * heads_[h].red * hw * sizeof(float)));
         const uint8_t* blob = reinterpret_cast<const uint8_t*>(blob_.p);
@@ -618,6 +620,7 @@ protected:
                 }
             std::unique_ptr<TileTab> tt(new TileTab());
             tt->n_tiles = (int)first.size();
+            tt->h_count = count;
             MZB_CUDA(tt->first.alloc(first.size() * sizeof(int)));
             MZB_CUDA(tt->count.alloc(count.size() * sizeof(int)));
             MZB_CUDA(cudaMemcpy(tt->first.p, first.data(), first.size() * sizeof(int), cudaMemcpyHostToDevice));
@@ -675,18 +678,32 @@ protected:
             std::vector<long long> h((size_t)tt->n_tiles * fused::F_MAX_PHASES * 4);
             MZB_CUDA(cudaMemcpy(h.data(), tim_.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
             fprintf(stderr, "[fused] %d tiles, %d phases; per phase avg cycles over tiles: wait(prev epi done -> mma start) | mma issue | mma start -> accum full | epilogue\n", tt->n_tiles, a.n_phases);
+            const int gsel = getenv("MZB_FUSED_TIMING_G") ? atoi(getenv("MZB_FUSED_TIMING_G")) : 0;   // only tiles of this many games (0 = all)
             for (int p = 0; p < a.n_phases; ++p) {
                 double issue = 0, full = 0, epi = 0, gap = 0;
+                int n = 0;
                 for (int t = 0; t < tt->n_tiles; ++t) {
+                    if (gsel && tt->h_count[t] != gsel) continue;
                     const long long* d = &h[((size_t)t * fused::F_MAX_PHASES + p) * 4];
                     issue += d[1] - d[0]; full += d[2] - d[0]; epi += d[3] - d[2];
                     if (p > 0) gap += d[0] - h[((size_t)t * fused::F_MAX_PHASES + p - 1) * 4 + 3];
+                    ++n;
                 }
-                const int n = tt->n_tiles;
+                if (n == 0) n = 1;
                 fprintf(stderr, "[fused]  phase %2d nkb %3d flags %3d: gap %7.0f | issue %7.0f | full %7.0f | epi %7.0f\n", p, a.ph[p].nkb, a.ph[p].flags, gap / n, issue / n, full / n, epi / n);
             }
-            const long long* d0 = &h[0];
-            fprintf(stderr, "[fused]  tile 0 span %lld cycles\n", h[((size_t)(a.n_phases - 1)) * 4 + 3] - d0[0]);
+            // whole-CTA view, by tile size: start -> first MMA (prologue + input load), first MMA -> last epilogue end, -> CTA end
+            double pro[fused::F_MAX_G + 1] = {0}, body[fused::F_MAX_G + 1] = {0}, tail[fused::F_MAX_G + 1] = {0};
+            int cnt[fused::F_MAX_G + 1] = {0};
+            for (int t = 0; t < tt->n_tiles; ++t) {
+                const long long* row = &h[(size_t)t * fused::F_MAX_PHASES * 4];
+                const long long* ends = row + (size_t)(fused::F_MAX_PHASES - 1) * 4;
+                const int g = tt->h_count[t];
+                pro[g] += row[0] - ends[0]; body[g] += row[(size_t)(a.n_phases - 1) * 4 + 3] - row[0]; tail[g] += ends[1] - row[(size_t)(a.n_phases - 1) * 4 + 3];
+                ++cnt[g];
+            }
+            for (int g = 1; g <= fused::F_MAX_G; ++g)
+                if (cnt[g]) fprintf(stderr, "[fused]  tiles of %d games: %d; prologue %7.0f | phases %7.0f | tail %7.0f cycles\n", g, cnt[g], pro[g] / cnt[g], body[g] / cnt[g], tail[g] / cnt[g]);
         }
         static const bool sync_debug = getenv("MZB_FUSED_SYNC") != nullptr;
         if (sync_debug) {

@@ -66,7 +66,22 @@ struct Phase {
     int red_head0, red_n0, red_head1, red_n1;   // PH_RED: rows [0,n0) -> red[head0], rows [n0, n0+n1) -> red[head1]
                                                 // PH_MLP: hidden rows [0,n0) belong to head0, [n0, n0+n1) to head1 (n1 = 0: one head)
     int z_k0, z_k1;                             // PH_RED with Z: first K index of head0 / head1 inside Z
+    // MMA issue parameters, derived on the host (derive_issue_fields) so that the issuing warp reads them as plain uniform
+    // constant-bank loads: no division, no select on the device
+    int kpt;               // K stages per tap
+    int tap_off0;          // B row offset of the first tap: -(W+2) for 3x3, 0 for 1x1 / MLP
+    uint32_t kk_b, cc_b;   // B descriptor step per MMA (16 K elements) / per K stage, in 16-byte units
+    uint32_t is_mlp, onto; // 0 / 1
 };
+inline void derive_issue_fields(Phase& ph, int R, int W) {
+    const bool mlp = (ph.flags & 128) != 0;   // PH_MLP
+    ph.kpt = ph.taps > 0 && ph.nkb > 0 ? ph.nkb / ph.taps : 1;
+    ph.tap_off0 = (ph.taps == 9) ? -(W + 2) : 0;
+    ph.kk_b = mlp ? 32u : 2u * (uint32_t)R;
+    ph.cc_b = mlp ? 128u : 8u * (uint32_t)R;
+    ph.is_mlp = mlp ? 1u : 0u;
+    ph.onto = (ph.flags & 2) ? 1u : 0u;       // PH_ACC_R2
+}
 
 // one head's MLP tail (layers >= 1) and output transform, for the in-kernel path
 struct HeadTail {
@@ -158,8 +173,11 @@ __device__ __forceinline__ void epi_store16(uint32_t* v, float bias, uint32_t m,
 
 __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_constant__ FusedArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int game0 = a.tile_first[blockIdx.x], G = a.tile_count[blockIdx.x];
+    // warp index / tile size through a lane-0 shuffle: the compiler's uniformity analysis then knows they are warp-uniform,
+    // so the role branches below are uniform branches and the MMA issuer's operands can live in uniform registers
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
+    const int game0 = __shfl_sync(0xffffffffu, a.tile_first[blockIdx.x], 0), G = __shfl_sync(0xffffffffu, a.tile_count[blockIdx.x], 0);
+    if (a.tim && tid == 0) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 1) * 4 + 0] = clock64();   // CTA start (last row is free: n_phases < F_MAX_PHASES)
     const int P = a.P, R = a.R, HALO = a.HALO, C = a.C, KC = C >> 3, HW = a.HW, W1 = a.W + 1;
     const int N = (G * P + 15) & ~15;
     uint8_t* X = smem;
@@ -224,7 +242,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = *tmem_ptr;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_ptr, 0);
 
     if (warp == 0) {
         if (lane == 0) {   // ===== weight producer: every stage of every phase, in order, as far ahead as the ring allows =====
@@ -234,7 +252,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 const int nkb = a.ph[p].nkb;
                 for (int kb = 0; kb < nkb; kb += 2, ++it) {
                     const uint32_t s = it % F_NSTAGE;
-                    const uint32_t bytes = (uint32_t)min(2, nkb - kb) * F_KB_BYTES;
+                    uint32_t bytes = (uint32_t)min(2, nkb - kb) * F_KB_BYTES;
+                    if (a.dbg_flags & 2) bytes = 256;   // timing experiment only (wrong results): take the weight stream out of the picture
                     if (it >= F_NSTAGE) mbar_wait_dbg(&empty[s], ((it / F_NSTAGE) - 1) & 1, a.dbg, 1, (int)it);
                     mbar_expect_tx(&full[s], bytes);
                     bulk_g2s(stages + s * F_STAGE_BYTES, src, bytes, &full[s]);
@@ -243,52 +262,73 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {   // ===== MMA issuer =====
+        // ===== MMA issuer =====
+        // The WHOLE warp runs this loop and only the tcgen05 instructions are predicated on lane 0: every descriptor word is
+        // then provably warp-uniform and lives in uniform registers.  With a single-lane branch around the loop the compiler
+        // moved each operand vector->uniform per MMA (R2UR + ELECT loops): ~117 cycles per MMA whatever N (measured: 3-game
+        // tiles, N = 176, floor 88, ran no faster than 4-game tiles).
+        {
+            const bool leader = elect_one();   // warp 1 is converged here and stays so: the same lane is elected every time
             const uint32_t idescN = idesc_bf16_f32(128u, (uint32_t)N), idesc16 = idesc_bf16_f32(128u, 16u);
             // descriptors: everything but the 14-bit start-address field is constant, so the loop only adds to the low words
             const uint64_t da0 = smem_desc_kmajor_noswizzle(smem_u32(stages), 128 * 16, 128);
             const uint64_t db0 = smem_desc_kmajor_noswizzle(smem_u32(X) + (uint32_t)HALO * 16u, (uint32_t)R * 16u, 128);
-            const uint64_t dz0 = smem_desc_kmajor_noswizzle(smem_u32(Z), 256, 128);
+            const uint64_t dz0 = smem_desc_kmajor_noswizzle((smem_u32(pixmask + 8) + 127u) & ~127u, 256, 128);   // = Z, in 32-bit shared-space arithmetic (uniform datapath)
             const uint32_t a_hi = (uint32_t)(da0 >> 32), x_hi = (uint32_t)(db0 >> 32), z_hi = (uint32_t)(dz0 >> 32);
             const uint32_t a_lo0 = (uint32_t)da0, b_lo0 = (uint32_t)db0, z_lo0 = (uint32_t)dz0;
             uint32_t it = 0, ar = 0;
             for (int p = 0; p < a.n_phases; ++p) {
                 if (p > 0 || a.preload) { mbar_wait_dbg(act_ready, ar & 1, a.dbg, 2, p); ++ar; tc_fence_after(); }
-                if (a.tim) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 0] = clock64();
-                const int nkb = a.ph[p].nkb, taps = a.ph[p].taps;
-                const bool onto = (a.ph[p].flags & PH_ACC_R2) != 0;
-                const uint32_t d_tmem = tmem + (onto ? (uint32_t)F_R2_COL : 0u);
-                const int kpt = taps > 0 ? nkb / taps : 1;
-                int tap = (taps == 9) ? 0 : 4, cc = 0;
-                const bool mlp = (a.ph[p].flags & PH_MLP) != 0;   // B = Z: 16 rows per K chunk (head0's games, head1's games), N = 16
-                const uint32_t idesc = mlp ? idesc16 : idescN;
-                const uint32_t b_hi = mlp ? z_hi : x_hi;
-                const uint32_t kk_b = mlp ? 32u : 2u * (uint32_t)R;    // two 8-element K chunks per MMA, in 16-byte units
-                const uint32_t cc_b = mlp ? 128u : 8u * (uint32_t)R;    // eight K chunks per weight image
-                uint32_t b_tap = mlp ? z_lo0 : b_lo0 + (uint32_t)((tap / 3 - 1) * W1 + (tap % 3 - 1));
+                const long long t_ph = a.tim ? clock64() : 0;
+                long long w_full = 0;   // dbg_flags bit 0: the "issue" column reports the cycles spent waiting for weight slots
+                if (a.tim && leader) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 0] = t_ph;
+                const int nkb = a.ph[p].nkb, kpt = a.ph[p].kpt;
+                const uint32_t is_mlp = a.ph[p].is_mlp, onto = a.ph[p].onto;   // 0 / 1: arithmetic instead of selects keeps the chain uniform
+                const uint32_t d_tmem = tmem + onto * (uint32_t)F_R2_COL;
+                const uint32_t idesc = idescN + is_mlp * (idesc16 - idescN);      // MLP: B = Z, 16 rows per K chunk (head0's games, head1's games), N = 16
+                const uint32_t b_hi = x_hi + is_mlp * (z_hi - x_hi);
+                const uint32_t kk_b = a.ph[p].kk_b;    // two 8-element K chunks per MMA, in 16-byte units
+                const uint32_t cc_b = a.ph[p].cc_b;    // eight K chunks per weight image
+                uint32_t b_cur = b_lo0 + is_mlp * (z_lo0 - b_lo0) + (uint32_t)a.ph[p].tap_off0;   // B start of the current K stage
+                int cc = 0, tx = 0;
                 for (int kb = 0; kb < nkb; ++it) {
                     const uint32_t s = it % F_NSTAGE;
-                    const int n = min(2, nkb - kb);
                     const uint32_t a_lo = a_lo0 + s * (F_STAGE_BYTES >> 4);
-                    mbar_wait_dbg(&full[s], (it / F_NSTAGE) & 1, a.dbg, 3, (int)it);
+                    if (a.tim && (a.dbg_flags & 1)) { const long long t = clock64(); mbar_wait_dbg(&full[s], (it / F_NSTAGE) & 1, a.dbg, 3, (int)it); w_full += clock64() - t; }
+                    else mbar_wait_dbg(&full[s], (it / F_NSTAGE) & 1, a.dbg, 3, (int)it);
                     tc_fence_after();
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        if (h < n) {
+                        if (kb < nkb) {
                             const uint32_t ah = a_lo + h * (F_KB_BYTES >> 4);
-                            const uint32_t b_lo = b_tap + (uint32_t)cc * cc_b;
-                            mma_bf16_lohi_rt(d_tmem, ah, a_hi, b_lo, b_hi, idesc, (onto || kb != 0) ? 1u : 0u);
-                            mma_bf16_lohi<1>(d_tmem, ah + 256u, a_hi, b_lo + kk_b, b_hi, idesc);
-                            mma_bf16_lohi<1>(d_tmem, ah + 512u, a_hi, b_lo + 2u * kk_b, b_hi, idesc);
-                            mma_bf16_lohi<1>(d_tmem, ah + 768u, a_hi, b_lo + 3u * kk_b, b_hi, idesc);
+                            const uint32_t acc0 = (onto | (uint32_t)(kb != 0)) ? 1u : 0u;
+                            // ptxas keeps the loop-carried b_cur in a vector register; an opaque lane-0 shuffle (which it knows to be
+                            // warp-uniform) moves it to the uniform file ONCE per K stage instead of once per MMA
+                            uint32_t ub;
+                            asm volatile("shfl.sync.idx.b32 %0, %1, 0, 0x1f, 0xffffffff;" : "=r"(ub) : "r"(b_cur));
+                            if (leader) {
+                                mma_bf16_lohi_rt(d_tmem, ah, a_hi, ub, b_hi, idesc, acc0);
+                                mma_bf16_lohi<1>(d_tmem, ah + 256u, a_hi, ub + kk_b, b_hi, idesc);
+                                mma_bf16_lohi<1>(d_tmem, ah + 512u, a_hi, ub + 2u * kk_b, b_hi, idesc);
+                                mma_bf16_lohi<1>(d_tmem, ah + 768u, a_hi, ub + 3u * kk_b, b_hi, idesc);
+                            }
                             ++kb;
-                            if (++cc == kpt && !mlp) { cc = 0; ++tap; b_tap = b_lo0 + (uint32_t)((tap / 3 - 1) * W1 + (tap % 3 - 1)); }
+                            b_cur += cc_b;
+                            if (++cc == kpt) {   // next tap: back to channel 0, one pixel to the right or to the start of the next row
+                                cc = 0;
+                                b_cur += ((tx == 2) ? (uint32_t)(W1 - 2) : 1u) - (uint32_t)kpt * cc_b;
+                                tx = (tx == 2) ? 0 : tx + 1;
+                            }
                         }
                     }
-                    mma_commit(&empty[s]);
+                    if (leader) mma_commit(&empty[s]);
+                    __syncwarp();
                 }
-                if (nkb > 0) mma_commit(accum_full); else mbar_arrive(accum_full);
-                if (a.tim) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 1] = clock64();
+                if (leader) {
+                    if (nkb > 0) mma_commit(accum_full); else mbar_arrive(accum_full);
+                    if (a.tim) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 1] = (a.dbg_flags & 1) ? t_ph + w_full : clock64();
+                }
+                __syncwarp();
             }
         }
     } else {
@@ -589,6 +629,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem, F_TMEM_COLS);
+    if (a.tim && tid == 0) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 1) * 4 + 1] = clock64();   // CTA end
 }
 
 // ------------------------------------------------------------------ head MLPs on the reduced activations

@@ -110,6 +110,10 @@ int main(int argc, char** argv) {
     const int R = 243;
     add("noswz N=224 (kernel layout)", 224, 0, 2048, 128, R * 16, 128, 9 * 16, 0, 0);
     add("noswz N=224 + fill", 224, 0, 2048, 128, R * 16, 128, 9 * 16, 0, 1);
+    add("noswz N=176 (3-game tile)", 176, 0, 2048, 128, R * 16, 128, 9 * 16, 0, 0);
+    add("noswz N=176 + fill", 176, 0, 2048, 128, R * 16, 128, 9 * 16, 0, 1);
+    add("noswz N=112 (half tile)", 112, 0, 2048, 128, R * 16, 128, 9 * 16, 0, 0);
+    add("noswz N=112 + fill", 112, 0, 2048, 128, R * 16, 128, 9 * 16, 0, 1);
     add("noswz N=224 aligned B, LBO=4096", 224, 0, 2048, 128, 4096, 128, 0, 0, 0);
     add("noswz N=256 aligned", 256, 0, 2048, 128, 4096, 128, 0, 0, 0);
     add("noswz N=128 aligned", 128, 0, 2048, 128, 4096, 128, 0, 0, 0);

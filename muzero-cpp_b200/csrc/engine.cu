@@ -155,10 +155,13 @@ int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out) {
     MZB_CUDA(cudaSetDevice(device));
     MZB_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     MZB_CUDA(cudaStreamCreateWithFlags(&e->aux, cudaStreamNonBlocking));
+    for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) MZB_CUDA(cudaStreamCreateWithFlags(&e->pipe[i], cudaStreamNonBlocking));
     MZB_CUDA(cudaEventCreate(&e->ev_start));
     MZB_CUDA(cudaEventCreate(&e->ev_root));
     MZB_CUDA(cudaEventCreate(&e->ev_end));
     MZB_CUDA(cudaEventCreateWithFlags(&e->ev_aux, cudaEventDisableTiming));
+    MZB_CUDA(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+    for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) MZB_CUDA(cudaEventCreateWithFlags(&e->ev_join[i], cudaEventDisableTiming));
     rc = alloc_trees(e.get());
     if (rc) return rc;
     const int T = e->cfg.max_trees, n = e->cfg.num_simulations;
@@ -189,9 +192,12 @@ void mzb_engine_destroy(mzb_engine* e) {
     if (e->ev_root) cudaEventDestroy(e->ev_root);
     if (e->ev_end) cudaEventDestroy(e->ev_end);
     if (e->ev_aux) cudaEventDestroy(e->ev_aux);
+    if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+    for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) if (e->ev_join[i]) cudaEventDestroy(e->ev_join[i]);
     e->net.reset();
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->aux) cudaStreamDestroy(e->aux);
+    for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) if (e->pipe[i]) cudaStreamDestroy(e->pipe[i]);
     delete e;
 }
 

@@ -43,8 +43,11 @@ struct mzb_engine {
     std::unique_ptr<NetBackend> net;
     bool weights_loaded = false;
     std::vector<float> action_planes;   // owned copy of cfg.action_planes
+    static constexpr int MAX_PARTS = 4;
     cudaStream_t stream = nullptr, aux = nullptr;
-    cudaEvent_t ev_start = nullptr, ev_root = nullptr, ev_end = nullptr, ev_aux = nullptr;
+    cudaStream_t pipe[MAX_PARTS - 1] = {nullptr, nullptr, nullptr};   // streams of parts 1.. of the pipelined simulation loop (part 0 runs on `stream`)
+    cudaEvent_t ev_start = nullptr, ev_root = nullptr, ev_end = nullptr, ev_aux = nullptr, ev_fork = nullptr;
+    cudaEvent_t ev_join[MAX_PARTS - 1] = {nullptr, nullptr, nullptr};
     // trees
     TreeDev td;
     DevBuf meta, prior, value_sum, reward, mm_min, mm_max, root_to_play, n_legal, n_slots, max_depth, mt, mt_idx,

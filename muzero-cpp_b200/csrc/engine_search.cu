@@ -91,6 +91,44 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
     ++launches;
     MZB_CUDA(cudaEventRecord(e->ev_root, s));
     // ---- simulation loop: tree step <-> recurrent inference, lock-step over all trees (mcts.cpp:52-79) ----
+    // Pipelined loop: the cohort is cut into K parts (default 2), each on its own stream, when the backend allows it.  Trees
+    // are independent, so while one part's towers own the SMs another part's tree step (a few blocks without shared memory)
+    // runs beside them and its towers queue up behind — the tree step, the launch gaps and the tail of each tower launch
+    // leave the critical path.  Results are bit-identical to the single-stream loop (a tree's arithmetic does not depend on
+    // its neighbours in a tile; tests/test_gpu_pipeline.py).
+    static const int pipe_min = getenv("MZB_PIPELINE_MIN_TREES") ? atoi(getenv("MZB_PIPELINE_MIN_TREES")) : 256;
+    static const int pipe_parts = getenv("MZB_PIPELINE_PARTS") ? std::max(2, std::min((int)mzb_engine::MAX_PARTS, atoi(getenv("MZB_PIPELINE_PARTS")))) : 2;
+    const bool pipelined = !synthetic && e->net->recurrent_concurrent() && pipe_min > 0 && T >= pipe_min && T >= pipe_parts;
+    if (pipelined) {
+        const int K = pipe_parts;
+        cudaStream_t st[mzb_engine::MAX_PARTS];
+        int t0[mzb_engine::MAX_PARTS + 1];
+        NetOutputs o[mzb_engine::MAX_PARTS];
+        for (int k = 0; k <= K; ++k) t0[k] = (int)((long)T * k / K);
+        MZB_CUDA(cudaEventRecord(e->ev_fork, s));
+        for (int k = 0; k < K; ++k) {
+            st[k] = k == 0 ? s : e->pipe[k - 1];
+            if (k > 0) MZB_CUDA(cudaStreamWaitEvent(st[k], e->ev_fork, 0));
+            o[k] = tree_outputs(e);
+            o[k].value += t0[k]; o[k].reward += t0[k]; o[k].policy += (size_t)t0[k] * A;
+        }
+        e->net->set_pipelined(true);
+        for (int sim = 0; sim <= n && !rc; ++sim) {
+            for (int k = 0; k < K && !rc; ++k) {
+                launch_tree_step_range(td, t0[k], t0[k + 1], sim, st[k]);
+                ++launches;
+                if (sim == n) continue;
+                rc = e->net->recurrent(t0[k + 1] - t0[k], td.in_slot + t0[k], td.action + t0[k], td.out_slot + t0[k], o[k], st[k]);
+                launches += e->net->launches_recurrent();
+            }
+        }
+        e->net->set_pipelined(false);
+        if (rc) return rc;
+        for (int k = 1; k < K; ++k) {
+            MZB_CUDA(cudaEventRecord(e->ev_join[k - 1], st[k]));
+            MZB_CUDA(cudaStreamWaitEvent(s, e->ev_join[k - 1], 0));
+        }
+    } else
     for (int sim = 0; sim <= n; ++sim) {
         launch_tree_step(td, T, sim, s);
         ++launches;

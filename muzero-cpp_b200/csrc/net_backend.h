@@ -37,6 +37,12 @@ public:
     virtual int recurrent(int B, const int* d_in_slot, const int* d_action, const int* d_out_slot,
                           const NetOutputs& out, cudaStream_t s) = 0;
     // kernels launched by one initial()/recurrent() call (for gpu_launches accounting)
+    // true when two recurrent() calls on disjoint tree ranges may be in flight on different streams at once (no shared
+    // scratch): lets the search pipeline two half-cohorts so that one half's tree step hides behind the other's towers
+    virtual bool recurrent_concurrent() const { return false; }
+    // hint: the following recurrent() calls are parts of a pipelined loop (the GPU always has another part's CTAs to run), so
+    // tiles should be as full as possible rather than balanced over the SMs of one launch
+    virtual void set_pipelined(bool) {}
     virtual int launches_initial() const = 0;
     virtual int launches_recurrent() const = 0;
 };

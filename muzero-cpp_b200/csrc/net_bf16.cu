@@ -436,7 +436,7 @@ protected:
         int R = halo + nmax + halo;
         if ((R & 1) == 0) ++R;
         const int x_bytes = (int)((((size_t)(C / 8) * R * 16) + 127) / 128 * 128);
-        if (fused::fused_smem_bytes(x_bytes, 0) > 227 * 1024) return MZB_OK;
+        if (fused::fused_smem_bytes(x_bytes, 0, P) > 227 * 1024) return MZB_OK;
         // in-kernel head MLPs (first layer on the tensor core): needs <= 8 games per tile, stacked widths <= 128
         const HeadHost& hR = plan.reward_head; const HeadHost& hP = plan.policy_head; const HeadHost& hV = plan.value_head;
         int z_bytes = 0, z_rp = 0;
@@ -448,10 +448,10 @@ protected:
             if (ok && !no_z) {
                 z_rp = (std::max(hR.red, std::max(hP.red, hV.red)) + 7) / 8 * 8;
                 z_bytes = (P * z_rp + KB - 1) / KB * KB / 8 * 256;   // [K / 8][16 rows][16 B]
-                if (fused::fused_smem_bytes(x_bytes, z_bytes) > 227 * 1024) z_bytes = 0;
+                if (fused::fused_smem_bytes(x_bytes, z_bytes, P) > 227 * 1024) z_bytes = 0;
             }
         }
-        const size_t smem = fused::fused_smem_bytes(x_bytes, z_bytes);
+        const size_t smem = fused::fused_smem_bytes(x_bytes, z_bytes, P);
         // extra weights
         conv1_rel_[0] = pack_conv1(hr, 1, C, extra, &conv1_bias_rel_[0]);
         conv1_rel_[1] = pack_conv1(hpv, 2, C, extra, &conv1_bias_rel_[1]);
@@ -602,10 +602,18 @@ protected:
     // balanced tiles: every SM gets ceil-or-floor(B / SMs) games, cut into as few tiles of <= gmax games as possible,
     // emitted wave by wave (the hardware scheduler hands out CTAs in index order)
     int tiles_for(int B, int gmax, const TileTab** out) {
-        auto it = tiles_.find(B);
+        const long key = (long)B * 2 + (pipelined_ ? 1 : 0);
+        auto it = tiles_.find(key);
         if (it == tiles_.end()) {
             std::vector<int> first, count;
             const int S = n_sm_ > 0 ? n_sm_ : 148;
+            if (pipelined_) {
+                // part of a pipelined loop: full tiles (a tile costs nearly the same whatever it holds — the weight stream and the
+                // fixed phases do not shrink with it), the remainder spread over the last tiles
+                const int nt = (B + gmax - 1) / gmax;
+                int g = 0;
+                for (int k = 0; k < nt; ++k) { const int part = B / nt + (k >= nt - B % nt ? 1 : 0); first.push_back(g); count.push_back(part); g += part; }
+            } else {
             const int per = (B + S - 1) / S;
             const int waves = (per + gmax - 1) / gmax;
             std::vector<int> left(S), next(S);
@@ -618,6 +626,7 @@ protected:
                     first.push_back(next[k]); count.push_back(part);
                     next[k] += part; left[k] -= part;
                 }
+            }
             std::unique_ptr<TileTab> tt(new TileTab());
             tt->n_tiles = (int)first.size();
             tt->h_count = count;
@@ -625,7 +634,7 @@ protected:
             MZB_CUDA(tt->count.alloc(count.size() * sizeof(int)));
             MZB_CUDA(cudaMemcpy(tt->first.p, first.data(), first.size() * sizeof(int), cudaMemcpyHostToDevice));
             MZB_CUDA(cudaMemcpy(tt->count.p, count.data(), count.size() * sizeof(int), cudaMemcpyHostToDevice));
-            it = tiles_.emplace(B, std::move(tt)).first;
+            it = tiles_.emplace(key, std::move(tt)).first;
         }
         *out = it->second.get();
         return MZB_OK;
@@ -737,6 +746,11 @@ protected:
     }
 
 public:
+    // the one-launch fused recurrent pass keeps everything in shared memory / TMEM: no global scratch shared between calls
+    void set_pipelined(bool on) override { pipelined_ = on; }
+    bool recurrent_concurrent() const override {
+        return uploaded_ && fused_final_ && fused_rec_.ok && fused_rec_.args.z_bytes > 0 && !getenv("MZB_FUSED_TIMING");
+    }
     int recurrent(int B, const int* d_in_slot, const int* d_action, const int* d_out_slot, const NetOutputs& out, cudaStream_t s) override {
         MZB_REQUIRE(uploaded_, "weights not loaded (mzb_load_weights)");
         int rc = finalize_fused();
@@ -780,6 +794,7 @@ public:
 protected:
     FusedChain fused_rec_, fused_init_;
     bool fused_final_ = false;
+    bool pipelined_ = false;
     size_t conv1_rel_[2] = {0, 0}, conv1_bias_rel_[2] = {0, 0}, w0t_rel_[3] = {0, 0, 0};
     size_t mlp0_rel_[2] = {0, 0}, mlp0_bias_rel_[2] = {0, 0};
     int mlp0_nkb_[2] = {0, 0};
@@ -788,7 +803,7 @@ protected:
     int mlp_mg_ = 16, n_sm_ = 0;
     int* dbg_host_ = nullptr; int* dbg_dev_ = nullptr;
     DevBuf tim_;
-    std::map<int, std::unique_ptr<TileTab>> tiles_;
+    std::map<long, std::unique_ptr<TileTab>> tiles_;
 
     int fast_conv(const direct::ConvCall<bf16>& call, cudaStream_t s) override {
         const direct::ConvDev& c = *call.conv;

@@ -114,8 +114,12 @@ struct FusedArgs {
 };
 
 constexpr int F_HS_BYTES = 2 * 8 * 128 * 4;   // two ping-pong buffers [8 games][128 stacked units] fp32 for the MLP tails
-inline size_t fused_smem_bytes(int x_bytes, int z_bytes) {
-    return (size_t)x_bytes + (size_t)F_NSTAGE * F_STAGE_BYTES + 256 + 1024 + 3 * F_MAX_G * 4 + 32 + 128 + (z_bytes ? (size_t)z_bytes + F_HS_BYTES + 128 : 0);
+// pixel table entries: look-ups run in 8-row chunks up to P + 7.  Sized by P (not a flat 256) so that the CTA stays >= 1 KB under
+// the SM's shared memory: a tree-step block (no shared memory of its own, 1 KB driver reserve) must fit BESIDE a tower CTA
+// for the pipelined simulation loop to overlap the two.
+__host__ __device__ inline int fused_ptab_entries(int P) { return (P + 8 + 63) & ~63; }
+inline size_t fused_smem_bytes(int x_bytes, int z_bytes, int P) {
+    return (size_t)x_bytes + (size_t)F_NSTAGE * F_STAGE_BYTES + 256 + (size_t)fused_ptab_entries(P) * 4 + 3 * F_MAX_G * 4 + 32 + 128 + (z_bytes ? (size_t)z_bytes + F_HS_BYTES + 128 : 0);
 }
 
 // explicit shared-space accesses (32-bit shared addresses: no generic-pointer conversion per access)
@@ -188,7 +192,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
     uint64_t* act_ready = accum_full + 1;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(act_ready + 1);
     int* pixtab = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(full) + 256);   // [P] row within a game -> pixel or -1
-    int* g_in = pixtab + 256;
+    const int PT = fused_ptab_entries(P);
+    int* g_in = pixtab + PT;
     int* g_out = g_in + F_MAX_G;
     int* g_act = g_out + F_MAX_G;
     uint32_t* pixmask = reinterpret_cast<uint32_t*>(g_act + F_MAX_G);   // [8] bit r = row r of a game is a real pixel
@@ -208,7 +213,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
         g_out[tid] = a.out_slot ? a.out_slot[game] : game;
         g_act[tid] = a.action ? a.action[game] : 0;
     }
-    for (int r = tid; r < 256; r += F_THREADS) {
+    for (int r = tid; r < PT; r += F_THREADS) {
         const int yy = r / W1, xx = r - yy * W1;
         pixtab[r] = (r < P && yy >= 1 && yy <= a.H && xx < a.W) ? (yy - 1) * a.W + xx : -1;
     }

@@ -154,10 +154,10 @@ __global__ void tree_root_kernel(TreeDev td, int n_trees, const uint32_t* legal_
 }
 
 // ------------------------------------------------------------------ one simulation step
-__global__ void __launch_bounds__(128) tree_step_kernel(TreeDev td, int n_trees, int sim) {
-    const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+__global__ void __launch_bounds__(128) tree_step_kernel(TreeDev td, int t_first, int t_end, int sim) {
+    const int t = t_first + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     const int lane = threadIdx.x & 31;
-    if (t >= n_trees) return;
+    if (t >= t_end) return;
     const long sb = (long)t * td.slots_per_tree;
     int4* meta = td.meta + sb;
     double* prior = td.prior + sb;
@@ -414,7 +414,10 @@ void launch_tree_root(const TreeDev& td, int n_trees, const uint32_t* d_legal_ma
     tree_root_kernel<<<warps_grid(n_trees, 128), 128, 0, s>>>(td, n_trees, d_legal_mask, d_to_play, d_add_noise, d_noise);
 }
 void launch_tree_step(const TreeDev& td, int n_trees, int sim, cudaStream_t s) {
-    tree_step_kernel<<<warps_grid(n_trees, 128), 128, 0, s>>>(td, n_trees, sim);
+    tree_step_kernel<<<warps_grid(n_trees, 128), 128, 0, s>>>(td, 0, n_trees, sim);
+}
+void launch_tree_step_range(const TreeDev& td, int t_first, int t_end, int sim, cudaStream_t s) {
+    tree_step_kernel<<<warps_grid(t_end - t_first, 128), 128, 0, s>>>(td, t_first, t_end, sim);
 }
 void launch_tree_stats(const TreeDev& td, int n_trees, const ResultDev& r, cudaStream_t s) {
     tree_stats_kernel<<<warps_grid(n_trees, 128), 128, 0, s>>>(td, n_trees, r);

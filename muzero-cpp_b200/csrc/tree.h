@@ -40,6 +40,8 @@ void launch_tree_root(const TreeDev& td, int n_trees, const uint32_t* d_legal_ma
 // simulation step `sim` in [0, n_sims]:  (sim > 0: expand + backup of the previous selection)  then
 // (sim < n_sims: select a leaf and publish the network request)
 void launch_tree_step(const TreeDev& td, int n_trees, int sim, cudaStream_t s);
+// the same step for trees [t_first, t_end) only: the two half-cohorts of the pipelined simulation loop
+void launch_tree_step_range(const TreeDev& td, int t_first, int t_end, int sim, cudaStream_t s);
 // get_search_statistics (mcts.cpp:179-200) into device SoA result arrays
 struct ResultDev {
     double* root_value; int* max_tree_depth; int* n_children; int* child_actions; int* child_visits;

@@ -21,6 +21,8 @@ ms, nl = eng.bench_recurrent(T, 2)
 print("recurrent: %.3f ms/pass, %d launches, %.0f states/s" % (ms, nl, T / ms * 1e3))
 rng = np.random.default_rng(0)
 obs = rng.random((T, eng.shapes.initial_flat_size), dtype=np.float32)
-res = eng.run(obs, np.full(T, (1 << cfg.num_actions) - 1, np.uint32), np.zeros(T, np.int32), np.ones(T, np.uint8))
+reps = int(os.environ.get("MZB_PROFILE_SEARCHES", "1"))
+for _ in range(reps):
+    res = eng.run(obs, np.full(T, (1 << cfg.num_actions) - 1, np.uint32), np.zeros(T, np.int32), np.ones(T, np.uint8))
 print("search:", eng.last_search_timing())
 eng.close()

@@ -274,7 +274,7 @@ public:
     const char* name() const override { return "bf16-tcgen05"; }
 
 protected:
-    struct Packed { bool ok = false; size_t off = 0; UmmaGeom g; };
+    struct Packed { bool ok = false; bool image = false; size_t off = 0; UmmaGeom g; };   // ok: the per-layer kernel takes it; image: packed weights exist (enough for the fused chain)
 
     bool eligible(const Conv3Host& c, UmmaGeom* g) const {
         if (c.stride != 1 || c.cin % KB != 0 || c.cout > UM || c.cout % 8 != 0) return false;
@@ -293,8 +293,11 @@ protected:
             for (size_t i = 0; i < tw[t]->convs.size(); ++i) {
                 const Conv3Host& c = tw[t]->convs[i];
                 Packed p;
-                if (!eligible(c, &p.g)) continue;
-                p.ok = true;
+                // the weight image only needs a 64-multiple of input channels and <= 128 outputs; the per-layer kernel
+                // additionally wants its own tile geometry to fit twice per SM
+                if (c.stride != 1 || c.cin % KB != 0 || c.cout > UM || c.cout % 8 != 0 || c.in_h != c.out_h || c.in_w != c.out_w) continue;
+                p.image = true;
+                p.ok = eligible(c, &p.g);
                 while (extra->size() % 128) extra->push_back(0);
                 p.off = extra->size();
                 const int kb_per_tap = c.cin / KB;
@@ -413,42 +416,52 @@ protected:
         tiles_.clear();
         static const bool disabled = getenv("MZB_NO_FUSED") != nullptr;
         if (disabled) return MZB_OK;
+        // MZB_VERBOSE=1 names the condition that keeps a network off the fused chain (it then runs the per-layer path)
+#define MZB_FUSE_REJECT(why) do { if (getenv("MZB_VERBOSE")) fprintf(stderr, "[bf16] fused chain not used: %s\n", why); return MZB_OK; } while (0)
         const NetDims& d = plan.dims;
         const int C = d.C, H = d.h, W = d.w;
-        if (C % KB != 0 || C > UM) return MZB_OK;
+        if (C % KB != 0 || C > UM) MZB_FUSE_REJECT("channels not a multiple of 64 or above 128");
         const int P = ((H + 1) * (W + 1) + 7) / 8 * 8;
-        if (P > 256) return MZB_OK;
+        if (P > 256) MZB_FUSE_REJECT("padded board above 256 rows");
         const HeadHost* hr[1] = {&plan.reward_head};
         const HeadHost* hpv[2] = {&plan.policy_head, &plan.value_head};
-        if (plan.reward_head.red > UM || plan.policy_head.red + plan.value_head.red > UM) return MZB_OK;
+        if (plan.reward_head.red > UM || plan.policy_head.red + plan.value_head.red > UM) MZB_FUSE_REJECT("reduced head channels above 128");
         for (const HeadHost* h : {&plan.reward_head, &plan.policy_head, &plan.value_head}) {
-            if ((int)h->W.size() > fused::MLP_MAX_LAYERS) return MZB_OK;
-            for (size_t i = 1; i < h->sizes.size(); ++i) if (h->sizes[i] > 256) return MZB_OK;
+            if ((int)h->W.size() > fused::MLP_MAX_LAYERS) MZB_FUSE_REJECT("MLP deeper than 6 layers");
+            for (size_t i = 1; i < h->sizes.size(); ++i) if (h->sizes[i] > 256) MZB_FUSE_REJECT("MLP layer wider than 256");
         }
         const bool dyn_ok = tower_fusable(plan.dynamics, true, C, H, W) && packed_[1].size() == plan.dynamics.convs.size();
         const bool pred_ok = tower_fusable(plan.prediction, false, C, H, W);
-        if (!dyn_ok || !pred_ok) return MZB_OK;
-        for (int t = 1; t < 3; ++t) for (const Packed& p : packed_[t]) if (!p.ok) return MZB_OK;
-        // geometry
-        const int gmax = std::min(256 / P, fused::F_MAX_G);
-        const int nmax = (gmax * P + 15) / 16 * 16;
-        const int halo = W + 2;
-        int R = halo + nmax + halo;
-        if ((R & 1) == 0) ++R;
-        const int x_bytes = (int)((((size_t)(C / 8) * R * 16) + 127) / 128 * 128);
-        if (fused::fused_smem_bytes(x_bytes, 0, P) > 227 * 1024) return MZB_OK;
-        // in-kernel head MLPs (first layer on the tensor core): needs <= 8 games per tile, stacked widths <= 128
+        if (!dyn_ok) MZB_FUSE_REJECT("dynamics tower is not head conv + residual blocks at constant shape");
+        if (!pred_ok) MZB_FUSE_REJECT("prediction tower is not residual blocks at constant shape");
+        for (int t = 1; t < 3; ++t) for (const Packed& p : packed_[t]) if (!p.image) MZB_FUSE_REJECT("a convolution has no packed tensor-core image (channels / stride)");
+        // geometry: as many games per tile as 256 accumulator columns hold; the in-kernel head MLPs (first layer on the tensor
+        // core, one launch per inference) need <= 8 games per tile and stacked widths <= 128, and are preferred over wider tiles
         const HeadHost& hR = plan.reward_head; const HeadHost& hP = plan.policy_head; const HeadHost& hV = plan.value_head;
-        int z_bytes = 0, z_rp = 0;
+        const int halo = W + 2;
+        int gmax = 0, R = 0, x_bytes = 0, z_bytes = 0, z_rp = 0;
+        auto geometry = [&](int g) {
+            gmax = g;
+            const int nmax = (gmax * P + 15) / 16 * 16;
+            R = halo + nmax + halo;
+            if ((R & 1) == 0) ++R;
+            x_bytes = (int)((((size_t)(C / 8) * R * 16) + 127) / 128 * 128);
+        };
         {
-            bool ok = gmax <= 8 && hP.W.size() == hV.W.size() && hR.sizes[1] <= UM;
+            bool ok = hP.W.size() == hV.W.size() && hR.sizes[1] <= UM;
             for (size_t l = 1; ok && l < hP.sizes.size(); ++l) ok = hP.sizes[l] + hV.sizes[l] <= UM;
             for (size_t l = 1; ok && l < hR.sizes.size(); ++l) ok = hR.sizes[l] <= UM;
             static const bool no_z = getenv("MZB_NO_INKERNEL_MLP") != nullptr;
             if (ok && !no_z) {
+                geometry(std::min(std::min(256 / P, fused::F_MAX_G), 8));
                 z_rp = (std::max(hR.red, std::max(hP.red, hV.red)) + 7) / 8 * 8;
                 z_bytes = (P * z_rp + KB - 1) / KB * KB / 8 * 256;   // [K / 8][16 rows][16 B]
                 if (fused::fused_smem_bytes(x_bytes, z_bytes, P) > 227 * 1024) z_bytes = 0;
+            }
+            if (!z_bytes) {
+                z_rp = 0;
+                geometry(std::min(256 / P, fused::F_MAX_G));
+                if (fused::fused_smem_bytes(x_bytes, 0, P) > 227 * 1024) MZB_FUSE_REJECT("tile does not fit shared memory");
             }
         }
         const size_t smem = fused::fused_smem_bytes(x_bytes, z_bytes, P);
@@ -496,7 +509,7 @@ protected:
         for (size_t k = 1; k < tw.convs.size(); ++k) {
             const Conv3Host& c = tw.convs[k];
             if (c.stride != 1 || c.cin != C || c.cout != C || c.in_h != H || c.in_w != W) return false;
-            if (!packed_[0][k].ok) return false;
+            if (!packed_[0][k].image) return false;
         }
         return true;
     }

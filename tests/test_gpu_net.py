@@ -152,7 +152,7 @@ def test_custom_action_planes():
 
 
 # ---------------------------------------------------------------- bf16 tcgen05 mode
-@pytest.mark.parametrize("game,B", [("c4d", 13), ("c4r", 9), ("ttt", 37)])
+@pytest.mark.parametrize("game,B", [("c4d", 13), ("c4r", 9), ("ttt", 37), ("ale", 6)])
 def test_bf16_matches_oracle_random_weights(game, B):
     """north star: bf16 mode within 2e-2 relative of the libtorch fp32 model on the same random-init weights"""
     ncfg = V.preset(game)

@@ -7,3 +7,4 @@ tail -5 gpurun_out/pytest_gpu.log
 timeout 900 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
 cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
 timeout 600 python bench.py --steps 3 --warmup 3 --workload c4r --no-cpu-baseline > gpurun_out/bench_c4r.json 2> gpurun_out/bench_c4r.err; cat gpurun_out/bench_c4r.json
+for w in reanalyze ttt ale; do timeout 600 python bench.py --steps 2 --warmup 3 --workload $w --no-cpu-baseline > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err; echo "$w rc=$?"; cut -c1-400 gpurun_out/bench_$w.json; tail -2 gpurun_out/bench_$w.err; done

@@ -521,8 +521,15 @@ protected:
         ph.w_off = (uint32_t)(fp32_bytes_ + packed_[tower][index].off);
         ph.taps = 9; ph.nkb = 9 * (c.cin / KB);
         ph.bias_off = (int)(c.bias_off * sizeof(float));
-        ph.table_off = c.has_table ? (int)(c.table_off * sizeof(float)) : -1;
-        ph.flags = flags | (c.relu ? fused::PH_RELU : 0) | (c.has_table ? fused::PH_TABLE : 0);
+        ph.table_off = -1;
+        ph.flags = flags | (c.relu ? fused::PH_RELU : 0);
+        if (c.has_table) {
+            // dynamics head: the action planes' contribution is a per-action table [A][HW][C].  The epilogue warps stage it in
+            // the (still unused) R2 accumulator WHILE the head's MMAs run into R1, and the epilogue adds the two — no table
+            // look-ups (L2 latency chains) behind the MMAs.  Only the first phase of a chain may do so (R2 must be free).
+            fa->table_off = (int)(c.table_off * sizeof(float));
+            ph.flags |= fused::PH_TABLE;
+        }
     }
     void add_blocks(fused::FusedArgs* fa, int tower, size_t first_step) {
         for (size_t i = first_step; i < steps_[tower].size(); ++i) {
@@ -715,17 +722,18 @@ protected:
                 fprintf(stderr, "[fused]  phase %2d nkb %3d flags %3d: gap %7.0f | issue %7.0f | full %7.0f | epi %7.0f\n", p, a.ph[p].nkb, a.ph[p].flags, gap / n, issue / n, full / n, epi / n);
             }
             // whole-CTA view, by tile size: start -> first MMA (prologue + input load), first MMA -> last epilogue end, -> CTA end
-            double pro[fused::F_MAX_G + 1] = {0}, body[fused::F_MAX_G + 1] = {0}, tail[fused::F_MAX_G + 1] = {0};
+            double pro[fused::F_MAX_G + 1] = {0}, body[fused::F_MAX_G + 1] = {0}, tail[fused::F_MAX_G + 1] = {0}, setup[fused::F_MAX_G + 1] = {0}, inp[fused::F_MAX_G + 1] = {0};
             int cnt[fused::F_MAX_G + 1] = {0};
             for (int t = 0; t < tt->n_tiles; ++t) {
                 const long long* row = &h[(size_t)t * fused::F_MAX_PHASES * 4];
                 const long long* ends = row + (size_t)(fused::F_MAX_PHASES - 1) * 4;
                 const int g = tt->h_count[t];
+                setup[g] += ends[2] - ends[0]; inp[g] += ends[3] - ends[2];
                 pro[g] += row[0] - ends[0]; body[g] += row[(size_t)(a.n_phases - 1) * 4 + 3] - row[0]; tail[g] += ends[1] - row[(size_t)(a.n_phases - 1) * 4 + 3];
                 ++cnt[g];
             }
             for (int g = 1; g <= fused::F_MAX_G; ++g)
-                if (cnt[g]) fprintf(stderr, "[fused]  tiles of %d games: %d; prologue %7.0f | phases %7.0f | tail %7.0f cycles\n", g, cnt[g], pro[g] / cnt[g], body[g] / cnt[g], tail[g] / cnt[g]);
+                if (cnt[g]) fprintf(stderr, "[fused]  tiles of %d games: %d; prologue %7.0f (set-up %5.0f, input %5.0f) | phases %7.0f | tail %7.0f cycles\n", g, cnt[g], pro[g] / cnt[g], setup[g] / cnt[g], inp[g] / cnt[g], body[g] / cnt[g], tail[g] / cnt[g]);
         }
         static const bool sync_debug = getenv("MZB_FUSED_SYNC") != nullptr;
         if (sync_debug) {

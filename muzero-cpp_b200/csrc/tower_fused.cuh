@@ -49,7 +49,7 @@ enum : int {
     PH_RELU = 1,      // ReLU in the epilogue
     PH_ACC_R2 = 2,    // accumulate into R2 on top of the block input stored there (second conv of a residual block)
     PH_STASH = 4,     // keep the epilogue result in R2 (fp32) as the next block's skip input
-    PH_TABLE = 8,     // add the per-action table (dynamics head: contribution of the action planes)
+    PH_TABLE = 8,     // dynamics head: stage the per-action table in R2 during the MMAs, add it in the epilogue
     PH_WRITE_X = 16,  // store the epilogue result into X (bf16)
     PH_RED = 32,      // 1x1 head convolution: rows of R1 -> red[] buffers (no activation)
     PH_NORM = 64,     // normalize_hidden_state on R2 -> X, node pool slot, R2
@@ -61,7 +61,7 @@ struct Phase {
     int nkb;               // 64-wide K stages (taps * C / 64); 0 = no tensor work
     int taps;              // 9 (3x3) or 1 (1x1)
     int bias_off;          // byte offset of the fp32 bias vector, -1 = none
-    int table_off;         // byte offset of the fp32 [A][HW][C] table (PH_TABLE)
+    int table_off;         // unused (kept for layout stability)
     int flags;
     int red_head0, red_n0, red_head1, red_n1;   // PH_RED: rows [0,n0) -> red[head0], rows [n0, n0+n1) -> red[head1]
                                                 // PH_MLP: hidden rows [0,n0) belong to head0, [n0, n0+n1) to head1 (n1 = 0: one head)
@@ -107,6 +107,7 @@ struct FusedArgs {
     int dbg_flags;                                            // experiments: bit 0 = all taps unshifted (timing only, wrong results)
     int* dbg;                                                 // host-mapped diagnostics (barrier time-outs), may be null
     long long* tim;                                           // optional [tile][phase][4] clocks: mma start, mma issued, accum full, epilogue done
+    int table_off;                                            // PH_TABLE: byte offset of the fp32 per-action table [A][HW][C]
     int z_bytes;                                              // > 0: head inputs stay in shared memory (Z) and the MLPs run in-kernel
     int z_rp;                                                 // channels per padded pixel row in Z's K order (multiple of 8)
     HeadTail head[3];
@@ -175,6 +176,31 @@ __device__ __forceinline__ void epi_store16(uint32_t* v, float bias, uint32_t m,
     epi_pair<12, RELU>(v[12], v[13], bias, m, xa); epi_pair<14, RELU>(v[14], v[15], bias, m, xa);
 }
 
+// Per-action table of the dynamics head -> R2 (fp32), for the games of one epilogue warp.  All of a game's loads are issued
+// before the first is used: the L2 latency is paid once per 64 columns, not once per 8-column chunk.  Kept out of line so that its
+// 64 staging registers do not weigh on the register allocation of the per-layer epilogue.
+__device__ __noinline__ void stage_table(const float* table_ch, const int* g_act, uint32_t pt, uint32_t t_r2, int P, int G, int hsel, long a_stride, int C, bool ch_ok) {
+    for (int g = hsel; g < G; g += F_EPI_SPLIT) {
+        const float* tg = table_ch + (long)g_act[g] * a_stride;
+        for (int cb = 0; cb < P; cb += 64) {
+            uint32_t tv[64];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                if (cb + 8 * k < P) {
+                    int pix[8];
+                    lds_v4(pt + (cb + 8 * k) * 4, pix); lds_v4(pt + (cb + 8 * k) * 4 + 16, pix + 4);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) tv[8 * k + j] = (ch_ok && pix[j] >= 0) ? __float_as_uint(__ldg(tg + (long)pix[j] * C)) : 0u;
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                if (cb + 8 * k < P) tmem_st8(t_r2 + (uint32_t)(g * P + cb + 8 * k), tv + 8 * k);
+        }
+    }
+    tmem_st_wait();
+}
+
 __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_constant__ FusedArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     // warp index / tile size through a lane-0 shuffle: the compiler's uniformity analysis then knows they are warp-uniform,
@@ -226,7 +252,10 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
         pixmask[tid] = m;
     }
     for (int i = tid; i < a.z_bytes / 16; i += F_THREADS) reinterpret_cast<uint4*>(Z)[i] = make_uint4(0u, 0u, 0u, 0u);
+    tc_fence_before();
     __syncthreads();
+    tc_fence_after();
+    if (a.tim && tid == 0) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 1) * 4 + 2] = clock64();   // set-up done
     // ---- chain input -> X (zero padded), 16 bytes = 8 channels of one pixel per request ----
     {
         const int kc = tid % KC, r0 = tid / KC, rstep = F_THREADS / KC;
@@ -242,12 +271,13 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
         }
     }
+    const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_ptr, 0);
     cp_async_wait_all();
     fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_ptr, 0);
+    if (a.tim && tid == 0) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 1) * 4 + 3] = clock64();   // chain input (and table) resident
 
     if (warp == 0) {
         if (lane == 0) {   // ===== weight producer: every stage of every phase, in order, as far ahead as the ring allows =====
@@ -373,6 +403,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             const int flags = ph.flags;
             // the per-channel bias is fetched BEFORE waiting for the accumulator: its L2 latency hides behind the MMAs
             const float bias_pf = (ph.bias_off >= 0) ? __ldg(reinterpret_cast<const float*>(a.blob + ph.bias_off) + ch) : 0.f;
+            if (flags & PH_TABLE)   // dynamics head: per-action table -> R2 (fp32) while the MMAs of this phase run into R1
+                stage_table(reinterpret_cast<const float*>(a.blob + a.table_off) + ch, g_act, pt, t_lane + (uint32_t)F_R2_COL, P, G, hsel, (long)HW * C, C, ch_ok);
             mbar_wait_dbg(accum_full, p & 1, a.dbg, 4, p);
             tc_fence_after();
             if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 2] = clock64();
@@ -472,28 +504,23 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 const uint32_t src_col = (flags & PH_ACC_R2) ? (uint32_t)F_R2_COL : 0u;
                 const float bias = ch_ok ? bias_pf : 0.f;
                 const bool relu = (flags & PH_RELU) != 0, stash = (flags & PH_STASH) != 0, wx = (flags & PH_WRITE_X) != 0 && ch_ok;
-                if (flags & PH_TABLE) {   // dynamics head: + per-action table (needs the pixel index: 8-column chunks)
-                    const float* table = reinterpret_cast<const float*>(a.blob + ph.table_off);
+                if (flags & PH_TABLE) {   // accumulator (R1) + staged per-action table (R2), 16 columns at a time
                     for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                         const int cbase = g * P;
-                        const float* tg = ch_ok ? table + (long)g_act[g] * HW * C + ch : nullptr;
-                        for (int c0 = 0; c0 < P; c0 += 8) {
-                            int pix[8];
-                            lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
-                            uint32_t v[8];
-                            tmem_ld8(t_lane + src_col + cbase + c0, v);
-                            float tv[8];
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) tv[j] = (tg && pix[j] >= 0) ? tg[(long)pix[j] * C] : 0.f;
+                        for (int c0 = 0; c0 < P; c0 += 16) {
+                            uint32_t v[16], w[16];
+                            tmem_ld16(t_lane + src_col + cbase + c0, v);
+                            tmem_ld16(t_lane + F_R2_COL + cbase + c0, w);
+                            const uint32_t m = lds_u32(pm + (c0 >> 5) * 4) >> (c0 & 16);
                             tmem_ld_wait();
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                float y = __uint_as_float(v[j]) + bias + tv[j];
-                                if (relu) y = fmaxf(y, 0.f);
-                                v[j] = __float_as_uint(y);
-                                if (wx && pix[j] >= 0) sts_u16(xs + (uint32_t)(cbase + c0 + j) * 16, __bfloat16_as_ushort(__float2bfloat16(y)));
+                            for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+                            const uint32_t xa = xs + (uint32_t)(cbase + c0) * 16;
+                            if (relu) epi_store16<true>(v, bias, wx ? m : 0u, xa); else epi_store16<false>(v, bias, wx ? m : 0u, xa);
+                            if (stash) {
+                                tmem_st8(t_lane + F_R2_COL + cbase + c0, v);
+                                if (c0 + 8 < P) tmem_st8(t_lane + F_R2_COL + cbase + c0 + 8, v + 8);
                             }
-                            if (stash) tmem_st8(t_lane + F_R2_COL + cbase + c0, v);
                         }
                     }
                 } else {

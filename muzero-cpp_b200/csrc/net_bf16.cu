@@ -255,6 +255,47 @@ __global__ void __launch_bounds__(UMMA_THREADS, 2) umma_conv3_kernel(UmmaArgs a)
 
 namespace {
 
+// Representation head convolution for a thin observation (ResidualHeadImpl, model_layers.cpp:95-109: conv3x3 + folded BN +
+// ReLU on cin = 3..16 planes).  One block per game, one thread per output channel: the zero-padded observation and the
+// [tap][cin][cout] weights sit in shared memory, reads are a broadcast (x) and a conflict-free row (w).  Reads the caller's
+// NCHW fp32 rows directly and writes NHWC bf16 — replaces a layout-conversion launch plus the generic direct kernel (142 us
+// for 1024 Connect4 boards) with ~10 us.
+__global__ void __launch_bounds__(128) head_conv_small_kernel(const float* __restrict__ obs, long obs_stride, const float* __restrict__ w,
+                                                              const float* __restrict__ bias, bf16* __restrict__ out, long out_stride,
+                                                              int cin, int cout, int H, int W, int relu) {
+    extern __shared__ float hsm[];
+    const int PW = W + 2, PH = H + 2;
+    float* xs = hsm;                         // [cin][PH][PW], zero border
+    float* ws = hsm + cin * PH * PW;         // [9 * cin][cout]
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const float* ob = obs + (long)b * obs_stride;
+    for (int i = tid; i < cin * PH * PW; i += blockDim.x) {
+        const int c = i / (PH * PW), r = i - c * PH * PW, y = r / PW - 1, x = r % PW - 1;
+        xs[i] = (y >= 0 && y < H && x >= 0 && x < W) ? ob[(c * H + y) * W + x] : 0.f;
+    }
+    for (int i = tid; i < 9 * cin * cout; i += blockDim.x) ws[i] = w[i];
+    __syncthreads();
+    for (int co = tid; co < cout; co += blockDim.x) {
+        const float bv = bias[co];
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x) {
+                float acc = 0.f;
+                for (int tap = 0; tap < 9; ++tap) {
+                    const float* xp = xs + (y + tap / 3) * PW + (x + tap % 3);
+                    const float* wp = ws + (long)tap * cin * cout + co;
+                    for (int c = 0; c < cin; ++c) acc += xp[c * PH * PW] * wp[c * cout];
+                }
+                acc += bv;
+                if (relu) acc = fmaxf(acc, 0.f);
+                out[(long)b * out_stride + (long)(y * W + x) * cout + co] = __float2bfloat16(acc);
+            }
+    }
+}
+
+}  // namespace
+
+namespace {
+
 // geometry of the padded resident tile for an H x W board; returns false when the shape does not fit the tensor path
 bool make_geom(int H, int W, int C, UmmaGeom* g) {
     g->H = H; g->W = W;
@@ -354,15 +395,22 @@ protected:
         extra->resize(off + (size_t)kbs * STAGE_BYTES, 0);
         bf16* dst = reinterpret_cast<bf16*>(extra->data() + off);
         std::vector<float> bias(128, 0.f);
+        // <= 32 stacked rows: the same rows are repeated in all four TMEM lane quarters (rows sr, 32 + sr, 64 + sr, 96 + sr), so
+        // that every epilogue warp — a warp only reaches its own quarter — can take a share of the columns (tower_fused.cuh, PH_RED)
+        int total = 0;
+        for (int h = 0; h < nh; ++h) total += hh[h]->red;
+        const int rep = total <= 32 ? 4 : 1;
         int row0 = 0;
         for (int h = 0; h < nh; ++h) {
             for (int r = 0; r < hh[h]->red; ++r) {
                 const int sr = row0 + r;                         // stacked row
-                const int lane = sr;
-                bias[sr] = hh[h]->b1[r];
-                for (int k = 0; k < C; ++k) {
-                    const int cc = k / KB, kc = (k % KB) / 8, e = k % 8;
-                    dst[(((size_t)cc * 8 + kc) * UM + lane) * 8 + e] = __float2bfloat16(hh[h]->w1[(size_t)r * C + k]);
+                for (int q = 0; q < rep; ++q) {
+                    const int lane = sr + 32 * q;
+                    bias[lane] = hh[h]->b1[r];
+                    for (int k = 0; k < C; ++k) {
+                        const int cc = k / KB, kc = (k % KB) / 8, e = k % 8;
+                        dst[(((size_t)cc * 8 + kc) * UM + lane) * 8 + e] = __float2bfloat16(hh[h]->w1[(size_t)r * C + k]);
+                    }
                 }
             }
             row0 += hh[h]->red;
@@ -573,14 +621,21 @@ protected:
         int dev = 0;
         MZB_CUDA(cudaGetDevice(&dev));
         MZB_CUDA(cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, dev));
-        size_t phases_rec = 1 + 2 * (steps_[1].size() - 1) + 1 + 2 * steps_[2].size() + 1 + 2;
+        size_t phases_rec = 1 + 2 * (steps_[1].size() - 1) + 2 + 2 * steps_[2].size() + 1 + 2;
         if (phases_rec > (size_t)fused::F_MAX_PHASES) { fused_rec_.ok = false; fused_init_.ok = false; return MZB_OK; }
         {   // recurrent: dynamics head, dynamics blocks, reward conv1x1 + normalise, prediction blocks, policy/value conv1x1
             fused::FusedArgs* fa = &fused_rec_.args;
             fa->n_phases = 0; fa->preload = 0;
             add_conv_phase(fa, 1, steps_[1][0].conv0, fused::PH_WRITE_X | fused::PH_STASH);
             add_blocks(fa, 1, 1);
-            add_conv1_phase(fa, 0, fused::PH_NORM, C);
+            if (fa->z_bytes) {
+                // reward 1x1 conv -> Z, then normalisation as its own MMA-less phase that releases the MMA warp BEFORE it starts:
+                // the reward MLP's first layer (reads Z only) runs on the tensor core while the epilogue warps normalise
+                add_conv1_phase(fa, 0, 0, C);
+                add_conv1_phase(fa, -1, fused::PH_NORM | fused::PH_EARLY, C);
+            } else {
+                add_conv1_phase(fa, 0, fused::PH_NORM, C);
+            }
             add_mlp_phase(fa, 0);
             add_blocks(fa, 2, 0);
             add_conv1_phase(fa, 1, 0, C);
@@ -795,11 +850,21 @@ public:
         if (!fused_init_.ok) return direct::DirectBackend<bf16>::initial(d_obs, B, d_out_slot, out, s);
         MZB_REQUIRE(B <= max_batch_, "batch %d above engine capacity %d", B, max_batch_);
         const NetDims& d = plan_dims_;
-        long total = (long)B * d.initial_flat();
-        direct::nchw_to_nhwc_kernel<bf16><<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_obs, bufA_.as<bf16>(), nullptr, (long)d.initial_flat(), B, d.cin, d.in_h * d.in_w);
-        launches_ = 1;
-        rc = launch_conv(convs_[0][0], B, bufA_.as<bf16>(), nullptr, (long)d.initial_flat(), bufB_.as<bf16>(), nullptr, nullptr, 0, nullptr, s);
-        if (rc) return rc;
+        const direct::ConvDev& c0 = convs_[0][0];
+        const size_t head_smem = ((size_t)c0.cin * (c0.in_h + 2) * (c0.in_w + 2) + (size_t)9 * c0.cin * c0.cout) * sizeof(float);
+        if (c0.stride == 1 && c0.cin <= 16 && !c0.has_table && c0.in_h == c0.out_h && c0.in_w == c0.out_w && head_smem <= 48 * 1024) {
+            const float* base = blob_.as<float>();
+            head_conv_small_kernel<<<B, 128, head_smem, s>>>(d_obs, (long)d.initial_flat(), base + c0.w_off, base + c0.bias_off, bufB_.as<bf16>(),
+                                                            (long)slot_elems_, c0.cin, c0.cout, c0.in_h, c0.in_w, c0.relu);
+            MZB_CUDA(cudaGetLastError());
+            launches_ = 1;
+        } else {
+            long total = (long)B * d.initial_flat();
+            direct::nchw_to_nhwc_kernel<bf16><<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_obs, bufA_.as<bf16>(), nullptr, (long)d.initial_flat(), B, d.cin, d.in_h * d.in_w);
+            launches_ = 1;
+            rc = launch_conv(c0, B, bufA_.as<bf16>(), nullptr, (long)d.initial_flat(), bufB_.as<bf16>(), nullptr, nullptr, 0, nullptr, s);
+            if (rc) return rc;
+        }
         rc = launch_fused(fused_init_, B, bufB_.as<bf16>(), nullptr, (long)slot_elems_, d_out_slot, nullptr, out, s);
         if (rc) return rc;
         if (!fused_init_.args.z_bytes) {
@@ -808,7 +873,7 @@ public:
         }
         initial_reward_kernel<<<(B + 127) / 128, 128, 0, s>>>(out.reward, B, renc_.support, (float)renc_.step, (float)renc_.min_value, renc_.contractive);
         MZB_CUDA(cudaGetLastError());
-        launches_initial_ = launches_ + 3;
+        launches_initial_ = launches_ + 2 + (fused_init_.args.z_bytes ? 0 : 1);   // + fused chain, (+ MLP kernel), + initial reward
         return MZB_OK;
     }
 

@@ -53,6 +53,7 @@ enum : int {
     PH_WRITE_X = 16,  // store the epilogue result into X (bf16)
     PH_RED = 32,      // 1x1 head convolution: rows of R1 -> red[] buffers (no activation)
     PH_NORM = 64,     // normalize_hidden_state on R2 -> X, node pool slot, R2
+    PH_EARLY = 256,   // (with PH_NORM) the next phase does not read this one's output: release the MMA warp before the epilogue work
     PH_MLP = 128,     // head MLPs: first layer on the tensor core (A = stacked W0 images, B = Z), later layers + output transform on CUDA cores
 };
 
@@ -398,6 +399,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             __syncwarp();
             if (lane == 0) mbar_arrive(act_ready);
         }
+        bool pool_pending = false;
         for (int p = 0; p < a.n_phases; ++p) {
             const Phase& ph = a.ph[p];
             const int flags = ph.flags;
@@ -408,10 +410,37 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             mbar_wait_dbg(accum_full, p & 1, a.dbg, 4, p);
             tc_fence_after();
             if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 2] = clock64();
+            if (flags & PH_EARLY) {   // nothing the next phase reads is produced here (its inputs were fenced by the previous arrive)
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(act_ready);
+            }
             if (flags & PH_RED) {
                 // 1x1 head convolution: lane = stacked reduced channel (head0's rows, then head1's), column = padded pixel row
                 const int nred = ph.red_n0 + ph.red_n1;
-                if (32 * q < nred) {   // warp-uniform; lanes beyond nred only skip the stores
+                if (a.z_bytes && nred <= 32) {
+                    // the stacked rows are repeated in every lane quarter (pack_conv1): quarter q takes the 16-column chunks
+                    // k = q, q + 4, ... of its games, so all eight warps share the work instead of the two of quarter 0
+                    const bool row_ok = lane < nred;
+                    const bool second = lane >= ph.red_n0;
+                    const int rr = second ? lane - ph.red_n0 : lane;
+                    const float bias = row_ok ? bias_pf : 0.f;
+                    const uint32_t zl = smem_u32(Z) + (second ? 128u : 0u) + (uint32_t)((rr >> 3) * 256 + (rr & 7) * 2);
+                    const uint32_t cstride = (uint32_t)(a.z_rp >> 3) * 256u;
+                    for (int g = hsel; g < G; g += F_EPI_SPLIT) {
+                        const int cbase = g * P;
+                        for (int c0 = 16 * q; c0 < P; c0 += 64) {
+                            uint32_t v[16];
+                            tmem_ld16(t_lane + cbase + c0, v);
+                            tmem_ld_wait();
+                            const uint32_t za = zl + (uint32_t)g * 16u + (uint32_t)c0 * cstride;
+#pragma unroll
+                            for (int j = 0; j < 16; ++j)
+                                if (row_ok && c0 + j < P)
+                                    sts_u16(za + (uint32_t)j * cstride, __bfloat16_as_ushort(__float2bfloat16(__uint_as_float(v[j]) + bias)));
+                        }
+                    }
+                } else if (32 * q < nred) {   // warp-uniform; lanes beyond nred only skip the stores
                     const bool row_ok = ch < nred;
                     const bool second = ch >= ph.red_n0;
                     const int rr = second ? ch - ph.red_n0 : ch;
@@ -570,7 +599,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             fence_proxy_async_smem();   // generic-proxy stores into X / Z -> visible to the tensor core's operand reads
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(act_ready);
+            if (lane == 0 && !(flags & PH_EARLY)) mbar_arrive(act_ready);
             if (flags & PH_MLP) {
                 // remaining layers (model_layers.cpp:46-65) and the output transform on CUDA cores, overlapped with the next
                 // phase's MMAs: policy softmax (vprnet.cpp:118-119,178-179) / ValueEncoder::decode (util.cpp:80-87)
@@ -639,7 +668,9 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");   // Hs is free again
             }
-            if (flags & PH_NORM) {
+            if (flags & PH_EARLY) pool_pending = true;   // the copy below would sit on the critical path: do it after the next arrive
+            if (((flags & PH_NORM) && !(flags & PH_EARLY)) || (pool_pending && !(flags & PH_EARLY))) {
+                pool_pending = false;
                 // child hidden state -> node pool, straight from X (bf16, already normalised): 16-byte coalesced stores,
                 // overlapped with the next phase's MMAs (which only read X)
                 asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");   // every epilogue warp has finished writing X

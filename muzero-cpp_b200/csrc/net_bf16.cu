@@ -787,6 +787,17 @@ protected:
                 pro[g] += row[0] - ends[0]; body[g] += row[(size_t)(a.n_phases - 1) * 4 + 3] - row[0]; tail[g] += ends[1] - row[(size_t)(a.n_phases - 1) * 4 + 3];
                 ++cnt[g];
             }
+            {   // last MLP phase, relative to its accumulator-ready time: Hs ready | layers done | outputs written | phase end
+                double m0 = 0, m1 = 0, m2 = 0, m3 = 0;
+                for (int t = 0; t < tt->n_tiles; ++t) {
+                    const long long* row = &h[(size_t)t * fused::F_MAX_PHASES * 4];
+                    const long long* pr = row + (size_t)(fused::F_MAX_PHASES - 2) * 4;
+                    const long long* last = row + (size_t)(a.n_phases - 1) * 4;
+                    m0 += pr[0] - last[2]; m1 += pr[1] - last[2]; m2 += pr[2] - last[2]; m3 += last[3] - last[2];
+                }
+                const int n = tt->n_tiles;
+                fprintf(stderr, "[fused]  last MLP tail: Hs ready %6.0f | layers done %6.0f | outputs written %6.0f | end %6.0f\n", m0 / n, m1 / n, m2 / n, m3 / n);
+            }
             for (int g = 1; g <= fused::F_MAX_G; ++g)
                 if (cnt[g]) fprintf(stderr, "[fused]  tiles of %d games: %d; prologue %7.0f (set-up %5.0f, input %5.0f) | phases %7.0f | tail %7.0f cycles\n", g, cnt[g], pro[g] / cnt[g], setup[g] / cnt[g], inp[g] / cnt[g], body[g] / cnt[g], tail[g] / cnt[g]);
         }

@@ -604,68 +604,109 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 // remaining layers (model_layers.cpp:46-65) and the output transform on CUDA cores, overlapped with the next
                 // phase's MMAs: policy softmax (vprnet.cpp:118-119,178-179) / ValueEncoder::decode (util.cpp:80-87)
                 asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");
+                if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 2) * 4 + 0] = clock64();
                 const int et = tid - 64;
                 const int nh = ph.red_n1 > 0 ? 2 : 1;
                 float* cur = Hs;
                 float* nxt = Hs + 8 * 128;
                 const int n_layers = a.head[ph.red_head0].n_layers;
                 for (int l = 1; l < n_layers; ++l) {
-                    for (int hh = 0; hh < nh; ++hh) {
-                        const HeadTail& hd = a.head[hh ? ph.red_head1 : ph.red_head0];
-                        const int nin = hd.sizes[l], nout = hd.sizes[l + 1];
-                        const int ibase = hh ? a.head[ph.red_head0].sizes[l] : 0, obase = hh ? a.head[ph.red_head0].sizes[l + 1] : 0;
-                        const float* __restrict__ Wl = hd.W[l];
-                        // four threads per output: the weight rows come from L2, so the loads of a dot product must
-                        // be issued together rather than chained
-                        for (int base = 0; base < G * nout; base += F_EPI_THREADS / 4) {   // warp-uniform trip count
-                            const int i = base + (et >> 2), part = et & 3;
-                            const bool on = i < G * nout;
-                            const int g = on ? i / nout : 0, o = on ? i - g * nout : 0;
-                            const float* wr = Wl + (long)o * nin;
-                            const float* xr = cur + g * 128 + ibase;
-                            float acc = 0.f;
-                            if (on) {
-#pragma unroll 8
-                                for (int k = part; k < nin; k += 4) acc += __ldg(wr + k) * xr[k];
-                            }
-                            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-                            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-                            if (on && part == 0) {
-                                acc += hd.b[l][o];
-                                if (l < n_layers - 1) acc = fmaxf(acc, 0.f);
-                                nxt[g * 128 + obase + o] = acc;
-                            }
+                    // both heads in ONE pass (their weight rows come from L2: one exposed latency per layer, not one per head);
+                    // 4 threads per output when that fits the 256 epilogue threads, else 2
+                    const HeadTail& h0 = a.head[ph.red_head0];
+                    const HeadTail& h1 = a.head[ph.red_head1];
+                    const int nin0 = h0.sizes[l], nout0 = h0.sizes[l + 1], nout1 = nh > 1 ? h1.sizes[l + 1] : 0;
+                    const int tot = nout0 + nout1;
+                    const int tpo = (G * tot * 4 <= F_EPI_THREADS) ? 4 : 2;   // warp-uniform
+                    for (int base = 0; base < G * tot; base += F_EPI_THREADS / tpo) {   // warp-uniform trip count
+                        const int i = base + et / tpo, part = et % tpo;
+                        const bool on = i < G * tot;
+                        const int g = on ? i / tot : 0, o = on ? i - g * tot : 0;
+                        const bool second = o >= nout0;
+                        const HeadTail& hd = second ? h1 : h0;
+                        const int oo = second ? o - nout0 : o;
+                        const int nin = hd.sizes[l];
+                        const float* wr = hd.W[l] + (long)oo * nin;
+                        const float* xr = cur + g * 128 + (second ? nin0 : 0);
+                        const float bl = (on && part == 0) ? __ldg(hd.b[l] + oo) : 0.f;   // in flight together with the weights
+                        float acc = 0.f;
+                        if (on) {
+        #pragma unroll 16
+                            for (int k = part; k < nin; k += tpo) acc += __ldg(wr + k) * xr[k];
+                        }
+                        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+                        if (tpo == 4) acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+                        if (on && part == 0) {
+                            acc += bl;
+                            if (l < n_layers - 1) acc = fmaxf(acc, 0.f);
+                            nxt[g * 128 + (second ? nout0 : 0) + oo] = acc;
                         }
                     }
                     asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");
                     float* t = cur; cur = nxt; nxt = t;
                 }
-                if (et < G * nh) {
-                    const int g = et / nh, hh = et - g * nh;
+                if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 2) * 4 + 1] = clock64();
+                // output transform, one warp per (game, head), lane = logit: softmax by warp reductions (vprnet.cpp:118-119,
+                // 178-179) / expected support value + inverse contractive map (util.cpp:80-87).  Heads wider than a warp take the
+                // serial form on one lane.
+                for (int item = (tid - 64) >> 5; item < G * nh; item += F_EPI_WARPS) {   // warp-uniform
+                    const int g = item / nh, hh = item - g * nh;
                     const HeadTail& hd = a.head[hh ? ph.red_head1 : ph.red_head0];
                     const int n = hd.sizes[n_layers];
                     const float* lg = cur + g * 128 + (hh ? a.head[ph.red_head0].sizes[n_layers] : 0);
-                    float mx = lg[0];
-                    for (int i = 1; i < n; ++i) mx = fmaxf(mx, lg[i]);
-                    float sum = 0.f;
-                    for (int i = 0; i < n; ++i) sum += expf(lg[i] - mx);
                     const long b = game0 + g;
-                    if (hd.out_kind == 0) {
-                        for (int i = 0; i < n; ++i) hd.out[b * hd.out_stride + i] = (double)(expf(lg[i] - mx) / sum);
-                    } else {
-                        float ev = 0.f;
-                        for (int i = 0; i < n; ++i) ev += (float)i * (expf(lg[i] - mx) / sum);
-                        float v = ev * hd.step + hd.min_value;
-                        if (hd.contractive) {
-                            const float eps = 0.001f;
-                            const float sg = (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f);
-                            const float inner = sqrtf(1.f + (4.f * eps) * (fabsf(v) + 1.f + eps)) - 1.f;
-                            const float qq = inner / (2.f * eps);
-                            v = sg * (qq * qq - 1.f);
+                    if (n <= 32) {
+                        const float x = lane < n ? lg[lane] : -3.402823466e38f;
+                        float mx = x;
+        #pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                        const float e = lane < n ? expf(x - mx) : 0.f;
+                        float sum = e;
+        #pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                        const float pr = e / sum;
+                        if (hd.out_kind == 0) {
+                            if (lane < n) hd.out[b * hd.out_stride + lane] = (double)pr;
+                        } else {
+                            // sum_i i * p_i in index order, as the reference's torch::sum over the support does on one row
+                            float ev = (float)lane * pr;   // lanes >= n hold 0
+        #pragma unroll
+                            for (int o = 16; o > 0; o >>= 1) ev += __shfl_xor_sync(0xffffffffu, ev, o);
+                            if (lane == 0) {
+                                float v = ev * hd.step + hd.min_value;
+                                if (hd.contractive) {
+                                    const float eps = 0.001f;
+                                    const float sg = (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f);
+                                    const float inner = sqrtf(1.f + (4.f * eps) * (fabsf(v) + 1.f + eps)) - 1.f;
+                                    const float qq = inner / (2.f * eps);
+                                    v = sg * (qq * qq - 1.f);
+                                }
+                                hd.out[b * hd.out_stride] = (double)v;
+                            }
                         }
-                        hd.out[b * hd.out_stride] = (double)v;
+                    } else if (lane == 0) {
+                        float mx = lg[0];
+                        for (int i = 1; i < n; ++i) mx = fmaxf(mx, lg[i]);
+                        float sum = 0.f;
+                        for (int i = 0; i < n; ++i) sum += expf(lg[i] - mx);
+                        if (hd.out_kind == 0) {
+                            for (int i = 0; i < n; ++i) hd.out[b * hd.out_stride + i] = (double)(expf(lg[i] - mx) / sum);
+                        } else {
+                            float ev = 0.f;
+                            for (int i = 0; i < n; ++i) ev += (float)i * (expf(lg[i] - mx) / sum);
+                            float v = ev * hd.step + hd.min_value;
+                            if (hd.contractive) {
+                                const float eps = 0.001f;
+                                const float sg = (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f);
+                                const float inner = sqrtf(1.f + (4.f * eps) * (fabsf(v) + 1.f + eps)) - 1.f;
+                                const float qq = inner / (2.f * eps);
+                                v = sg * (qq * qq - 1.f);
+                            }
+                            hd.out[b * hd.out_stride] = (double)v;
+                        }
                     }
                 }
+                if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 2) * 4 + 2] = clock64();
                 asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");   // Hs is free again
             }
             if (flags & PH_EARLY) pool_pending = true;   // the copy below would sit on the critical path: do it after the next arrive

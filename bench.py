@@ -56,7 +56,7 @@ def ncu_traffic(workload, trees):
 
 class ClockSampler:
     """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md clocks line).  NVML in a
-    thread every 5 ms (a 50-simulation search lasts ~17 ms, shorter than one `nvidia-smi -lms` period); falls back to
+    thread every 25 ms (NVML queries take driver locks that delay kernel launches: sampled sparsely on purpose; the default 20 steps give ~10 samples); falls back to
     the nvidia-smi loop when the NVML binding is missing."""
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
     BITS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
@@ -96,7 +96,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.005)
+            time.sleep(0.025)
 
     def _read(self):
         for line in self.proc.stdout:

@@ -22,6 +22,7 @@
 
 #include <map>
 
+#include "conv_band.cuh"
 #include "net_direct.cuh"
 #include "tower_fused.cuh"
 #include "umma.cuh"
@@ -336,9 +337,12 @@ protected:
                 Packed p;
                 // the weight image only needs a 64-multiple of input channels and <= 128 outputs; the per-layer kernel
                 // additionally wants its own tile geometry to fit twice per SM
-                if (c.stride != 1 || c.cin % KB != 0 || c.cout > UM || c.cout % 8 != 0 || c.in_h != c.out_h || c.in_w != c.out_w) continue;
+                // (a stride-2 conv is the stride-1 conv sampled at even positions: same image, taken by the band kernel only)
+                const bool same = c.stride == 1 && c.in_h == c.out_h && c.in_w == c.out_w;
+                const bool half = c.stride == 2 && c.out_h == (c.in_h + 1) / 2 && c.out_w == (c.in_w + 1) / 2;
+                if ((!same && !half) || c.cin % KB != 0 || c.cout > UM || c.cout % 8 != 0) continue;
                 p.image = true;
-                p.ok = eligible(c, &p.g);
+                p.ok = same && eligible(c, &p.g);
                 while (extra->size() % 128) extra->push_back(0);
                 p.off = extra->size();
                 const int kb_per_tap = c.cin / KB;
@@ -905,7 +909,7 @@ protected:
     int fast_conv(const direct::ConvCall<bf16>& call, cudaStream_t s) override {
         const direct::ConvDev& c = *call.conv;
         const Packed& p = packed_[c.tower][c.index];
-        if (!p.ok) return 0;
+        if (!p.ok) return p.image && !c.has_table ? band_conv(call, p, s) : 0;
         const float* base = blob_.as<float>();
         UmmaArgs a;
         a.in = call.in; a.in_slot = call.in_slot; a.in_stride = call.in_stride;
@@ -945,7 +949,44 @@ protected:
         return 1;
     }
 
+    // boards too large for a whole-game tile (downsample representation head): one CTA per band of rows (conv_band.cuh)
+    int band_conv(const direct::ConvCall<bf16>& call, const Packed& p, cudaStream_t s) {
+        static const bool off = getenv("MZB_NO_BAND_CONV") != nullptr;
+        if (off) return 0;
+        const direct::ConvDev& c = *call.conv;
+        band::BandArgs a;
+        a.stride = c.stride;
+        a.rb = band::band_rows(c.in_h, c.in_w);
+        if (c.stride == 2) a.rb = a.rb / 2 * 2;   // bands start on even rows
+        if (a.rb < 1) return 0;
+        a.bands = (c.in_h + a.rb - 1) / a.rb;
+        a.N = ((a.rb + 2) * (c.in_w + 1) + 15) / 16 * 16;
+        a.HALO = c.in_w + 2;
+        a.R = a.HALO + a.N + a.HALO;
+        a.x_bytes = (int)((((size_t)(c.cin / 8) * a.R * 16) + 127) / 128 * 128);
+        // fp32 output staging reuses the ring after the MMAs: it must hold rb rows x W pixels x cout floats
+        const size_t stage_need = (size_t)a.rb * c.in_w * c.cout * sizeof(float);
+        a.nstage = (band::band_smem_bytes(a.x_bytes, 2) <= 113 * 1024 && stage_need <= 2 * (size_t)band::B_STAGE_BYTES) ? 2 : 4;
+        const size_t smem = band::band_smem_bytes(a.x_bytes, a.nstage);
+        if (a.N > 256 || smem > 227 * 1024 || stage_need > (size_t)a.nstage * band::B_STAGE_BYTES) return 0;
+        if (!band_attr_set_) {
+            MZB_CUDA(cudaFuncSetAttribute(band::conv_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            band_attr_set_ = true;
+        }
+        a.in = call.in; a.in_slot = call.in_slot; a.in_stride = call.in_stride;
+        a.out = call.out; a.out_slot = call.out_slot; a.out_stride = call.out_stride;
+        a.res = call.res; a.res_slot = call.res_slot; a.res_stride = call.res_stride;
+        a.wimg = reinterpret_cast<const uint8_t*>(blob_.p) + fp32_bytes_ + p.off;
+        a.bias = blob_.as<float>() + c.bias_off;
+        a.H = c.in_h; a.W = c.in_w; a.cin = c.cin; a.cout = c.cout; a.relu = c.relu;
+        band::conv_band_kernel<<<call.B * a.bands, band::B_THREADS, smem, s>>>(a);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("conv_band_kernel launch failed: %s", cudaGetErrorString(e)); return MZB_ERR_CUDA; }
+        return 1;
+    }
+
     std::vector<Packed> packed_[3];
+    bool band_attr_set_ = false;
     DevBuf dbg_;
     bool attr_set_ = false;
 };

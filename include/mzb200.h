@@ -156,6 +156,13 @@ int mzb_search_get_trace(mzb_engine* e, int n_trees, int32_t* parent /*[T][n]*/,
 int mzb_search_get_records(mzb_engine* e, int n_trees, double* value /*[T][n+1]*/, double* reward /*[T][n+1]*/,
                            double* policy /*[T][n+1][A]*/);
 
+/* ValueEncoder::encode (util.cpp:59-76) and ::decode (util.cpp:80-87) of the engine's value (which = 0) or reward (which = 1)
+ * encoder, on the GPU, host pointers in and out: n scalars <-> n rows of support_size floats (mzb_shapes gives the sizes).
+ * decode is what the head kernels fuse during inference; encode builds categorical targets (VPRNetModel::Learn's callers,
+ * vprnet.cpp:240-243) and backs the reference's own round-trip tests (tests/util_test.cpp). */
+int mzb_value_encode(mzb_engine* e, int which, const float* x, int n, float* support /*[n][S]*/);
+int mzb_value_decode(mzb_engine* e, int which, const float* logits /*[n][S]*/, int n, int take_softmax, float* x /*[n]*/);
+
 /* derived shapes (VPRNetModel ctor, vprnet.cpp:41-46; ValueEncoder::get_support_size, util.cpp:91-102) */
 typedef struct {
     int32_t initial_channels, initial_flat_size; /* Cin, Cin*H*W */

@@ -20,6 +20,7 @@ SOURCES = [
     ("engine.cu", []),
     ("engine_search.cu", []),
     ("engine_nccl.cu", []),
+    ("value_encoder.cu", ["-fmad=false"]),
 ]
 
 

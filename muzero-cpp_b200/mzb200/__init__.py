@@ -148,7 +148,7 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_nccl_unique_id", "mzb_nccl_init", "mzb_broadcast_weights", "mzb_weights_checksum",
            "mzb_initial_inference", "mzb_recurrent_inference", "mzb_bench_recurrent", "mzb_search_seed", "mzb_search_batch_slots",
            "mzb_search_batch", "mzb_search_batch_device_obs", "mzb_last_search_timing", "mzb_search_set_recording",
-           "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes"]
+           "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes", "mzb_value_encode", "mzb_value_decode"]
 
 
 def load_library(path=None):
@@ -186,6 +186,8 @@ def load_library(path=None):
     lib.mzb_search_get_trace.argtypes = [C.c_void_p, C.c_int, ip, ip]
     lib.mzb_search_get_records.argtypes = [C.c_void_p, C.c_int, dp, dp, dp]
     lib.mzb_get_shapes.argtypes = [C.c_void_p, C.POINTER(_CShapes)]
+    lib.mzb_value_encode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, fp]
+    lib.mzb_value_decode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, C.c_int, fp]
     _lib = lib
     return lib
 
@@ -260,6 +262,21 @@ class Engine:
         sh = _CShapes()
         self._check(self.lib.mzb_get_shapes(self._h, C.byref(sh)))
         return sh
+
+    # ValueEncoder::encode / decode (util.cpp:59-87); which = 0 value encoder, 1 reward encoder
+    def value_encode(self, x, which=0):
+        x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
+        S = self.shapes.value_support_size if which == 0 else self.shapes.reward_support_size
+        out = np.empty((x.shape[0], S), np.float32)
+        self._check(self.lib.mzb_value_encode(self._h, which, _ptr(x, C.c_float), x.shape[0], _ptr(out, C.c_float)))
+        return out
+
+    def value_decode(self, logits, which=0, take_softmax=True):
+        S = self.shapes.value_support_size if which == 0 else self.shapes.reward_support_size
+        lg = np.ascontiguousarray(logits, dtype=np.float32).reshape(-1, S)
+        out = np.empty(lg.shape[0], np.float32)
+        self._check(self.lib.mzb_value_decode(self._h, which, _ptr(lg, C.c_float), lg.shape[0], int(bool(take_softmax)), _ptr(out, C.c_float)))
+        return out
 
     # VPRNetModel::LoadCheckpoint (vprnet.cpp:66-74): named fp32 tensors of the module archive
     def load_weights(self, tensors: dict):

@@ -156,6 +156,32 @@ int mzb_search_get_trace(mzb_engine* e, int n_trees, int32_t* parent /*[T][n]*/,
 int mzb_search_get_records(mzb_engine* e, int n_trees, double* value /*[T][n+1]*/, double* reward /*[T][n+1]*/,
                            double* policy /*[T][n+1][A]*/);
 
+/* ---- The callers' side: observation history and action selection for cohorts of games ----
+ * Device-resident observation history per tree slot, stacked on the GPU the way GameHistory::get_stacked_observations
+ * (types.cpp:16-42) does on the host: current frame, then for each of the previous `stacked_observations` steps the frame and
+ * the planes of the action taken from it, zero planes where the game is younger.  play_game (self_play.cpp:84-160) maps to:
+ *   reset -> mzb_obs_ring_reset;  game_history.observation_history/action_history.push_back -> mzb_obs_ring_push (one new frame
+ *   per game and move crosses PCIe, not the stacked observation);  get_stacked_observations(-1, ...) + mcts.run ->
+ *   mzb_search_batch_ring;  select_action -> mzb_select_actions.
+ * action_planes_initial: config.action_representation_initial pre-evaluated, [num_actions][action_channels * h * w] at
+ * OBSERVATION resolution; NULL = the shipped examples' constant plane action / num_actions. */
+int mzb_obs_ring_create(mzb_engine* e, const float* action_planes_initial);
+int mzb_obs_ring_reset(mzb_engine* e, const int32_t* slots, int n);
+/* frames [n][c*h*w] (one raw observation per game); actions[i] = the action that led to it (ignored for a game's first frame:
+ * the reference stores a dummy 0 there, self_play.cpp:91) */
+int mzb_obs_ring_push(mzb_engine* e, const int32_t* slots, const float* frames, const int32_t* actions, int n);
+/* the stacked observations of the slots' current positions, copied to the host (checking / callers that want the tensor) */
+int mzb_obs_ring_stacked(mzb_engine* e, const int32_t* slots, int n, float* out /*[n][initial_flat_size]*/);
+/* mzb_search_batch_slots with the observations taken from the ring (stacked on the device, no host copy) */
+int mzb_search_batch_ring(mzb_engine* e, const int32_t* slots, const uint32_t* legal_mask, const int32_t* to_play,
+                          const uint8_t* add_noise, int n_trees, mzb_search_result* out);
+/* select_action (self_play.cpp:21-39): row i of `stats` with slot i's actor generator — std::mt19937(config.seed + actor_num),
+ * self_play.cpp:233, a stream of its own next to the search's.  temperature <= 0: first maximum of the relative visits;
+ * otherwise one std::discrete_distribution draw over visits^(1/temperature). */
+int mzb_actor_seed(mzb_engine* e, const int32_t* slots, const int32_t* seeds, int n);
+int mzb_select_actions(mzb_engine* e, const int32_t* slots, const mzb_search_result* stats, int n, const double* temperature,
+                       int32_t* actions_out);
+
 /* ValueEncoder::encode (util.cpp:59-76) and ::decode (util.cpp:80-87) of the engine's value (which = 0) or reward (which = 1)
  * encoder, on the GPU, host pointers in and out: n scalars <-> n rows of support_size floats (mzb_shapes gives the sizes).
  * decode is what the head kernels fuse during inference; encode builds categorical targets (VPRNetModel::Learn's callers,

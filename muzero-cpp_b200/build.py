@@ -21,6 +21,7 @@ SOURCES = [
     ("engine_search.cu", []),
     ("engine_nccl.cu", []),
     ("value_encoder.cu", ["-fmad=false"]),
+    ("selfplay.cu", []),
 ]
 
 

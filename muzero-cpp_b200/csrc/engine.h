@@ -34,6 +34,9 @@ struct HostMt {
 
 using namespace mzb;
 
+namespace mzb { struct ObsRing; void obs_ring_free(ObsRing*); }
+struct ObsRingDeleter { void operator()(mzb::ObsRing* r) const { mzb::obs_ring_free(r); } };
+
 struct mzb_engine {
     mzb_config cfg;
     int device = 0;
@@ -67,6 +70,8 @@ struct mzb_engine {
     // compat-path scratch
     DevBuf c_hidden_in, c_hidden_out, c_action;
     mzb_search_timing timing;
+    // device-resident observation history + actor generators (selfplay.cu)
+    std::unique_ptr<mzb::ObsRing, ObsRingDeleter> ring;
     // nccl (dlopen'ed)
     void* nccl_lib = nullptr;
     void* nccl_comm = nullptr;

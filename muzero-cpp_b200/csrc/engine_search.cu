@@ -179,6 +179,47 @@ int check_search_args(mzb_engine* e, const void* obs, const uint32_t* legal_mask
 
 }  // namespace
 
+namespace mzb {
+// A search over chosen tree slots whose observation rows already sit in e->d_obs (ordered like `slots`): gathers the slots' RNG
+// rows into a compact block, searches, scatters the advanced generators back.  Shared by mzb_search_batch_slots (rows uploaded
+// from the host) and mzb_search_batch_ring (rows stacked on the device from the observation ring, selfplay.cu).
+int search_with_device_obs_slots(mzb_engine* e, const int32_t* slots, const uint32_t* legal_mask, const int32_t* to_play,
+                                 const uint8_t* add_noise, int n_trees, mzb_search_result* out) {
+    int rc = check_search_args(e, e->d_obs.p, legal_mask, to_play, add_noise, n_trees);
+    if (rc) return rc;
+    MZB_REQUIRE(slots, "null slot list");
+    const int T = e->cfg.max_trees;
+    std::vector<uint8_t> seen(T, 0);
+    for (int i = 0; i < n_trees; ++i) {
+        MZB_REQUIRE(slots[i] >= 0 && slots[i] < T, "row %d: slot %d outside [0, %d)", i, slots[i], T);
+        MZB_REQUIRE(!seen[slots[i]], "slot %d appears twice", slots[i]);
+        seen[slots[i]] = 1;
+    }
+    if (!e->d_slots.p) {
+        MZB_CUDA(e->d_slots.alloc((size_t)T * sizeof(int)));
+        MZB_CUDA(e->mt_rows.alloc((size_t)T * 624 * sizeof(uint32_t)));
+        MZB_CUDA(e->mt_idx_rows.alloc((size_t)T * sizeof(int)));
+    }
+    cudaStream_t s = e->stream;
+    MZB_CUDA(cudaMemcpyAsync(e->d_slots.p, slots, (size_t)n_trees * sizeof(int), cudaMemcpyHostToDevice, s));
+    uint32_t* home = e->td.mt;
+    int* home_idx = e->td.mt_idx;
+    launch_mt_move(home, home_idx, e->mt_rows.as<uint32_t>(), e->mt_idx_rows.as<int>(), e->d_slots.as<int>(), n_trees, 0, s);
+    MZB_CUDA(cudaStreamSynchronize(s));   // the Dirichlet draws on the aux stream read the gathered rows
+    const int stride = (e->cfg.evaluator == MZB_EVAL_SYNTHETIC) ? 1 : e->dims.initial_flat();
+    e->td.mt = e->mt_rows.as<uint32_t>();
+    e->td.mt_idx = e->mt_idx_rows.as<int>();
+    rc = search_impl(e, e->d_obs.as<float>(), stride, legal_mask, to_play, add_noise, n_trees, out);
+    e->td.mt = home;
+    e->td.mt_idx = home_idx;
+    if (rc) return rc;
+    launch_mt_move(home, home_idx, e->mt_rows.as<uint32_t>(), e->mt_idx_rows.as<int>(), e->d_slots.as<int>(), n_trees, 1, s);
+    MZB_CUDA(cudaStreamSynchronize(s));
+    MZB_CUDA(cudaGetLastError());
+    return MZB_OK;
+}
+}  // namespace mzb
+
 extern "C" {
 
 int mzb_search_batch(mzb_engine* e, const float* obs, const uint32_t* legal_mask, const int32_t* to_play,
@@ -197,37 +238,10 @@ int mzb_search_batch_slots(mzb_engine* e, const float* obs, const int32_t* slots
     int rc = check_search_args(e, obs, legal_mask, to_play, add_noise, n_trees);
     if (rc) return rc;
     MZB_REQUIRE(slots, "null slot list");
-    const int T = e->cfg.max_trees;
-    std::vector<uint8_t> seen(T, 0);
-    for (int i = 0; i < n_trees; ++i) {
-        MZB_REQUIRE(slots[i] >= 0 && slots[i] < T, "row %d: slot %d outside [0, %d)", i, slots[i], T);
-        MZB_REQUIRE(!seen[slots[i]], "slot %d appears twice", slots[i]);
-        seen[slots[i]] = 1;
-    }
     MZB_CUDA(cudaSetDevice(e->device));
-    if (!e->d_slots.p) {
-        MZB_CUDA(e->d_slots.alloc((size_t)T * sizeof(int)));
-        MZB_CUDA(e->mt_rows.alloc((size_t)T * 624 * sizeof(uint32_t)));
-        MZB_CUDA(e->mt_idx_rows.alloc((size_t)T * sizeof(int)));
-    }
-    cudaStream_t s = e->stream;
-    MZB_CUDA(cudaMemcpyAsync(e->d_slots.p, slots, (size_t)n_trees * sizeof(int), cudaMemcpyHostToDevice, s));
-    uint32_t* home = e->td.mt;
-    int* home_idx = e->td.mt_idx;
-    launch_mt_move(home, home_idx, e->mt_rows.as<uint32_t>(), e->mt_idx_rows.as<int>(), e->d_slots.as<int>(), n_trees, 0, s);
     const int stride = (e->cfg.evaluator == MZB_EVAL_SYNTHETIC) ? 1 : e->dims.initial_flat();
-    MZB_CUDA(cudaMemcpyAsync(e->d_obs.p, obs, (size_t)n_trees * stride * sizeof(float), cudaMemcpyHostToDevice, s));
-    MZB_CUDA(cudaStreamSynchronize(s));   // the Dirichlet draws on the aux stream read the gathered rows
-    e->td.mt = e->mt_rows.as<uint32_t>();
-    e->td.mt_idx = e->mt_idx_rows.as<int>();
-    rc = search_impl(e, e->d_obs.as<float>(), stride, legal_mask, to_play, add_noise, n_trees, out);
-    e->td.mt = home;
-    e->td.mt_idx = home_idx;
-    if (rc) return rc;
-    launch_mt_move(home, home_idx, e->mt_rows.as<uint32_t>(), e->mt_idx_rows.as<int>(), e->d_slots.as<int>(), n_trees, 1, s);
-    MZB_CUDA(cudaStreamSynchronize(s));
-    MZB_CUDA(cudaGetLastError());
-    return MZB_OK;
+    MZB_CUDA(cudaMemcpyAsync(e->d_obs.p, obs, (size_t)n_trees * stride * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    return search_with_device_obs_slots(e, slots, legal_mask, to_play, add_noise, n_trees, out);
 }
 
 int mzb_search_batch_device_obs(mzb_engine* e, const float* d_obs, const uint32_t* legal_mask, const int32_t* to_play,

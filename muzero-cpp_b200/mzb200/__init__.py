@@ -148,7 +148,9 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_nccl_unique_id", "mzb_nccl_init", "mzb_broadcast_weights", "mzb_weights_checksum",
            "mzb_initial_inference", "mzb_recurrent_inference", "mzb_bench_recurrent", "mzb_search_seed", "mzb_search_batch_slots",
            "mzb_search_batch", "mzb_search_batch_device_obs", "mzb_last_search_timing", "mzb_search_set_recording",
-           "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes", "mzb_value_encode", "mzb_value_decode"]
+           "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes", "mzb_value_encode", "mzb_value_decode",
+           "mzb_obs_ring_create", "mzb_obs_ring_reset", "mzb_obs_ring_push", "mzb_obs_ring_stacked", "mzb_search_batch_ring",
+           "mzb_actor_seed", "mzb_select_actions"]
 
 
 def load_library(path=None):
@@ -186,6 +188,14 @@ def load_library(path=None):
     lib.mzb_search_get_trace.argtypes = [C.c_void_p, C.c_int, ip, ip]
     lib.mzb_search_get_records.argtypes = [C.c_void_p, C.c_int, dp, dp, dp]
     lib.mzb_get_shapes.argtypes = [C.c_void_p, C.POINTER(_CShapes)]
+    u32p, u8p = C.POINTER(C.c_uint32), C.POINTER(C.c_uint8)
+    lib.mzb_obs_ring_create.argtypes = [C.c_void_p, fp]
+    lib.mzb_obs_ring_reset.argtypes = [C.c_void_p, ip, C.c_int]
+    lib.mzb_obs_ring_push.argtypes = [C.c_void_p, ip, fp, ip, C.c_int]
+    lib.mzb_obs_ring_stacked.argtypes = [C.c_void_p, ip, C.c_int, fp]
+    lib.mzb_search_batch_ring.argtypes = [C.c_void_p, ip, u32p, ip, u8p, C.c_int, C.POINTER(_CSearchResult)]
+    lib.mzb_actor_seed.argtypes = [C.c_void_p, ip, ip, C.c_int]
+    lib.mzb_select_actions.argtypes = [C.c_void_p, ip, C.POINTER(_CSearchResult), C.c_int, dp, ip]
     lib.mzb_value_encode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, fp]
     lib.mzb_value_decode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, C.c_int, fp]
     _lib = lib
@@ -262,6 +272,73 @@ class Engine:
         sh = _CShapes()
         self._check(self.lib.mzb_get_shapes(self._h, C.byref(sh)))
         return sh
+
+    # ---- the callers' side: device-resident observation history (types.cpp:16-42) and action selection (self_play.cpp:21-39)
+    def ring_create(self, action_planes_initial=None):
+        if action_planes_initial is not None:
+            self._planes_initial = np.ascontiguousarray(action_planes_initial, dtype=np.float32)
+            self._check(self.lib.mzb_obs_ring_create(self._h, _ptr(self._planes_initial, C.c_float)))
+        else:
+            self._check(self.lib.mzb_obs_ring_create(self._h, None))
+
+    def ring_reset(self, slots):
+        sl = np.ascontiguousarray(slots, dtype=np.int32).reshape(-1)
+        self._check(self.lib.mzb_obs_ring_reset(self._h, _ptr(sl, C.c_int32), sl.shape[0]))
+
+    def ring_push(self, slots, frames, actions):
+        sl = np.ascontiguousarray(slots, dtype=np.int32).reshape(-1)
+        fr = np.ascontiguousarray(frames, dtype=np.float32).reshape(sl.shape[0], -1)
+        ac = np.ascontiguousarray(actions, dtype=np.int32).reshape(-1)
+        c = self.config
+        if fr.shape[1] != c.observation_shape[0] * c.observation_shape[1] * c.observation_shape[2] or ac.shape[0] != sl.shape[0]:
+            raise MzbError("frames / actions disagree with the slot list or the observation shape")
+        self._check(self.lib.mzb_obs_ring_push(self._h, _ptr(sl, C.c_int32), _ptr(fr, C.c_float), _ptr(ac, C.c_int32), sl.shape[0]))
+
+    def ring_stacked(self, slots):
+        sl = np.ascontiguousarray(slots, dtype=np.int32).reshape(-1)
+        out = np.empty((sl.shape[0], self.shapes.initial_flat_size), np.float32)
+        self._check(self.lib.mzb_obs_ring_stacked(self._h, _ptr(sl, C.c_int32), sl.shape[0], _ptr(out, C.c_float)))
+        return out
+
+    def _result_arrays(self, T):
+        A = self.config.num_actions
+        res = MCTSReturn(np.empty(T, np.float64), np.empty(T, np.int32), np.empty(T, np.int32),
+                         np.empty((T, A), np.int32), np.empty((T, A), np.int32), np.empty((T, A), np.float64),
+                         np.empty((T, A), np.float64))
+        return res, self._cresult(res)
+
+    @staticmethod
+    def _cresult(res):
+        return _CSearchResult(_ptr(res.root_value, C.c_double), _ptr(res.max_tree_depth, C.c_int32),
+                              _ptr(res.n_children, C.c_int32), _ptr(res.child_actions, C.c_int32),
+                              _ptr(res.child_visits, C.c_int32), _ptr(res.children_relative_visit, C.c_double),
+                              _ptr(res.emperical_policy, C.c_double))
+
+    def run_ring(self, slots, legal_mask, to_play, add_exploration_noise) -> MCTSReturn:
+        sl = np.ascontiguousarray(slots, dtype=np.int32).reshape(-1)
+        legal = np.ascontiguousarray(legal_mask, dtype=np.uint32).reshape(-1)
+        tp = np.ascontiguousarray(to_play, dtype=np.int32).reshape(-1)
+        noise = np.ascontiguousarray(add_exploration_noise, dtype=np.uint8).reshape(-1)
+        T = sl.shape[0]
+        if legal.shape[0] != T or tp.shape[0] != T or noise.shape[0] != T:
+            raise MzbError("per-tree inputs disagree on the number of trees")
+        res, cr = self._result_arrays(T)
+        self._check(self.lib.mzb_search_batch_ring(self._h, _ptr(sl, C.c_int32), _ptr(legal, C.c_uint32), _ptr(tp, C.c_int32),
+                                                   _ptr(noise, C.c_uint8), T, C.byref(cr)))
+        return res
+
+    def actor_seed(self, slots, seeds):
+        sl = np.ascontiguousarray(slots, dtype=np.int32).reshape(-1)
+        sd = np.ascontiguousarray(seeds, dtype=np.int32).reshape(-1)
+        self._check(self.lib.mzb_actor_seed(self._h, _ptr(sl, C.c_int32), _ptr(sd, C.c_int32), sl.shape[0]))
+
+    def select_actions(self, slots, stats: MCTSReturn, temperature):
+        sl = np.ascontiguousarray(slots, dtype=np.int32).reshape(-1)
+        tmp = np.ascontiguousarray(np.broadcast_to(np.asarray(temperature, np.float64), sl.shape), dtype=np.float64)
+        out = np.empty(sl.shape[0], np.int32)
+        cr = self._cresult(stats)
+        self._check(self.lib.mzb_select_actions(self._h, _ptr(sl, C.c_int32), C.byref(cr), sl.shape[0], _ptr(tmp, C.c_double), _ptr(out, C.c_int32)))
+        return out
 
     # ValueEncoder::encode / decode (util.cpp:59-87); which = 0 value encoder, 1 reward encoder
     def value_encode(self, x, which=0):

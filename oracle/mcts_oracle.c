@@ -346,3 +346,28 @@ void mzo_run_replay(const mzo_config* cfg, int seed, uint32_t legal_mask, int to
     mzo_mcts_run(m, legal, nl, to_play, add_noise, replay_eval, &ctx, result, trace_parent, trace_action);
     mzo_mcts_destroy(m);
 }
+
+/* ------------------------------------------------------------------ action selection (self_play.cpp:21-39)
+ * temperature <= 0: first maximum of the relative visits (std::max_element).  Otherwise weights = visits^(1/T) and one draw
+ * of std::discrete_distribution<> (libstdc++ bits/random.tcc: param_type::_M_initialize normalises the weights by their
+ * std::accumulate sum, takes partial sums and pins the last to 1; operator() = lower_bound of one generate_canonical<double,53>
+ * draw in that table; a single weight draws nothing and returns 0). */
+int mzo_select_action(mzo_mt19937* g, const double* rel_visits, const int32_t* actions, int n, double temperature) {
+    if (temperature <= 0) {
+        int best = 0;
+        for (int i = 1; i < n; ++i) if (rel_visits[best] < rel_visits[i]) best = i;
+        return actions[best];
+    }
+    double w[MZO_MAX_ACTIONS], cp[MZO_MAX_ACTIONS];
+    for (int i = 0; i < n; ++i) w[i] = pow(rel_visits[i], 1.0 / temperature);
+    if (n < 2) return actions[0];
+    double sum = 0.0;
+    for (int i = 0; i < n; ++i) sum += w[i];
+    double run = 0.0;
+    for (int i = 0; i < n; ++i) { w[i] /= sum; run += w[i]; cp[i] = run; }
+    cp[n - 1] = 1.0;
+    const double p = canonical(g);
+    int lo = 0, hi = n;   /* std::lower_bound: first element not less than p */
+    while (lo < hi) { int mid = lo + (hi - lo) / 2; if (cp[mid] < p) lo = mid + 1; else hi = mid; }
+    return actions[lo];
+}

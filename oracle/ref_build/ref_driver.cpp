@@ -11,9 +11,14 @@
 //          (MZBT file written by the engine) and dump results + trace (end-to-end decision parity).
 //   bench  time MCTS::run over VPRNetEvaluator/DeviceManager on libtorch CPU (the reported CPU baseline).
 //   encoder dump ValueEncoder support size / decode for given bounds (util.cpp:45-102).
+//   stack  GameHistory::get_stacked_observations (types.cpp:16-42) on a synthetic game history.
+//   select the action-selection rule of self_play.cpp:21-39 over libstdc++'s discrete_distribution.
 #include <torch/torch.h>
 
+#include <algorithm>
 #include <atomic>
+#include <cmath>
+#include <random>
 #include <chrono>
 #include <cinttypes>
 #include <cstdio>
@@ -521,6 +526,70 @@ static int mode_encoder(const Args& a) {
     return 0;
 }
 
+// stack: GameHistory::get_stacked_observations (types.cpp:16-42), the UNMODIFIED reference function, on a synthetic game:
+// observation t = c*h*w values (t+1) + 0.001*k (k = flat index), action_history = {0, a_1, a_2, ...} with a_t = (7*t + 3) % A
+// (self_play.cpp:91-92,158-159 build the two vectors exactly so), action planes = constant a / A (the shipped examples').
+// Prints the stacked observation for every step of the game, then for the python-style negative index -1.
+static int mode_stack(const Args& a) {
+    const int c = a.i("c", 2), h = a.i("h", 3), w = a.i("w", 4), ach = a.i("ach", 1), S = a.i("stack", 3), steps = a.i("steps", 6), A = a.i("actions", 5);
+    g_plane_hw_initial = ach * h * w;
+    g_num_actions = A;
+    types::GameHistory hist;
+    types::ObservationShape shape{c, h, w};
+    for (int t = 0; t < steps; ++t) {
+        Observation o(c * h * w);
+        for (int k = 0; k < c * h * w; ++k) o[k] = (float)(t + 1) + 0.001f * k;
+        hist.action_history.push_back(t == 0 ? 0 : (7 * t + 3) % A);
+        hist.observation_history.push_back(o);
+    }
+    printf("shape c=%d h=%d w=%d ach=%d stack=%d steps=%d actions=%d\n", c, h, w, ach, S, steps, A);
+    for (int t = -1; t < steps; ++t) {
+        Observation st = hist.get_stacked_observations(t, S, shape, ach, encode_action_initial);
+        printf("step %d n=%zu", t, st.size());
+        for (float v : st) printf(" %a", (double)v);
+        printf("\n");
+    }
+    return 0;
+}
+
+// select: the action-selection rule of self_play.cpp:21-39 driven by libstdc++'s OWN std::discrete_distribution / std::mt19937
+// (the third-party arithmetic the reference function delegates to; the function itself sits in an anonymous namespace and
+// cannot be linked, so its few lines are restated here around the real library classes).  One rng per run, `draws` selections
+// from it over random visit distributions: prints the inputs and the chosen action of every draw.
+static int mode_select(const Args& a) {
+    const int seed = a.i("seed", 0), draws = a.i("draws", 20), A = a.i("actions", 7);
+    const double temperature = a.d("temperature", 1.0);
+    std::mt19937 rng(seed);
+    std::mt19937 gen(seed * 7919 + 13);   // input generator, separate from the rng under test
+    printf("select seed=%d draws=%d actions=%d temperature=%a\n", seed, draws, A, temperature);
+    for (int d = 0; d < draws; ++d) {
+        const int n = 1 + (int)(gen() % A);
+        std::vector<int> acts(A);
+        for (int i = 0; i < A; ++i) acts[i] = i;
+        for (int i = A - 1; i > 0; --i) std::swap(acts[i], acts[gen() % (i + 1)]);
+        acts.resize(n);
+        std::vector<int> visits(n);
+        int total = 0;
+        for (int i = 0; i < n; ++i) { visits[i] = (int)(gen() % 40); total += visits[i]; }
+        if (total == 0) { visits[0] = 1; total = 1; }
+        std::vector<double> rel(n);
+        for (int i = 0; i < n; ++i) rel[i] = (double)visits[i] / total;
+        int chosen;
+        if (temperature <= 0) {
+            chosen = acts[std::distance(rel.begin(), std::max_element(rel.begin(), rel.end()))];
+        } else {
+            std::vector<double> wts = rel;
+            for (auto& v : wts) v = std::pow(v, 1.0 / temperature);
+            std::discrete_distribution<> dist(wts.begin(), wts.end());
+            chosen = acts[dist(rng)];
+        }
+        printf("draw n=%d", n);
+        for (int i = 0; i < n; ++i) printf(" %d:%a", acts[i], rel[i]);
+        printf(" -> %d\n", chosen);
+    }
+    return 0;
+}
+
 int main(int argc, char** argv) {
     if (argc < 2) { std::cerr << "usage: ref_driver <mcts|net|replay|bench|bench_rec|encoder> key=value ..." << std::endl; return 2; }
     Args a(argc, argv);
@@ -531,6 +600,8 @@ int main(int argc, char** argv) {
     if (mode == "bench") return mode_bench(a);
     if (mode == "bench_rec") return mode_bench_rec(a);
     if (mode == "encoder") return mode_encoder(a);
+    if (mode == "stack") return mode_stack(a);
+    if (mode == "select") return mode_select(a);
     std::cerr << "unknown mode " << mode << std::endl;
     return 2;
 }

@@ -487,16 +487,19 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
             }
             if (flags & PH_NORM) {
                 // normalize_hidden_state (models.cpp:16-26): a thread owns one channel, its columns are the pixels
+                const int nskip = (W1 >> 3) << 3;   // the pad row of a game: no real pixel, nothing to normalise (its R2 columns are never read)
                 for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                     const int cbase = g * P;
                     float mn = 3.402823466e38f, mx = -3.402823466e38f;
                     if (a.normalize) {
-                        for (int c0 = 0; c0 < P; c0 += 32) {
+                        for (int c0 = nskip; c0 < P; c0 += 32) {
                             const bool two = P - c0 > 16;
                             uint32_t v[32];
                             tmem_ld16(t_lane + F_R2_COL + cbase + c0, v);
                             if (two) tmem_ld16(t_lane + F_R2_COL + cbase + c0 + 16, v + 16);
-                            const uint32_t m = lds_u32(pm + (c0 >> 5) * 4);
+                            const int mw_i = c0 >> 5, mw_s = c0 & 31;
+                            uint32_t m = lds_u32(pm + mw_i * 4) >> mw_s;
+                            if (mw_s && mw_i + 1 < 8) m |= lds_u32(pm + (mw_i + 1) * 4) << (32 - mw_s);
                             tmem_ld_wait();
 #pragma unroll
                             for (int j = 0; j < 32; ++j)
@@ -507,12 +510,14 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                     if (scale < 1e-5f) scale = 1e-5f;
                     if (!a.normalize) { mn = 0.f; scale = 1.f; }
                     const float inv = 1.0f / scale;
-                    for (int c0 = 0; c0 < P; c0 += 32) {
+                    for (int c0 = nskip; c0 < P; c0 += 32) {
                         const bool two = P - c0 > 16;
                         uint32_t v[32];
                         tmem_ld16(t_lane + F_R2_COL + cbase + c0, v);
                         if (two) tmem_ld16(t_lane + F_R2_COL + cbase + c0 + 16, v + 16);
-                        const uint32_t m = lds_u32(pm + (c0 >> 5) * 4);
+                        const int mw_i = c0 >> 5, mw_s = c0 & 31;
+                        uint32_t m = lds_u32(pm + mw_i * 4) >> mw_s;
+                        if (mw_s && mw_i + 1 < 8) m |= lds_u32(pm + (mw_i + 1) * 4) << (32 - mw_s);
                         tmem_ld_wait();
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
@@ -553,14 +558,19 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                         }
                     }
                 } else {
+                    // a game's first W + 1 rows are its zero pad row: nothing to read or store there (whole 8-column groups only,
+                    // to keep the TMEM column addresses aligned) — C4: 48 instead of 64 columns per game through the TMEM read port
+                    const int skip = (W1 >> 3) << 3;
                     for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                         const int cbase = g * P;
-                        for (int c0 = 0; c0 < P; c0 += 32) {
+                        for (int c0 = skip; c0 < P; c0 += 32) {
                             const bool two = P - c0 > 16;
                             uint32_t v[32];
                             tmem_ld16(t_lane + src_col + cbase + c0, v);
                             if (two) tmem_ld16(t_lane + src_col + cbase + c0 + 16, v + 16);
-                            const uint32_t m = lds_u32(pm + (c0 >> 5) * 4);
+                            const int mw_i = c0 >> 5, mw_s = c0 & 31;
+                            uint32_t m = lds_u32(pm + mw_i * 4) >> mw_s;
+                            if (mw_s && mw_i + 1 < 8) m |= lds_u32(pm + (mw_i + 1) * 4) << (32 - mw_s);
                             tmem_ld_wait();
                             const uint32_t mw = wx ? m : 0u;
                             const uint32_t xa = xs + (uint32_t)(cbase + c0) * 16;

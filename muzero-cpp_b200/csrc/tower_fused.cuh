@@ -541,11 +541,13 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                 if (flags & PH_TABLE) {   // accumulator (R1) + staged per-action table (R2), 16 columns at a time
                     for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                         const int cbase = g * P;
-                        for (int c0 = 0; c0 < P; c0 += 16) {
+                        for (int c0 = (W1 >> 3) << 3; c0 < P; c0 += 16) {   // (from the first real row on, as below)
                             uint32_t v[16], w[16];
                             tmem_ld16(t_lane + src_col + cbase + c0, v);
                             tmem_ld16(t_lane + F_R2_COL + cbase + c0, w);
-                            const uint32_t m = lds_u32(pm + (c0 >> 5) * 4) >> (c0 & 16);
+                            const int mw_i = c0 >> 5, mw_s = c0 & 31;
+                            uint32_t m = lds_u32(pm + mw_i * 4) >> mw_s;
+                            if (mw_s > 16 && mw_i + 1 < 8) m |= lds_u32(pm + (mw_i + 1) * 4) << (32 - mw_s);
                             tmem_ld_wait();
 #pragma unroll
                             for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));

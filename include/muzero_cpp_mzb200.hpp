@@ -1,0 +1,524 @@
+// muzero_cpp_mzb200.hpp — the reference's OWN names for the search hot path, backed by libmzb200.so.
+//
+// A muzero-cpp translation unit that today includes mcts.h / vprnet.h / vprnet_evaluator.h / device_manager.h / config.h /
+// abstract_game.h for the self-play search (self_play.cpp, muzero.cpp:60-63,82,109-112,161-163, tests/mcts_test.cpp) compiles
+// against this header unchanged: same namespaces, class names, constructor and method signatures, value-semantics and
+// "no error codes" behaviour (a failing engine call prints mzb_last_error() and aborts).  Header-only, C++17, no torch, no abseil.
+//
+//   reference (file:line)                                   here
+//   ------------------------------------------------------  ---------------------------------------------------------------
+//   types::* (types.h:18-78)                                 muzero_cpp::types::* (aliases, ObservationShape, StepReturn, MCTSReturn)
+//   muzero_config::MuZeroConfig (config.h:15-117)            same fields and defaults (the learner / replay fields are carried, unused)
+//   AbstractGame (abstract_game.h:12-67)                     same eight virtuals
+//   VPRNetModel (vprnet.h:26-140)                            one resident engine per model; batch {Initial,Recurrent}Inference
+//   DeviceManager / DeviceLoan (device_manager.h:29-109)     least-outstanding-requests loans over the models
+//   Evaluator, VPRNetEvaluator (vprnet_evaluator.h:35-102)   blocking one-request calls coalesced into engine batches by the
+//                                                             callers themselves (leader/follower; no runner threads or promises)
+//   algorithm::MCTS (mcts.h:113-187)                          run(): VPRNetEvaluator -> lock-step device search of the model's
+//                                                             cohort; any other Evaluator subclass -> device tree kernels with
+//                                                             host callbacks per simulation (MZB_EVAL_HOST)
+//
+// What is NOT here: Learn / SaveCheckpoint / LoadCheckpoint (learner side; weights arrive through
+// VPRNetModel::LoadWeights) and the host MCTSNode helpers select_child / ucb_score / backpropogate (the tree lives in HBM).
+#pragma once
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <limits>
+#include <string>
+
+#include "mzb200_facade.hpp"
+
+namespace muzero_cpp {
+
+namespace types {   // types.h:18-78
+using Player = int;
+using Action = int;
+constexpr Player InvalidPlayer = -1;
+constexpr Action InvalidAction = -1;
+using Observation = std::vector<float>;
+struct ObservationShape {
+    int c, h, w;
+    bool operator==(const ObservationShape& o) const { return c == o.c && h == o.h && w == o.w; }
+    bool operator!=(const ObservationShape& o) const { return !(*this == o); }
+};
+using ActionRepresentationFunction = std::function<Observation(Action)>;
+using SoftmaxTemperatureFunction = std::function<double(int)>;
+enum class OpponentTypes { Self, Random, Expert, Human };
+enum CheckpointStep { kMostRecentCheckpointStep = -1, kBestPerformanceCheckpointStep = -2 };
+struct StepReturn { Observation observation; double reward; bool done; };
+using MCTSReturn = mzb200::MCTSReturn;   // same five fields in the same order (types.h:70-76)
+constexpr double NINF_D = std::numeric_limits<double>::lowest();
+constexpr double INF_D = std::numeric_limits<double>::max();
+}  // namespace types
+
+namespace muzero_config {   // config.h:15-117, field for field
+struct MuZeroNetworkConfig {
+    double learning_rate = 3e-4, l2_weight_decay = 1e-4;
+    bool downsample = false, normalize_hidden_states = true;
+    int resnet_channels = 128, representation_blocks = 4, dynamics_blocks = 4, prediction_blocks = 4;
+    int reward_reduced_channels = 16, policy_reduced_channels = 16, value_reduced_channels = 16;
+    std::vector<int> reward_head_layers{64}, policy_head_layers{64}, value_head_layers{64};
+};
+struct MuZeroConfig {
+    int seed = 0, checkpoint_interval = 100, model_sync_interval = 100;
+    std::string path = "/opt/muzero-cpp/", devices = "cpu:0";
+    bool explicit_learning = false;
+    int num_actors = 1, num_reanalyze_actors = 0, num_evaluators = 1;
+    int initial_inference_batch_size = 1, recurrent_inference_batch_size = 1;
+    int initial_inference_threads = 1, recurrent_inference_threads = 1;
+    int max_training_steps = 100000;
+    bool resume = false;
+    types::CheckpointStep testing_checkpoint = types::CheckpointStep::kMostRecentCheckpointStep;
+    types::ObservationShape observation_shape{1, 1, 1};
+    std::vector<types::Action> action_space;
+    int action_channels = 1, num_players = 1, stacked_observations = 0;
+    double value_upperbound = types::NINF_D, value_lowerbound = types::INF_D;
+    double min_reward = -300, max_reward = 300, min_value = -300, max_value = 300;
+    bool use_contractive_mapping = true;
+    types::Player muzero_player = 0;
+    types::OpponentTypes opponent_type = types::OpponentTypes::Self;
+    int max_moves = -1, num_simulations = 50;
+    double discount = 0.997, dirichlet_alpha = 0.3, dirichlet_epsilon = 0.25, pb_c_base = 19652, pb_c_init = 1.25;
+    int batch_size = 128, min_sample_size = 256;
+    double value_loss_weight = 1;
+    int td_steps = 10, num_unroll_steps = 5, max_history_len = -1;
+    double train_reanalyze_ratio = 0;
+    int replay_buffer_size = 100000, reanalyze_buffer_size = 100000;
+    double per_alpha = 1, per_beta = 1, per_epsilon = 0.01, per_beta_increment = 0.001;
+    MuZeroNetworkConfig network_config;
+    types::ActionRepresentationFunction action_representation_initial, action_representation_recurrent;
+    types::SoftmaxTemperatureFunction visit_softmax_temperature;
+};
+}  // namespace muzero_config
+
+class AbstractGame {   // abstract_game.h:12-67
+public:
+    virtual ~AbstractGame() = default;
+    virtual types::Observation reset() = 0;
+    virtual types::StepReturn step(types::Action action) = 0;
+    virtual types::Player to_play() const = 0;
+    virtual std::vector<types::Action> legal_actions() const = 0;
+    virtual types::Action expert_action() = 0;
+    virtual types::Action human_to_action() = 0;
+    virtual void render() {}
+    virtual std::string action_to_string(types::Action action) const = 0;
+};
+
+namespace detail {
+[[noreturn]] inline void fatal(const std::string& msg) {
+    std::fprintf(stderr, "mzb200: %s\n", msg.c_str());
+    std::abort();
+}
+inline void copy_layers(const std::vector<int>& src, int32_t* dst, int32_t* n) {
+    if ((int)src.size() > MZB_MAX_HEAD_LAYERS) fatal("more head layers than MZB_MAX_HEAD_LAYERS");
+    *n = (int32_t)src.size();
+    std::copy(src.begin(), src.end(), dst);
+}
+// MuZeroConfig -> the POD the C ABI takes.  action_planes stays NULL (the examples' constant plane action / num_actions)
+// unless action_representation_recurrent is set; the caller owns `planes`.
+inline mzb_config to_pod(const muzero_config::MuZeroConfig& c, int max_trees, int precision, int evaluator, std::vector<float>* planes) {
+    mzb_config p;
+    std::memset(&p, 0, sizeof(p));
+    p.observation_c = c.observation_shape.c; p.observation_h = c.observation_shape.h; p.observation_w = c.observation_shape.w;
+    p.num_actions = (int32_t)c.action_space.size();
+    for (size_t i = 0; i < c.action_space.size(); ++i)
+        if (c.action_space[i] != (types::Action)i) fatal("action_space must be {0, ..., num_actions-1} (config.h:55)");
+    p.action_channels = c.action_channels; p.num_players = c.num_players; p.stacked_observations = c.stacked_observations;
+    p.value_upperbound = c.value_upperbound; p.value_lowerbound = c.value_lowerbound;
+    p.min_reward = c.min_reward; p.max_reward = c.max_reward; p.min_value = c.min_value; p.max_value = c.max_value;
+    p.use_contractive_mapping = c.use_contractive_mapping;
+    p.num_simulations = c.num_simulations; p.discount = c.discount;
+    p.dirichlet_alpha = c.dirichlet_alpha; p.dirichlet_epsilon = c.dirichlet_epsilon; p.pb_c_base = c.pb_c_base; p.pb_c_init = c.pb_c_init;
+    p.seed = c.seed;
+    const muzero_config::MuZeroNetworkConfig& n = c.network_config;
+    p.downsample = n.downsample; p.normalize_hidden_states = n.normalize_hidden_states;
+    p.resnet_channels = n.resnet_channels; p.representation_blocks = n.representation_blocks;
+    p.dynamics_blocks = n.dynamics_blocks; p.prediction_blocks = n.prediction_blocks;
+    p.reward_reduced_channels = n.reward_reduced_channels; p.policy_reduced_channels = n.policy_reduced_channels;
+    p.value_reduced_channels = n.value_reduced_channels;
+    copy_layers(n.reward_head_layers, p.reward_head_layers, &p.n_reward_head_layers);
+    copy_layers(n.policy_head_layers, p.policy_head_layers, &p.n_policy_head_layers);
+    copy_layers(n.value_head_layers, p.value_head_layers, &p.n_value_head_layers);
+    if (c.action_representation_recurrent && planes) {   // vprnet.cpp:143: evaluated once per action instead of once per request
+        planes->clear();
+        for (types::Action a : c.action_space) {
+            const types::Observation plane = c.action_representation_recurrent(a);
+            planes->insert(planes->end(), plane.begin(), plane.end());
+        }
+        p.action_planes = planes->data();
+    }
+    p.max_trees = max_trees; p.precision = precision; p.evaluator = evaluator;
+    return p;
+}
+// "cuda:3" / "cuda" -> ordinal.  There is no CPU path: the reference's "cpu" / "/cpu:0" device strings fail loudly.
+inline int cuda_ordinal(const std::string& device) {
+    const size_t at = device.find("cuda");
+    if (at == std::string::npos) fatal("device \"" + device + "\": libmzb200 has no CPU path, use cuda:N");
+    const size_t colon = device.find(':', at);
+    return colon == std::string::npos ? 0 : std::atoi(device.c_str() + colon + 1);
+}
+}  // namespace detail
+
+// vprnet.h:26-140.  One model = one GPU-resident engine: weights, node pool and max_trees tree slots, where max_trees covers
+// every MCTS object the reference would create for this config (actors + reanalyze actors + evaluators, self_play.cpp:228-275)
+// and both inference batch sizes.
+class VPRNetModel {
+public:
+    struct InitialInferenceInputs { types::Observation stacked_observation; };               // vprnet.h:52-55
+    struct RecurrentInferenceInputs { types::Action action; types::Observation encoded_state; };   // vprnet.h:58-61
+    struct InferenceOutputs {                                                                  // vprnet.h:64-69
+        double value; double reward; std::vector<double> policy; types::Observation encoded_state;
+    };
+
+    // precision: MZB_BF16 (tensor-core towers) or MZB_FP32_CHECK; MZB200_PRECISION=fp32 in the environment overrides.
+    VPRNetModel(const muzero_config::MuZeroConfig& config, const std::string& device = "cuda:0", int precision = MZB_BF16)
+        : st_(new State) {
+        const char* env = std::getenv("MZB200_PRECISION");
+        if (env && std::string(env) == "fp32") precision = MZB_FP32_CHECK;
+        st_->device = device;
+        const int trees = std::max({config.num_actors + config.num_reanalyze_actors + config.num_evaluators,
+                                    config.initial_inference_batch_size, config.recurrent_inference_batch_size, 1});
+        const mzb_config pod = detail::to_pod(config, trees, precision, MZB_EVAL_NETWORK, &st_->planes);
+        st_->engine = std::make_shared<mzb200::Engine>(pod, detail::cuda_ordinal(device));
+        const char* dl = std::getenv("MZB200_COHORT_DEADLINE_US");
+        st_->cohort = std::make_shared<mzb200::Cohort>(st_->engine, std::chrono::microseconds(dl ? std::atol(dl) : 1000));
+        st_->shapes = st_->engine->shapes();
+        st_->num_actions = pod.num_actions;
+    }
+    VPRNetModel(VPRNetModel&&) = default;
+    VPRNetModel& operator=(VPRNetModel&&) = default;
+    VPRNetModel(const VPRNetModel&) = delete;
+    VPRNetModel& operator=(const VPRNetModel&) = delete;
+
+    void print() const {
+        std::printf("mzb200 engine on %s: hidden %dx%dx%d, weights %lld B, node pool %lld B\n", st_->device.c_str(), st_->shapes.enc_c,
+                    st_->shapes.enc_h, st_->shapes.enc_w, (long long)st_->shapes.weight_blob_bytes, (long long)st_->shapes.node_pool_bytes);
+    }
+
+    std::vector<InferenceOutputs> InitialInference(std::vector<InitialInferenceInputs>& inputs) {   // vprnet.cpp:77-129
+        const int B = (int)inputs.size(), flat = st_->shapes.initial_flat_size;
+        std::vector<float> rows((size_t)B * flat);
+        for (int b = 0; b < B; ++b) {
+            if ((int)inputs[b].stacked_observation.size() != flat) detail::fatal("InitialInference: observation of the wrong size");
+            std::copy(inputs[b].stacked_observation.begin(), inputs[b].stacked_observation.end(), rows.begin() + (size_t)b * flat);
+        }
+        Outputs o(B, st_->num_actions, st_->shapes.recurrent_flat_size);
+        {
+            std::lock_guard<std::mutex> call(st_->engine->call_mutex());
+            mzb200::check(mzb_initial_inference(st_->engine->handle(), rows.data(), B, o.value.data(), o.reward.data(), o.policy.data(), o.hidden.data()),
+                          "mzb_initial_inference");
+        }
+        return o.unpack();
+    }
+    std::vector<InferenceOutputs> RecurrentInference(std::vector<RecurrentInferenceInputs>& inputs) {   // vprnet.cpp:131-189
+        const int B = (int)inputs.size(), flat = st_->shapes.recurrent_flat_size;
+        std::vector<float> rows((size_t)B * flat);
+        std::vector<int32_t> actions(B);
+        for (int b = 0; b < B; ++b) {
+            if ((int)inputs[b].encoded_state.size() != flat) detail::fatal("RecurrentInference: encoded state of the wrong size");
+            std::copy(inputs[b].encoded_state.begin(), inputs[b].encoded_state.end(), rows.begin() + (size_t)b * flat);
+            actions[b] = inputs[b].action;
+        }
+        Outputs o(B, st_->num_actions, flat);
+        {
+            std::lock_guard<std::mutex> call(st_->engine->call_mutex());
+            mzb200::check(mzb_recurrent_inference(st_->engine->handle(), rows.data(), actions.data(), B, o.value.data(), o.reward.data(),
+                                                  o.policy.data(), o.hidden.data()), "mzb_recurrent_inference");
+        }
+        return o.unpack();
+    }
+
+    // Stands in for LoadCheckpoint (vprnet.cpp:66-74) until the native archive reader exists: the module's named fp32 tensors.
+    void LoadWeights(const std::vector<mzb_tensor_desc>& tensors) {
+        std::lock_guard<std::mutex> call(st_->engine->call_mutex());
+        st_->engine->LoadWeights(tensors);
+    }
+    const std::string Device() const { return st_->device; }
+
+    // mzb200 side
+    std::shared_ptr<mzb200::Engine> engine() const { return st_->engine; }
+    std::shared_ptr<mzb200::Cohort> cohort() const { return st_->cohort; }
+
+private:
+    struct Outputs {
+        int B, A, S;
+        std::vector<double> value, reward, policy;
+        std::vector<float> hidden;
+        Outputs(int b, int a, int s) : B(b), A(a), S(s), value(b), reward(b), policy((size_t)b * a), hidden((size_t)b * s) {}
+        std::vector<InferenceOutputs> unpack() const {
+            std::vector<InferenceOutputs> out(B);
+            for (int b = 0; b < B; ++b) {
+                out[b].value = value[b]; out[b].reward = reward[b];
+                out[b].policy.assign(policy.begin() + (size_t)b * A, policy.begin() + (size_t)(b + 1) * A);
+                out[b].encoded_state.assign(hidden.begin() + (size_t)b * S, hidden.begin() + (size_t)(b + 1) * S);
+            }
+            return out;
+        }
+    };
+    struct State {
+        std::string device;
+        std::vector<float> planes;
+        std::shared_ptr<mzb200::Engine> engine;
+        std::shared_ptr<mzb200::Cohort> cohort;
+        mzb_shapes shapes;
+        int num_actions = 0;
+    };
+    std::unique_ptr<State> st_;
+};
+
+// device_manager.h:29-109: hands out the model with the fewest outstanding requests; device 0 is left to the learner while
+// SetLearning(true) and more than one device exists.
+class DeviceManager {
+public:
+    DeviceManager() = default;
+    void AddDevice(VPRNetModel model) { slots_.emplace_back(new Slot{std::move(model), 0, 0}); }   // not thread safe (as the reference)
+
+    class DeviceLoan {
+    public:
+        DeviceLoan(DeviceLoan&& o) noexcept : owner_(o.owner_), model_(o.model_), id_(o.id_), n_(o.n_) { o.owner_ = nullptr; }
+        DeviceLoan& operator=(DeviceLoan&& o) noexcept {
+            if (this != &o) { release(); owner_ = o.owner_; model_ = o.model_; id_ = o.id_; n_ = o.n_; o.owner_ = nullptr; }
+            return *this;
+        }
+        DeviceLoan(const DeviceLoan&) = delete;
+        DeviceLoan& operator=(const DeviceLoan&) = delete;
+        ~DeviceLoan() { release(); }
+        VPRNetModel* operator->() { return model_; }
+        int device_id() const { return id_; }
+
+    private:
+        friend class DeviceManager;
+        DeviceLoan(DeviceManager* owner, VPRNetModel* model, int id, int n) : owner_(owner), model_(model), id_(id), n_(n) {}
+        void release() { if (owner_) owner_->give_back(id_, n_); owner_ = nullptr; }
+        DeviceManager* owner_;
+        VPRNetModel* model_;
+        int id_, n_;
+    };
+
+    DeviceLoan Get(int requests, int device_id = -1) {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (slots_.empty()) detail::fatal("DeviceManager::Get with no devices");
+        if (device_id < 0) {
+            const int first = (learning_ && slots_.size() > 1) ? 1 : 0;
+            device_id = first;
+            for (int i = first + 1; i < (int)slots_.size(); ++i)
+                if (slots_[i]->outstanding < slots_[device_id]->outstanding) device_id = i;
+        }
+        slots_[device_id]->outstanding += requests;
+        return DeviceLoan(this, &slots_[device_id]->model, device_id, requests);
+    }
+    void SetLearning(bool value) { std::lock_guard<std::mutex> lk(mu_); learning_ = value; }
+    int Count() const { return (int)slots_.size(); }
+
+    // mzb200 side: an MCTS object lives on ONE device for its lifetime (its tree slot and RNG stream are resident there);
+    // it goes to the device with the fewest resident searchers, honouring the learner's reservation of device 0.
+    VPRNetModel* attach_searcher(int* device_id) {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (slots_.empty()) detail::fatal("DeviceManager has no devices");
+        const int first = (learning_ && slots_.size() > 1) ? 1 : 0;
+        int best = first;
+        for (int i = first + 1; i < (int)slots_.size(); ++i)
+            if (slots_[i]->searchers < slots_[best]->searchers) best = i;
+        ++slots_[best]->searchers;
+        *device_id = best;
+        return &slots_[best]->model;
+    }
+    void detach_searcher(int device_id) { std::lock_guard<std::mutex> lk(mu_); --slots_[device_id]->searchers; }
+
+private:
+    struct Slot { VPRNetModel model; int outstanding; int searchers; };
+    void give_back(int id, int n) { std::lock_guard<std::mutex> lk(mu_); slots_[id]->outstanding -= n; }
+    std::vector<std::unique_ptr<Slot>> slots_;   // stable addresses: loans and searchers keep VPRNetModel*
+    bool learning_ = false;
+    std::mutex mu_;
+};
+
+class Evaluator {   // vprnet_evaluator.h:35-41
+public:
+    virtual ~Evaluator() = default;
+    virtual VPRNetModel::InferenceOutputs InitialInference(const types::Observation& stacked_observations) = 0;
+    virtual VPRNetModel::InferenceOutputs RecurrentInference(const types::Observation& hidden_state, types::Action action) = 0;
+};
+
+// vprnet_evaluator.h:44-102, vprnet_evaluator.cpp:25-178.  Same contract — many threads call the one-request methods and block
+// until their answer is ready; requests are served in batches of up to batch_size, or fewer once the oldest has waited 1 ms —
+// but no runner threads, queue items or promises: the caller that completes a batch (or sees the deadline pass) becomes its
+// leader, borrows the least-loaded model, runs ONE engine call for the batch and wakes the others.  `threads` bounds how many
+// batches may be in flight at once, which is what the reference's runner-thread counts control.
+class VPRNetEvaluator : public Evaluator {
+public:
+    explicit VPRNetEvaluator(DeviceManager* device_manager, int batch_size_initial, int initial_inference_threads,
+                             int batch_size_recurrent, int recurrent_inference_threads)
+        : dm_(*device_manager), initial_(batch_size_initial, initial_inference_threads), recurrent_(batch_size_recurrent, recurrent_inference_threads) {}
+
+    VPRNetModel::InferenceOutputs InitialInference(const types::Observation& stacked_observations) override {
+        Request rq;
+        rq.input = &stacked_observations;
+        return initial_.submit(rq, [this](std::vector<Request*>& batch) {
+            std::vector<VPRNetModel::InitialInferenceInputs> in(batch.size());
+            for (size_t i = 0; i < batch.size(); ++i) in[i].stacked_observation = *batch[i]->input;
+            auto out = dm_.Get((int)batch.size())->InitialInference(in);
+            for (size_t i = 0; i < batch.size(); ++i) batch[i]->output = std::move(out[i]);
+        });
+    }
+    VPRNetModel::InferenceOutputs RecurrentInference(const types::Observation& hidden_state, types::Action action) override {
+        Request rq;
+        rq.input = &hidden_state; rq.action = action;
+        return recurrent_.submit(rq, [this](std::vector<Request*>& batch) {
+            std::vector<VPRNetModel::RecurrentInferenceInputs> in(batch.size());
+            for (size_t i = 0; i < batch.size(); ++i) { in[i].action = batch[i]->action; in[i].encoded_state = *batch[i]->input; }
+            auto out = dm_.Get((int)batch.size())->RecurrentInference(in);
+            for (size_t i = 0; i < batch.size(); ++i) batch[i]->output = std::move(out[i]);
+        });
+    }
+    DeviceManager& device_manager() { return dm_; }
+    // batches served so far / requests served so far (the reference logs neither; used by tests to see that batching happens)
+    long batches_served() const { return initial_.batches + recurrent_.batches; }
+    long requests_served() const { return initial_.requests + recurrent_.requests; }
+
+private:
+    struct Request {
+        const types::Observation* input = nullptr;
+        types::Action action = 0;
+        VPRNetModel::InferenceOutputs output;
+        bool taken = false, done = false;
+    };
+    struct BatchPoint {
+        BatchPoint(int batch_size, int threads) : batch_size(std::max(1, batch_size)), max_in_flight(std::max(1, threads)) {}
+        template <class Run>
+        VPRNetModel::InferenceOutputs submit(Request& rq, Run run) {
+            std::unique_lock<std::mutex> lk(mu);
+            if (pending.empty()) oldest = std::chrono::steady_clock::now();
+            pending.push_back(&rq);
+            cv.notify_all();
+            while (!rq.done) {
+                const bool due = (int)pending.size() >= batch_size || std::chrono::steady_clock::now() - oldest >= deadline;
+                if (!rq.taken && due && in_flight < max_in_flight) {
+                    std::vector<Request*> batch;
+                    const size_t n = std::min(pending.size(), (size_t)batch_size);
+                    batch.assign(pending.begin(), pending.begin() + n);
+                    pending.erase(pending.begin(), pending.begin() + n);
+                    for (Request* r : batch) r->taken = true;
+                    if (!pending.empty()) oldest = std::chrono::steady_clock::now();
+                    ++in_flight;
+                    lk.unlock();
+                    run(batch);
+                    lk.lock();
+                    --in_flight; ++batches; requests += (long)batch.size();
+                    for (Request* r : batch) r->done = true;
+                    cv.notify_all();
+                } else if (!rq.taken && in_flight < max_in_flight) {
+                    cv.wait_until(lk, oldest + deadline);
+                } else {
+                    cv.wait(lk);
+                }
+            }
+            return std::move(rq.output);
+        }
+        const int batch_size, max_in_flight;
+        const std::chrono::microseconds deadline{1000};   // vprnet_evaluator.cpp:118
+        std::mutex mu;
+        std::condition_variable cv;
+        std::vector<Request*> pending;
+        std::chrono::steady_clock::time_point oldest;
+        int in_flight = 0;
+        long batches = 0, requests = 0;
+    };
+    DeviceManager& dm_;
+    BatchPoint initial_, recurrent_;
+};
+
+namespace algorithm {
+
+// mcts.h:113-187.  Thread-confined, one per actor, as in the reference.
+class MCTS {
+public:
+    MCTS(const muzero_config::MuZeroConfig& config, int seed, std::shared_ptr<Evaluator> vpr_eval) : eval_(std::move(vpr_eval)) {
+        if (auto net = std::dynamic_pointer_cast<VPRNetEvaluator>(eval_)) {
+            // the search runs where the weights are: a tree slot of the chosen model's cohort
+            dm_ = &net->device_manager();
+            VPRNetModel* model = dm_->attach_searcher(&device_id_);
+            device_search_.reset(new mzb200::MCTS(model->cohort(), seed));
+        } else {
+            // a user-defined Evaluator (tests/mcts_test.cpp:16-27): a private one-tree engine whose two inference calls come back here
+            const mzb_config pod = detail::to_pod(config, 1, MZB_FP32_CHECK, MZB_EVAL_HOST, nullptr);
+            host_engine_.reset(new mzb200::Engine(pod, 0));
+            node_state_.resize(config.num_simulations + 1);
+            mzb_host_evaluator cb;
+            cb.user = this; cb.initial = &MCTS::host_initial; cb.recurrent = &MCTS::host_recurrent;
+            mzb200::check(mzb_set_host_evaluator(host_engine_->handle(), &cb), "mzb_set_host_evaluator");
+            const int32_t sd = seed;
+            mzb200::check(mzb_search_seed(host_engine_->handle(), 0, 1, &sd), "mzb_search_seed");
+            num_actions_ = pod.num_actions;
+        }
+    }
+    MCTS() = delete;
+    MCTS(const MCTS&) = delete;
+    MCTS& operator=(const MCTS&) = delete;
+    ~MCTS() {
+        device_search_.reset();
+        if (dm_) dm_->detach_searcher(device_id_);
+    }
+
+    types::MCTSReturn run(const types::Observation& stacked_observation, const std::vector<types::Action>& legal_actions,
+                          types::Player to_play, bool add_exploration_noise) {
+        if (device_search_) return device_search_->run(stacked_observation, legal_actions, to_play, add_exploration_noise);
+        const int A = num_actions_;
+        uint32_t mask = 0;
+        for (types::Action a : legal_actions) mask |= 1u << a;
+        const int32_t tp = to_play;
+        const uint8_t noise = add_exploration_noise ? 1 : 0;
+        // the engine's row is initial_flat_size floats; a test evaluator may be handed any observation, so pad / trim a copy
+        const mzb_shapes sh = host_engine_->shapes();
+        std::vector<float> row(sh.initial_flat_size, 0.f);
+        std::copy(stacked_observation.begin(), stacked_observation.begin() + std::min(row.size(), stacked_observation.size()), row.begin());
+        root_obs_ = &stacked_observation;
+        int32_t n_children = 0, depth = 0;
+        double root = 0;
+        std::vector<int32_t> actions(A);
+        std::vector<double> rel(A), pol(A);
+        mzb_search_result out{};
+        out.root_value = &root; out.max_tree_depth = &depth; out.n_children = &n_children;
+        out.child_actions = actions.data(); out.children_relative_visit = rel.data(); out.emperical_policy = pol.data();
+        mzb200::check(mzb_search_batch(host_engine_->handle(), row.data(), &mask, &tp, &noise, 1, &out), "mzb_search_batch");
+        types::MCTSReturn r;
+        r.root_value = root; r.max_tree_depth = depth; r.emperical_policy = pol;
+        r.children_relative_visit.assign(rel.begin(), rel.begin() + n_children);
+        r.child_actions.assign(actions.begin(), actions.begin() + n_children);
+        return r;
+    }
+
+private:
+    int store(const VPRNetModel::InferenceOutputs& o, int node, double* value, double* reward, double* policy) {
+        if ((int)o.policy.size() != num_actions_) return -1;
+        *value = o.value; *reward = o.reward;
+        std::copy(o.policy.begin(), o.policy.end(), policy);
+        node_state_[node] = o.encoded_state;
+        return 0;
+    }
+    static int host_initial(void* user, int, const int32_t*, const float*, int, double* value, double* reward, double* policy) {
+        MCTS* self = static_cast<MCTS*>(user);
+        return self->store(self->eval_->InitialInference(*self->root_obs_), 0, value, reward, policy);
+    }
+    static int host_recurrent(void* user, int, const int32_t*, const int32_t* parent_node, const int32_t* action, int child_node,
+                              double* value, double* reward, double* policy) {
+        MCTS* self = static_cast<MCTS*>(user);
+        return self->store(self->eval_->RecurrentInference(self->node_state_[parent_node[0]], action[0]), child_node, value, reward, policy);
+    }
+
+    std::shared_ptr<Evaluator> eval_;
+    // VPRNetEvaluator path
+    DeviceManager* dm_ = nullptr;
+    int device_id_ = -1;
+    std::unique_ptr<mzb200::MCTS> device_search_;
+    // user-evaluator path
+    std::unique_ptr<mzb200::Engine> host_engine_;
+    std::vector<types::Observation> node_state_;   // encoded_state of every expanded node, by expansion order
+    const types::Observation* root_obs_ = nullptr;
+    int num_actions_ = 0;
+};
+
+}  // namespace algorithm
+}  // namespace muzero_cpp

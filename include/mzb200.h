@@ -32,8 +32,11 @@ typedef enum {
 /* what stands behind Evaluator::{Initial,Recurrent}Inference (muzero-cpp/vprnet_evaluator.h:35-41) */
 typedef enum {
     MZB_EVAL_NETWORK = 0,   /* the VPRNet towers (vprnet.cpp / models.cpp / model_layers.cpp) */
-    MZB_EVAL_SYNTHETIC = 1  /* deterministic hash evaluator "SE": pins the tree kernels bit-exactly and measures them
+    MZB_EVAL_SYNTHETIC = 1, /* deterministic hash evaluator "SE": pins the tree kernels bit-exactly and measures them
                                alone (the stub still moves one hidden state parent->child per simulation) */
+    MZB_EVAL_HOST = 2       /* a caller-supplied Evaluator subclass (e.g. tests/mcts_test.cpp:16-27 TestEvaluator): the tree
+                               kernels run on the GPU, the two inference calls go to host callbacks once per cohort and
+                               simulation (mzb_set_host_evaluator).  Compatibility / test path, not a throughput path. */
 } mzb_evaluator;
 
 /* POD mirror of muzero_config::MuZeroConfig + MuZeroNetworkConfig (muzero-cpp/config.h:15-117), restricted to the
@@ -100,6 +103,19 @@ const char* mzb_version(void);
  * MCTS::MCTS (mcts.cpp:17-31) for max_trees tree slots.  device = CUDA ordinal. */
 int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out);
 void mzb_engine_destroy(mzb_engine* e);
+
+/* MZB_EVAL_HOST: the two pure virtuals of Evaluator (vprnet_evaluator.h:35-41), batched over the rows of a cohort.
+ * slot[i] = tree slot of row i.  Nodes are named by expansion order (root 0; the node expanded by simulation s is s + 1), so
+ * the callee can keep each node's encoded_state itself: `recurrent` expands node `child_node` of every row under
+ * parent_node[i] by action[i].  Outputs: value[n], reward[n], policy[n][num_actions].  Non-zero return aborts the search. */
+typedef struct {
+    void* user;
+    int (*initial)(void* user, int n, const int32_t* slot, const float* obs, int obs_stride, double* value, double* reward,
+                   double* policy);
+    int (*recurrent)(void* user, int n, const int32_t* slot, const int32_t* parent_node, const int32_t* action, int child_node,
+                     double* value, double* reward, double* policy);
+} mzb_host_evaluator;
+int mzb_set_host_evaluator(mzb_engine* e, const mzb_host_evaluator* evaluator);
 
 /* Replaces: VPRNetModel::LoadCheckpoint (vprnet.cpp:66-74): takes the module's named fp32 tensors (78 params + 60
  * buffers for the shipped Connect4 net), folds eval-mode BN (eps 1e-4) and packs them for the kernels. */

@@ -67,10 +67,14 @@ public:
     // VPRNetModel::LoadCheckpoint (vprnet.cpp:66-74): the module's named fp32 tensors
     void LoadWeights(const std::vector<mzb_tensor_desc>& tensors) { check(mzb_load_weights(e_, tensors.data(), (int)tensors.size()), "mzb_load_weights"); }
     mzb_shapes shapes() const { mzb_shapes s; check(mzb_get_shapes(e_, &s), "mzb_get_shapes"); return s; }
+    // An engine is driven by one host thread at a time (mzb200.h): callers that share it (a Cohort's searches next to
+    // VPRNetEvaluator batches) serialise on this mutex.
+    std::mutex& call_mutex() { return call_mu_; }
 
 private:
     mzb_config cfg_;
     mzb_engine* e_ = nullptr;
+    std::mutex call_mu_;
 };
 
 // VPRNetModel's batch inference API (vprnet.h:64-110) on host vectors.
@@ -88,6 +92,7 @@ public:
         for (int b = 0; b < B; ++b) std::copy(stacked_observations[b].begin(), stacked_observations[b].end(), obs.begin() + (size_t)b * sh_.initial_flat_size);
         std::vector<double> v(B), r(B), p((size_t)B * A);
         std::vector<float> h((size_t)B * sh_.recurrent_flat_size);
+        std::lock_guard<std::mutex> call(eng_->call_mutex());
         check(mzb_initial_inference(eng_->handle(), obs.data(), B, v.data(), r.data(), p.data(), h.data()), "mzb_initial_inference");
         return unpack(B, A, v, r, p, h);
     }
@@ -98,6 +103,7 @@ public:
         std::vector<int32_t> act(actions.begin(), actions.end());
         std::vector<double> v(B), r(B), p((size_t)B * A);
         std::vector<float> h((size_t)B * sh_.recurrent_flat_size);
+        std::lock_guard<std::mutex> call(eng_->call_mutex());
         check(mzb_recurrent_inference(eng_->handle(), hin.data(), act.data(), B, v.data(), r.data(), p.data(), h.data()), "mzb_recurrent_inference");
         return unpack(B, A, v, r, p, h);
     }
@@ -135,6 +141,7 @@ public:
             if (!used_[s]) {
                 used_[s] = 1; ++members_;
                 const int32_t sd = seed;
+                std::lock_guard<std::mutex> call(eng_->call_mutex());
                 check(mzb_search_seed(eng_->handle(), s, 1, &sd), "mzb_search_seed");
                 return s;
             }
@@ -195,8 +202,11 @@ private:
         mzb_search_result out{};
         out.root_value = root.data(); out.max_tree_depth = depth.data(); out.n_children = n_children.data();
         out.child_actions = actions.data(); out.children_relative_visit = rel.data(); out.emperical_policy = pol.data();
-        check(mzb_search_batch_slots(eng_->handle(), obs.data(), slots.data(), masks.data(), to_play.data(), noise.data(), n, &out),
-              "mzb_search_batch_slots");
+        {
+            std::lock_guard<std::mutex> call(eng_->call_mutex());
+            check(mzb_search_batch_slots(eng_->handle(), obs.data(), slots.data(), masks.data(), to_play.data(), noise.data(), n, &out),
+                  "mzb_search_batch_slots");
+        }
         lk.lock();
         for (int i = 0; i < n; ++i) {
             MCTSReturn& r = batch[i]->result;

@@ -174,7 +174,10 @@ int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out) {
         e->se.node_cid = e->se_cid.as<uint32_t>();
         e->se.pool = e->se_pool.as<float>();
         MZB_CUDA(e->d_obs.alloc((size_t)T * sizeof(float)));
+    } else if (e->cfg.evaluator == MZB_EVAL_HOST) {
+        MZB_CUDA(e->d_obs.alloc((size_t)T * e->dims.initial_flat() * sizeof(float)));
     } else {
+        MZB_REQUIRE(e->cfg.evaluator == MZB_EVAL_NETWORK, "unknown evaluator kind %d", e->cfg.evaluator);
         e->net.reset(e->cfg.precision == MZB_BF16 ? make_bf16_backend() : make_fp32_backend());
         MZB_REQUIRE(e->net != nullptr, "precision mode %d is not available in this build", e->cfg.precision);
         MZB_CUDA(e->d_obs.alloc((size_t)T * e->dims.initial_flat() * sizeof(float)));
@@ -216,7 +219,7 @@ int mzb_get_shapes(mzb_engine* e, mzb_shapes* o) {
 
 int mzb_load_weights(mzb_engine* e, const mzb_tensor_desc* tensors, int n_tensors) {
     MZB_REQUIRE(e && tensors && n_tensors > 0, "null argument");
-    MZB_REQUIRE(e->net != nullptr, "engine was created with the synthetic evaluator; it has no network");
+    MZB_REQUIRE(e->net != nullptr, "engine was created with the synthetic or a host evaluator; it has no network");
     MZB_CUDA(cudaSetDevice(e->device));
     TensorMap tm;
     for (int i = 0; i < n_tensors; ++i) {
@@ -255,6 +258,13 @@ int mzb_search_seed(mzb_engine* e, int first_slot, int n, const int32_t* seeds) 
     launch_mt_seed(e->td.mt, e->td.mt_idx, e->d_to_play.as<int>(), first_slot, n, e->stream);
     MZB_CUDA(cudaGetLastError());
     MZB_CUDA(cudaStreamSynchronize(e->stream));
+    return MZB_OK;
+}
+
+int mzb_set_host_evaluator(mzb_engine* e, const mzb_host_evaluator* evaluator) {
+    MZB_REQUIRE(e && evaluator && evaluator->initial && evaluator->recurrent, "null argument");
+    MZB_REQUIRE(e->cfg.evaluator == MZB_EVAL_HOST, "engine was not created with MZB_EVAL_HOST");
+    e->host_eval = *evaluator;
     return MZB_OK;
 }
 

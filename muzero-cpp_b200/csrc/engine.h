@@ -61,6 +61,10 @@ struct mzb_engine {
     DevBuf d_obs, d_legal, d_to_play, d_add_noise, d_noise, d_root_slots, d_iota;
     DevBuf d_slots, mt_rows, mt_idx_rows;   // mzb_search_batch_slots: slot list and compact RNG rows
     DevBuf r_root_value, r_depth, r_nchild, r_actions, r_visits, r_rel, r_policy;
+    // MZB_EVAL_HOST: caller-supplied Evaluator callbacks; host rows of the search in flight
+    mzb_host_evaluator host_eval = {nullptr, nullptr, nullptr};
+    const float* h_obs_rows = nullptr;
+    const int32_t* h_slot_rows = nullptr;
     // SE stub
     SEDev se;
     DevBuf se_cid, se_pool;

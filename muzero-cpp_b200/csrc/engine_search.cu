@@ -35,6 +35,7 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
     const int A = c.num_actions, n = c.num_simulations;
     TreeDev& td = e->td;
     const bool synthetic = c.evaluator == MZB_EVAL_SYNTHETIC;
+    const bool host = c.evaluator == MZB_EVAL_HOST;
     const uint32_t full = (A >= 32) ? 0xffffffffu : ((1u << A) - 1u);
     bool any_noise = false;
     for (int t = 0; t < T; ++t) {
@@ -46,7 +47,28 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
     int64_t launches = 0;
     MZB_CUDA(cudaEventRecord(e->ev_start, s));
     // ---- root: initial inference (async) ----
-    if (synthetic) {
+    std::vector<int32_t> hv_slot, hv_parent, hv_action;
+    std::vector<double> hv_out;
+    // MZB_EVAL_HOST: outputs of one Evaluator call for all rows -> the arrays the tree kernels read
+    auto host_outputs_to_device = [&]() -> int {
+        MZB_CUDA(cudaMemcpyAsync(td.value, hv_out.data(), T * sizeof(double), cudaMemcpyHostToDevice, s));
+        MZB_CUDA(cudaMemcpyAsync(td.reward_out, hv_out.data() + T, T * sizeof(double), cudaMemcpyHostToDevice, s));
+        MZB_CUDA(cudaMemcpyAsync(td.policy, hv_out.data() + 2 * (size_t)T, (size_t)T * A * sizeof(double), cudaMemcpyHostToDevice, s));
+        MZB_CUDA(cudaStreamSynchronize(s));
+        return MZB_OK;
+    };
+    if (host) {
+        MZB_REQUIRE(e->host_eval.initial && e->host_eval.recurrent, "no host evaluator set (mzb_set_host_evaluator)");
+        MZB_REQUIRE(e->h_obs_rows, "a host evaluator needs host observations (mzb_search_batch / mzb_search_batch_slots)");
+        hv_slot.resize(T); hv_parent.resize(T); hv_action.resize(T);
+        hv_out.assign((size_t)T * (2 + A), 0.0);
+        for (int t = 0; t < T; ++t) hv_slot[t] = e->h_slot_rows ? e->h_slot_rows[t] : t;
+        int hrc = e->host_eval.initial(e->host_eval.user, T, hv_slot.data(), e->h_obs_rows, obs_stride, hv_out.data(),
+                                       hv_out.data() + T, hv_out.data() + 2 * (size_t)T);
+        MZB_REQUIRE(hrc == 0, "host evaluator: InitialInference failed (%d)", hrc);
+        hrc = host_outputs_to_device();
+        if (hrc) return hrc;
+    } else if (synthetic) {
         launch_se_initial(td, e->se, T, d_obs, obs_stride, s);
         ++launches;
     } else {
@@ -98,7 +120,7 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
     // its neighbours in a tile; tests/test_gpu_pipeline.py).
     static const int pipe_min = getenv("MZB_PIPELINE_MIN_TREES") ? atoi(getenv("MZB_PIPELINE_MIN_TREES")) : 256;
     static const int pipe_parts = getenv("MZB_PIPELINE_PARTS") ? std::max(2, std::min((int)mzb_engine::MAX_PARTS, atoi(getenv("MZB_PIPELINE_PARTS")))) : 2;
-    const bool pipelined = !synthetic && e->net->recurrent_concurrent() && pipe_min > 0 && T >= pipe_min && T >= pipe_parts;
+    const bool pipelined = !synthetic && !host && e->net->recurrent_concurrent() && pipe_min > 0 && T >= pipe_min && T >= pipe_parts;
     if (pipelined) {
         const int K = pipe_parts;
         cudaStream_t st[mzb_engine::MAX_PARTS];
@@ -133,7 +155,18 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
         launch_tree_step(td, T, sim, s);
         ++launches;
         if (sim == n) break;
-        if (synthetic) {
+        if (host) {
+            // Evaluator::RecurrentInference(parent.encoded_state, action) for every row (mcts.cpp:69-71)
+            MZB_CUDA(cudaMemcpyAsync(hv_parent.data(), td.in_slot, T * sizeof(int), cudaMemcpyDeviceToHost, s));
+            MZB_CUDA(cudaMemcpyAsync(hv_action.data(), td.action, T * sizeof(int), cudaMemcpyDeviceToHost, s));
+            MZB_CUDA(cudaStreamSynchronize(s));
+            for (int t = 0; t < T; ++t) hv_parent[t] -= t * (n + 1);   // pool slot -> node id (expansion order)
+            int hrc = e->host_eval.recurrent(e->host_eval.user, T, hv_slot.data(), hv_parent.data(), hv_action.data(), sim + 1,
+                                             hv_out.data(), hv_out.data() + T, hv_out.data() + 2 * (size_t)T);
+            MZB_REQUIRE(hrc == 0, "host evaluator: RecurrentInference failed (%d)", hrc);
+            hrc = host_outputs_to_device();
+            if (hrc) return hrc;
+        } else if (synthetic) {
             launch_se_recurrent(td, e->se, T, s);
             ++launches;
         } else {
@@ -173,7 +206,7 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
 int check_search_args(mzb_engine* e, const void* obs, const uint32_t* legal_mask, const int32_t* to_play, const uint8_t* add_noise, int T) {
     MZB_REQUIRE(e && obs && legal_mask && to_play && add_noise, "null argument");
     MZB_REQUIRE(T >= 1 && T <= e->cfg.max_trees, "n_trees %d outside [1, max_trees=%d]", T, e->cfg.max_trees);
-    MZB_REQUIRE(e->cfg.evaluator == MZB_EVAL_SYNTHETIC || e->weights_loaded, "weights not loaded (mzb_load_weights)");
+    MZB_REQUIRE(e->cfg.evaluator != MZB_EVAL_NETWORK || e->weights_loaded, "weights not loaded (mzb_load_weights)");
     return MZB_OK;
 }
 
@@ -230,7 +263,10 @@ int mzb_search_batch(mzb_engine* e, const float* obs, const uint32_t* legal_mask
     const int stride = (e->cfg.evaluator == MZB_EVAL_SYNTHETIC) ? 1 : e->dims.initial_flat();
     // host -> device copy of the observations (pageable or pinned caller memory) on the search stream
     MZB_CUDA(cudaMemcpyAsync(e->d_obs.p, obs, (size_t)n_trees * stride * sizeof(float), cudaMemcpyHostToDevice, e->stream));
-    return search_impl(e, e->d_obs.as<float>(), stride, legal_mask, to_play, add_noise, n_trees, out);
+    e->h_obs_rows = obs; e->h_slot_rows = nullptr;
+    rc = search_impl(e, e->d_obs.as<float>(), stride, legal_mask, to_play, add_noise, n_trees, out);
+    e->h_obs_rows = nullptr;
+    return rc;
 }
 
 int mzb_search_batch_slots(mzb_engine* e, const float* obs, const int32_t* slots, const uint32_t* legal_mask,
@@ -241,7 +277,10 @@ int mzb_search_batch_slots(mzb_engine* e, const float* obs, const int32_t* slots
     MZB_CUDA(cudaSetDevice(e->device));
     const int stride = (e->cfg.evaluator == MZB_EVAL_SYNTHETIC) ? 1 : e->dims.initial_flat();
     MZB_CUDA(cudaMemcpyAsync(e->d_obs.p, obs, (size_t)n_trees * stride * sizeof(float), cudaMemcpyHostToDevice, e->stream));
-    return search_with_device_obs_slots(e, slots, legal_mask, to_play, add_noise, n_trees, out);
+    e->h_obs_rows = obs; e->h_slot_rows = slots;
+    rc = search_with_device_obs_slots(e, slots, legal_mask, to_play, add_noise, n_trees, out);
+    e->h_obs_rows = nullptr; e->h_slot_rows = nullptr;
+    return rc;
 }
 
 int mzb_search_batch_device_obs(mzb_engine* e, const float* d_obs, const uint32_t* legal_mask, const int32_t* to_play,

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "libmzb200.so")
 MAX_ACTIONS = 32
 MAX_HEAD_LAYERS = 8
 FP32_CHECK, BF16 = 0, 1
-EVAL_NETWORK, EVAL_SYNTHETIC = 0, 1
+EVAL_NETWORK, EVAL_SYNTHETIC, EVAL_HOST = 0, 1, 2
 INF_D = float(np.finfo(np.float64).max)    # types::INF_D  (types.h:78)
 NINF_D = -float(np.finfo(np.float64).max)  # types::NINF_D (types.h:77)
 
@@ -142,6 +142,17 @@ class InferenceOutputs:  # B x VPRNetModel::InferenceOutputs (vprnet.h:64-69), S
     encoded_state: np.ndarray
 
 
+# mzb_host_evaluator (MZB_EVAL_HOST): the two pure virtuals of the reference's Evaluator as batched callbacks
+_HOST_INITIAL = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_float), C.c_int,
+                            C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double))
+_HOST_RECURRENT = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int,
+                              C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double))
+
+
+class _CHostEvaluator(C.Structure):
+    _fields_ = [("user", C.c_void_p), ("initial", _HOST_INITIAL), ("recurrent", _HOST_RECURRENT)]
+
+
 _lib = None
 
 EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_destroy", "mzb_load_weights",
@@ -150,7 +161,7 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_search_batch", "mzb_search_batch_device_obs", "mzb_last_search_timing", "mzb_search_set_recording",
            "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes", "mzb_value_encode", "mzb_value_decode",
            "mzb_obs_ring_create", "mzb_obs_ring_reset", "mzb_obs_ring_push", "mzb_obs_ring_stacked", "mzb_search_batch_ring",
-           "mzb_actor_seed", "mzb_select_actions"]
+           "mzb_actor_seed", "mzb_select_actions", "mzb_set_host_evaluator"]
 
 
 def load_library(path=None):
@@ -196,6 +207,7 @@ def load_library(path=None):
     lib.mzb_search_batch_ring.argtypes = [C.c_void_p, ip, u32p, ip, u8p, C.c_int, C.POINTER(_CSearchResult)]
     lib.mzb_actor_seed.argtypes = [C.c_void_p, ip, ip, C.c_int]
     lib.mzb_select_actions.argtypes = [C.c_void_p, ip, C.POINTER(_CSearchResult), C.c_int, dp, ip]
+    lib.mzb_set_host_evaluator.argtypes = [C.c_void_p, C.POINTER(_CHostEvaluator)]
     lib.mzb_value_encode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, fp]
     lib.mzb_value_decode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, C.c_int, fp]
     _lib = lib
@@ -420,6 +432,38 @@ class Engine:
         return ms.value, nl.value
 
     # MCTS::MCTS rng_(seed) (mcts.cpp:26)
+    def set_host_evaluator(self, initial, recurrent):
+        """EVAL_HOST engines: `initial(slots, obs[n][stride]) -> (value[n], reward[n], policy[n][A])` and
+        `recurrent(slots, parent_node[n], action[n], child_node) -> (value, reward, policy)` stand behind the reference's
+        Evaluator::InitialInference / RecurrentInference (vprnet_evaluator.h:35-41); nodes are named by expansion order."""
+        A = self.config.num_actions
+
+        def _store(out, n, value, reward, policy):
+            v, r, p = out
+            np.ctypeslib.as_array(value, (n,))[:] = np.asarray(v, np.float64)
+            np.ctypeslib.as_array(reward, (n,))[:] = np.asarray(r, np.float64)
+            np.ctypeslib.as_array(policy, (n, A))[:] = np.asarray(p, np.float64).reshape(n, A)
+
+        def _initial(_user, n, slot, obs, stride, value, reward, policy):
+            try:
+                _store(initial(np.ctypeslib.as_array(slot, (n,)).copy(), np.ctypeslib.as_array(obs, (n, stride)).copy()), n, value, reward, policy)
+                return 0
+            except Exception as e:  # surfaces as an MzbError from the search call
+                self._host_error = e
+                return 1
+
+        def _recurrent(_user, n, slot, parent, action, child, value, reward, policy):
+            try:
+                _store(recurrent(np.ctypeslib.as_array(slot, (n,)).copy(), np.ctypeslib.as_array(parent, (n,)).copy(),
+                                 np.ctypeslib.as_array(action, (n,)).copy(), child), n, value, reward, policy)
+                return 0
+            except Exception as e:
+                self._host_error = e
+                return 1
+
+        self._host_cb = _CHostEvaluator(None, _HOST_INITIAL(_initial), _HOST_RECURRENT(_recurrent))   # keep the thunks alive
+        self._check(self.lib.mzb_set_host_evaluator(self._h, C.byref(self._host_cb)))
+
     def seed_slots(self, seeds, first_slot=0):
         s = np.ascontiguousarray(seeds, dtype=np.int32)
         self._check(self.lib.mzb_search_seed(self._h, first_slot, s.shape[0], _ptr(s, C.c_int32)))

@@ -1,0 +1,39 @@
+"""The reference's own class names over libmzb200.so (include/muzero_cpp_mzb200.hpp): muzero_cpp::algorithm::MCTS, Evaluator,
+VPRNetEvaluator, DeviceManager, VPRNetModel, MuZeroConfig.  tests/cpp/compat_test.cpp uses them the way tests/mcts_test.cpp,
+muzero.cpp and self_play.cpp do.  CPU: the header compiles with plain g++ (no CUDA, torch or abseil headers), links against the
+library and fails loudly without a GPU.  GPU: the reference's TestEvaluator searches return the reference's values (SURVEY.md
+Appendix B) from the device tree kernels; VPRNetModel matches the reference's network outputs; actor threads over a
+VPRNetEvaluator reproduce one direct batched search bit for bit."""
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = os.path.join(ROOT, "tests", "cpp", "compat_test.cpp")
+BIN = os.path.join(ROOT, "tests", "cpp", "compat_test")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def _build():
+    import mzb200
+    mzb200.load_library()   # builds nothing, but fails loudly if the library is absent
+    lib = os.path.join(ROOT, "muzero-cpp_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I", os.path.join(ROOT, "include"), "-o", BIN, SRC,
+                           "-L", lib, "-lmzb200", "-Wl,-rpath," + lib, "-lpthread"])
+
+
+def test_compat_header_compiles_and_fails_loudly_without_gpu():
+    import torch
+    _build()
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu test")
+    out = subprocess.run([BIN, GOLDEN], capture_output=True, text=True, timeout=120)
+    assert out.returncode != 0 and "mzb_engine_create" in out.stdout + out.stderr
+
+
+@pytest.mark.gpu
+def test_reference_names_on_the_gpu():
+    _build()
+    out = subprocess.run([BIN, GOLDEN], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "compat_test: ok" in out.stdout, out.stdout + out.stderr

@@ -118,3 +118,68 @@ def test_edge_cases_and_errors():
     res = eng.run(keys[:2], np.array([0x7f, 0x7f], np.uint32), np.zeros(2, np.int32), np.ones(2, np.uint8))
     assert res.root_value.shape == (2,)
     eng.close()
+
+
+def _table_evaluator(tree_seed, A):
+    """A deterministic evaluator whose outputs depend on the whole (parent node, action, new node) triple — the information a
+    user-defined Evaluator subclass (vprnet_evaluator.h:35-41) can see through the encoded states it returns."""
+    def ev(parent, action, new_node):
+        rng = np.random.default_rng([tree_seed, parent + 1, action + 1, new_node])
+        p = rng.random(A) + 0.05
+        return float(rng.uniform(-1, 1)), (0.0 if parent < 0 else float(rng.uniform(-0.5, 0.5))), [float(x) for x in p / p.sum()]
+    return ev
+
+
+@pytest.mark.parametrize("A,players,sims,noise", [(6, 2, 10, False), (7, 2, 50, True), (18, 1, 30, True)])
+def test_host_evaluator_path_matches_oracle(A, players, sims, noise):
+    """MZB_EVAL_HOST: a caller-supplied evaluator behind the device tree kernels (the path muzero_cpp::algorithm::MCTS takes for a
+    user Evaluator subclass).  Every tree gets different, history-dependent outputs; decisions must equal the oracle's bit for bit,
+    over two consecutive runs on the same RNG streams, with a ragged slot subset in the second."""
+    import mzb200
+    T, seed = 12, 5
+    kw = dict(num_actions=A, num_players=players, num_simulations=sims)
+    if players == 1:
+        kw.update(lower="INF", upper="NINF")
+    eng = _engine_for(kw, T, seed, se_ranges=(0.0, 0.0, 0.0, 0.0))
+    eng.close()
+    cfg = eng.config
+    cfg.evaluator = mzb200.EVAL_HOST
+    eng = mzb200.Engine(cfg, 0)
+    eng.set_recording(True)
+    evs = [_table_evaluator(100 + t, A) for t in range(T)]
+
+    def initial(slots, obs):
+        out = [evs[int(s)](-1, -1, 0) for s in slots]
+        return [o[0] for o in out], [o[1] for o in out], [o[2] for o in out]
+
+    def recurrent(slots, parent, action, child):
+        out = [evs[int(s)](int(p), int(a), child) for s, p, a in zip(slots, parent, action)]
+        return [o[0] for o in out], [o[1] for o in out], [o[2] for o in out]
+
+    eng.set_host_evaluator(initial, recurrent)
+    okw = dict(kw)
+    if players == 1:
+        okw.update(lower=O.INF_D, upper=O.NINF_D)
+    ocfg = O.make_config(**okw)
+    oracles = [O.mcts_create(ocfg, seed + t) for t in range(T)]
+    width = eng.shapes.initial_flat_size
+    for run, slots in enumerate([list(range(T)), [9, 2, 4, 11, 0]]):
+        n = len(slots)
+        masks = np.array([((1 << A) - 1) if (s + run) % 3 else (((1 << A) - 1) & ~0b10) for s in slots], np.uint32)
+        to_play = np.array([(s + run) % players for s in slots], np.int32)
+        res = eng.run(np.zeros((n, width), np.float32), masks, to_play, np.full(n, noise, np.uint8), slots=np.array(slots, np.int32))
+        trace = eng.get_trace(n)
+        for i, s in enumerate(slots):
+            legal = [a for a in range(A) if (int(masks[i]) >> a) & 1]
+            want = O.mcts_run(oracles[s], legal, int(to_play[i]), noise, evs[s])
+            got = _engine_result(res, i, trace)
+            assert H.results_equal(want, got), (run, s, want, got)
+    for m in oracles:
+        O.mcts_destroy(m)
+    # an evaluator that throws surfaces as an error of the search call, not as a silent result
+    def broken(slots, parent, action, child):
+        raise RuntimeError("boom")
+    eng.set_host_evaluator(initial, broken)
+    with pytest.raises(mzb200.MzbError):
+        eng.run(np.zeros((1, width), np.float32), np.array([1], np.uint32), np.array([0], np.int32), np.zeros(1, np.uint8))
+    eng.close()

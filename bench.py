@@ -336,24 +336,36 @@ def main():
     eng.close()
 
     if rank == 0 and world == 1:
-        # tree kernels alone (HBM bound): same search with the network stubbed by the SE evaluator
-        scfg = mzb200.preset(preset_name, max_trees=T, evaluator=mzb200.EVAL_SYNTHETIC)
-        seng = mzb200.Engine(scfg, local_rank)
-        keys = (np.arange(T) + 1).astype(np.float32)
-        for _ in range(3):
-            seng.run(keys, masks, to_play, noise)
-        ms = 0.0
-        for _ in range(5):
-            seng.run(keys, masks, to_play, noise)
-            ms += seng.last_search_timing()["sim_loop_ms"]
-        sims_s = 5 * T * sims / (ms / 1000.0)
+        # tree kernels alone (HBM bound): same search with the network stubbed by the SE evaluator, which still moves one hidden
+        # state parent -> child per simulation.  At the workload's cohort the step is launch/latency bound (1024 warps); the
+        # second figure uses a cohort large enough for HBM to be the limit.
         S_h = 4 * eng.shapes.recurrent_flat_size
         d = 4
         b_sim = 2 * S_h + d * 28 * A + 32 * A + 36 * (d + 1) + (4 + 16 + 4 * A)
-        line["roofline_tree"] = dict(bound="hbm", achieved=b_sim * sims_s / 1e9, peak=pk["hbm"], unit="GB/s",
-                                     frac=b_sim * sims_s / 1e9 / pk["hbm"], traffic=None, bytes_per_sim=b_sim,
-                                     sims_per_s=sims_s, kernel="tree_step + SE stub (hidden-state move)")
-        seng.close()
+
+        def tree_leg(Tt):
+            scfg = mzb200.preset(preset_name, max_trees=Tt, evaluator=mzb200.EVAL_SYNTHETIC)
+            seng = mzb200.Engine(scfg, local_rank)
+            keys = (np.arange(Tt) + 1).astype(np.float32)
+            m = np.full(Tt, (1 << A) - 1, np.uint32)
+            tp = (np.arange(Tt) % cfg.num_players).astype(np.int32)
+            nz = np.ones(Tt, np.uint8)
+            for _ in range(3):
+                seng.run(keys, m, tp, nz)
+            ms = 0.0
+            for _ in range(5):
+                seng.run(keys, m, tp, nz)
+                ms += seng.last_search_timing()["sim_loop_ms"]
+            seng.close()
+            sims_s = 5 * Tt * sims / (ms / 1000.0)
+            return dict(bound="hbm", achieved=b_sim * sims_s / 1e9, peak=pk["hbm"], unit="GB/s", frac=b_sim * sims_s / 1e9 / pk["hbm"],
+                        traffic=None, bytes_per_sim=b_sim, sims_per_s=sims_s, trees=Tt, us_per_simulation_step=ms * 1000.0 / (5 * sims),
+                        kernel="tree_step + SE stub (outputs + bulk-copy hidden-state move through shared memory)")
+
+        line["roofline_tree"] = tree_leg(T)
+        T_big = 16384
+        if T_big > T and T_big * (sims + 1) * S_h < 40e9:
+            line["roofline_tree_large_cohort"] = tree_leg(T_big)
         if not args.no_cpu_baseline:
             res = run_reference_cpu(preset_name, args.cpu_seconds, sims)
             if res and "error" not in res:

@@ -167,8 +167,7 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
             hrc = host_outputs_to_device();
             if (hrc) return hrc;
         } else if (synthetic) {
-            launch_se_recurrent(td, e->se, T, s);
-            ++launches;
+            launches += launch_se_recurrent(td, e->se, T, s);
         } else {
             rc = e->net->recurrent(T, td.in_slot, td.action, td.out_slot, tree_outputs(e), s);
             if (rc) return rc;

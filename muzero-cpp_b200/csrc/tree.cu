@@ -7,6 +7,7 @@
 // warp-shuffle reduction.  Integer RNG (std::mt19937 + libstdc++'s std::shuffle / Lemire downscaling) is restated
 // on the device so that the per-visit child shuffle (mcts.cpp:112) is reproduced bit for bit.
 #include "tree.h"
+#include "umma.cuh"
 
 namespace mzb {
 namespace {
@@ -249,6 +250,7 @@ __global__ void __launch_bounds__(128) tree_step_kernel(TreeDev td, int t_first,
         // coalesced child-statistics loads: lane j <-> child j
         int4 cm = make_int4(0, 0, -1, -1); double cp = 0.0, cvs = 0.0, cr = 0.0;
         if (lane < n) { cm = meta[cb + lane]; cp = prior[cb + lane]; cvs = value_sum[cb + lane]; cr = reward[cb + lane]; }
+        const double pbc_n = __ldg(td.pbc_table + N);   // in flight with the child loads, consumed after the shuffle
         // std::shuffle(children) — physically permutes the child records
         const int perm = shuffle_perm(rng, n, lane);
         int4 pm;
@@ -259,7 +261,7 @@ __global__ void __launch_bounds__(128) tree_step_kernel(TreeDev td, int t_first,
         // ucb_score (mcts.cpp:127-141)
         double score = 0.0;
         if (lane < n) {
-            double pb_c = td.pbc_table[N];
+            double pb_c = pbc_n;
             const double ratio = sqrt((double)N) / (double)(pm.x + 1);
             pb_c = pb_c * ratio;
             const double prior_score = pb_c * pp;
@@ -341,22 +343,24 @@ __device__ __forceinline__ uint32_t se_mix(uint32_t x) {
     x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
     return x;
 }
-__device__ void se_outputs(const TreeDev& td, const SEDev& se, int t, uint32_t cid) {
-    const double u = (double)(se_mix(cid ^ 0x1111U) >> 8) / 16777216.0;
-    const double vspan = se.vhi - se.vlo;
-    const double vs = u * vspan;
-    td.value[t] = se.vlo + vs;
-    const double u2 = (double)(se_mix(cid ^ 0x2222U) >> 8) / 16777216.0;
-    const double rspan = se.rhi - se.rlo;
-    const double rs = u2 * rspan;
-    td.reward_out[t] = se.rlo + rs;
-    double sum = 0.0;
-    for (int i = 0; i < td.A; ++i) {
-        const double w = (double)(1U + (se_mix(cid ^ (0x3333U + 0x101U * (uint32_t)i)) & 0x3FFU));
-        td.policy[(long)t * td.A + i] = w;
-        sum = sum + w;
+// Whole warp: lane i produces policy weight i.  The weights are integers in [1, 1024] held in f64, so their sum is exact in any
+// order and equals the evaluator's sequential sum (oracle/se_evaluator.h) bit for bit.
+__device__ void se_outputs(const TreeDev& td, const SEDev& se, int t, uint32_t cid, int lane) {
+    if (lane == 0) {
+        const double u = (double)(se_mix(cid ^ 0x1111U) >> 8) / 16777216.0;
+        const double vspan = se.vhi - se.vlo;
+        const double vs = u * vspan;
+        td.value[t] = se.vlo + vs;
+        const double u2 = (double)(se_mix(cid ^ 0x2222U) >> 8) / 16777216.0;
+        const double rspan = se.rhi - se.rlo;
+        const double rs = u2 * rspan;
+        td.reward_out[t] = se.rlo + rs;
     }
-    for (int i = 0; i < td.A; ++i) td.policy[(long)t * td.A + i] = td.policy[(long)t * td.A + i] / sum;
+    const double w = (lane < td.A) ? (double)(1U + (se_mix(cid ^ (0x3333U + 0x101U * (uint32_t)lane)) & 0x3FFU)) : 0.0;
+    double sum = w;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(FULL, sum, off);
+    if (lane < td.A) td.policy[(long)t * td.A + lane] = w / sum;
 }
 __global__ void se_initial_kernel(TreeDev td, SEDev se, int n_trees, const float* obs, int obs_stride) {
     const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -364,7 +368,8 @@ __global__ void se_initial_kernel(TreeDev td, SEDev se, int n_trees, const float
     if (t >= n_trees) return;
     const uint32_t key = (uint32_t)obs[(long)t * obs_stride];
     const uint32_t cid = se_mix(key ^ 0x9e3779b9U) & 0xFFFFFFU;
-    if (lane == 0) { se.node_cid[(long)t * (td.n_sims + 1)] = cid; se_outputs(td, se, t, cid); }
+    if (lane == 0) se.node_cid[(long)t * (td.n_sims + 1)] = cid;
+    se_outputs(td, se, t, cid, lane);
     float* dst = se.pool + (long)t * (td.n_sims + 1) * se.slot_floats;
     for (int i = lane; i < se.slot_floats; i += 32) dst[i] = (float)((cid + i) & 0xFF) * (1.0f / 256.0f);
 }
@@ -377,13 +382,35 @@ __global__ void se_recurrent_kernel(TreeDev td, SEDev se, int n_trees) {
     const uint32_t pc = se.node_cid[in_slot];
     const uint32_t cid = se_mix(pc * 31U + (uint32_t)td.action[t] + 0x85ebca6bU) & 0xFFFFFFU;
     (void)pool_base;
-    if (lane == 0) { se.node_cid[out_slot] = cid; se_outputs(td, se, t, cid); }
-    // the stub still moves one hidden state parent -> child, 16 B per lane per request (S_h read + S_h write)
+    if (lane == 0) se.node_cid[out_slot] = cid;
+    se_outputs(td, se, t, cid, lane);
+    if (se.slot_floats % 4 == 0) return;   // the hidden state travels by bulk copy (se_move_kernel)
+    // odd state sizes: 16 B per lane per request (S_h read + S_h write)
     const float4* src = reinterpret_cast<const float4*>(se.pool + (long)in_slot * se.slot_floats);
     float4* dst = reinterpret_cast<float4*>(se.pool + (long)out_slot * se.slot_floats);
     const int n4 = (se.slot_floats % 4 == 0) ? (se.slot_floats >> 2) : 0;
     for (int i = lane; i < n4; i += 32) dst[i] = src[i];
     for (int i = (n4 << 2) + lane; i < se.slot_floats; i += 32) se.pool[(long)out_slot * se.slot_floats + i] = se.pool[(long)in_slot * se.slot_floats + i];
+}
+
+// The stub's hidden-state move, parent slot -> child slot, staged through shared memory: one CTA per tree, one elected thread,
+// two 1-D bulk copies (global -> smem on an mbarrier, smem -> global as a bulk group).  The copy engine moves the 16-byte
+// lines; no register traffic.  ~10 CTAs of a Connect4 state (21.5 KB) are resident per SM, so 1024+ trees are all in flight.
+__global__ void __launch_bounds__(32) se_move_kernel(TreeDev td, SEDev se, int n_trees) {
+    extern __shared__ __align__(128) unsigned char stage[];
+    __shared__ __align__(8) uint64_t bar;
+    const int t = blockIdx.x;
+    if (t >= n_trees || threadIdx.x != 0) return;
+    const uint32_t bytes = (uint32_t)se.slot_floats * 4u;
+    const float* src = se.pool + (long)td.in_slot[t] * se.slot_floats;
+    float* dst = se.pool + (long)td.out_slot[t] * se.slot_floats;
+    umma::mbar_init(&bar, 1);
+    umma::fence_mbar_init();
+    umma::mbar_expect_tx(&bar, bytes);
+    umma::bulk_g2s(stage, src, bytes, &bar);
+    umma::mbar_wait(&bar, 0);
+    umma::bulk_s2g(dst, stage, bytes);
+    umma::bulk_commit_wait_all();
 }
 
 __global__ void mt_seed_kernel(uint32_t* mt, int* idx, const int* seeds, int first_slot, int n) {
@@ -425,8 +452,19 @@ void launch_tree_stats(const TreeDev& td, int n_trees, const ResultDev& r, cudaS
 void launch_se_initial(const TreeDev& td, const SEDev& se, int n_trees, const float* d_obs, int obs_stride, cudaStream_t s) {
     se_initial_kernel<<<warps_grid(n_trees, 128), 128, 0, s>>>(td, se, n_trees, d_obs, obs_stride);
 }
-void launch_se_recurrent(const TreeDev& td, const SEDev& se, int n_trees, cudaStream_t s) {
+int launch_se_recurrent(const TreeDev& td, const SEDev& se, int n_trees, cudaStream_t s) {
     se_recurrent_kernel<<<warps_grid(n_trees, 128), 128, 0, s>>>(td, se, n_trees);
+    if (se.slot_floats % 4 == 0) {
+        const size_t bytes = (size_t)se.slot_floats * 4;
+        static bool attr_set = false;   // states above the 48 KB default need the opt-in (ALE: 18 KB, C4d: 21.5 KB do not)
+        if (!attr_set && bytes > 48 * 1024) {
+            cudaFuncSetAttribute(se_move_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            attr_set = true;
+        }
+        se_move_kernel<<<n_trees, 32, bytes, s>>>(td, se, n_trees);
+        return 2;
+    }
+    return 1;
 }
 void launch_mt_move(uint32_t* d_mt_home, int* d_idx_home, uint32_t* d_mt_rows, int* d_idx_rows, const int* d_slots, int n,
                     int dir, cudaStream_t s) {

@@ -57,7 +57,8 @@ struct SEDev {
     double vlo, vhi, rlo, rhi;
 };
 void launch_se_initial(const TreeDev& td, const SEDev& se, int n_trees, const float* d_obs, int obs_stride, cudaStream_t s);
-void launch_se_recurrent(const TreeDev& td, const SEDev& se, int n_trees, cudaStream_t s);
+// returns the number of kernels launched (outputs + the bulk-copy state mover)
+int launch_se_recurrent(const TreeDev& td, const SEDev& se, int n_trees, cudaStream_t s);
 
 // RNG streams of a subset of slots <-> compact rows (mzb_search_batch_slots): dir 0 = gather rows <- slots, 1 = scatter back
 void launch_mt_move(uint32_t* d_mt_home, int* d_idx_home, uint32_t* d_mt_rows, int* d_idx_rows, const int* d_slots, int n,

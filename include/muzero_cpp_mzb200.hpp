@@ -14,6 +14,7 @@
 //   DeviceManager / DeviceLoan (device_manager.h:29-109)     least-outstanding-requests loans over the models
 //   Evaluator, VPRNetEvaluator (vprnet_evaluator.h:35-102)   blocking one-request calls coalesced into engine batches by the
 //                                                             callers themselves (leader/follower; no runner threads or promises)
+//   play_game (self_play.cpp:84-183)                         SelfPlayCohort: all live games searched in one lock-step batch per move
 //   algorithm::MCTS (mcts.h:113-187)                          run(): VPRNetEvaluator -> lock-step device search of the model's
 //                                                             cohort; any other Evaluator subclass -> device tree kernels with
 //                                                             host callbacks per simulation (MZB_EVAL_HOST)
@@ -521,4 +522,137 @@ private:
 };
 
 }  // namespace algorithm
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The callers' side for cohorts of games: play_game (self_play.cpp:84-183) for MANY games at once.
+// The reference runs one actor thread per game, each blocking on its own MCTS::run; here every live game of the cohort is
+// searched in ONE lock-step device search per move, fed from the device-resident observation ring (one raw frame per game and
+// move crosses PCIe instead of the stacked observation), and the moves are drawn by the engine's per-actor generators
+// (std::mt19937(config.seed + actor_num), self_play.cpp:233).  Per game, the result is what play_game hands to the
+// trajectory queue: the same GameHistory fields, filled in the same order.
+namespace types {
+struct GameHistory {   // types.h:110-118, the fields play_game fills
+    std::vector<Observation> observation_history;
+    std::vector<Action> action_history;
+    std::vector<double> reward_history;
+    std::vector<Player> to_play_history;
+    std::vector<std::vector<Action>> legal_actions;
+    std::vector<double> root_values;
+    std::vector<std::vector<double>> child_visits;
+    void store_search_statistics(double root_value, const std::vector<double>& relative_visits) {   // types.cpp:10-13
+        root_values.push_back(root_value);
+        child_visits.push_back(relative_visits);
+    }
+};
+}  // namespace types
+
+class SelfPlayCohort {
+public:
+    // games[i] plays on tree slot i of the model's engine with search seed search_seeds[i] and actor seed actor_seeds[i]
+    // (the reference gives both `config.seed + actor_num`, self_play.cpp:232-233).
+    SelfPlayCohort(const muzero_config::MuZeroConfig& config, VPRNetModel& model, std::vector<AbstractGame*> games,
+                   const std::vector<int>& search_seeds, const std::vector<int>& actor_seeds)
+        : config_(config), engine_(model.engine()), games_(std::move(games)), A_((int)config.action_space.size()) {
+        const int n = (int)games_.size();
+        if (n < 1 || n > engine_->config().max_trees) detail::fatal("SelfPlayCohort: more games than tree slots (raise num_actors)");
+        if ((int)search_seeds.size() != n || (int)actor_seeds.size() != n) detail::fatal("SelfPlayCohort: one seed pair per game");
+        std::vector<float> planes;   // action_representation_initial (types.h:43) pre-evaluated at observation resolution
+        if (config.action_representation_initial)
+            for (types::Action a : config.action_space) {
+                const types::Observation pl = config.action_representation_initial(a);
+                planes.insert(planes.end(), pl.begin(), pl.end());
+            }
+        std::vector<int32_t> slots(n), ss(search_seeds.begin(), search_seeds.end()), as(actor_seeds.begin(), actor_seeds.end());
+        for (int i = 0; i < n; ++i) slots[i] = i;
+        std::lock_guard<std::mutex> call(engine_->call_mutex());
+        mzb200::check(mzb_obs_ring_create(engine_->handle(), planes.empty() ? nullptr : planes.data()), "mzb_obs_ring_create");
+        mzb200::check(mzb_search_seed(engine_->handle(), 0, n, ss.data()), "mzb_search_seed");
+        mzb200::check(mzb_actor_seed(engine_->handle(), slots.data(), as.data(), n), "mzb_actor_seed");
+    }
+
+    // One game per slot from reset() to the end; training_step picks the temperature (self_play.cpp:104-105).
+    // Actors only (opponent = Self, exploration noise on); is_evaluator = true gives temperature 0 and no noise for Self opponents.
+    std::vector<types::GameHistory> play(int training_step, bool is_evaluator = false) {
+        const int n = (int)games_.size();
+        const double temperature = (is_evaluator || !config_.visit_softmax_temperature) ? 0.0 : config_.visit_softmax_temperature(training_step);
+        std::vector<types::GameHistory> hist(n);
+        std::vector<int32_t> live(n), zeros(n, 0);
+        const size_t frame = (size_t)config_.observation_shape.c * config_.observation_shape.h * config_.observation_shape.w;
+        std::vector<float> frames((size_t)n * frame);
+        for (int i = 0; i < n; ++i) {   // self_play.cpp:88-95
+            live[i] = i;
+            const types::Observation o = games_[i]->reset();
+            if (o.size() != frame) detail::fatal("AbstractGame::reset: observation size differs from observation_shape");
+            std::copy(o.begin(), o.end(), frames.begin() + (size_t)i * frame);
+            hist[i].action_history.push_back(0);
+            hist[i].observation_history.push_back(o);
+            hist[i].reward_history.push_back(0);
+            hist[i].to_play_history.push_back(games_[i]->to_play());
+            hist[i].legal_actions.push_back(games_[i]->legal_actions());
+        }
+        {
+            std::lock_guard<std::mutex> call(engine_->call_mutex());
+            mzb200::check(mzb_obs_ring_reset(engine_->handle(), live.data(), n), "mzb_obs_ring_reset");
+            mzb200::check(mzb_obs_ring_push(engine_->handle(), live.data(), frames.data(), zeros.data(), n), "mzb_obs_ring_push");
+        }
+        while (!live.empty()) {
+            const int m = (int)live.size();
+            std::vector<uint32_t> mask(m, 0);
+            std::vector<int32_t> to_play(m), n_children(m), depth(m), child_actions((size_t)m * A_), actions(m);
+            std::vector<uint8_t> noise(m, is_evaluator ? 0 : 1);
+            std::vector<double> root(m), rel((size_t)m * A_), pol((size_t)m * A_), temps(m, temperature);
+            for (int k = 0; k < m; ++k) {
+                for (types::Action a : hist[live[k]].legal_actions.back()) mask[k] |= 1u << a;
+                to_play[k] = games_[live[k]]->to_play();
+            }
+            mzb_search_result out{};
+            out.root_value = root.data(); out.max_tree_depth = depth.data(); out.n_children = n_children.data();
+            out.child_actions = child_actions.data(); out.children_relative_visit = rel.data(); out.emperical_policy = pol.data();
+            {   // get_stacked_observations(-1, ...) + mcts.run + select_action for every live game (self_play.cpp:119-133)
+                std::lock_guard<std::mutex> call(engine_->call_mutex());
+                mzb200::check(mzb_search_batch_ring(engine_->handle(), live.data(), mask.data(), to_play.data(), noise.data(), m, &out),
+                              "mzb_search_batch_ring");
+                mzb200::check(mzb_select_actions(engine_->handle(), live.data(), &out, m, temps.data(), actions.data()), "mzb_select_actions");
+            }
+            std::vector<int32_t> next_live, pushed_actions;
+            std::vector<float> next_frames;
+            for (int k = 0; k < m; ++k) {
+                const int g = live[k];
+                types::GameHistory& h = hist[g];
+                h.store_search_statistics(root[k], std::vector<double>(pol.begin() + (size_t)k * A_, pol.begin() + (size_t)(k + 1) * A_));
+                const types::StepReturn st = games_[g]->step(actions[k]);
+                // the reference's own termination rule, kept verbatim (self_play.cpp:149-150): with max_moves > 0 a game also ends
+                // while FEWER than max_moves searches have been stored
+                const bool done = st.done || (config_.max_moves > 0 && (int)h.root_values.size() < config_.max_moves);
+                h.action_history.push_back(actions[k]);
+                h.observation_history.push_back(st.observation);
+                h.reward_history.push_back(st.reward);
+                h.to_play_history.push_back(games_[g]->to_play());
+                h.legal_actions.push_back(games_[g]->legal_actions());
+                if (done) continue;
+                if (st.observation.size() != frame) detail::fatal("AbstractGame::step: observation size differs from observation_shape");
+                next_live.push_back(g);
+                pushed_actions.push_back(actions[k]);
+                next_frames.insert(next_frames.end(), st.observation.begin(), st.observation.end());
+            }
+            if (!next_live.empty()) {
+                std::lock_guard<std::mutex> call(engine_->call_mutex());
+                mzb200::check(mzb_obs_ring_push(engine_->handle(), next_live.data(), next_frames.data(), pushed_actions.data(), (int)next_live.size()),
+                              "mzb_obs_ring_push");
+            }
+            live.swap(next_live);
+            ++moves_;
+        }
+        return hist;
+    }
+    long cohort_moves() const { return moves_; }   // lock-step searches run so far
+
+private:
+    muzero_config::MuZeroConfig config_;
+    std::shared_ptr<mzb200::Engine> engine_;
+    std::vector<AbstractGame*> games_;
+    int A_;
+    long moves_ = 0;
+};
+
 }  // namespace muzero_cpp

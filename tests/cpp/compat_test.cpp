@@ -4,12 +4,14 @@
 //       returns for the same calls (oracle/_ref reproduces them, tests/test_oracle_cpu.py);
 //   (2) VPRNetModel batch inference against the reference's VPRNetModel outputs (tests/golden/net_tiny.mzbt);
 //   (3) actor threads blocking on VPRNetEvaluator one-request calls (vprnet_evaluator.cpp's contract);
-//   (4) actor threads calling MCTS::run over a VPRNetEvaluator, against one direct batched engine search.
+//   (4) actor threads calling MCTS::run over a VPRNetEvaluator, against one direct batched engine search;
+//   (5) SelfPlayCohort (play_game for a cohort of AbstractGames) against the reference's thread-per-actor loop.
 // Usage: compat_test <tests/golden dir>
 #define MZB200_FACADE_THROW
 #include <atomic>
 #include <cmath>
 #include <cstdio>
+#include <random>
 #include <thread>
 
 #include "muzero_cpp_mzb200.hpp"
@@ -233,10 +235,141 @@ static void network_paths(const std::string& golden_dir) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// (5) SelfPlayCohort against the reference's actor pattern.  A toy two-player game with ragged lengths and changing legal moves.
+class DriftGame : public AbstractGame {
+public:
+    explicit DriftGame(int id) : id_(id) {}
+    Observation reset() override { k_ = 0; return obs(); }
+    StepReturn step(Action a) override {
+        ++k_;
+        last_ = a;
+        return {obs(), 0.25 * a - 0.5, k_ >= 3 + id_ % 3};
+    }
+    Player to_play() const override { return (k_ + id_) % 2; }
+    std::vector<Action> legal_actions() const override {
+        std::vector<Action> l;
+        for (Action a = 0; a < 5; ++a) if (!(k_ % 2 == 1 && a == (k_ + id_) % 5)) l.push_back(a);
+        return l;
+    }
+    Action expert_action() override { return legal_actions()[0]; }
+    Action human_to_action() override { return legal_actions()[0]; }
+    std::string action_to_string(Action a) const override { return std::to_string(a); }
+
+private:
+    Observation obs() const {
+        Observation o(24);
+        for (int i = 0; i < 12; ++i) { const double x = (id_ * 7 + k_ * 3 + i + last_) * 0.137; o[i] = (float)(x - std::floor(x)); }
+        for (int i = 12; i < 24; ++i) o[i] = to_play() ? 1.f : -1.f;
+        return o;
+    }
+    int id_, k_ = 0, last_ = 0;
+};
+
+// GameHistory::get_stacked_observations(-1, ...) as the reference's actor computes it on the host (types.cpp:16-42), restated for the check
+static Observation stacked(const GameHistory& h, const muzero_config::MuZeroConfig& c) {
+    const int step = (int)h.observation_history.size() - 1, flat = c.observation_shape.h * c.observation_shape.w;
+    Observation out = h.observation_history[step];
+    for (int past = step - 1; past >= step - c.stacked_observations; --past) {
+        if (past >= 0) {
+            out.insert(out.end(), h.observation_history[past].begin(), h.observation_history[past].end());
+            const Observation planes = c.action_representation_initial(h.action_history[past + 1]);
+            out.insert(out.end(), planes.begin(), planes.end());
+        } else {
+            out.insert(out.end(), (size_t)(c.observation_shape.c + c.action_channels) * flat, 0.f);
+        }
+    }
+    return out;
+}
+
+static void self_play_cohort(const std::string& golden_dir) {
+    std::vector<mzbt::Tensor> g;
+    mzbt::load(golden_dir + "/net_tiny.mzbt", g);
+    const std::vector<mzb_tensor_desc> weights = weight_descs(g);
+    const int n = 6;
+    muzero_config::MuZeroConfig config = tiny_config(n);
+    config.seed = 11;
+    config.action_representation_initial = [](Action a) { return Observation(12, (float)a / 5.f); };
+    config.visit_softmax_temperature = [](int step) { return step < 100 ? 1.0 : 0.25; };
+
+    // (a) the reference's pattern: one thread, one MCTS, one std::mt19937 per game (self_play.cpp:84-183, 228-238)
+    std::vector<GameHistory> want(n);
+    {
+        DeviceManager dm;
+        VPRNetModel model(config, "cuda:0", MZB_FP32_CHECK);
+        model.LoadWeights(weights);
+        dm.AddDevice(std::move(model));
+        auto evaluator = std::make_shared<VPRNetEvaluator>(&dm, 4, 1, 4, 1);
+        std::vector<std::unique_ptr<algorithm::MCTS>> mcts(n);
+        for (int i = 0; i < n; ++i) mcts[i].reset(new algorithm::MCTS(config, config.seed + i, evaluator));
+        std::vector<std::thread> actors;
+        for (int i = 0; i < n; ++i)
+            actors.emplace_back([&, i] {
+                DriftGame game(i);
+                std::mt19937 rng(config.seed + i);
+                GameHistory& h = want[i];
+                h.action_history.push_back(0);
+                h.observation_history.push_back(game.reset());
+                h.reward_history.push_back(0);
+                h.to_play_history.push_back(game.to_play());
+                h.legal_actions.push_back(game.legal_actions());
+                const double temperature = config.visit_softmax_temperature(0);
+                bool done = false;
+                while (!done) {
+                    MCTSReturn st = mcts[i]->run(stacked(h, config), game.legal_actions(), game.to_play(), true);
+                    std::vector<double> w = st.children_relative_visit;
+                    for (double& v : w) v = std::pow(v, 1.0 / temperature);
+                    std::discrete_distribution<> d(w.begin(), w.end());
+                    const Action a = st.child_actions[d(rng)];
+                    h.store_search_statistics(st.root_value, st.emperical_policy);
+                    StepReturn sr = game.step(a);
+                    done = sr.done;
+                    h.action_history.push_back(a);
+                    h.observation_history.push_back(sr.observation);
+                    h.reward_history.push_back(sr.reward);
+                    h.to_play_history.push_back(game.to_play());
+                    h.legal_actions.push_back(game.legal_actions());
+                }
+                mcts[i].reset();   // a finished actor leaves the cohort
+            });
+        for (auto& t : actors) t.join();
+    }
+    // (b) the cohort driver on a second model with the same weights
+    VPRNetModel model(config, "cuda:0", MZB_FP32_CHECK);
+    model.LoadWeights(weights);
+    std::vector<std::unique_ptr<DriftGame>> owned;
+    std::vector<AbstractGame*> games;
+    std::vector<int> seeds;
+    for (int i = 0; i < n; ++i) { owned.emplace_back(new DriftGame(i)); games.push_back(owned.back().get()); seeds.push_back(config.seed + i); }
+    SelfPlayCohort cohort(config, model, games, seeds, seeds);
+    std::vector<GameHistory> got = cohort.play(/*training_step*/ 0);
+    EXPECT(cohort.cohort_moves() == 5, "lock-step searches: %ld (longest game has 5 moves)", cohort.cohort_moves());
+    for (int i = 0; i < n; ++i) {
+        EXPECT((int)got[i].root_values.size() == 3 + i % 3, "game %d: %zu moves", i, got[i].root_values.size());
+        EXPECT(got[i].action_history == want[i].action_history, "game %d: actions differ from the actor path", i);
+        EXPECT(got[i].root_values == want[i].root_values, "game %d: root values differ", i);
+        EXPECT(got[i].child_visits == want[i].child_visits, "game %d: stored policies differ", i);
+        EXPECT(got[i].observation_history == want[i].observation_history && got[i].reward_history == want[i].reward_history &&
+               got[i].to_play_history == want[i].to_play_history && got[i].legal_actions == want[i].legal_actions, "game %d: history differs", i);
+    }
+    // the same games once more on the same cohort: generators have advanced, histories stay well-formed
+    std::vector<GameHistory> again = cohort.play(/*training_step*/ 200);
+    for (int i = 0; i < n; ++i) {
+        EXPECT(again[i].action_history.size() == again[i].root_values.size() + 1, "game %d: history lengths", i);
+        for (size_t m = 0; m + 1 < again[i].action_history.size(); ++m) {
+            const auto& legal = again[i].legal_actions[m];
+            EXPECT(std::find(legal.begin(), legal.end(), again[i].action_history[m + 1]) != legal.end(), "game %d move %zu: illegal action", i, m);
+            double sum = 0;
+            for (double v : again[i].child_visits[m]) sum += v;
+            EXPECT(std::fabs(sum - 1.0) < 1e-12, "game %d move %zu: policy sums to %g", i, m, sum);
+        }
+    }
+}
+
 int main(int argc, char** argv) {
     try {
         appendix_b();
-        if (argc > 1) network_paths(argv[1]);
+        if (argc > 1) { network_paths(argv[1]); self_play_cohort(argv[1]); }
     } catch (const std::exception& e) {
         std::printf("compat_test: %s\n", e.what());
         return 1;

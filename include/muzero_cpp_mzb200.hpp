@@ -15,6 +15,7 @@
 //   Evaluator, VPRNetEvaluator (vprnet_evaluator.h:35-102)   blocking one-request calls coalesced into engine batches by the
 //                                                             callers themselves (leader/follower; no runner threads or promises)
 //   play_game (self_play.cpp:84-183)                         SelfPlayCohort: all live games searched in one lock-step batch per move
+//   reanalyze (self_play.cpp:186-225)                        ReanalyzeCohort: position i of every sampled history in one batch
 //   algorithm::MCTS (mcts.h:113-187)                          run(): VPRNetEvaluator -> lock-step device search of the model's
 //                                                             cohort; any other Evaluator subclass -> device tree kernels with
 //                                                             host callbacks per simulation (MZB_EVAL_HOST)
@@ -653,6 +654,80 @@ private:
     std::vector<AbstractGame*> games_;
     int A_;
     long moves_ = 0;
+};
+
+// reanalyze (self_play.cpp:186-225) for a cohort of sampled histories: the reference re-searches the positions of ONE history
+// one after another on one actor's MCTS object; here history r lives on tree slot r (so its searches consume that slot's RNG
+// stream in the reference's order) and position i of EVERY history is searched in one lock-step batch.  Frames are replayed
+// through the observation ring, which rebuilds get_stacked_observations(i, ...) on the device.
+class ReanalyzeCohort {
+public:
+    ReanalyzeCohort(const muzero_config::MuZeroConfig& config, VPRNetModel& model, const std::vector<int>& search_seeds)
+        : config_(config), engine_(model.engine()), A_((int)config.action_space.size()), n_((int)search_seeds.size()) {
+        if (n_ < 1 || n_ > engine_->config().max_trees) detail::fatal("ReanalyzeCohort: more histories than tree slots");
+        std::vector<float> planes;
+        if (config.action_representation_initial)
+            for (types::Action a : config.action_space) {
+                const types::Observation pl = config.action_representation_initial(a);
+                planes.insert(planes.end(), pl.begin(), pl.end());
+            }
+        std::vector<int32_t> ss(search_seeds.begin(), search_seeds.end());
+        std::lock_guard<std::mutex> call(engine_->call_mutex());
+        mzb200::check(mzb_obs_ring_create(engine_->handle(), planes.empty() ? nullptr : planes.data()), "mzb_obs_ring_create");
+        mzb200::check(mzb_search_seed(engine_->handle(), 0, n_, ss.data()), "mzb_search_seed");
+    }
+
+    // histories[r] is updated in place: root_values[i] and child_visits[i] of every stored position (self_play.cpp:213-214)
+    void reanalyze(std::vector<types::GameHistory*>& histories) {
+        if ((int)histories.size() > n_) detail::fatal("ReanalyzeCohort: more histories than seeded slots");
+        const size_t frame = (size_t)config_.observation_shape.c * config_.observation_shape.h * config_.observation_shape.w;
+        std::vector<int32_t> all(histories.size());
+        size_t longest = 0;
+        for (size_t r = 0; r < histories.size(); ++r) { all[r] = (int32_t)r; longest = std::max(longest, histories[r]->root_values.size()); }
+        {
+            std::lock_guard<std::mutex> call(engine_->call_mutex());
+            mzb200::check(mzb_obs_ring_reset(engine_->handle(), all.data(), (int)all.size()), "mzb_obs_ring_reset");
+        }
+        for (size_t i = 0; i < longest; ++i) {
+            std::vector<int32_t> live, led_by;
+            std::vector<float> frames;
+            std::vector<uint32_t> mask;
+            std::vector<int32_t> to_play;
+            for (size_t r = 0; r < histories.size(); ++r) {
+                const types::GameHistory& h = *histories[r];
+                if (i >= h.root_values.size()) continue;
+                if (h.observation_history[i].size() != frame) detail::fatal("ReanalyzeCohort: observation size differs from observation_shape");
+                live.push_back((int32_t)r);
+                led_by.push_back(h.action_history[i]);
+                frames.insert(frames.end(), h.observation_history[i].begin(), h.observation_history[i].end());
+                uint32_t m = 0;
+                for (types::Action a : h.legal_actions[i]) m |= 1u << a;
+                mask.push_back(m);
+                to_play.push_back(h.to_play_history[i]);
+            }
+            const int m = (int)live.size();
+            std::vector<uint8_t> noise(m, 1);
+            std::vector<double> root(m), pol((size_t)m * A_);
+            mzb_search_result out{};
+            out.root_value = root.data(); out.emperical_policy = pol.data();
+            {
+                std::lock_guard<std::mutex> call(engine_->call_mutex());
+                mzb200::check(mzb_obs_ring_push(engine_->handle(), live.data(), frames.data(), led_by.data(), m), "mzb_obs_ring_push");
+                mzb200::check(mzb_search_batch_ring(engine_->handle(), live.data(), mask.data(), to_play.data(), noise.data(), m, &out),
+                              "mzb_search_batch_ring");
+            }
+            for (int k = 0; k < m; ++k) {
+                types::GameHistory& h = *histories[live[k]];
+                h.root_values[i] = root[k];
+                h.child_visits[i].assign(pol.begin() + (size_t)k * A_, pol.begin() + (size_t)(k + 1) * A_);
+            }
+        }
+    }
+
+private:
+    muzero_config::MuZeroConfig config_;
+    std::shared_ptr<mzb200::Engine> engine_;
+    int A_, n_;
 };
 
 }  // namespace muzero_cpp

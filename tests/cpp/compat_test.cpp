@@ -352,6 +352,47 @@ static void self_play_cohort(const std::string& golden_dir) {
         EXPECT(got[i].observation_history == want[i].observation_history && got[i].reward_history == want[i].reward_history &&
                got[i].to_play_history == want[i].to_play_history && got[i].legal_actions == want[i].legal_actions, "game %d: history differs", i);
     }
+    // (6) reanalyze (self_play.cpp:186-225): the reference's loop — one MCTS object per reanalyze actor re-searching its history
+    //     position by position — against ReanalyzeCohort on the played histories
+    {
+        std::vector<GameHistory> ref_path = got, cohort_path = got;
+        {
+            DeviceManager dm;
+            VPRNetModel m2(config, "cuda:0", MZB_FP32_CHECK);
+            m2.LoadWeights(weights);
+            dm.AddDevice(std::move(m2));
+            auto evaluator = std::make_shared<VPRNetEvaluator>(&dm, 4, 1, 4, 1);
+            std::vector<std::unique_ptr<algorithm::MCTS>> mcts(n);
+            for (int i = 0; i < n; ++i) mcts[i].reset(new algorithm::MCTS(config, 500 + i, evaluator));
+            std::vector<std::thread> actors;
+            for (int r = 0; r < n; ++r)
+                actors.emplace_back([&, r] {
+                    GameHistory& h = ref_path[r];
+                    for (int i = 0; i < (int)h.root_values.size(); ++i) {
+                        GameHistory upto = h;   // get_stacked_observations(i, ...): the history as it stood at step i
+                        upto.observation_history.resize(i + 1);
+                        MCTSReturn st = mcts[r]->run(stacked(upto, config), h.legal_actions[i], h.to_play_history[i], true);
+                        h.root_values[i] = st.root_value;
+                        h.child_visits[i] = st.emperical_policy;
+                    }
+                    mcts[r].reset();
+                });
+            for (auto& t : actors) t.join();
+        }
+        VPRNetModel m3(config, "cuda:0", MZB_FP32_CHECK);
+        m3.LoadWeights(weights);
+        std::vector<int> rseeds;
+        for (int i = 0; i < n; ++i) rseeds.push_back(500 + i);
+        ReanalyzeCohort re(config, m3, rseeds);
+        std::vector<GameHistory*> ptrs;
+        for (auto& h : cohort_path) ptrs.push_back(&h);
+        re.reanalyze(ptrs);
+        for (int r = 0; r < n; ++r) {
+            EXPECT(cohort_path[r].root_values == ref_path[r].root_values, "reanalyze history %d: root values differ", r);
+            EXPECT(cohort_path[r].child_visits == ref_path[r].child_visits, "reanalyze history %d: policies differ", r);
+            EXPECT(cohort_path[r].root_values != got[r].root_values, "reanalyze history %d: nothing was re-searched", r);
+        }
+    }
     // the same games once more on the same cohort: generators have advanced, histories stay well-formed
     std::vector<GameHistory> again = cohort.play(/*training_step*/ 200);
     for (int i = 0; i < n; ++i) {

@@ -21,7 +21,8 @@
 //                                                             host callbacks per simulation (MZB_EVAL_HOST)
 //
 // What is NOT here: Learn / SaveCheckpoint / LoadCheckpoint (learner side; weights arrive through
-// VPRNetModel::LoadWeights) and the host MCTSNode helpers select_child / ucb_score / backpropogate (the tree lives in HBM).
+// VPRNetModel::LoadWeights).  MCTS::select_child / ucb_score / backpropogate take hand-built MCTSNode records like the reference's
+// and run them through the device step (mzb_debug_*): the arithmetic under test is the tree kernel's, not a host copy.
 #pragma once
 #include <algorithm>
 #include <cstdlib>
@@ -434,15 +435,39 @@ private:
 
 namespace algorithm {
 
+// mcts.h:19-75 as a HOST record: what a caller (tests/mcts_test.cpp) assembles by hand and passes to the three public helpers
+// of MCTS below.  The search itself never builds these — its trees are structure-of-arrays pools in HBM — so only the
+// bookkeeping members exist here; add_exploration_noise and get_search_statistics run inside MCTS::run (tree_root_kernel,
+// tree_stats_kernel) and are pinned through its goldens.
+struct MCTSNode {
+    int visit_count = 0;
+    types::Player to_play = types::InvalidPlayer;
+    types::Action action = types::InvalidAction;
+    double prior = 0, value_sum = 0, reward = 0;
+    std::vector<MCTSNode> children;
+    types::Observation encoded_state;
+    MCTSNode(types::Action action, double prior) : action(action), prior(prior) {}
+    MCTSNode() = delete;
+    bool is_expanded() const { return !children.empty(); }                              // mcts.cpp:146-148
+    double value() const { return visit_count == 0 ? 0 : value_sum / visit_count; }     // mcts.cpp:151-153
+    void expand(const std::vector<types::Action>& actions, types::Player player, double r, const std::vector<double>& policy_probs,
+                const types::Observation& state) {                                      // mcts.cpp:157-167
+        to_play = player; reward = r; encoded_state = state;
+        for (types::Action a : actions) children.emplace_back(a, policy_probs[a]);
+    }
+};
+
 // mcts.h:113-187.  Thread-confined, one per actor, as in the reference.
 class MCTS {
 public:
-    MCTS(const muzero_config::MuZeroConfig& config, int seed, std::shared_ptr<Evaluator> vpr_eval) : eval_(std::move(vpr_eval)) {
+    MCTS(const muzero_config::MuZeroConfig& config, int seed, std::shared_ptr<Evaluator> vpr_eval)
+        : eval_(std::move(vpr_eval)), players_(config.num_players), mm_min_(config.value_lowerbound), mm_max_(config.value_upperbound) {
         if (auto net = std::dynamic_pointer_cast<VPRNetEvaluator>(eval_)) {
             // the search runs where the weights are: a tree slot of the chosen model's cohort
             dm_ = &net->device_manager();
             VPRNetModel* model = dm_->attach_searcher(&device_id_);
             device_search_.reset(new mzb200::MCTS(model->cohort(), seed));
+            dm_engine_ = model->engine();
         } else {
             // a user-defined Evaluator (tests/mcts_test.cpp:16-27): a private one-tree engine whose two inference calls come back here
             const mzb_config pod = detail::to_pod(config, 1, MZB_FP32_CHECK, MZB_EVAL_HOST, nullptr);
@@ -492,7 +517,90 @@ public:
         return r;
     }
 
+    // ---- the three public helpers (mcts.h:149-172), run by the DEVICE step on an upload of the caller's nodes ----
+    // select_child (mcts.cpp:110-124): shuffles node->children with this object's generator, returns the first strict pUCT maximum
+    MCTSNode* select_child(MCTSNode* node) {
+        std::vector<int32_t> tags;
+        const int chosen = device_select(node, /*restore_rng*/ 0, &tags, nullptr);
+        std::vector<MCTSNode> shuffled;
+        shuffled.reserve(node->children.size());
+        for (int32_t tag : tags) shuffled.push_back(std::move(node->children[tag]));
+        node->children = std::move(shuffled);
+        return &node->children[chosen];
+    }
+    // ucb_score (mcts.cpp:127-141)
+    double ucb_score(MCTSNode* parent, MCTSNode* child) {
+        std::vector<int32_t> tags;
+        std::vector<double> scores;
+        device_select(parent, /*restore_rng*/ 1, &tags, &scores);
+        const int32_t want = (int32_t)(child - parent->children.data());
+        for (size_t j = 0; j < tags.size(); ++j) if (tags[j] == want) return scores[j];
+        detail::fatal("ucb_score: child is not a child of parent");
+    }
+    // backpropogate (mcts.cpp:90-107); updates this object's MinMaxStats like the reference's member
+    void backpropogate(std::vector<MCTSNode*>& search_path, double value, types::Player to_play) {
+        const int len = (int)search_path.size();
+        const types::Player root_tp = (players_ == 2) ? ((to_play + (len - 1)) % 2) : 0;   // players alternate down the path
+        std::vector<int32_t> meta(4 * len), path(len);
+        std::vector<double> prior(len), vsum(len), rew(len);
+        for (int i = 0; i < len; ++i) {
+            const MCTSNode& nd = *search_path[i];
+            if (nd.to_play != types::InvalidPlayer && nd.to_play != (root_tp + i) % players_)
+                detail::fatal("backpropogate: players do not alternate along the path (the device tree derives to_play from depth)");
+            meta[4 * i] = nd.visit_count; meta[4 * i + 1] = nd.action; meta[4 * i + 2] = -1; meta[4 * i + 3] = i;
+            prior[i] = nd.prior; vsum[i] = nd.value_sum; rew[i] = nd.reward; path[i] = i;
+        }
+        mzb_debug_tree t{};
+        t.n_nodes = len; t.meta = meta.data(); t.prior = prior.data(); t.value_sum = vsum.data(); t.reward = rew.data();
+        t.minmax_minimum = mm_min_; t.minmax_maximum = mm_max_; t.root_to_play = root_tp; t.n_root_children = 0;
+        const std::vector<double> policy(helper_actions(), 1.0 / helper_actions());
+        double mm[2];
+        with_helper_engine([&](mzb_engine* e, int slot) {
+            mzb200::check(mzb_debug_tree_write(e, slot, &t), "mzb_debug_tree_write");
+            mzb200::check(mzb_debug_backpropagate(e, slot, path.data(), len, value, search_path.back()->reward, policy.data()), "mzb_debug_backpropagate");
+            mzb200::check(mzb_debug_tree_read(e, slot, len, meta.data(), nullptr, vsum.data(), nullptr, mm), "mzb_debug_tree_read");
+        });
+        for (int i = 0; i < len; ++i) { search_path[i]->visit_count = meta[4 * i]; search_path[i]->value_sum = vsum[i]; }
+        mm_min_ = mm[0]; mm_max_ = mm[1];
+    }
+
 private:
+    int helper_actions() const { return host_engine_ ? num_actions_ : dm_engine_->config().num_actions; }
+    template <class Fn>
+    void with_helper_engine(Fn fn) {
+        if (host_engine_) { fn(host_engine_->handle(), 0); return; }
+        std::lock_guard<std::mutex> call(dm_engine_->call_mutex());
+        fn(dm_engine_->handle(), device_search_->slot());
+    }
+    // uploads `node` and its children (as leaves), runs the device selection step; returns the chosen child's position and the
+    // children's tags (original positions) in post-shuffle order
+    int device_select(MCTSNode* node, int restore_rng, std::vector<int32_t>* tags, std::vector<double>* scores) {
+        const int n = (int)node->children.size();
+        if (n < 1 || n > helper_actions()) detail::fatal("select_child: node has no children (or more than num_actions)");
+        std::vector<int32_t> meta(4 * (n + 1));
+        std::vector<double> prior(n + 1), vsum(n + 1), rew(n + 1), sc(helper_actions());
+        meta[0] = node->visit_count; meta[1] = node->action; meta[2] = 1; meta[3] = 0;
+        prior[0] = node->prior; vsum[0] = node->value_sum; rew[0] = node->reward;
+        for (int j = 0; j < n; ++j) {
+            const MCTSNode& c = node->children[j];
+            meta[4 * (j + 1)] = c.visit_count; meta[4 * (j + 1) + 1] = c.action; meta[4 * (j + 1) + 2] = -1; meta[4 * (j + 1) + 3] = j;
+            prior[j + 1] = c.prior; vsum[j + 1] = c.value_sum; rew[j + 1] = c.reward;
+        }
+        mzb_debug_tree t{};
+        t.n_nodes = n + 1; t.meta = meta.data(); t.prior = prior.data(); t.value_sum = vsum.data(); t.reward = rew.data();
+        t.minmax_minimum = mm_min_; t.minmax_maximum = mm_max_;
+        t.root_to_play = (node->to_play >= 0 && node->to_play < players_) ? node->to_play : 0; t.n_root_children = n;
+        int32_t chosen = 0;
+        with_helper_engine([&](mzb_engine* e, int slot) {
+            mzb200::check(mzb_debug_tree_write(e, slot, &t), "mzb_debug_tree_write");
+            mzb200::check(mzb_debug_select_child(e, slot, restore_rng, &chosen, sc.data()), "mzb_debug_select_child");
+            mzb200::check(mzb_debug_tree_read(e, slot, n + 1, meta.data(), nullptr, nullptr, nullptr, nullptr), "mzb_debug_tree_read");
+        });
+        tags->resize(n);
+        for (int j = 0; j < n; ++j) (*tags)[j] = meta[4 * (j + 1) + 3];
+        if (scores) scores->assign(sc.begin(), sc.begin() + n);
+        return chosen - 1;
+    }
     int store(const VPRNetModel::InferenceOutputs& o, int node, double* value, double* reward, double* policy) {
         if ((int)o.policy.size() != num_actions_) return -1;
         *value = o.value; *reward = o.reward;
@@ -515,11 +623,15 @@ private:
     DeviceManager* dm_ = nullptr;
     int device_id_ = -1;
     std::unique_ptr<mzb200::MCTS> device_search_;
+    std::shared_ptr<mzb200::Engine> dm_engine_;
     // user-evaluator path
     std::unique_ptr<mzb200::Engine> host_engine_;
     std::vector<types::Observation> node_state_;   // encoded_state of every expanded node, by expansion order
     const types::Observation* root_obs_ = nullptr;
     int num_actions_ = 0;
+    // helpers: MinMaxStats(value_lowerbound, value_upperbound) as the reference's member (mcts.cpp:25), advanced by backpropogate
+    int players_;
+    double mm_min_, mm_max_;
 };
 
 }  // namespace algorithm

@@ -172,6 +172,33 @@ int mzb_search_get_trace(mzb_engine* e, int n_trees, int32_t* parent /*[T][n]*/,
 int mzb_search_get_records(mzb_engine* e, int n_trees, double* value /*[T][n+1]*/, double* reward /*[T][n+1]*/,
                            double* policy /*[T][n+1][A]*/);
 
+/* Unit-level parity hooks for the reference's hand-built trees (tests/mcts_test.cpp:30-153 drives MCTS::backpropogate,
+ * select_child and ucb_score on MCTSNode objects it assembles itself).  A tree is uploaded into tree slot `slot` in the engine's
+ * own layout — nodes in slot order, the children of a node contiguous, root = node 0 — one device step runs on it, and it is
+ * read back.  meta rows are {visit_count, action, child_base (-1 = not expanded), tag}; the tag travels with its record through
+ * the physical child shuffle of select_child (mcts.cpp:112).  Nodes below the root are taken to have num_actions children, as
+ * MCTS::run creates them (mcts.cpp:72). */
+typedef struct {
+    int32_t n_nodes;
+    const int32_t* meta;                        /* [n_nodes][4] */
+    const double *prior, *value_sum, *reward;   /* [n_nodes] */
+    double minmax_minimum, minmax_maximum;      /* MinMaxStats state (mcts.h:79-112) */
+    int32_t root_to_play, n_root_children;
+} mzb_debug_tree;
+int mzb_debug_tree_write(mzb_engine* e, int slot, const mzb_debug_tree* tree);
+int mzb_debug_tree_read(mzb_engine* e, int slot, int n_nodes, int32_t* meta, double* prior, double* value_sum, double* reward,
+                        double* minmax /*[2] = minimum, maximum*/);
+/* MCTS::select_child(root) (mcts.cpp:110-124) on the uploaded tree with the slot's RNG stream: shuffles the root's child
+ * records in place and returns the node index of the chosen child; scores[j] = ucb_score(root, child j) (mcts.cpp:127-141) in
+ * the post-shuffle order (num_actions entries, first n_root_children valid).  restore_rng != 0 puts the slot's generator back
+ * afterwards (ucb_score itself draws nothing). */
+int mzb_debug_select_child(mzb_engine* e, int slot, int restore_rng, int32_t* chosen_node, double* scores);
+/* MCTS::backpropogate(search_path, value, to_play) (mcts.cpp:90-107) along path[0..len) (node indices, root first; the leaf's
+ * to_play is root_to_play + len - 1 mod players); the device step also expands the leaf as MCTS::run would (reward
+ * leaf_reward, num_actions children with `policy` priors appended at node index n_nodes).  The MinMaxStats state is updated. */
+int mzb_debug_backpropagate(mzb_engine* e, int slot, const int32_t* path, int len, double value, double leaf_reward,
+                            const double* policy);
+
 /* ---- The callers' side: observation history and action selection for cohorts of games ----
  * Device-resident observation history per tree slot, stacked on the GPU the way GameHistory::get_stacked_observations
  * (types.cpp:16-42) does on the host: current frame, then for each of the previous `stacked_observations` steps the frame and

@@ -268,6 +268,117 @@ int mzb_set_host_evaluator(mzb_engine* e, const mzb_host_evaluator* evaluator) {
     return MZB_OK;
 }
 
+// ---- unit-level parity hooks (tests/mcts_test.cpp's hand-built trees on the device step)
+static int debug_slot_check(mzb_engine* e, int slot) {
+    MZB_REQUIRE(e, "null argument");
+    MZB_REQUIRE(slot >= 0 && slot < e->cfg.max_trees, "slot %d outside [0, %d)", slot, e->cfg.max_trees);
+    MZB_CUDA(cudaSetDevice(e->device));
+    return MZB_OK;
+}
+
+int mzb_debug_tree_write(mzb_engine* e, int slot, const mzb_debug_tree* t) {
+    int rc = debug_slot_check(e, slot);
+    if (rc) return rc;
+    MZB_REQUIRE(t && t->meta && t->prior && t->value_sum && t->reward, "null argument");
+    const TreeDev& td = e->td;
+    MZB_REQUIRE(t->n_nodes >= 1 && t->n_nodes + td.A <= td.slots_per_tree, "%d nodes do not fit a tree slot (%d node slots)", t->n_nodes, td.slots_per_tree);
+    MZB_REQUIRE(t->n_root_children >= 0 && t->n_root_children <= td.A, "bad root child count");
+    MZB_REQUIRE(t->root_to_play >= 0 && t->root_to_play < td.players, "root_to_play out of range");
+    for (int i = 0; i < t->n_nodes; ++i) {
+        const int cb = t->meta[4 * i + 2];
+        MZB_REQUIRE(cb < 0 || (cb > i && cb + (i == 0 ? t->n_root_children : td.A) <= t->n_nodes), "node %d: child_base %d outside the tree", i, cb);
+    }
+    const size_t sb = (size_t)slot * td.slots_per_tree, n = t->n_nodes;
+    MZB_CUDA(cudaMemcpy(td.meta + sb, t->meta, n * sizeof(int4), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td.prior + sb, t->prior, n * sizeof(double), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td.value_sum + sb, t->value_sum, n * sizeof(double), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td.reward + sb, t->reward, n * sizeof(double), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td.mm_min + slot, &t->minmax_minimum, sizeof(double), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td.mm_max + slot, &t->minmax_maximum, sizeof(double), cudaMemcpyHostToDevice));
+    const int zero = 0;
+    MZB_CUDA(cudaMemcpy(td.root_to_play + slot, &t->root_to_play, sizeof(int), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td.n_legal + slot, &t->n_root_children, sizeof(int), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td.n_slots + slot, &t->n_nodes, sizeof(int), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td.max_depth + slot, &zero, sizeof(int), cudaMemcpyHostToDevice));
+    return MZB_OK;
+}
+
+int mzb_debug_tree_read(mzb_engine* e, int slot, int n_nodes, int32_t* meta, double* prior, double* value_sum, double* reward, double* minmax) {
+    int rc = debug_slot_check(e, slot);
+    if (rc) return rc;
+    const TreeDev& td = e->td;
+    MZB_REQUIRE(n_nodes >= 1 && n_nodes <= td.slots_per_tree, "bad node count");
+    const size_t sb = (size_t)slot * td.slots_per_tree, n = n_nodes;
+    if (meta) MZB_CUDA(cudaMemcpy(meta, td.meta + sb, n * sizeof(int4), cudaMemcpyDeviceToHost));
+    if (prior) MZB_CUDA(cudaMemcpy(prior, td.prior + sb, n * sizeof(double), cudaMemcpyDeviceToHost));
+    if (value_sum) MZB_CUDA(cudaMemcpy(value_sum, td.value_sum + sb, n * sizeof(double), cudaMemcpyDeviceToHost));
+    if (reward) MZB_CUDA(cudaMemcpy(reward, td.reward + sb, n * sizeof(double), cudaMemcpyDeviceToHost));
+    if (minmax) {
+        MZB_CUDA(cudaMemcpy(minmax, td.mm_min + slot, sizeof(double), cudaMemcpyDeviceToHost));
+        MZB_CUDA(cudaMemcpy(minmax + 1, td.mm_max + slot, sizeof(double), cudaMemcpyDeviceToHost));
+    }
+    return MZB_OK;
+}
+
+int mzb_debug_select_child(mzb_engine* e, int slot, int restore_rng, int32_t* chosen_node, double* scores) {
+    int rc = debug_slot_check(e, slot);
+    if (rc) return rc;
+    MZB_REQUIRE(chosen_node, "null argument");
+    MZB_REQUIRE(e->cfg.num_simulations >= 1, "needs num_simulations >= 1");
+    if (!e->dbg_score.p) MZB_CUDA(e->dbg_score.alloc(32 * sizeof(double)));
+    int4 root;
+    MZB_CUDA(cudaMemcpy(&root, e->td.meta + (size_t)slot * e->td.slots_per_tree, sizeof(int4), cudaMemcpyDeviceToHost));
+    MZB_REQUIRE(root.z >= 0, "the root is not expanded");
+    MZB_REQUIRE(root.x >= 0 && root.x <= e->cfg.num_simulations + 1, "root visit count %d outside the pb_c table", root.x);
+    TreeDev td = e->td;
+    td.dbg_score = e->dbg_score.as<double>();
+    td.trace_parent = nullptr; td.trace_action = nullptr; td.rec_value = nullptr; td.rec_reward = nullptr; td.rec_policy = nullptr;
+    std::vector<uint32_t> saved_mt(restore_rng ? 624 : 0);
+    int saved_idx = 0;
+    if (restore_rng) {
+        MZB_CUDA(cudaMemcpy(saved_mt.data(), e->td.mt + (size_t)slot * 624, 624 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+        MZB_CUDA(cudaMemcpy(&saved_idx, e->td.mt_idx + slot, sizeof(int), cudaMemcpyDeviceToHost));
+    }
+    // step 0 = selection only; stops below the root when the chosen child is not expanded
+    launch_tree_step_range(td, slot, slot + 1, 0, e->stream);
+    MZB_CUDA(cudaGetLastError());
+    MZB_CUDA(cudaStreamSynchronize(e->stream));
+    if (restore_rng) {
+        MZB_CUDA(cudaMemcpy(e->td.mt + (size_t)slot * 624, saved_mt.data(), 624 * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        MZB_CUDA(cudaMemcpy(e->td.mt_idx + slot, &saved_idx, sizeof(int), cudaMemcpyHostToDevice));
+    }
+    std::vector<int> path(e->cfg.num_simulations + 2);
+    MZB_CUDA(cudaMemcpy(path.data(), e->td.path_slot + (size_t)slot * (e->cfg.num_simulations + 2), 2 * sizeof(int), cudaMemcpyDeviceToHost));
+    *chosen_node = path[1];
+    if (scores) MZB_CUDA(cudaMemcpy(scores, e->dbg_score.p, e->cfg.num_actions * sizeof(double), cudaMemcpyDeviceToHost));
+    return MZB_OK;
+}
+
+int mzb_debug_backpropagate(mzb_engine* e, int slot, const int32_t* path, int len, double value, double leaf_reward, const double* policy) {
+    int rc = debug_slot_check(e, slot);
+    if (rc) return rc;
+    const TreeDev& td0 = e->td;
+    const int n = e->cfg.num_simulations, A = e->cfg.num_actions;
+    MZB_REQUIRE(path && policy, "null argument");
+    MZB_REQUIRE(n >= 1 && len >= 1 && len <= n + 2, "path length %d outside [1, num_simulations + 2]", len);
+    int n_slots = 0;
+    MZB_CUDA(cudaMemcpy(&n_slots, td0.n_slots + slot, sizeof(int), cudaMemcpyDeviceToHost));
+    MZB_REQUIRE(n_slots + A <= td0.slots_per_tree, "no room to expand the leaf");
+    for (int i = 0; i < len; ++i) MZB_REQUIRE(path[i] >= 0 && path[i] < n_slots, "path[%d] = %d is not a node", i, path[i]);
+    MZB_CUDA(cudaMemcpy(td0.path_slot + (size_t)slot * (n + 2), path, len * sizeof(int), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td0.path_len + slot, &len, sizeof(int), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td0.value + slot, &value, sizeof(double), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td0.reward_out + slot, &leaf_reward, sizeof(double), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpy(td0.policy + (size_t)slot * A, policy, A * sizeof(double), cudaMemcpyHostToDevice));
+    TreeDev td = e->td;
+    td.trace_parent = nullptr; td.trace_action = nullptr; td.rec_value = nullptr; td.rec_reward = nullptr; td.rec_policy = nullptr;
+    // step n = expansion + backup only (no further selection)
+    launch_tree_step_range(td, slot, slot + 1, n, e->stream);
+    MZB_CUDA(cudaGetLastError());
+    MZB_CUDA(cudaStreamSynchronize(e->stream));
+    return MZB_OK;
+}
+
 int mzb_search_set_recording(mzb_engine* e, int enabled) {
     MZB_REQUIRE(e, "null argument");
     MZB_CUDA(cudaSetDevice(e->device));

@@ -57,6 +57,7 @@ struct mzb_engine {
         path_slot, path_len, in_slot, out_slot, action, value, reward_out, policy, pbc_table;
     DevBuf trace_parent, trace_action, rec_value, rec_reward, rec_policy;
     bool recording = false;
+    DevBuf dbg_score;   // mzb_debug_select_child
     // search inputs / outputs on the device
     DevBuf d_obs, d_legal, d_to_play, d_add_noise, d_noise, d_root_slots, d_iota;
     DevBuf d_slots, mt_rows, mt_idx_rows;   // mzb_search_batch_slots: slot list and compact RNG rows

@@ -275,6 +275,7 @@ __global__ void __launch_bounds__(128) tree_step_kernel(TreeDev td, int t_first,
             }
             score = prior_score + value_score;
         }
+        if (td.dbg_score && len == 1) td.dbg_score[lane] = score;
         // first strict arg-max over children 0..n-1 (mcts.cpp:115-121)
         int best = lane;
         bool valid = lane < n;
@@ -344,7 +345,7 @@ __device__ __forceinline__ uint32_t se_mix(uint32_t x) {
     return x;
 }
 // Whole warp: lane i produces policy weight i.  The weights are integers in [1, 1024] held in f64, so their sum is exact in any
-// order and equals the evaluator's sequential sum (oracle/se_evaluator.h) bit for bit.
+// order and equals a sequential sum bit for bit.
 __device__ void se_outputs(const TreeDev& td, const SEDev& se, int t, uint32_t cid, int lane) {
     if (lane == 0) {
         const double u = (double)(se_mix(cid ^ 0x1111U) >> 8) / 16777216.0;

@@ -32,6 +32,7 @@ struct TreeDev {
     // optional recording (parity hooks); null when disabled
     int* trace_parent; int* trace_action;                  // [T][n_sims]
     double* rec_value; double* rec_reward; double* rec_policy;   // [T][n_sims+1], [T][n_sims+1], [T][n_sims+1][A]
+    double* dbg_score;                                     // [32]: pUCT scores of the root's children (mzb_debug_select_child only)
 };
 
 // root set-up after the initial inference: expand(legal), optional noise, minmax reset (mcts.cpp:39-49)

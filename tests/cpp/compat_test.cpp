@@ -6,6 +6,7 @@
 //   (3) actor threads blocking on VPRNetEvaluator one-request calls (vprnet_evaluator.cpp's contract);
 //   (4) actor threads calling MCTS::run over a VPRNetEvaluator, against one direct batched engine search;
 //   (5) SelfPlayCohort (play_game for a cohort of AbstractGames) against the reference's thread-per-actor loop.
+//   (0) tests/mcts_test.cpp's five unit tests (backpropogate, select_child, ucb_score, MinMaxStats, MCTSNode) on the device step.
 // Usage: compat_test <tests/golden dir>
 #define MZB200_FACADE_THROW
 #include <atomic>
@@ -45,6 +46,175 @@ static void expect_return(const char* name, const MCTSReturn& r, const Golden& g
     EXPECT(r.emperical_policy.size() == g.policy.size(), "%s: policy size", name);
     for (size_t i = 0; i < g.policy.size() && i < r.emperical_policy.size(); ++i)
         EXPECT(std::fabs(r.emperical_policy[i] - g.policy[i]) < 1e-12, "%s: policy[%zu] %.17g != %.17g", name, i, r.emperical_policy[i], g.policy[i]);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// (0) tests/mcts_test.cpp:30-224, function by function, with the reference's own expected values.  The MCTSNode records are
+//     assembled by hand exactly as there; select_child / ucb_score / backpropogate run on the DEVICE step (mzb_debug_*).
+#define REQUIRE_NEAR(a, b, tol) EXPECT(std::fabs((a) - (b)) <= (tol), "%s = %.9g, expected %.9g", #a, (double)(a), (double)(b))
+#define REQUIRE_EQUAL(a, b) EXPECT((a) == (b), "%s != %s", #a, #b)
+
+static void mcts_backpropogate_test(const muzero_config::MuZeroConfig& config) {   // tests/mcts_test.cpp:30-97
+    using algorithm::MCTSNode;
+    for (int players = 2; players >= 1; --players) {
+        muzero_config::MuZeroConfig c = config;
+        c.num_players = players;
+        algorithm::MCTS mcts_(c, c.seed, std::make_shared<TestEvaluator>());
+        MCTSNode root(-1, 0);
+        std::vector<Action> actions{0, 1, 4, 5};
+        Player player = 0;
+        std::vector<double> policy_probs{0.01, 0.2, 0.3, 0.1, 0.5, 0.4};
+        Observation encoded_state;
+        MCTSNode* node = &root;
+        std::vector<MCTSNode*> search_path{node};
+        for (int i = 0; i < 4; ++i) {
+            node->expand(actions, player, 0.1, policy_probs, encoded_state);
+            player = (player + 1) % players;
+            node = &node->children[0];
+            node->reward = 0.1;
+            search_path.push_back(node);
+        }
+        node->expand(actions, player, 0.1, policy_probs, encoded_state);
+        const std::vector<double> expected_values = players == 2 ? std::vector<double>{1, -0.4, 0.3, -0.05, 0.125}
+                                                                 : std::vector<double>{1, 0.6, 0.4, 0.3, 0.25};
+        mcts_.backpropogate(search_path, 1, player);
+        for (int i = (int)search_path.size() - 1; i >= 0; --i) {
+            REQUIRE_NEAR(search_path[i]->value(), expected_values[expected_values.size() - i - 1], 0.001);
+            REQUIRE_EQUAL(search_path[i]->visit_count, 1);
+        }
+    }
+}
+
+static void mcts_select_child_test(const muzero_config::MuZeroConfig& config) {    // tests/mcts_test.cpp:100-135
+    using algorithm::MCTSNode;
+    algorithm::MCTS mcts_(config, config.seed, std::make_shared<TestEvaluator>());
+    MCTSNode root(-1, 0);
+    std::vector<Action> actions{0, 1, 4, 5};
+    std::vector<double> policy_probs{0.01, 0.2, 0.3, 0.1, 0.5, 0.4};
+    root.expand(actions, 0, 10, policy_probs, Observation());
+    for (auto& ch : root.children) { ch.reward = 1; ch.visit_count = 1; ch.value_sum = 0.5; }
+    // Root has no visits, so prior has no influence: every score ties and the seeded shuffle decides (mcts_test.cpp:118-119)
+    MCTSNode* child = mcts_.select_child(&root);
+    REQUIRE_EQUAL(child->action, 0);
+    std::vector<Action> seen;
+    for (auto& ch : root.children) seen.push_back(ch.action);
+    std::sort(seen.begin(), seen.end());
+    EXPECT(seen == actions, "select_child lost or duplicated a child while shuffling");
+    root.visit_count += 1;
+    child = mcts_.select_child(&root);
+    REQUIRE_EQUAL(child->action, 4);
+    for (auto& ch : root.children)
+        if (ch.action == 1) { ch.value_sum -= 100; ch.visit_count += 100; }
+    child = mcts_.select_child(&root);
+    REQUIRE_EQUAL(child->action, 1);
+}
+
+static void mcts_ucb_test(const muzero_config::MuZeroConfig& config) {             // tests/mcts_test.cpp:138-153
+    using algorithm::MCTSNode;
+    algorithm::MCTS mcts_(config, config.seed, std::make_shared<TestEvaluator>());
+    MCTSNode root(-1, 0);
+    std::vector<double> policy_probs{0.01, 0.2, 0.3, 0.1, 0.5, 0.4};
+    root.visit_count = 2;
+    root.expand({0, 1, 4, 5}, 0, 10, policy_probs, Observation());
+    root.children[0].reward = 2;
+    root.children[0].value_sum = -8;
+    root.children[0].visit_count = 10;
+    REQUIRE_NEAR(mcts_.ucb_score(&root, &root.children[0]), 2.401782, 0.001);
+    REQUIRE_EQUAL(root.children[0].action, 0);   // ucb_score neither shuffles nor draws
+}
+
+// MinMaxStats (mcts.h:79-112, tests/mcts_test.cpp:156-188) as the tree kernels hold it: normalize(v) is the value term of the
+// pUCT score of a once-visited child with reward v under an unvisited parent (the prior term vanishes, mcts.cpp:130-139);
+// update(v) is one backup through a lone root whose expansion reward is v and whose value is 0 (mcts.cpp:99).
+struct DeviceMinMax {
+    mzb200::Engine eng;
+    double lo, hi, init_lo, init_hi;
+    DeviceMinMax(const mzb_config& pod, double minimum, double maximum) : eng(pod, 0), lo(minimum), hi(maximum), init_lo(minimum), init_hi(maximum) {}
+    void reset() { lo = init_lo; hi = init_hi; }
+    double normalize(double v) {
+        const int32_t meta[8] = {0, -1, 1, 0, 1, 0, -1, 0};
+        const double prior[2] = {0, 0.5}, vsum[2] = {0, 0}, rew[2] = {0, v};
+        mzb_debug_tree t{2, meta, prior, vsum, rew, lo, hi, 0, 1};
+        mzb200::check(mzb_debug_tree_write(eng.handle(), 0, &t), "write");
+        int32_t chosen;
+        std::vector<double> scores(eng.config().num_actions);
+        mzb200::check(mzb_debug_select_child(eng.handle(), 0, 1, &chosen, scores.data()), "select");
+        return scores[0];
+    }
+    void update(double v) {
+        const int32_t meta[4] = {0, -1, -1, 0}, path[1] = {0};
+        const double zero[1] = {0};
+        mzb_debug_tree t{1, meta, zero, zero, zero, lo, hi, 0, 0};
+        mzb200::check(mzb_debug_tree_write(eng.handle(), 0, &t), "write");
+        const std::vector<double> policy(eng.config().num_actions, 0.0);
+        mzb200::check(mzb_debug_backpropagate(eng.handle(), 0, path, 1, 0.0, v, policy.data()), "backup");
+        double mm[2];
+        mzb200::check(mzb_debug_tree_read(eng.handle(), 0, 1, nullptr, nullptr, nullptr, nullptr, mm), "read");
+        lo = mm[0]; hi = mm[1];
+    }
+};
+
+static void minmax_stats_test(const muzero_config::MuZeroConfig& config) {
+    muzero_config::MuZeroConfig c = config;
+    c.num_players = 1; c.discount = 1.0;
+    const mzb_config pod = detail::to_pod(c, 1, MZB_FP32_CHECK, MZB_EVAL_HOST, nullptr);
+    {   // default bounds
+        DeviceMinMax minmax_stats(pod, INF_D, NINF_D);
+        REQUIRE_EQUAL(minmax_stats.normalize(10), 10);
+        minmax_stats.update(2);
+        REQUIRE_EQUAL(minmax_stats.normalize(10), 10);
+        minmax_stats.update(12);
+        REQUIRE_EQUAL(minmax_stats.normalize(10), 0.8);
+        REQUIRE_EQUAL(minmax_stats.normalize(2), 0.0);
+        REQUIRE_EQUAL(minmax_stats.normalize(12), 1.0);
+        minmax_stats.reset();
+        REQUIRE_EQUAL(minmax_stats.normalize(10), 10);
+        minmax_stats.update(2);
+        REQUIRE_EQUAL(minmax_stats.normalize(10), 10);
+    }
+    {   // bounds given
+        DeviceMinMax minmax_stats(pod, 0, 1);
+        REQUIRE_EQUAL(minmax_stats.normalize(0.5), 0.5);
+        REQUIRE_EQUAL(minmax_stats.normalize(0), 0.0);
+        REQUIRE_EQUAL(minmax_stats.normalize(1), 1.0);
+        minmax_stats.update(0.5);
+        REQUIRE_EQUAL(minmax_stats.normalize(0.5), 0.5);
+        REQUIRE_EQUAL(minmax_stats.normalize(0), 0.0);
+        REQUIRE_EQUAL(minmax_stats.normalize(1), 1.0);
+    }
+}
+
+static void mctsnode_test() {                                                      // tests/mcts_test.cpp:191-213 (bookkeeping part)
+    algorithm::MCTSNode root(-1, 0);
+    EXPECT(!root.is_expanded(), "fresh node is expanded");
+    REQUIRE_EQUAL(root.value(), 0);
+    std::vector<Action> actions{0, 1, 4, 5};
+    std::vector<double> policy_probs{0.01, 0.2, 0.3, 0.1, 0.5, 0.25};
+    root.expand(actions, 0, 10, policy_probs, Observation());
+    root.value_sum += 10;
+    root.visit_count += 2;
+    REQUIRE_EQUAL(root.children.size(), actions.size());
+    REQUIRE_EQUAL(root.reward, 10);
+    REQUIRE_EQUAL(root.value(), 5);
+    EXPECT(root.is_expanded(), "expanded node is not expanded");
+    for (size_t i = 0; i < root.children.size(); ++i) {
+        REQUIRE_EQUAL(root.children[i].prior, policy_probs[actions[i]]);
+        REQUIRE_EQUAL(root.children[i].action, actions[i]);
+        EXPECT(!root.children[i].is_expanded(), "fresh child is expanded");
+    }
+}
+
+static void reference_unit_tests() {
+    muzero_config::MuZeroConfig config;   // tests/mcts_test.cpp:229-241
+    config.seed = 0; config.num_players = 2; config.num_simulations = 10;
+    config.dirichlet_alpha = 0.3; config.dirichlet_epsilon = 0.25; config.pb_c_base = 1; config.pb_c_init = 0; config.discount = 0.5;
+    config.value_lowerbound = 0; config.value_upperbound = 1;
+    config.action_space = {0, 1, 2, 3, 4, 5};
+    mcts_backpropogate_test(config);
+    mcts_select_child_test(config);
+    mcts_ucb_test(config);
+    minmax_stats_test(config);
+    mctsnode_test();
 }
 
 static void appendix_b() {
@@ -409,6 +579,7 @@ static void self_play_cohort(const std::string& golden_dir) {
 
 int main(int argc, char** argv) {
     try {
+        reference_unit_tests();
         appendix_b();
         if (argc > 1) { network_paths(argv[1]); self_play_cohort(argv[1]); }
     } catch (const std::exception& e) {

@@ -563,16 +563,26 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                     // a game's first W + 1 rows are its zero pad row: nothing to read or store there (whole 8-column groups only,
                     // to keep the TMEM column addresses aligned) — C4: 48 instead of 64 columns per game through the TMEM read port
                     const int skip = (W1 >> 3) << 3;
-                    for (int g = hsel; g < G; g += F_EPI_SPLIT) {
+                    // Games go to the two warp halves alternately; the odd game out of a 1- or 3-game tile is cut at a column
+                    // boundary and shared, so that a 3-game tile's epilogue costs 1.5 games per warp, not 2.
+                    static_assert(F_EPI_SPLIT == 2, "the column split below assumes two warp halves");
+                    const int G2 = G & ~1;
+                    const int mid = skip + ((((P - skip) >> 1) + 7) & ~7);
+                    const int n_mine = (G2 > hsel ? (G2 - hsel + 1) >> 1 : 0) + (G & 1);
+                    for (int i = 0; i < n_mine; ++i) {
+                        int g = hsel + 2 * i, c_lo = skip, c_hi = P;
+                        if (g >= G2) { g = G - 1; if (hsel == 0) c_hi = mid; else c_lo = mid; }
                         const int cbase = g * P;
-                        for (int c0 = skip; c0 < P; c0 += 32) {
-                            const bool two = P - c0 > 16;
+                        for (int c0 = c_lo; c0 < c_hi; c0 += 32) {
+                            const int left = c_hi - c0;
+                            const bool two = left > 16;
                             uint32_t v[32];
                             tmem_ld16(t_lane + src_col + cbase + c0, v);
                             if (two) tmem_ld16(t_lane + src_col + cbase + c0 + 16, v + 16);
                             const int mw_i = c0 >> 5, mw_s = c0 & 31;
                             uint32_t m = lds_u32(pm + mw_i * 4) >> mw_s;
                             if (mw_s && mw_i + 1 < 8) m |= lds_u32(pm + (mw_i + 1) * 4) << (32 - mw_s);
+                            if (left < 32) m &= (1u << left) - 1u;
                             tmem_ld_wait();
                             const uint32_t mw = wx ? m : 0u;
                             const uint32_t xa = xs + (uint32_t)(cbase + c0) * 16;
@@ -581,7 +591,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                             if (stash) {
 #pragma unroll
                                 for (int k = 0; k < 4; ++k)
-                                    if (c0 + 8 * k < P) tmem_st8(t_lane + F_R2_COL + cbase + c0 + 8 * k, v + 8 * k);
+                                    if (c0 + 8 * k < c_hi) tmem_st8(t_lane + F_R2_COL + cbase + c0 + 8 * k, v + 8 * k);
                             }
                         }
                     }

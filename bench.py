@@ -158,6 +158,18 @@ def run_reference_cpu(game, seconds_target, sims):
     return best
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    import ctypes
+    sys.stdout.flush()
+    ctypes.CDLL(None).fflush(None)   # C stdio buffers of the libraries, while fd 1 is still stderr
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -170,6 +182,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     args = ap.parse_args()
+    # stdout carries exactly one JSON line.  Libraries print there too (NCCL's "NCCL version ..." banner under torchrun), so
+    # file descriptor 1 points at stderr while the work runs and is put back for the line itself (emit()).
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
     rank = int(os.environ.get("RANK", "0"))
@@ -213,7 +231,7 @@ def main():
                                           res.get("batch", 0), res.get("torch_threads", "?"))),
                     e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                     wall_s=time.time() - t0)
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     import numpy as np
@@ -248,8 +266,13 @@ def main():
         eng.nccl_init(uid[0], rank, world)
         torch.cuda.synchronize()
         t0 = time.time()
-        eng.broadcast_weights(0)
-        sync_ms = 1000 * (time.time() - t0)
+        eng.broadcast_weights(0)          # first call: includes NCCL's lazy connection set-up
+        sync_first_ms = 1000 * (time.time() - t0)
+        dist.barrier()
+        t0 = time.time()
+        for _ in range(5):                # steady state = what every model_sync_interval costs
+            eng.broadcast_weights(0)
+        sync_ms = 1000 * (time.time() - t0) / 5
         sums = [None] * world
         dist.all_gather_object(sums, eng.weights_checksum())
         assert len(set(sums)) == 1, "weight broadcast left replicas different"
@@ -333,6 +356,8 @@ def main():
                 gpu_launches=int(launches), roofline=roofline, recurrent_states_per_s=states_per_s)
     if sync_ms is not None:
         line["weight_sync_ms"] = sync_ms
+        line["weight_sync_first_ms"] = sync_first_ms
+        line["weight_sync_bytes"] = int(eng.get_shapes().weight_blob_bytes)
     eng.close()
 
     if rank == 0 and world == 1:
@@ -376,7 +401,7 @@ def main():
                 res = run_port_cpu(preset_name, args.cpu_seconds, sims)
                 line["cpu_baseline"] = dict(value=res["sims_per_s"], unit=UNIT, cores=1, kind="port", sample=res["sample"])
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -20,9 +20,9 @@
 //                                                             cohort; any other Evaluator subclass -> device tree kernels with
 //                                                             host callbacks per simulation (MZB_EVAL_HOST)
 //
-// What is NOT here: Learn / SaveCheckpoint / LoadCheckpoint (learner side; weights arrive through
-// VPRNetModel::LoadWeights).  MCTS::select_child / ucb_score / backpropogate take hand-built MCTSNode records like the reference's
-// and run them through the device step (mzb_debug_*): the arithmetic under test is the tree kernel's, not a host copy.
+// What is NOT here: Learn / SaveCheckpoint (learner side).  LoadCheckpoint reads the reference's own files.
+// MCTS::select_child / ucb_score / backpropogate take hand-built MCTSNode records like the reference's and run them through the
+// device step (mzb_debug_*): the arithmetic under test is the tree kernel's, not a host copy.
 #pragma once
 #include <algorithm>
 #include <cstdlib>
@@ -181,6 +181,7 @@ public:
         const char* env = std::getenv("MZB200_PRECISION");
         if (env && std::string(env) == "fp32") precision = MZB_FP32_CHECK;
         st_->device = device;
+        st_->path = config.path + "/checkpoints/";   // vprnet.cpp:32
         const int trees = std::max({config.num_actors + config.num_reanalyze_actors + config.num_evaluators,
                                     config.initial_inference_batch_size, config.recurrent_inference_batch_size, 1});
         const mzb_config pod = detail::to_pod(config, trees, precision, MZB_EVAL_NETWORK, &st_->planes);
@@ -233,7 +234,14 @@ public:
         return o.unpack();
     }
 
-    // Stands in for LoadCheckpoint (vprnet.cpp:66-74) until the native archive reader exists: the module's named fp32 tensors.
+    // vprnet.cpp:66-74: reads "<path>.pt" as torch::save wrote it (vprnet.cpp:58-63) with the library's own archive reader — no
+    // libtorch.  The "-optimizer.pt" file next to it is the learner's and is not read.
+    void LoadCheckpoint(const std::string& path) {
+        std::lock_guard<std::mutex> call(st_->engine->call_mutex());
+        mzb200::check(mzb_load_checkpoint(st_->engine->handle(), (path + ".pt").c_str()), "mzb_load_checkpoint");
+    }
+    void LoadCheckpoint(int step) { LoadCheckpoint(st_->path + "checkpoint-" + std::to_string(step)); }
+    // The same hand-over without a file: the module's named fp32 tensors (a learner in the same process, tests).
     void LoadWeights(const std::vector<mzb_tensor_desc>& tensors) {
         std::lock_guard<std::mutex> call(st_->engine->call_mutex());
         st_->engine->LoadWeights(tensors);
@@ -261,7 +269,7 @@ private:
         }
     };
     struct State {
-        std::string device;
+        std::string device, path;
         std::vector<float> planes;
         std::shared_ptr<mzb200::Engine> engine;
         std::shared_ptr<mzb200::Cohort> cohort;

@@ -121,6 +121,19 @@ int mzb_set_host_evaluator(mzb_engine* e, const mzb_host_evaluator* evaluator);
  * buffers for the shipped Connect4 net), folds eval-mode BN (eps 1e-4) and packs them for the kernels. */
 int mzb_load_weights(mzb_engine* e, const mzb_tensor_desc* tensors, int n_tensors);
 
+/* Replaces: the read half of VPRNetModel::LoadCheckpoint(path) (vprnet.cpp:71-74): reads the module archive
+ * torch::save(model_, "<path>.pt") wrote (vprnet.cpp:58-63; a ZIP of stored members with a protocol-2 pickle of the module tree)
+ * natively — no libtorch — and loads its float32 parameters and buffers like mzb_load_weights.  `path` is the file itself
+ * (the facade appends ".pt" like the reference).  The "-optimizer.pt" file belongs to the learner and is not read.
+ * mzb_checkpoint_open/count/tensor/close expose the parsed tensors (names as in the archive, row-major float32 copies valid
+ * until close) without touching a GPU. */
+typedef struct mzb_checkpoint mzb_checkpoint;
+int mzb_checkpoint_open(const char* path, mzb_checkpoint** out);
+int mzb_checkpoint_count(const mzb_checkpoint* checkpoint);
+int mzb_checkpoint_tensor(const mzb_checkpoint* checkpoint, int index, mzb_tensor_desc* out);
+void mzb_checkpoint_close(mzb_checkpoint* checkpoint);
+int mzb_load_checkpoint(mzb_engine* e, const char* path);
+
 /* Replaces: the disk round trip SaveCheckpoint -> LoadCheckpoint of learner.cpp:93-101 / muzero.cpp:142-148.
  * One ncclBroadcast of the packed weight blob from `root` to all ranks.  id = 128-byte ncclUniqueId. */
 int mzb_nccl_unique_id(char id_out[128]);

@@ -14,6 +14,7 @@ COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-st
 # (source, extra flags).  tree.cu: no FMA contraction — f64 search arithmetic must round like the x86-64 reference.
 SOURCES = [
     ("net_plan.cpp", ["-x", "cu"]),
+    ("checkpoint.cpp", ["-x", "cu"]),
     ("net_fp32.cu", []),
     ("net_bf16.cu", []),
     ("tree.cu", ["-fmad=false"]),

@@ -162,6 +162,7 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes", "mzb_value_encode", "mzb_value_decode",
            "mzb_obs_ring_create", "mzb_obs_ring_reset", "mzb_obs_ring_push", "mzb_obs_ring_stacked", "mzb_search_batch_ring",
            "mzb_actor_seed", "mzb_select_actions", "mzb_set_host_evaluator",
+           "mzb_checkpoint_open", "mzb_checkpoint_count", "mzb_checkpoint_tensor", "mzb_checkpoint_close", "mzb_load_checkpoint",
            "mzb_debug_tree_write", "mzb_debug_tree_read", "mzb_debug_select_child", "mzb_debug_backpropagate"]
 
 
@@ -208,6 +209,12 @@ def load_library(path=None):
     lib.mzb_search_batch_ring.argtypes = [C.c_void_p, ip, u32p, ip, u8p, C.c_int, C.POINTER(_CSearchResult)]
     lib.mzb_actor_seed.argtypes = [C.c_void_p, ip, ip, C.c_int]
     lib.mzb_select_actions.argtypes = [C.c_void_p, ip, C.POINTER(_CSearchResult), C.c_int, dp, ip]
+    lib.mzb_checkpoint_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    lib.mzb_checkpoint_count.argtypes = [C.c_void_p]
+    lib.mzb_checkpoint_tensor.argtypes = [C.c_void_p, C.c_int, C.POINTER(_CTensorDesc)]
+    lib.mzb_checkpoint_close.argtypes = [C.c_void_p]
+    lib.mzb_checkpoint_close.restype = None
+    lib.mzb_load_checkpoint.argtypes = [C.c_void_p, C.c_char_p]
     lib.mzb_set_host_evaluator.argtypes = [C.c_void_p, C.POINTER(_CHostEvaluator)]
     lib.mzb_value_encode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, fp]
     lib.mzb_value_decode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, C.c_int, fp]
@@ -217,6 +224,27 @@ def load_library(path=None):
 
 def _ptr(a, ct):
     return a.ctypes.data_as(C.POINTER(ct))
+
+
+def read_checkpoint(path):
+    """The float32 tensors of a reference checkpoint file (torch::save module archive, vprnet.cpp:58-63), parsed natively by
+    libmzb200 (no torch): {dotted name: ndarray}.  Needs no GPU."""
+    lib = load_library()
+    h = C.c_void_p()
+    if lib.mzb_checkpoint_open(os.fsencode(path), C.byref(h)) != 0:
+        raise MzbError(lib.mzb_last_error().decode())
+    try:
+        out = {}
+        for i in range(lib.mzb_checkpoint_count(h)):
+            d = _CTensorDesc()
+            if lib.mzb_checkpoint_tensor(h, i, C.byref(d)) != 0:
+                raise MzbError(lib.mzb_last_error().decode())
+            shape = tuple(int(d.dims[k]) for k in range(d.ndim))
+            n = int(np.prod(shape)) if shape else 1
+            out[d.name.decode(errors="replace")] = np.ctypeslib.as_array(d.data, (n,)).reshape(shape).copy()
+        return out
+    finally:
+        lib.mzb_checkpoint_close(h)
 
 
 class Engine:
@@ -381,6 +409,10 @@ class Engine:
             for k in range(a.ndim):
                 descs[i].dims[k] = a.shape[k]
         self._check(self.lib.mzb_load_weights(self._h, descs, len(tensors)))
+
+    def load_checkpoint(self, path):
+        """VPRNetModel::LoadCheckpoint's read half (vprnet.cpp:71-74): the reference's own .pt file, parsed without libtorch"""
+        self._check(self.lib.mzb_load_checkpoint(self._h, os.fsencode(path)))
 
     def weights_checksum(self):
         out = C.c_uint64()

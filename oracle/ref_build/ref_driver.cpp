@@ -326,6 +326,11 @@ static int mode_net(const Args& a) {
     std::string base = vm.SaveCheckpoint(-7);
     torch::save(net, base + ".pt");
     vm.LoadCheckpoint(-7);
+    if (a.has("ckpt_out")) {   // keep the archive torch::save wrote (the file format VPRNetModel::LoadCheckpoint reads) as a fixture
+        std::ifstream src(base + ".pt", std::ios::binary);
+        std::ofstream dst(a.str("ckpt_out", ""), std::ios::binary);
+        dst << src.rdbuf();
+    }
 
     mzbt::Writer w;
     dump_weights(w, net);

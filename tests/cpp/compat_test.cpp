@@ -504,9 +504,10 @@ static void self_play_cohort(const std::string& golden_dir) {
             });
         for (auto& t : actors) t.join();
     }
-    // (b) the cohort driver on a second model with the same weights
+    // (b) the cohort driver on a second model, its weights read from the checkpoint file the reference wrote for them
+    //     (VPRNetModel::LoadCheckpoint(path) appends ".pt", vprnet.cpp:71-74)
     VPRNetModel model(config, "cuda:0", MZB_FP32_CHECK);
-    model.LoadWeights(weights);
+    model.LoadCheckpoint(golden_dir + "/checkpoint_tiny");
     std::vector<std::unique_ptr<DriftGame>> owned;
     std::vector<AbstractGame*> games;
     std::vector<int> seeds;

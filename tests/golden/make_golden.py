@@ -6,6 +6,7 @@
 Outputs (committed):
   mcts_se.json    MCTS::run results + expansion traces for the SE synthetic evaluator over several configs
   net_tiny.mzbt   weights / inputs / outputs of VPRNetModel::{Initial,Recurrent}Inference, plain head
+  checkpoint_tiny.pt  the module archive torch::save wrote for net_tiny's weights (what VPRNetModel::LoadCheckpoint reads)
   net_tinyds.mzbt same for the downsample head
   encoder.json    ValueEncoder support sizes and decode known answers
 """
@@ -47,7 +48,8 @@ def main():
         cases.append(dict(name=name, config=okw, trees=T, runs=runs, legal_mode=legal_mode, noise=noise, seed=seed, results=res))
     with open(os.path.join(HERE, "mcts_se.json"), "w") as f:
         json.dump(cases, f)
-    O.run_ref("net", "game=tiny", "batch=3", "seed=3", "out=" + os.path.join(HERE, "net_tiny.mzbt"))
+    O.run_ref("net", "game=tiny", "batch=3", "seed=3", "out=" + os.path.join(HERE, "net_tiny.mzbt"),
+              "ckpt_out=" + os.path.join(HERE, "checkpoint_tiny.pt"))
     O.run_ref("net", "game=tinyds", "batch=2", "seed=4", "out=" + os.path.join(HERE, "net_tinyds.mzbt"))
     enc = []
     for lo, hi, extra in [(-10, 10, []), (-22, 22, []), (-1, 1, []), (-21, 21, []), (-300, 300, []), (-5, 7, ["no_contractive"])]:

@@ -300,6 +300,8 @@ def main():
             fn()
             tm = eng.last_search_timing()
             dev_ms += tm["total_ms"]
+            split["root_ms"] += tm["root_ms"]
+            split["sim_loop_ms"] += tm["sim_loop_ms"]
             launches += tm["kernel_launches"]
         barrier()
         wall_ms = 1000 * (time.time() - t0)
@@ -309,6 +311,7 @@ def main():
             dev_ms, wall_ms = float(t[0]), float(t[1])
         return dev_ms, wall_ms, launches
 
+    split = dict(root_ms=0.0, sim_loop_ms=0.0)   # rank-local split of the device time: root (initial inference + expansion) | simulations
     run_dev = lambda: eng.run(None, masks, to_play, noise, device_obs_ptr=obs_dev.data_ptr())
     run_host = lambda: eng.run(obs_host.numpy(), masks, to_play, noise)
     for _ in range(args.warmup):
@@ -317,6 +320,8 @@ def main():
     sampler.start()
     dev_ms, wall_ms, launches = timed(run_dev, args.steps)
     clocks = sampler.stop()
+    step_split = dict(root_ms_per_step=split["root_ms"] / args.steps, sim_loop_ms_per_step=split["sim_loop_ms"] / args.steps,
+                      sims_per_s_without_initial_inference=T * sims * args.steps / (split["sim_loop_ms"] / 1000.0) * world)
     for _ in range(1):
         run_host()
     e2e_dev_ms, e2e_wall_ms, _ = timed(run_host, args.steps)
@@ -353,7 +358,7 @@ def main():
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=int(T * flat * 4 + T * (4 + 4 + 1)),
                          d2h_bytes_per_step=int(T * (8 + 4 + 4 + A * (4 + 4 + 8 + 8))), ms_per_step=e2e_wall_ms / args.steps,
                          device_ms_per_step=e2e_dev_ms / args.steps),
-                gpu_launches=int(launches), roofline=roofline, recurrent_states_per_s=states_per_s)
+                gpu_launches=int(launches), roofline=roofline, recurrent_states_per_s=states_per_s, step_split=step_split)
     if sync_ms is not None:
         line["weight_sync_ms"] = sync_ms
         line["weight_sync_first_ms"] = sync_first_ms
@@ -387,6 +392,19 @@ def main():
                         traffic=None, bytes_per_sim=b_sim, sims_per_s=sims_s, trees=Tt, us_per_simulation_step=ms * 1000.0 / (5 * sims),
                         kernel="tree_step + SE stub (outputs + bulk-copy hidden-state move through shared memory)")
 
+        # BASELINE metric M2: recurrent_inference states/s with device-resident inputs, by batch size
+        by_batch = {}
+        for B in (1024, 4096, 16384):
+            pool_bytes = B * (sims + 3) * eng.shapes.recurrent_flat_size * 2
+            if pool_bytes > 60e9:
+                continue
+            beng = mzb200.Engine(mzb200.preset(preset_name, max_trees=B, precision=precision), local_rank)
+            beng.load_weights(W)
+            b_ms, _ = beng.bench_recurrent(B, 20)
+            by_batch[str(B)] = dict(states_per_s=B / (b_ms / 1000.0), ms_per_pass=b_ms, tflops=frec * B / (b_ms / 1000.0) / 1e12,
+                                    frac_of_sustained_peak=frec * B / (b_ms / 1000.0) / 1e12 / pk["tf_sustained"])
+            beng.close()
+        line["recurrent_states_per_s_by_batch"] = by_batch
         line["roofline_tree"] = tree_leg(T)
         T_big = 16384
         if T_big > T and T_big * (sims + 1) * S_h < 40e9:

@@ -797,18 +797,35 @@ __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_con
         for (int j0 = 0; j0 < n1; j0 += 64) {
             const int j = j0 + tx;
             float acc[4] = {0.f, 0.f, 0.f, 0.f};
-            for (int k0 = 0; k0 < n0; k0 += MLP_KT) {
+            // the next K tile's global loads are issued before this tile is multiplied: their latency (the kernel's main
+            // stall, ncu source page) hides behind the FMAs instead of sitting in front of the shared-memory stores
+            constexpr int XR = 16 * MLP_KT / MLP_THREADS, WR = MLP_KT * 64 / MLP_THREADS;
+            float xq[XR], wq[WR];
+            auto gload = [&](int k0) {
                 const int kt = min(MLP_KT, n0 - k0);
-                __syncthreads();
-                for (int i = tid; i < 16 * MLP_KT; i += MLP_THREADS) {
-                    const int g = i / MLP_KT, k = i - g * MLP_KT;
-                    xs[g * (MLP_KT + 4) + k] = (g < nb && k < kt) ? hd.x[(long)(b0 + g) * n0 + k0 + k] : 0.f;
+#pragma unroll
+                for (int r = 0; r < XR; ++r) {
+                    const int i = tid + r * MLP_THREADS, g = i / MLP_KT, k = i - g * MLP_KT;
+                    xq[r] = (g < nb && k < kt) ? __ldg(hd.x + (long)(b0 + g) * n0 + k0 + k) : 0.f;
                 }
-                for (int i = tid; i < MLP_KT * 64; i += MLP_THREADS) {
-                    const int k = i >> 6, jj = i & 63;
-                    ws[i] = (k < kt && j0 + jj < n1) ? hd.w0t[(long)(k0 + k) * n1 + j0 + jj] : 0.f;
+#pragma unroll
+                for (int r = 0; r < WR; ++r) {
+                    const int i = tid + r * MLP_THREADS, k = i >> 6, jj = i & 63;
+                    wq[r] = (k < kt && j0 + jj < n1) ? __ldg(hd.w0t + (long)(k0 + k) * n1 + j0 + jj) : 0.f;
                 }
+            };
+            gload(0);
+            for (int k0 = 0; k0 < n0; k0 += MLP_KT) {
                 __syncthreads();
+#pragma unroll
+                for (int r = 0; r < XR; ++r) {
+                    const int i = tid + r * MLP_THREADS, g = i / MLP_KT, k = i - g * MLP_KT;
+                    xs[g * (MLP_KT + 4) + k] = xq[r];
+                }
+#pragma unroll
+                for (int r = 0; r < WR; ++r) ws[tid + r * MLP_THREADS] = wq[r];
+                __syncthreads();
+                if (k0 + MLP_KT < n0) gload(k0 + MLP_KT);
                 const float* xr = xs + (ty * 4) * (MLP_KT + 4);
 #pragma unroll
                 for (int k = 0; k < MLP_KT; k += 4) {
@@ -838,15 +855,21 @@ __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_con
     float* cur = bufA; float* nxt = bufB;
     for (int l = 1; l < hd.n_layers; ++l) {
         const int nin = hd.sizes[l], nout = hd.sizes[l + 1];
-        for (int o = tid; o < nb * nout; o += MLP_THREADS) {
+        // warp per output: the lanes walk the weight row together (one coalesced request instead of 32 scattered rows per load)
+        const int warp = tid >> 5, lane = tid & 31;
+        for (int o = warp; o < nb * nout; o += MLP_THREADS / 32) {
             const int g = o / nout, j = o - g * nout;
             const float* wr = hd.W[l] + (long)j * nin;
             const float* xr = cur + g * 256;
             float acc = 0.f;
-            for (int i = 0; i < nin; ++i) acc += wr[i] * xr[i];
-            acc += hd.b[l][j];
-            if (l < hd.n_layers - 1) acc = fmaxf(acc, 0.f);
-            nxt[g * 256 + j] = acc;
+            for (int i = lane; i < nin; i += 32) acc += __ldg(wr + i) * xr[i];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+            if (lane == 0) {
+                acc += hd.b[l][j];
+                if (l < hd.n_layers - 1) acc = fmaxf(acc, 0.f);
+                nxt[g * 256 + j] = acc;
+            }
         }
         __syncthreads();
         float* t = cur; cur = nxt; nxt = t;

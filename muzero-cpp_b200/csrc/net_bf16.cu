@@ -828,7 +828,7 @@ protected:
             ++n;
         }
         m.n_heads = n; m.B = B; m.mg = mlp_mg_;
-        const size_t smem = ((size_t)mlp_mg_ * 512 + 16 * (fused::MLP_KT + 4) + fused::MLP_KT * 64) * sizeof(float);
+        const size_t smem = ((size_t)mlp_mg_ * 512 + 16 * (fused::MLP_KT + 4) + fused::MLP_KT * 64 + fused::MLP_WT) * sizeof(float);
         (void)n0max;
         dim3 grid((B + mlp_mg_ - 1) / mlp_mg_, n);
         fused::mlp_heads_kernel<<<grid, fused::MLP_THREADS, smem, s>>>(m);

@@ -777,6 +777,7 @@ struct MlpHead {
 struct MlpArgs { MlpHead h[3]; int n_heads, B, mg; };
 
 constexpr int MLP_KT = 32;    // K tile of the first layer
+constexpr int MLP_WT = 64 * 65;   // floats of the transposed tail-layer weight buffer
 
 // One CTA = mg (<= 16) games of one head.  First layer (the only sizeable one: n0 = red*HW inputs) as a shared-memory
 // tiled SGEMM: x tile [mg][KT] and transposed-weight tile [KT][n1] staged per K step, thread = (output j, 4 games).
@@ -791,6 +792,7 @@ __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_con
     float* bufB = bufA + a.mg * 256;      // [mg][256]
     float* xs = bufB + a.mg * 256;        // [16][KT + 4]
     float* ws = xs + 16 * (MLP_KT + 4);   // [KT][n1]
+    float* wt = ws + MLP_KT * 64;         // [nin][nout + 1]: one tail layer's weights, transposed (layers up to 64 x 64)
     {
         const int groups = MLP_THREADS / 64;                 // 4 groups of 64 threads: group <-> 4 games
         const int tx = tid & 63, ty = tid >> 6;
@@ -855,7 +857,37 @@ __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_con
     float* cur = bufA; float* nxt = bufB;
     for (int l = 1; l < hd.n_layers; ++l) {
         const int nin = hd.sizes[l], nout = hd.sizes[l + 1];
-        // warp per output: the lanes walk the weight row together (one coalesced request instead of 32 scattered rows per load)
+        if (nin <= 64 && nout <= 64 && a.mg <= 16) {
+            // the layer's weights go through shared memory once, transposed and padded (conflict-free both ways); thread =
+            // (output j, 4 games): one weight load feeds four FMAs, the activations are warp-wide broadcasts
+            const int ld = nout + 1;
+            for (int i = tid; i < nin * nout; i += MLP_THREADS) {
+                const int j = i / nin, k = i - j * nin;
+                wt[k * ld + j] = __ldg(hd.W[l] + i);
+            }
+            __syncthreads();
+            const int j = tid & 63, g0 = (tid >> 6) * 4;
+            if (j < nout) {
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+                const float* xr = cur + g0 * 256;
+                for (int k = 0; k < nin; ++k) {
+                    const float w = wt[k * ld + j];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[q] += w * xr[q * 256 + k];
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (g0 + q < nb) {
+                        float v = acc[q] + hd.b[l][j];
+                        if (l < hd.n_layers - 1) v = fmaxf(v, 0.f);
+                        nxt[(g0 + q) * 256 + j] = v;
+                    }
+            }
+            __syncthreads();
+            float* t = cur; cur = nxt; nxt = t;
+            continue;
+        }
+        // wider layers: warp per output, the lanes walk the weight row together (one coalesced request per load)
         const int warp = tid >> 5, lane = tid & 31;
         for (int o = warp; o < nb * nout; o += MLP_THREADS / 32) {
             const int g = o / nout, j = o - g * nout;

@@ -526,7 +526,13 @@ protected:
             w0t_rel_[h] = extra->size();
             const int n0 = hh[h]->sizes[0], n1 = hh[h]->sizes[1];
             std::vector<float> wt((size_t)n0 * n1);
-            for (int j = 0; j < n1; ++j) for (int i = 0; i < n0; ++i) wt[(size_t)i * n1 + j] = hh[h]->W[0][(size_t)j * n0 + i];
+            // row i' = p * red + r of the transposed matrix <- input r * HW + p of the reference's flatten order: the fused kernel
+            // stores the reduced activations pixel-major so that a warp's channels are one contiguous run
+            const int red = hh[h]->red, hw = H * W;
+            for (int j = 0; j < n1; ++j)
+                for (int r = 0; r < red; ++r)
+                    for (int px = 0; px < hw; ++px)
+                        wt[((size_t)px * red + r) * n1 + j] = hh[h]->W[0][(size_t)j * n0 + (size_t)r * hw + px];
             const uint8_t* bp = reinterpret_cast<const uint8_t*>(wt.data());
             extra->insert(extra->end(), bp, bp + wt.size() * sizeof(float));
         }

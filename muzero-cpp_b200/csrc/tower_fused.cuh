@@ -466,8 +466,11 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                         }
                     } else {
                         const int head = second ? ph.red_head1 : ph.red_head0;
-                        float* dst0 = a.red[head] + (long)rr * HW;
-                        const long gstride = (long)a.red_rows[head] * HW;
+                        // [game][pixel][reduced channel]: the lanes of a warp (consecutive channels) store one contiguous run per
+                        // pixel; the first MLP layer's rows are permuted to this order on the host (w0t, net_bf16.cu)
+                        const int rows = a.red_rows[head];
+                        float* dst0 = a.red[head] + rr;
+                        const long gstride = (long)rows * HW;
                         for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                             float* dst = dst0 + (long)(game0 + g) * gstride;
                             const int cbase = g * P;
@@ -479,7 +482,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
                                 tmem_ld_wait();
 #pragma unroll
                                 for (int j = 0; j < 8; ++j)
-                                    if (pix[j] >= 0 && row_ok) dst[pix[j]] = __uint_as_float(v[j]) + bias;
+                                    if (pix[j] >= 0 && row_ok) dst[(long)pix[j] * rows] = __uint_as_float(v[j]) + bias;
                             }
                         }
                     }
@@ -759,7 +762,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
 }
 
 // ------------------------------------------------------------------ head MLPs on the reduced activations
-// red[head] : [B][n0] fp32, flatten order r*HW + p (models.cpp:114,161-162)  ->  MLP (model_layers.cpp:46-65)  ->
+// red[head] : [B][n0] fp32 in [pixel][reduced channel] order (the reference flattens r*HW + p, models.cpp:114,161-162; w0t's rows
+// are permuted to match)  ->  MLP (model_layers.cpp:46-65)  ->
 // policy softmax (vprnet.cpp:118-119,178-179) or support-to-scalar (ValueEncoder::decode, util.cpp:80-87).
 constexpr int MLP_THREADS = 256;
 constexpr int MLP_MAX_LAYERS = 6;

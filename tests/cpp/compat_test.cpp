@@ -578,11 +578,60 @@ static void self_play_cohort(const std::string& golden_dir) {
     }
 }
 
+// (7) DeviceManager with several models (two engines on the same GPU stand in for two devices): loans go to the model with the
+//     fewest outstanding requests, MCTS objects spread over the models, and device 0 is left to the learner while
+//     SetLearning(true) (device_manager.h:68-96, muzero.cpp:142-148)
+static void device_manager_policies(const std::string& golden_dir) {
+    muzero_config::MuZeroConfig config = tiny_config(4);
+    DeviceManager dm;
+    for (int d = 0; d < 2; ++d) {
+        VPRNetModel model(config, "cuda:0", MZB_FP32_CHECK);
+        model.LoadCheckpoint(golden_dir + "/checkpoint_tiny");
+        dm.AddDevice(std::move(model));
+    }
+    EXPECT(dm.Count() == 2, "Count() = %d", dm.Count());
+    {
+        DeviceManager::DeviceLoan a = dm.Get(5);          // both idle: device 0
+        DeviceManager::DeviceLoan b = dm.Get(3);          // device 1 has fewer outstanding requests
+        DeviceManager::DeviceLoan c = dm.Get(1);          // 5 vs 3: device 1 again
+        DeviceManager::DeviceLoan d = dm.Get(1, 0);       // explicit device
+        EXPECT(a.device_id() == 0 && b.device_id() == 1 && c.device_id() == 1 && d.device_id() == 0, "loans went to %d %d %d %d",
+               a.device_id(), b.device_id(), c.device_id(), d.device_id());
+    }
+    {
+        DeviceManager::DeviceLoan a = dm.Get(1);          // everything returned: device 0 again
+        EXPECT(a.device_id() == 0, "loans were not returned");
+        dm.SetLearning(true);
+        DeviceManager::DeviceLoan b = dm.Get(1), c = dm.Get(7);
+        EXPECT(b.device_id() == 1 && c.device_id() == 1, "device 0 took inference work while learning");
+        dm.SetLearning(false);
+    }
+    auto evaluator = std::make_shared<VPRNetEvaluator>(&dm, 2, 1, 2, 1);
+    std::vector<std::unique_ptr<algorithm::MCTS>> mcts;
+    for (int t = 0; t < 4; ++t) mcts.emplace_back(new algorithm::MCTS(config, 40 + t, evaluator));   // two per model
+    std::vector<MCTSReturn> got(4);
+    std::vector<std::thread> pool;
+    const Observation obs(60, 0.25f);
+    for (int t = 0; t < 4; ++t) pool.emplace_back([&, t] { got[t] = mcts[t]->run(obs, {0, 1, 2, 3, 4}, t % 2, false); });
+    for (auto& th : pool) th.join();
+    // same weights, same observation, no noise: objects on different models with the same to_play differ only through their seeds'
+    // shuffles, so root values agree to rounding and every policy is a distribution
+    for (int t = 0; t < 4; ++t) {
+        double sum = 0;
+        for (double v : got[t].emperical_policy) sum += v;
+        EXPECT(std::fabs(sum - 1.0) < 1e-12 && got[t].child_actions.size() == 5, "search %d on a two-model manager is malformed", t);
+    }
+    dm.SetLearning(true);
+    algorithm::MCTS late(config, 99, evaluator);           // must land on device 1 although it already holds two searchers
+    MCTSReturn r = late.run(obs, {0, 1, 2, 3, 4}, 0, false);
+    EXPECT(r.child_actions.size() == 5, "search while learning is malformed");
+}
+
 int main(int argc, char** argv) {
     try {
         reference_unit_tests();
         appendix_b();
-        if (argc > 1) { network_paths(argv[1]); self_play_cohort(argv[1]); }
+        if (argc > 1) { network_paths(argv[1]); self_play_cohort(argv[1]); device_manager_policies(argv[1]); }
     } catch (const std::exception& e) {
         std::printf("compat_test: %s\n", e.what());
         return 1;

@@ -254,7 +254,7 @@ int mzb_weights_checksum(mzb_engine* e, uint64_t* out) {
 int mzb_search_seed(mzb_engine* e, int first_slot, int n, const int32_t* seeds) {
     MZB_REQUIRE(e && seeds && first_slot >= 0 && n >= 0 && first_slot + n <= e->cfg.max_trees, "bad slot range");
     MZB_CUDA(cudaSetDevice(e->device));
-    MZB_CUDA(cudaMemcpy(e->d_to_play.p, seeds, n * sizeof(int), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpyAsync(e->d_to_play.p, seeds, n * sizeof(int), cudaMemcpyHostToDevice, e->stream));
     launch_mt_seed(e->td.mt, e->td.mt_idx, e->d_to_play.as<int>(), first_slot, n, e->stream);
     MZB_CUDA(cudaGetLastError());
     MZB_CUDA(cudaStreamSynchronize(e->stream));
@@ -289,17 +289,18 @@ int mzb_debug_tree_write(mzb_engine* e, int slot, const mzb_debug_tree* t) {
         MZB_REQUIRE(cb < 0 || (cb > i && cb + (i == 0 ? t->n_root_children : td.A) <= t->n_nodes), "node %d: child_base %d outside the tree", i, cb);
     }
     const size_t sb = (size_t)slot * td.slots_per_tree, n = t->n_nodes;
-    MZB_CUDA(cudaMemcpy(td.meta + sb, t->meta, n * sizeof(int4), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td.prior + sb, t->prior, n * sizeof(double), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td.value_sum + sb, t->value_sum, n * sizeof(double), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td.reward + sb, t->reward, n * sizeof(double), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td.mm_min + slot, &t->minmax_minimum, sizeof(double), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td.mm_max + slot, &t->minmax_maximum, sizeof(double), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpyAsync(td.meta + sb, t->meta, n * sizeof(int4), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td.prior + sb, t->prior, n * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td.value_sum + sb, t->value_sum, n * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td.reward + sb, t->reward, n * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td.mm_min + slot, &t->minmax_minimum, sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td.mm_max + slot, &t->minmax_maximum, sizeof(double), cudaMemcpyHostToDevice, e->stream));
     const int zero = 0;
-    MZB_CUDA(cudaMemcpy(td.root_to_play + slot, &t->root_to_play, sizeof(int), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td.n_legal + slot, &t->n_root_children, sizeof(int), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td.n_slots + slot, &t->n_nodes, sizeof(int), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td.max_depth + slot, &zero, sizeof(int), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpyAsync(td.root_to_play + slot, &t->root_to_play, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td.n_legal + slot, &t->n_root_children, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td.n_slots + slot, &t->n_nodes, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td.max_depth + slot, &zero, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaStreamSynchronize(e->stream));   // the uploads ride the engine's stream: ordered before the step that follows
     return MZB_OK;
 }
 
@@ -344,8 +345,9 @@ int mzb_debug_select_child(mzb_engine* e, int slot, int restore_rng, int32_t* ch
     MZB_CUDA(cudaGetLastError());
     MZB_CUDA(cudaStreamSynchronize(e->stream));
     if (restore_rng) {
-        MZB_CUDA(cudaMemcpy(e->td.mt + (size_t)slot * 624, saved_mt.data(), 624 * sizeof(uint32_t), cudaMemcpyHostToDevice));
-        MZB_CUDA(cudaMemcpy(e->td.mt_idx + slot, &saved_idx, sizeof(int), cudaMemcpyHostToDevice));
+        MZB_CUDA(cudaMemcpyAsync(e->td.mt + (size_t)slot * 624, saved_mt.data(), 624 * sizeof(uint32_t), cudaMemcpyHostToDevice, e->stream));
+        MZB_CUDA(cudaMemcpyAsync(e->td.mt_idx + slot, &saved_idx, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+        MZB_CUDA(cudaStreamSynchronize(e->stream));
     }
     std::vector<int> path(e->cfg.num_simulations + 2);
     MZB_CUDA(cudaMemcpy(path.data(), e->td.path_slot + (size_t)slot * (e->cfg.num_simulations + 2), 2 * sizeof(int), cudaMemcpyDeviceToHost));
@@ -365,11 +367,11 @@ int mzb_debug_backpropagate(mzb_engine* e, int slot, const int32_t* path, int le
     MZB_CUDA(cudaMemcpy(&n_slots, td0.n_slots + slot, sizeof(int), cudaMemcpyDeviceToHost));
     MZB_REQUIRE(n_slots + A <= td0.slots_per_tree, "no room to expand the leaf");
     for (int i = 0; i < len; ++i) MZB_REQUIRE(path[i] >= 0 && path[i] < n_slots, "path[%d] = %d is not a node", i, path[i]);
-    MZB_CUDA(cudaMemcpy(td0.path_slot + (size_t)slot * (n + 2), path, len * sizeof(int), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td0.path_len + slot, &len, sizeof(int), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td0.value + slot, &value, sizeof(double), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td0.reward_out + slot, &leaf_reward, sizeof(double), cudaMemcpyHostToDevice));
-    MZB_CUDA(cudaMemcpy(td0.policy + (size_t)slot * A, policy, A * sizeof(double), cudaMemcpyHostToDevice));
+    MZB_CUDA(cudaMemcpyAsync(td0.path_slot + (size_t)slot * (n + 2), path, len * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td0.path_len + slot, &len, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td0.value + slot, &value, sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td0.reward_out + slot, &leaf_reward, sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    MZB_CUDA(cudaMemcpyAsync(td0.policy + (size_t)slot * A, policy, A * sizeof(double), cudaMemcpyHostToDevice, e->stream));
     TreeDev td = e->td;
     td.trace_parent = nullptr; td.trace_action = nullptr; td.rec_value = nullptr; td.rec_reward = nullptr; td.rec_policy = nullptr;
     // step n = expansion + backup only (no further selection)

@@ -212,6 +212,11 @@ int mzb_debug_select_child(mzb_engine* e, int slot, int restore_rng, int32_t* ch
 int mzb_debug_backpropagate(mzb_engine* e, int slot, const int32_t* path, int len, double value, double leaf_reward,
                             const double* policy);
 
+/* MZB_EVAL_SYNTHETIC only: the hidden state the stub holds for node `node` (expansion order, 0 = root) of tree row `tree` after a
+ * search — recurrent_flat_size floats.  The stub moves one state parent -> child per simulation (se_move_kernel), so every
+ * expanded node must hold a copy of its tree's root state; tests check the mover through this. */
+int mzb_debug_se_state(mzb_engine* e, int tree, int node, float* out);
+
 /* ---- The callers' side: observation history and action selection for cohorts of games ----
  * Device-resident observation history per tree slot, stacked on the GPU the way GameHistory::get_stacked_observations
  * (types.cpp:16-42) does on the host: current frame, then for each of the previous `stacked_observations` steps the frame and

@@ -381,6 +381,17 @@ int mzb_debug_backpropagate(mzb_engine* e, int slot, const int32_t* path, int le
     return MZB_OK;
 }
 
+int mzb_debug_se_state(mzb_engine* e, int tree, int node, float* out) {
+    int rc = debug_slot_check(e, tree);
+    if (rc) return rc;
+    MZB_REQUIRE(e->cfg.evaluator == MZB_EVAL_SYNTHETIC && e->se.pool, "engine was not created with the synthetic evaluator");
+    MZB_REQUIRE(out && node >= 0 && node <= e->cfg.num_simulations, "node %d outside [0, num_simulations]", node);
+    MZB_CUDA(cudaStreamSynchronize(e->stream));
+    const size_t slot = (size_t)tree * (e->cfg.num_simulations + 1) + node;
+    MZB_CUDA(cudaMemcpy(out, e->se.pool + slot * e->se.slot_floats, (size_t)e->se.slot_floats * sizeof(float), cudaMemcpyDeviceToHost));
+    return MZB_OK;
+}
+
 int mzb_search_set_recording(mzb_engine* e, int enabled) {
     MZB_REQUIRE(e, "null argument");
     MZB_CUDA(cudaSetDevice(e->device));

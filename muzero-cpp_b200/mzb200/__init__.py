@@ -163,7 +163,7 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_obs_ring_create", "mzb_obs_ring_reset", "mzb_obs_ring_push", "mzb_obs_ring_stacked", "mzb_search_batch_ring",
            "mzb_actor_seed", "mzb_select_actions", "mzb_set_host_evaluator",
            "mzb_checkpoint_open", "mzb_checkpoint_count", "mzb_checkpoint_tensor", "mzb_checkpoint_close", "mzb_load_checkpoint",
-           "mzb_debug_tree_write", "mzb_debug_tree_read", "mzb_debug_select_child", "mzb_debug_backpropagate"]
+           "mzb_debug_se_state", "mzb_debug_tree_write", "mzb_debug_tree_read", "mzb_debug_select_child", "mzb_debug_backpropagate"]
 
 
 def load_library(path=None):
@@ -496,6 +496,12 @@ class Engine:
 
         self._host_cb = _CHostEvaluator(None, _HOST_INITIAL(_initial), _HOST_RECURRENT(_recurrent))   # keep the thunks alive
         self._check(self.lib.mzb_set_host_evaluator(self._h, C.byref(self._host_cb)))
+
+    def se_state(self, tree, node):
+        """EVAL_SYNTHETIC: the hidden state the stub holds for node `node` of tree row `tree` (checks the state mover)"""
+        out = np.empty(self.shapes.recurrent_flat_size, np.float32)
+        self._check(self.lib.mzb_debug_se_state(self._h, int(tree), int(node), _ptr(out, C.c_float)))
+        return out
 
     def seed_slots(self, seeds, first_slot=0):
         s = np.ascontiguousarray(seeds, dtype=np.int32)

@@ -183,3 +183,24 @@ def test_host_evaluator_path_matches_oracle(A, players, sims, noise):
     with pytest.raises(mzb200.MzbError):
         eng.run(np.zeros((1, width), np.float32), np.array([1], np.uint32), np.array([0], np.int32), np.zeros(1, np.uint8))
     eng.close()
+
+
+@pytest.mark.parametrize("shape,channels", [((3, 6, 7), 128), ((1, 3, 3), 5)])
+def test_se_state_mover_copies_parent_states(shape, channels):
+    """The stub's hidden-state move (se_move_kernel: bulk copies through shared memory; a per-lane loop for odd sizes): after a search
+    every expanded node holds its parent's state, hence its tree's root state, and trees do not leak into each other."""
+    import mzb200
+    T, sims = 37, 24
+    cfg = mzb200.MuZeroConfig(observation_shape=shape, num_actions=7, num_players=2, num_simulations=sims, seed=2, max_trees=T,
+                              evaluator=mzb200.EVAL_SYNTHETIC, network_config=mzb200.MuZeroNetworkConfig(resnet_channels=channels))
+    eng = mzb200.Engine(cfg, 0)
+    keys = H.se_keys(T, 0)
+    eng.run(keys.astype(np.float32), H.se_legal_masks(keys, 7, 0), np.arange(T, dtype=np.int32) % 2, np.ones(T, np.uint8))
+    roots = [eng.se_state(t, 0) for t in range(T)]
+    assert roots[0].shape[0] == channels * shape[1] * shape[2]
+    assert len({r.tobytes() for r in roots}) > T // 2          # roots differ between trees (position keys differ)
+    for t in (0, 1, 17, T - 1):
+        assert 0.0 <= roots[t].min() and roots[t].max() < 1.0 and roots[t].std() > 0
+        for node in (1, 2, sims // 2, sims):
+            assert np.array_equal(eng.se_state(t, node), roots[t]), (t, node)
+    eng.close()

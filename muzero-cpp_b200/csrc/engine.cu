@@ -153,7 +153,13 @@ int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out) {
     MZB_CUDA(cudaGetDeviceCount(&ndev));
     MZB_REQUIRE(device >= 0 && device < ndev, "CUDA device %d not present (%d devices)", device, ndev);
     MZB_CUDA(cudaSetDevice(device));
-    MZB_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    {
+        // tree kernels alone (SYNTHETIC): the search stream outranks the state mover's, so the latency-bound tree step of simulation
+        // i + 1 gets its few blocks onto the SMs between the mover's thousands of copy CTAs instead of queueing behind them
+        int lowest = 0, greatest = 0;
+        MZB_CUDA(cudaDeviceGetStreamPriorityRange(&lowest, &greatest));
+        MZB_CUDA(cudaStreamCreateWithPriority(&e->stream, cudaStreamNonBlocking, e->cfg.evaluator == MZB_EVAL_SYNTHETIC ? greatest : lowest));
+    }
     MZB_CUDA(cudaStreamCreateWithFlags(&e->aux, cudaStreamNonBlocking));
     for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) MZB_CUDA(cudaStreamCreateWithFlags(&e->pipe[i], cudaStreamNonBlocking));
     MZB_CUDA(cudaEventCreate(&e->ev_start));
@@ -173,6 +179,12 @@ int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out) {
         MZB_CUDA(e->se_pool.alloc((size_t)T * (n + 1) * e->se.slot_floats * sizeof(float)));
         e->se.node_cid = e->se_cid.as<uint32_t>();
         e->se.pool = e->se_pool.as<float>();
+        e->se.bulk = se_move_available(e->se.slot_floats) ? 1 : 0;
+        MZB_CUDA(e->se_mv.alloc((size_t)4 * T * sizeof(int)));
+        for (int k = 0; k < 2; ++k) {
+            MZB_CUDA(cudaEventCreateWithFlags(&e->ev_se_out[k], cudaEventDisableTiming));
+            MZB_CUDA(cudaEventCreateWithFlags(&e->ev_se_mv[k], cudaEventDisableTiming));
+        }
         MZB_CUDA(e->d_obs.alloc((size_t)T * sizeof(float)));
     } else if (e->cfg.evaluator == MZB_EVAL_HOST) {
         MZB_CUDA(e->d_obs.alloc((size_t)T * e->dims.initial_flat() * sizeof(float)));
@@ -197,6 +209,7 @@ void mzb_engine_destroy(mzb_engine* e) {
     if (e->ev_aux) cudaEventDestroy(e->ev_aux);
     if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) if (e->ev_join[i]) cudaEventDestroy(e->ev_join[i]);
+    for (int k = 0; k < 2; ++k) { if (e->ev_se_out[k]) cudaEventDestroy(e->ev_se_out[k]); if (e->ev_se_mv[k]) cudaEventDestroy(e->ev_se_mv[k]); }
     e->net.reset();
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->aux) cudaStreamDestroy(e->aux);

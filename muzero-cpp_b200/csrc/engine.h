@@ -68,7 +68,8 @@ struct mzb_engine {
     const int32_t* h_slot_rows = nullptr;
     // SE stub
     SEDev se;
-    DevBuf se_cid, se_pool;
+    DevBuf se_cid, se_pool, se_mv;   // se_mv: two (parent, child) slot-pair buffers for the state mover [2][2][T]
+    cudaEvent_t ev_se_out[2] = {nullptr, nullptr}, ev_se_mv[2] = {nullptr, nullptr};
     // pinned host staging
     void* h_pin = nullptr;
     size_t h_pin_bytes = 0;

@@ -150,6 +150,35 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
             MZB_CUDA(cudaEventRecord(e->ev_join[k - 1], st[k]));
             MZB_CUDA(cudaStreamWaitEvent(s, e->ev_join[k - 1], 0));
         }
+    } else if (synthetic) {
+        // tree kernels alone.  The stub's hidden-state move of simulation i (se_move_kernel, HBM-bound) runs on its own stream
+        // beside the tree step of simulation i + 1 (latency-bound, touches no hidden state): the outputs kernel snapshots the
+        // (parent, child) slot pairs into one of two buffers, which is reused only after its mover has finished.
+        cudaStream_t mv = e->pipe[0];
+        const int max_t = c.max_trees;
+        int used[2] = {0, 0};
+        for (int sim = 0; sim <= n; ++sim) {
+            launch_tree_step(td, T, sim, s);
+            ++launches;
+            if (sim == n) break;
+            const int k = sim & 1;
+            SEDev se = e->se;
+            se.mv_in = e->se_mv.as<int>() + (size_t)k * 2 * max_t;
+            se.mv_out = se.mv_in + max_t;
+            if (se.bulk && used[k]) MZB_CUDA(cudaStreamWaitEvent(s, e->ev_se_mv[k], 0));   // the mover of simulation sim - 2 has read them
+            launch_se_recurrent(td, se, T, s);
+            ++launches;
+            if (se.bulk) {
+                MZB_CUDA(cudaEventRecord(e->ev_se_out[k], s));
+                MZB_CUDA(cudaStreamWaitEvent(mv, e->ev_se_out[k], 0));
+                launch_se_move(se, T, mv);
+                ++launches;
+                MZB_CUDA(cudaEventRecord(e->ev_se_mv[k], mv));
+                used[k] = 1;
+            }
+        }
+        for (int k = 0; k < 2; ++k)
+            if (used[k]) MZB_CUDA(cudaStreamWaitEvent(s, e->ev_se_mv[k], 0));   // the search ends when the last states have landed
     } else
     for (int sim = 0; sim <= n; ++sim) {
         launch_tree_step(td, T, sim, s);
@@ -166,8 +195,6 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
             MZB_REQUIRE(hrc == 0, "host evaluator: RecurrentInference failed (%d)", hrc);
             hrc = host_outputs_to_device();
             if (hrc) return hrc;
-        } else if (synthetic) {
-            launches += launch_se_recurrent(td, e->se, T, s);
         } else {
             rc = e->net->recurrent(T, td.in_slot, td.action, td.out_slot, tree_outputs(e), s);
             if (rc) return rc;

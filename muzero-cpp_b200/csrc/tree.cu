@@ -385,7 +385,10 @@ __global__ void se_recurrent_kernel(TreeDev td, SEDev se, int n_trees) {
     (void)pool_base;
     if (lane == 0) se.node_cid[out_slot] = cid;
     se_outputs(td, se, t, cid, lane);
-    if (se.slot_floats % 4 == 0) return;   // the hidden state travels by bulk copy (se_move_kernel)
+    if (se.bulk) {   // the hidden state travels by bulk copy (se_move_kernel, on its own stream)
+        if (lane == 0) { se.mv_in[t] = in_slot; se.mv_out[t] = out_slot; }
+        return;
+    }
     // odd state sizes: 16 B per lane per request (S_h read + S_h write)
     const float4* src = reinterpret_cast<const float4*>(se.pool + (long)in_slot * se.slot_floats);
     float4* dst = reinterpret_cast<float4*>(se.pool + (long)out_slot * se.slot_floats);
@@ -397,14 +400,14 @@ __global__ void se_recurrent_kernel(TreeDev td, SEDev se, int n_trees) {
 // The stub's hidden-state move, parent slot -> child slot, staged through shared memory: one CTA per tree, one elected thread,
 // two 1-D bulk copies (global -> smem on an mbarrier, smem -> global as a bulk group).  The copy engine moves the 16-byte
 // lines; no register traffic.  ~10 CTAs of a Connect4 state (21.5 KB) are resident per SM, so 1024+ trees are all in flight.
-__global__ void __launch_bounds__(32) se_move_kernel(TreeDev td, SEDev se, int n_trees) {
+__global__ void __launch_bounds__(32) se_move_kernel(SEDev se, int n_trees) {
     extern __shared__ __align__(128) unsigned char stage[];
     __shared__ __align__(8) uint64_t bar;
     const int t = blockIdx.x;
     if (t >= n_trees || threadIdx.x != 0) return;
     const uint32_t bytes = (uint32_t)se.slot_floats * 4u;
-    const float* src = se.pool + (long)td.in_slot[t] * se.slot_floats;
-    float* dst = se.pool + (long)td.out_slot[t] * se.slot_floats;
+    const float* src = se.pool + (long)se.mv_in[t] * se.slot_floats;
+    float* dst = se.pool + (long)se.mv_out[t] * se.slot_floats;
     umma::mbar_init(&bar, 1);
     umma::fence_mbar_init();
     umma::mbar_expect_tx(&bar, bytes);
@@ -453,19 +456,18 @@ void launch_tree_stats(const TreeDev& td, int n_trees, const ResultDev& r, cudaS
 void launch_se_initial(const TreeDev& td, const SEDev& se, int n_trees, const float* d_obs, int obs_stride, cudaStream_t s) {
     se_initial_kernel<<<warps_grid(n_trees, 128), 128, 0, s>>>(td, se, n_trees, d_obs, obs_stride);
 }
-int launch_se_recurrent(const TreeDev& td, const SEDev& se, int n_trees, cudaStream_t s) {
+void launch_se_recurrent(const TreeDev& td, const SEDev& se, int n_trees, cudaStream_t s) {
     se_recurrent_kernel<<<warps_grid(n_trees, 128), 128, 0, s>>>(td, se, n_trees);
-    if (se.slot_floats % 4 == 0) {
-        const size_t bytes = (size_t)se.slot_floats * 4;
-        static bool attr_set = false;   // states above the 48 KB default need the opt-in (ALE: 18 KB, C4d: 21.5 KB do not)
-        if (!attr_set && bytes > 48 * 1024) {
-            cudaFuncSetAttribute(se_move_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-            attr_set = true;
-        }
-        se_move_kernel<<<n_trees, 32, bytes, s>>>(td, se, n_trees);
-        return 2;
+}
+bool se_move_available(int slot_floats) { return slot_floats % 4 == 0 && (size_t)slot_floats * 4 <= 200 * 1024; }
+void launch_se_move(const SEDev& se, int n_trees, cudaStream_t s) {
+    const size_t bytes = (size_t)se.slot_floats * 4;
+    static bool attr_set = false;   // states above the 48 KB default need the opt-in (ALE: 18 KB, C4d: 21.5 KB do not)
+    if (!attr_set && bytes > 48 * 1024) {
+        cudaFuncSetAttribute(se_move_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_set = true;
     }
-    return 1;
+    se_move_kernel<<<n_trees, 32, bytes, s>>>(se, n_trees);
 }
 void launch_mt_move(uint32_t* d_mt_home, int* d_idx_home, uint32_t* d_mt_rows, int* d_idx_rows, const int* d_slots, int n,
                     int dir, cudaStream_t s) {

@@ -56,10 +56,16 @@ struct SEDev {
     float* pool;             // [T * (n_sims + 1)][slot_floats]: one hidden state is moved parent -> child per simulation
     int slot_floats;
     double vlo, vhi, rlo, rhi;
+    int bulk;                // 1 = the state moves by bulk copy (se_move_kernel), 0 = per-lane copy inside the outputs kernel
+    int* mv_in; int* mv_out; // [T]: this simulation's (parent slot, child slot) pairs, snapshotted for the state mover, which runs on
+                             // its own stream beside the next tree step (two such buffers alternate)
 };
 void launch_se_initial(const TreeDev& td, const SEDev& se, int n_trees, const float* d_obs, int obs_stride, cudaStream_t s);
-// returns the number of kernels launched (outputs + the bulk-copy state mover)
-int launch_se_recurrent(const TreeDev& td, const SEDev& se, int n_trees, cudaStream_t s);
+// stub outputs (+ the per-lane state copy for state sizes the bulk copy cannot take); snapshots the slot pairs into se.mv_in / mv_out
+void launch_se_recurrent(const TreeDev& td, const SEDev& se, int n_trees, cudaStream_t s);
+// the bulk-copy state mover for the pairs in se.mv_in / mv_out; false when the state size needs the per-lane copy instead
+bool se_move_available(int slot_floats);
+void launch_se_move(const SEDev& se, int n_trees, cudaStream_t s);
 
 // RNG streams of a subset of slots <-> compact rows (mzb_search_batch_slots): dir 0 = gather rows <- slots, 1 = scatter back
 void launch_mt_move(uint32_t* d_mt_home, int* d_idx_home, uint32_t* d_mt_rows, int* d_idx_rows, const int* d_slots, int n,

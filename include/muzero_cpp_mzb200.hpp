@@ -692,7 +692,8 @@ public:
     }
 
     // One game per slot from reset() to the end; training_step picks the temperature (self_play.cpp:104-105).
-    // Actors only (opponent = Self, exploration noise on); is_evaluator = true gives temperature 0 and no noise for Self opponents.
+    // is_evaluator = false: an actor (opponent = Self, exploration noise on).  is_evaluator = true: temperature 0, no noise, and in
+    // games of two players config.opponent_type moves for the side that is not config.muzero_player (self_play.cpp:41-56,128-143).
     std::vector<types::GameHistory> play(int training_step, bool is_evaluator = false) {
         const int n = (int)games_.size();
         const double temperature = (is_evaluator || !config_.visit_softmax_temperature) ? 0.0 : config_.visit_softmax_temperature(training_step);
@@ -716,36 +717,59 @@ public:
             mzb200::check(mzb_obs_ring_reset(engine_->handle(), live.data(), n), "mzb_obs_ring_reset");
             mzb200::check(mzb_obs_ring_push(engine_->handle(), live.data(), frames.data(), zeros.data(), n), "mzb_obs_ring_push");
         }
+        // We always play against ourself if we are an actor or in 1 player games (self_play.cpp:108-109)
+        const types::OpponentTypes opponent = (!is_evaluator || config_.num_players == 1) ? types::OpponentTypes::Self : config_.opponent_type;
         while (!live.empty()) {
-            const int m = (int)live.size();
+            const int n_live = (int)live.size();
+            // who moves by search and who is moved by the evaluation opponent (self_play.cpp:128-143)
+            std::vector<int32_t> srch, opp, row_of(n, -1);
+            for (int g : live) {
+                if (opponent == types::OpponentTypes::Self || games_[g]->to_play() == config_.muzero_player) { row_of[g] = (int)srch.size(); srch.push_back(g); }
+                else opp.push_back(g);
+            }
+            const int m = (int)srch.size();
             std::vector<uint32_t> mask(m, 0);
             std::vector<int32_t> to_play(m), n_children(m), depth(m), child_actions((size_t)m * A_), actions(m);
             std::vector<uint8_t> noise(m, is_evaluator ? 0 : 1);
             std::vector<double> root(m), rel((size_t)m * A_), pol((size_t)m * A_), temps(m, temperature);
             for (int k = 0; k < m; ++k) {
-                for (types::Action a : hist[live[k]].legal_actions.back()) mask[k] |= 1u << a;
-                to_play[k] = games_[live[k]]->to_play();
+                for (types::Action a : hist[srch[k]].legal_actions.back()) mask[k] |= 1u << a;
+                to_play[k] = games_[srch[k]]->to_play();
             }
             mzb_search_result out{};
             out.root_value = root.data(); out.max_tree_depth = depth.data(); out.n_children = n_children.data();
             out.child_actions = child_actions.data(); out.children_relative_visit = rel.data(); out.emperical_policy = pol.data();
-            {   // get_stacked_observations(-1, ...) + mcts.run + select_action for every live game (self_play.cpp:119-133)
+            if (m > 0) {   // get_stacked_observations(-1, ...) + mcts.run + select_action for every searching game (self_play.cpp:119-133)
                 std::lock_guard<std::mutex> call(engine_->call_mutex());
-                mzb200::check(mzb_search_batch_ring(engine_->handle(), live.data(), mask.data(), to_play.data(), noise.data(), m, &out),
+                mzb200::check(mzb_search_batch_ring(engine_->handle(), srch.data(), mask.data(), to_play.data(), noise.data(), m, &out),
                               "mzb_search_batch_ring");
-                mzb200::check(mzb_select_actions(engine_->handle(), live.data(), &out, m, temps.data(), actions.data()), "mzb_select_actions");
+                mzb200::check(mzb_select_actions(engine_->handle(), srch.data(), &out, m, temps.data(), actions.data()), "mzb_select_actions");
+                ++moves_;
+            }
+            // select_opponent_action (self_play.cpp:41-56)
+            std::vector<types::Action> opp_action(n, types::InvalidAction);
+            if (!opp.empty() && opponent == types::OpponentTypes::Random) {
+                std::vector<int32_t> hi(opp.size()), pick(opp.size());
+                for (size_t k = 0; k < opp.size(); ++k) hi[k] = (int32_t)hist[opp[k]].legal_actions.back().size() - 1;
+                std::lock_guard<std::mutex> call(engine_->call_mutex());
+                mzb200::check(mzb_actor_uniform_int(engine_->handle(), opp.data(), hi.data(), (int)opp.size(), pick.data()), "mzb_actor_uniform_int");
+                for (size_t k = 0; k < opp.size(); ++k) opp_action[opp[k]] = hist[opp[k]].legal_actions.back()[pick[k]];
+            } else {
+                for (int g : opp) opp_action[g] = opponent == types::OpponentTypes::Expert ? games_[g]->expert_action() : games_[g]->human_to_action();
             }
             std::vector<int32_t> next_live, pushed_actions;
             std::vector<float> next_frames;
-            for (int k = 0; k < m; ++k) {
-                const int g = live[k];
+            for (int li = 0; li < n_live; ++li) {
+                const int g = live[li], k = row_of[g];
                 types::GameHistory& h = hist[g];
-                h.store_search_statistics(root[k], std::vector<double>(pol.begin() + (size_t)k * A_, pol.begin() + (size_t)(k + 1) * A_));
-                const types::StepReturn st = games_[g]->step(actions[k]);
+                // only searched moves store root statistics (self_play.cpp:131-133)
+                if (k >= 0) h.store_search_statistics(root[k], std::vector<double>(pol.begin() + (size_t)k * A_, pol.begin() + (size_t)(k + 1) * A_));
+                const types::Action played = k >= 0 ? actions[k] : opp_action[g];
+                const types::StepReturn st = games_[g]->step(played);
                 // the reference's own termination rule, kept verbatim (self_play.cpp:149-150): with max_moves > 0 a game also ends
                 // while FEWER than max_moves searches have been stored
                 const bool done = st.done || (config_.max_moves > 0 && (int)h.root_values.size() < config_.max_moves);
-                h.action_history.push_back(actions[k]);
+                h.action_history.push_back(played);
                 h.observation_history.push_back(st.observation);
                 h.reward_history.push_back(st.reward);
                 h.to_play_history.push_back(games_[g]->to_play());
@@ -753,7 +777,7 @@ public:
                 if (done) continue;
                 if (st.observation.size() != frame) detail::fatal("AbstractGame::step: observation size differs from observation_shape");
                 next_live.push_back(g);
-                pushed_actions.push_back(actions[k]);
+                pushed_actions.push_back(played);
                 next_frames.insert(next_frames.end(), st.observation.begin(), st.observation.end());
             }
             if (!next_live.empty()) {
@@ -762,7 +786,6 @@ public:
                               "mzb_obs_ring_push");
             }
             live.swap(next_live);
-            ++moves_;
         }
         return hist;
     }

@@ -242,6 +242,9 @@ int mzb_search_batch_ring(mzb_engine* e, const int32_t* slots, const uint32_t* l
 int mzb_actor_seed(mzb_engine* e, const int32_t* slots, const int32_t* seeds, int n);
 int mzb_select_actions(mzb_engine* e, const int32_t* slots, const mzb_search_result* stats, int n, const double* temperature,
                        int32_t* actions_out);
+/* select_opponent_action's Random branch (self_play.cpp:47-50): out[i] = std::uniform_int_distribution<>(0, upper_inclusive[i]) drawn
+ * from slot i's actor generator (the one mzb_select_actions uses, as the reference shares `rng` between the two). */
+int mzb_actor_uniform_int(mzb_engine* e, const int32_t* slots, const int32_t* upper_inclusive, int n, int32_t* out);
 
 /* ValueEncoder::encode (util.cpp:59-76) and ::decode (util.cpp:80-87) of the engine's value (which = 0) or reward (which = 1)
  * encoder, on the GPU, host pointers in and out: n scalars <-> n rows of support_size floats (mzb_shapes gives the sizes).

@@ -194,6 +194,21 @@ int mzb_actor_seed(mzb_engine* e, const int32_t* slots, const int32_t* seeds, in
     return MZB_OK;
 }
 
+// select_opponent_action's Random branch (self_play.cpp:47-50): std::uniform_int_distribution<>(0, n_legal - 1) on the slot's actor
+// generator — the same generator select_action draws from, as in the reference, so the streams stay in step
+int mzb_actor_uniform_int(mzb_engine* e, const int32_t* slots, const int32_t* upper_inclusive, int n, int32_t* out) {
+    int rc = ring_check(e, slots, n, false);
+    if (rc) return rc;
+    MZB_REQUIRE(upper_inclusive && out, "null argument");
+    for (int i = 0; i < n; ++i) {
+        MZB_REQUIRE(e->ring->actor_seeded[slots[i]], "slot %d: actor generator not seeded (mzb_actor_seed)", slots[i]);
+        MZB_REQUIRE(upper_inclusive[i] >= 0, "row %d: empty range", i);
+        std::uniform_int_distribution<> d(0, upper_inclusive[i]);
+        out[i] = d(e->ring->actor[slots[i]]);
+    }
+    return MZB_OK;
+}
+
 // select_action (self_play.cpp:21-39), row i of a batch of search results, with slot i's actor generator
 int mzb_select_actions(mzb_engine* e, const int32_t* slots, const mzb_search_result* stats, int n, const double* temperature, int32_t* actions_out) {
     int rc = ring_check(e, slots, n, false);

@@ -161,7 +161,7 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_search_batch", "mzb_search_batch_device_obs", "mzb_last_search_timing", "mzb_search_set_recording",
            "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes", "mzb_value_encode", "mzb_value_decode",
            "mzb_obs_ring_create", "mzb_obs_ring_reset", "mzb_obs_ring_push", "mzb_obs_ring_stacked", "mzb_search_batch_ring",
-           "mzb_actor_seed", "mzb_select_actions", "mzb_set_host_evaluator",
+           "mzb_actor_seed", "mzb_select_actions", "mzb_actor_uniform_int", "mzb_set_host_evaluator",
            "mzb_checkpoint_open", "mzb_checkpoint_count", "mzb_checkpoint_tensor", "mzb_checkpoint_close", "mzb_load_checkpoint",
            "mzb_debug_se_state", "mzb_debug_tree_write", "mzb_debug_tree_read", "mzb_debug_select_child", "mzb_debug_backpropagate"]
 

@@ -564,6 +564,74 @@ static void self_play_cohort(const std::string& golden_dir) {
             EXPECT(cohort_path[r].root_values != got[r].root_values, "reanalyze history %d: nothing was re-searched", r);
         }
     }
+    // (8) evaluator games (self_play.cpp:104-143 with is_evaluator): temperature 0, no noise, and a Random opponent that moves
+    //     for player 1 by std::uniform_int_distribution draws on the actor's own generator
+    {
+        muzero_config::MuZeroConfig ec = config;
+        ec.opponent_type = OpponentTypes::Random;
+        ec.muzero_player = 0;
+        std::vector<GameHistory> ref_games(n);
+        {
+            DeviceManager dm;
+            VPRNetModel m2(ec, "cuda:0", MZB_FP32_CHECK);
+            m2.LoadWeights(weights);
+            dm.AddDevice(std::move(m2));
+            auto evaluator = std::make_shared<VPRNetEvaluator>(&dm, 4, 1, 4, 1);
+            std::vector<std::unique_ptr<algorithm::MCTS>> mcts(n);
+            for (int i = 0; i < n; ++i) mcts[i].reset(new algorithm::MCTS(ec, 700 + i, evaluator));
+            std::vector<std::thread> actors;
+            for (int i = 0; i < n; ++i)
+                actors.emplace_back([&, i] {
+                    DriftGame game(i);
+                    std::mt19937 rng(700 + i);
+                    GameHistory& h = ref_games[i];
+                    h.action_history.push_back(0);
+                    h.observation_history.push_back(game.reset());
+                    h.reward_history.push_back(0);
+                    h.to_play_history.push_back(game.to_play());
+                    h.legal_actions.push_back(game.legal_actions());
+                    bool done = false;
+                    while (!done) {
+                        Action a;
+                        if (game.to_play() == ec.muzero_player) {
+                            MCTSReturn st = mcts[i]->run(stacked(h, ec), game.legal_actions(), game.to_play(), false);
+                            const auto best = std::max_element(st.children_relative_visit.begin(), st.children_relative_visit.end());
+                            a = st.child_actions[best - st.children_relative_visit.begin()];
+                            h.store_search_statistics(st.root_value, st.emperical_policy);
+                        } else {
+                            const std::vector<Action> legal = game.legal_actions();
+                            std::uniform_int_distribution<> d(0, (int)legal.size() - 1);
+                            a = legal[d(rng)];
+                        }
+                        StepReturn sr = game.step(a);
+                        done = sr.done;
+                        h.action_history.push_back(a);
+                        h.observation_history.push_back(sr.observation);
+                        h.reward_history.push_back(sr.reward);
+                        h.to_play_history.push_back(game.to_play());
+                        h.legal_actions.push_back(game.legal_actions());
+                    }
+                    mcts[i].reset();
+                });
+            for (auto& t : actors) t.join();
+        }
+        VPRNetModel m3(ec, "cuda:0", MZB_FP32_CHECK);
+        m3.LoadWeights(weights);
+        std::vector<std::unique_ptr<DriftGame>> eg;
+        std::vector<AbstractGame*> eptr;
+        std::vector<int> eseeds;
+        for (int i = 0; i < n; ++i) { eg.emplace_back(new DriftGame(i)); eptr.push_back(eg.back().get()); eseeds.push_back(700 + i); }
+        SelfPlayCohort ev(ec, m3, eptr, eseeds, eseeds);
+        std::vector<GameHistory> got_games = ev.play(0, /*is_evaluator*/ true);
+        int opponent_moves = 0;
+        for (int i = 0; i < n; ++i) {
+            EXPECT(got_games[i].action_history == ref_games[i].action_history, "evaluator game %d: actions differ from the actor path", i);
+            EXPECT(got_games[i].root_values == ref_games[i].root_values, "evaluator game %d: root values differ", i);
+            EXPECT(got_games[i].child_visits == ref_games[i].child_visits, "evaluator game %d: stored policies differ", i);
+            opponent_moves += (int)(got_games[i].action_history.size() - 1 - got_games[i].root_values.size());
+        }
+        EXPECT(opponent_moves > 0, "the Random opponent never moved");
+    }
     // the same games once more on the same cohort: generators have advanced, histories stay well-formed
     std::vector<GameHistory> again = cohort.play(/*training_step*/ 200);
     for (int i = 0; i < n; ++i) {

@@ -317,7 +317,7 @@ static int mode_net(const Args& a) {
     int B = a.i("batch", 4), seed = a.i("seed", 0);
     torch::manual_seed(seed);
     model::MuzeroNetwork net(c);
-    if (a.has("ckpt")) { torch::load(net, a.str("ckpt", "")); }
+    if (a.has("ckpt")) { torch::load(net, a.str("ckpt", ""), torch::Device(torch::kCPU)); }   // the shipped archive was saved from cuda:0
     else if (a.i("randomize_bn", 1)) { randomize_bn(net); }
     net->eval();
 
@@ -333,7 +333,7 @@ static int mode_net(const Args& a) {
     }
 
     mzbt::Writer w;
-    dump_weights(w, net);
+    if (!a.has("no_weights")) dump_weights(w, net);   // no_weights: the fixture refers to the checkpoint file itself
     int A = (int)c.action_space.size();
     int cin = net->get_initial_inference_channels();
     int flat = cin * c.observation_shape.h * c.observation_shape.w;

@@ -8,6 +8,7 @@ Outputs (committed):
   net_tiny.mzbt   weights / inputs / outputs of VPRNetModel::{Initial,Recurrent}Inference, plain head
   checkpoint_tiny.pt  the module archive torch::save wrote for net_tiny's weights (what VPRNetModel::LoadCheckpoint reads)
   net_tinyds.mzbt same for the downsample head
+  checkpoint_c4r_trained.pt / net_c4r_trained.mzbt  the shipped trained Connect4 checkpoint + the reference's outputs on it
   encoder.json    ValueEncoder support sizes and decode known answers
 """
 import json
@@ -51,6 +52,14 @@ def main():
     O.run_ref("net", "game=tiny", "batch=3", "seed=3", "out=" + os.path.join(HERE, "net_tiny.mzbt"),
               "ckpt_out=" + os.path.join(HERE, "checkpoint_tiny.pt"))
     O.run_ref("net", "game=tinyds", "batch=2", "seed=4", "out=" + os.path.join(HERE, "net_tinyds.mzbt"))
+    # TRAINED weights: the Connect4 checkpoint the reference ships (README.md:171,194), kept byte for byte as a data fixture;
+    # the expected outputs are the unmodified reference's on 16 Bernoulli(0.3) board-like inputs (weights stay in the .pt)
+    shipped = "/root/reference/examples/connect4/reanalyze-00/checkpoints/checkpoint--1.pt"
+    trained = os.path.join(HERE, "checkpoint_c4r_trained.pt")
+    with open(shipped, "rb") as src, open(trained, "wb") as dst:
+        dst.write(src.read())
+    O.run_ref("net", "game=c4r", "batch=16", "seed=5", "binary_obs=1", "no_weights", "ckpt=" + trained,
+              "out=" + os.path.join(HERE, "net_c4r_trained.mzbt"))
     enc = []
     for lo, hi, extra in [(-10, 10, []), (-22, 22, []), (-1, 1, []), (-21, 21, []), (-300, 300, []), (-5, 7, ["no_contractive"])]:
         txt = O.run_ref("encoder", "min=%g" % lo, "max=%g" % hi, "rows=6", "seed=1", *extra)

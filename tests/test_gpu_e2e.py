@@ -20,7 +20,10 @@ def _result(res, t, trace):
                 trace=list(zip([int(x) for x in trace[0][t]], [int(x) for x in trace[1][t]])))
 
 
-@pytest.mark.parametrize("game,T,sims,precision", [("tiny", 32, 20, 0), ("c4r", 48, 50, 0), ("ttt", 16, 25, 0)])
+@pytest.mark.parametrize("game,T,sims,precision", [
+    ("tiny", 32, 20, 0), ("c4r", 48, 50, 0), ("ttt", 16, 25, 0),
+    # the configurations bench.py measures: bf16 towers, full cohorts, the two-half-cohort pipeline on two streams
+    ("c4d", 1024, 50, 1), ("c4r", 1024, 50, 1), ("ttt", 1024, 25, 1), ("ale", 256, 50, 1)])
 def test_search_with_network_replays_bit_exactly(game, T, sims, precision):
     import mzb200
     ncfg = V.preset(game)
@@ -42,8 +45,9 @@ def test_search_with_network_replays_bit_exactly(game, T, sims, precision):
         res = eng.run(obs, masks, to_play, noise)
         trace = eng.get_trace(T)
         v, r, p = eng.get_records(T)
-        if move == 0:
-            # first-move root outputs are the network's: cross-check them against the fp32 oracle
+        if move == 0 and T <= 64:
+            # first-move root outputs are the network's: cross-check them against the fp32 oracle (the bf16 cohorts'
+            # network parity is tests/test_gpu_net.py's business; here only the decisions on the recorded outputs count)
             o0 = V.VPRNetOracle(ncfg, W).initial_inference(obs)
             np.testing.assert_allclose(v[:, 0], o0["value"], atol=1e-4)
             np.testing.assert_allclose(p[:, 0, :], o0["policy"], atol=1e-4)

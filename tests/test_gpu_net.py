@@ -92,6 +92,31 @@ def test_fp32_matches_reference_golden(game, golden_dir):
     eng.close()
 
 
+@pytest.mark.parametrize("precision", [0, 1])
+def test_trained_checkpoint_matches_reference_golden(precision, golden_dir):
+    """TRAINED weights: the Connect4 network the reference ships (tests/golden/checkpoint_c4r_trained.pt, BatchNorm running_var
+    with denormals ~7e-44, SURVEY §7 hard part 5), loaded by mzb_load_checkpoint (vprnet.cpp:66-74); expected outputs written by
+    the unmodified reference's VPRNetModel on that file (net_c4r_trained.mzbt, tests/golden/make_golden.py)."""
+    d = O.mzbt_load(os.path.join(golden_dir, "net_c4r_trained.mzbt"))
+    eng = _engine("c4r", 16, precision)
+    eng.load_checkpoint(os.path.join(golden_dir, "checkpoint_c4r_trained.pt"))
+    C = eng.shapes.enc_c
+    raw = None
+    if precision == 1:   # the bf16 hidden-state bound needs the un-normalised tower output: from the oracle, itself pinned on this fixture
+        import mzb200
+        net = V.VPRNetOracle(V.preset("c4r"), mzb200.read_checkpoint(os.path.join(golden_dir, "checkpoint_c4r_trained.pt")))
+        raw = {"init": net.initial_inference(d["in.obs"])["hidden_raw"],
+               "rec1": net.recurrent_inference(d["init.hidden"], d["in.a1"])["hidden_raw"],
+               "rec2": net.recurrent_inference(d["rec1.hidden"], d["in.a2"])["hidden_raw"]}
+    outs = {"init": eng.initial_inference(d["in.obs"]), "rec1": eng.recurrent_inference(d["init.hidden"], d["in.a1"]),
+            "rec2": eng.recurrent_inference(d["rec1.hidden"], d["in.a2"])}
+    for tag, g in outs.items():
+        for k in ("value", "reward", "policy"):
+            _check(getattr(g, k), d[tag + "." + k], precision, "trained %s %s" % (tag, k))
+        _check_hidden(g.encoded_state, d[tag + ".hidden"], raw[tag] if raw else None, precision, "trained %s hidden" % tag, C)
+    eng.close()
+
+
 @pytest.mark.parametrize("game,B", [("c4r", 9), ("ttt", 5), ("c4d", 4)])
 def test_fp32_matches_oracle_random_weights(game, B):
     ncfg = V.preset(game)

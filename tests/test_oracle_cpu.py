@@ -274,6 +274,23 @@ def test_network_oracle_matches_reference_golden(game, golden_dir):
     np.testing.assert_allclose(o1["reward_logits"], d["dbg.rec1.reward_logits"], atol=2e-6)
 
 
+def test_network_oracle_matches_reference_on_the_shipped_trained_checkpoint(golden_dir):
+    """TRAINED weights: tests/golden/checkpoint_c4r_trained.pt is the Connect4 network the reference ships
+    (examples/connect4/reanalyze-00/checkpoints/checkpoint--1.pt; its BatchNorm running_var holds denormals ~7e-44, SURVEY §7
+    hard part 5), net_c4r_trained.mzbt the unmodified reference's outputs on it (tests/golden/make_golden.py)."""
+    import mzb200
+    d = O.mzbt_load(os.path.join(golden_dir, "net_c4r_trained.mzbt"))
+    W = mzb200.read_checkpoint(os.path.join(golden_dir, "checkpoint_c4r_trained.pt"))
+    assert min(float(np.abs(v[v != 0]).min()) for k, v in W.items() if k.endswith("running_var") and (v != 0).any()) < 1e-38
+    net = V.VPRNetOracle(V.preset("c4r"), W)
+    o0 = net.initial_inference(d["in.obs"])
+    o1 = net.recurrent_inference(o0["hidden"], d["in.a1"])
+    o2 = net.recurrent_inference(o1["hidden"], d["in.a2"])
+    for pre, o in (("init", o0), ("rec1", o1), ("rec2", o2)):
+        for k in ("value", "reward", "policy", "hidden"):
+            np.testing.assert_allclose(o[k], d[pre + "." + k], rtol=0, atol=5e-6, err_msg="trained %s %s" % (pre, k))
+
+
 def test_random_weights_have_reference_names(golden_dir):
     for game in ("tiny", "tinyds"):
         d = O.mzbt_load(os.path.join(golden_dir, "net_%s.mzbt" % game))

@@ -132,30 +132,48 @@ class ClockSampler:
         return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm), source="nvidia-smi")
 
 
-def run_reference_cpu(game, seconds_target, sims):
+def run_reference_cpu(game, seconds_target, sims, steps=3, warmup=1):
     """The reference's own CPU path on this box's host cores (oracle/_ref/ref_driver bench: unmodified MCTS::run +
-    VPRNetEvaluator + DeviceManager + VPRNetModel on libtorch CPU, --devices=cpu,cpu semantics).  Bounded sample."""
+    VPRNetEvaluator + DeviceManager + VPRNetModel on libtorch CPU, --devices=cpu,cpu semantics) with all the host threads it can
+    use: torchrun's OMP_NUM_THREADS=1 is NOT inherited, libtorch gets one intra-op thread per core, and the arrangement is the
+    best of a sweep over actors in {4, cores} (evaluator batch = actors, README.md:87) x evaluator threads in {1, 2}
+    (SURVEY.md 8d).  `steps` timed steps after `warmup` untimed ones, each a bounded sample (the same number of searches per
+    actor), sized so that the whole run takes about `seconds_target`."""
     drv = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
     cores = os.cpu_count() or 1
     if not os.path.exists(drv):
         return None
-    actors = max(4, min(cores, 64))
-    # calibrate: one move per actor, then scale the number of moves to the time target
-    best = None
-    for moves in (1,):
-        out = subprocess.run([drv, "bench", "game=" + game, "sims=%d" % sims, "actors=%d" % actors, "batch=%d" % actors,
-                              "moves=%d" % moves, "devices=2"], capture_output=True, text=True, timeout=1200)
-        if out.returncode != 0:
-            return dict(error=out.stderr[-300:])
-        best = json.loads(out.stdout.strip().splitlines()[-1])
-    moves = int(max(1, min(50, seconds_target / max(best["seconds"], 1e-3))))
-    if moves > 1:
-        out = subprocess.run([drv, "bench", "game=" + game, "sims=%d" % sims, "actors=%d" % actors, "batch=%d" % actors,
-                              "moves=%d" % moves, "devices=2"], capture_output=True, text=True, timeout=1800)
-        if out.returncode == 0:
-            best = json.loads(out.stdout.strip().splitlines()[-1])
+    env = {k: v for k, v in os.environ.items() if k not in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OMP_PROC_BIND", "GOMP_CPU_AFFINITY")}
+    actors = sorted({4, max(4, min(cores, 64))})
+    base = [drv, "bench", "game=" + game, "sims=%d" % sims, "devices=2", "torch_threads=%d" % cores]
+    out = subprocess.run(base + ["actors=" + ",".join(map(str, actors)), "eval_threads=1,2", "moves=1", "steps=1", "warmup=1"],
+                         capture_output=True, text=True, timeout=1200, env=env)
+    if out.returncode != 0:
+        return dict(error=out.stderr[-300:])
+    cal = json.loads(out.stdout.strip().splitlines()[-1])
+    per_move = max(cal["seconds"], 1e-3)                       # one timed step of one move per actor, best arrangement
+    moves = int(max(1, min(50, round(seconds_target / max(1, steps + warmup) / per_move))))
+    out = subprocess.run(base + ["actors=%d" % cal["actors"], "eval_threads=%d" % cal["eval_threads"], "moves=%d" % moves,
+                                 "steps=%d" % steps, "warmup=%d" % warmup], capture_output=True, text=True, timeout=3600, env=env)
+    if out.returncode != 0:
+        return dict(error=out.stderr[-300:])
+    best = json.loads(out.stdout.strip().splitlines()[-1])
+    best["sweep"] = cal["sweep"]
     best["cores"] = cores
     return best
+
+
+def reference_sample_text(res, sims):
+    return ("%d actor threads x %d moves x %d sims per step, %d timed steps; evaluator batch %d, %d evaluator thread(s) per queue, 2 libtorch-CPU "
+            "model replicas, %s torch intra-op threads (best of the sweep %s)") % (
+        res["actors"], res["moves"], sims, res["steps"], res["batch"], res["eval_threads"], res["torch_threads"],
+        json.dumps([[x["actors"], x["eval_threads"], round(x["sims_per_s"])] for x in res.get("sweep", [])]))
+
+
+def workload_config(desc, T, sims):
+    """`config` of the JSON line: identical in both arms (the reference arm runs a bounded sample of the same workload)."""
+    return dict(workload=desc, trees_per_gpu=T, sims_per_move=sims, weights="random-init", data="synthetic observations of the config's shape",
+                l2="working set (node pool) exceeds the 126 MB L2; no explicit flush")
 
 
 _REAL_STDOUT = None
@@ -173,14 +191,16 @@ def emit(line):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=None, help="timed steps; default: as many as --seconds of searches take")
+    ap.add_argument("--seconds", type=float, default=5.0, help="length of the timed region when --steps is not given, and of the sustained leg")
+    ap.add_argument("--no-extras", action="store_true", help="skip the sustained leg and the other workloads' short lines")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c4d", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "fp32"])
     ap.add_argument("--trees", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--cpu-seconds", type=float, default=None, help="CPU-arm time budget (default: 15 s beside our arm, 60 s for --impl reference)")
     args = ap.parse_args()
     # stdout carries exactly one JSON line.  Libraries print there too (NCCL's "NCCL version ..." banner under torchrun), so
     # file descriptor 1 points at stderr while the work runs and is put back for the line itself (emit()).
@@ -200,36 +220,29 @@ def main():
     cfg0 = mzb200.preset(preset_name)
     sims = cfg0.num_simulations
 
+    T = args.trees or wl["trees"]
     if args.impl == "reference":
         if rank != 0:
             return 0
         t0 = time.time()
-        vals = []
-        for _ in range(max(1, args.warmup) - 1 + 0):
-            pass
-        res = None
-        for _ in range(max(1, min(args.steps, 3))):
-            res = run_reference_cpu(preset_name, args.cpu_seconds, sims)
-            if res is None or "error" in res:
-                break
-            vals.append(res["sims_per_s"])
-        if not vals:
+        K, Wm = args.steps or 5, args.warmup
+        res = run_reference_cpu(preset_name, args.cpu_seconds or 60.0, sims, steps=K, warmup=Wm)
+        if res is None or "error" in res:
             # the oracle port always exists: time the C/torch-CPU restatement instead
-            res = run_port_cpu(preset_name, args.cpu_seconds, sims)
-            vals = [res["sims_per_s"]]
-            kind = "port"
+            res = run_port_cpu(preset_name, args.cpu_seconds or 30.0, sims)
+            v, kind, step_ms, sample, K = res["sims_per_s"], "port", 1000.0 * res["seconds"], res["sample"], 1
         else:
-            kind = "reference"
-        v = sum(vals) / len(vals)
-        line = dict(metric=METRIC, value=v, unit=UNIT, n_gpus=args.gpus, steps=len(vals), warmup=0,
-                    ms_per_step=1000.0 * res["seconds"], higher_is_better=True, scaling="weak", vs_baseline=None,
+            v, kind, step_ms = res["sims_per_s"], "reference", 1000.0 * res["seconds"] / K
+            sample = reference_sample_text(res, sims)
+        line = dict(metric=METRIC, value=v, unit=UNIT, n_gpus=args.gpus, steps=K, warmup=Wm,
+                    ms_per_step=step_ms, higher_is_better=True, scaling="weak", vs_baseline=None,
                     dtype="f32", data="synthetic", impl="reference",
-                    config=dict(workload=wl["desc"], sims_per_move=sims),
-                    cpu_baseline=dict(value=v, unit=UNIT, cores=res.get("cores", os.cpu_count()), kind=kind,
-                                      sample="%d actor threads x %d moves x %d sims, evaluator batch %d, libtorch CPU (%s torch threads)" % (
-                                          res.get("actors", 0), int(res.get("sims", 0) / max(1, res.get("actors", 1)) / sims), sims,
-                                          res.get("batch", 0), res.get("torch_threads", "?"))),
+                    config=workload_config(wl["desc"], T, sims),
+                    cpu_baseline=dict(value=v, unit=UNIT, cores=res.get("cores", os.cpu_count()), kind=kind, sample=sample),
                     e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                    reference_arm=dict(note="thread-per-actor MCTS::run over VPRNetEvaluator/DeviceManager/VPRNetModel on libtorch CPU; "
+                                            "each step is a bounded sample of the workload (trees_per_gpu names the GPU arm's cohort)",
+                                       step_seconds=res.get("step_seconds"), sweep=res.get("sweep")),
                     wall_s=time.time() - t0)
         emit(line)
         return 0
@@ -242,49 +255,16 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    T = args.trees or wl["trees"]
     precision = {"bf16": mzb200.BF16, "fp32": mzb200.FP32_CHECK}.get(args.precision)
-    eng = None
     if precision is None:
         try:
-            eng = mzb200.Engine(mzb200.preset(preset_name, max_trees=T, precision=mzb200.BF16, seed=1000 * rank), local_rank)
+            mzb200.Engine(mzb200.preset("tiny", max_trees=4, precision=mzb200.BF16), local_rank).close()
             precision = mzb200.BF16
         except mzb200.MzbError as e:
             if "not available" not in str(e):
                 raise
             precision = mzb200.FP32_CHECK
-    cfg = mzb200.preset(preset_name, max_trees=T, precision=precision, seed=1000 * rank)
-    if eng is None:
-        eng = mzb200.Engine(cfg, local_rank)
-    # weights: rank 0 draws them, every other rank receives them with ONE ncclBroadcast of the packed blob
-    W = random_weights(cfg, seed=0 if rank == 0 else 1 + rank)
-    eng.load_weights(W)
-    sync_ms = None
-    if world > 1:
-        uid = [mzb200.Engine.nccl_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        eng.nccl_init(uid[0], rank, world)
-        torch.cuda.synchronize()
-        t0 = time.time()
-        eng.broadcast_weights(0)          # first call: includes NCCL's lazy connection set-up
-        sync_first_ms = 1000 * (time.time() - t0)
-        dist.barrier()
-        t0 = time.time()
-        for _ in range(5):                # steady state = what every model_sync_interval costs
-            eng.broadcast_weights(0)
-        sync_ms = 1000 * (time.time() - t0) / 5
-        sums = [None] * world
-        dist.all_gather_object(sums, eng.weights_checksum())
-        assert len(set(sums)) == 1, "weight broadcast left replicas different"
-
-    A = cfg.num_actions
-    flat = eng.shapes.initial_flat_size
-    rng = np.random.default_rng(rank)
-    obs_host = torch.from_numpy(rng.random((T, flat), dtype=np.float32)).pin_memory()
-    obs_dev = obs_host.cuda()
-    masks = np.full(T, (1 << A) - 1, np.uint32)
-    to_play = (np.arange(T) % cfg.num_players).astype(np.int32)
-    noise = np.ones(T, np.uint8)
+    pk = peaks()
 
     def barrier():
         torch.cuda.synchronize()
@@ -292,84 +272,158 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    def timed(fn, steps):
-        barrier()
-        dev_ms, t0 = 0.0, time.time()
-        launches = 0
-        for _ in range(steps):
-            fn()
-            tm = eng.last_search_timing()
-            dev_ms += tm["total_ms"]
-            split["root_ms"] += tm["root_ms"]
-            split["sim_loop_ms"] += tm["sim_loop_ms"]
-            launches += tm["kernel_launches"]
-        barrier()
-        wall_ms = 1000 * (time.time() - t0)
+    def measure(workload, T, steps, warmup, seconds, extras):
+        """One workload on this rank's GPU: W warm-up + K timed searches with device-resident observations (value), the same
+        through host buffers (e2e), and the dominant kernel alone (roofline).  steps=None: as many as `seconds` take."""
+        w = WORKLOADS[workload]
+        pname = w.get("preset", workload)
+        cfg = mzb200.preset(pname, max_trees=T, precision=precision, seed=1000 * rank)
+        eng = mzb200.Engine(cfg, local_rank)
+        # weights: rank 0 draws them, every other rank receives them with ONE ncclBroadcast of the packed blob
+        W = random_weights(cfg, seed=0 if rank == 0 else 1 + rank)
+        eng.load_weights(W)
+        out = dict()
         if world > 1:
-            t = torch.tensor([dev_ms, wall_ms], device="cuda", dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dev_ms, wall_ms = float(t[0]), float(t[1])
-        return dev_ms, wall_ms, launches
+            uid = [mzb200.Engine.nccl_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            eng.nccl_init(uid[0], rank, world)
+            torch.cuda.synchronize()
+            t0 = time.time()
+            eng.broadcast_weights(0)          # first call: includes NCCL's lazy connection set-up
+            out["weight_sync_first_ms"] = 1000 * (time.time() - t0)
+            dist.barrier()
+            t0 = time.time()
+            for _ in range(5):                # steady state = what every model_sync_interval costs
+                eng.broadcast_weights(0)
+            out["weight_sync_ms"] = 1000 * (time.time() - t0) / 5
+            out["weight_sync_bytes"] = int(eng.get_shapes().weight_blob_bytes)
+            sums = [None] * world
+            dist.all_gather_object(sums, eng.weights_checksum())
+            assert len(set(sums)) == 1, "weight broadcast left replicas different"
+        A, nsim = cfg.num_actions, cfg.num_simulations
+        flat = eng.shapes.initial_flat_size
+        rng = np.random.default_rng(rank)
+        obs_host = torch.from_numpy(rng.random((T, flat), dtype=np.float32)).pin_memory()
+        obs_dev = obs_host.cuda()
+        masks = np.full(T, (1 << A) - 1, np.uint32)
+        to_play = (np.arange(T) % cfg.num_players).astype(np.int32)
+        noise = np.ones(T, np.uint8)
+        split = dict(root_ms=0.0, sim_loop_ms=0.0)   # rank-local split of the device time: root (initial inference + expansion) | simulations
 
-    split = dict(root_ms=0.0, sim_loop_ms=0.0)   # rank-local split of the device time: root (initial inference + expansion) | simulations
-    run_dev = lambda: eng.run(None, masks, to_play, noise, device_obs_ptr=obs_dev.data_ptr())
-    run_host = lambda: eng.run(obs_host.numpy(), masks, to_play, noise)
-    for _ in range(args.warmup):
-        run_dev()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    dev_ms, wall_ms, launches = timed(run_dev, args.steps)
-    clocks = sampler.stop()
-    step_split = dict(root_ms_per_step=split["root_ms"] / args.steps, sim_loop_ms_per_step=split["sim_loop_ms"] / args.steps,
-                      sims_per_s_without_initial_inference=T * sims * args.steps / (split["sim_loop_ms"] / 1000.0) * world)
-    for _ in range(1):
+        def timed(fn, k):
+            barrier()
+            dev_ms, t0 = 0.0, time.time()
+            launches = 0
+            for _ in range(k):
+                fn()
+                tm = eng.last_search_timing()
+                dev_ms += tm["total_ms"]
+                split["root_ms"] += tm["root_ms"]
+                split["sim_loop_ms"] += tm["sim_loop_ms"]
+                launches += tm["kernel_launches"]
+            barrier()
+            wall_ms = 1000 * (time.time() - t0)
+            if world > 1:
+                t = torch.tensor([dev_ms, wall_ms], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dev_ms, wall_ms = float(t[0]), float(t[1])
+            return dev_ms, wall_ms, launches
+
+        run_dev = lambda: eng.run(None, masks, to_play, noise, device_obs_ptr=obs_dev.data_ptr())
+        run_host = lambda: eng.run(obs_host.numpy(), masks, to_play, noise)
+        for _ in range(warmup):
+            run_dev()
+        if steps is None:   # --seconds: derive K from one probe step (all ranks agree on the maximum)
+            probe_ms, _, _ = timed(run_dev, 1)
+            steps = int(max(3, min(20000, round(1000.0 * seconds / max(probe_ms, 1e-3)))))
+            if world > 1:
+                t = torch.tensor([steps], device="cuda", dtype=torch.int64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                steps = int(t[0])
+        split["root_ms"] = split["sim_loop_ms"] = 0.0
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        dev_ms, wall_ms, launches = timed(run_dev, steps)
+        clocks = sampler.stop()
+        step_split = dict(root_ms_per_step=split["root_ms"] / steps, sim_loop_ms_per_step=split["sim_loop_ms"] / steps,
+                          sims_per_s_without_initial_inference=T * nsim * steps / (split["sim_loop_ms"] / 1000.0) * world)
         run_host()
-    e2e_dev_ms, e2e_wall_ms, _ = timed(run_host, args.steps)
-    total_sims = world * T * sims * args.steps
-    value = total_sims / (dev_ms / 1000.0)
-    e2e_value = total_sims / (e2e_wall_ms / 1000.0)   # host clock: includes H2D, D2H and host-side noise generation
+        e2e_steps = steps if steps <= 200 else max(20, steps // 4)
+        e2e_dev_ms, e2e_wall_ms, _ = timed(run_host, e2e_steps)
+        value = world * T * nsim * steps / (dev_ms / 1000.0)
+        e2e_value = world * T * nsim * e2e_steps / (e2e_wall_ms / 1000.0)   # host clock: includes H2D, D2H and host-side noise generation
+        # bytes that cross PCIe per step through mzb_search_batch: observations + per-tree inputs + Dirichlet noise (f64) + the
+        # slots' mt19937 states BOTH ways (the gamma draws run on the host on the slots' own streams, engine_search.cu) | results
+        mt_bytes = T * (624 * 4 + 4)
+        h2d = T * flat * 4 + T * (4 + 4 + 1) + T * A * 8 + mt_bytes
+        d2h = T * (8 + 4 + 4 + A * (4 + 4 + 8 + 8)) + mt_bytes
+        out.update(steps=steps, value=value, ms_per_step=dev_ms / steps, wall_ms_per_step=wall_ms / steps, clocks=clocks,
+                   gpu_launches=int(launches), step_split=step_split, sims=nsim, T=T, cfg=cfg, W=W,
+                   e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h),
+                            ms_per_step=e2e_wall_ms / e2e_steps, device_ms_per_step=e2e_dev_ms / e2e_steps, steps=e2e_steps,
+                            rng_state_round_trip_bytes_each_way=int(mt_bytes)),
+                   node_pool_gb=eng.get_shapes().node_pool_bytes / 1e9, recurrent_flat_size=eng.shapes.recurrent_flat_size)
 
-    # roofline of the dominant kernels: the residual towers of recurrent_inference (tensor bound), measured live
-    pk = peaks()
-    frec = recurrent_flops(cfg)
-    rec_passes = 50   # ~15 ms of back-to-back launches, as long as one search step: a sustained, not a burst, measurement
-    rec_ms, rec_launches = eng.bench_recurrent(T, rec_passes)
-    states_per_s = T / (rec_ms / 1000.0)
-    achieved_tf = frec * states_per_s / 1e12
-    roofline = dict(bound="tensor", achieved=achieved_tf, peak=pk["tf_sustained"], unit="TFLOP/s",
-                    frac=achieved_tf / pk["tf_sustained"], traffic=ncu_traffic(args.workload, T),
-                    peak_source=pk["source"] + " (sustained bf16; %d back-to-back launches)" % rec_passes,
-                    frac_of_burst_peak=achieved_tf / pk["tf_burst"],
-                    kernel="tower_fused_kernel (one launch = recurrent_inference of all trees)" if rec_launches == 1 else "recurrent_inference towers",
-                    flops_per_state=frec, flops_per_launch=frec * T, launch_ms=rec_ms, states_per_s=states_per_s,
-                    launches_per_pass=rec_launches)
-    if world > 1:
-        t = torch.tensor([states_per_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        roofline["states_per_s_all_gpus"] = float(t[0])
+        # roofline of the dominant kernel: the residual towers of recurrent_inference (tensor bound), timed ALONE with CUDA events
+        # over back-to-back launches whose inputs rotate through the whole node pool (> L2).  50 launches (~12 ms at full clocks)
+        # are a burst measurement -> burst peak; the sustained leg below runs for seconds -> sustained peak.
+        frec = recurrent_flops(cfg)
+        rec_passes = 50
+        rec_ms, rec_launches = eng.bench_recurrent(T, rec_passes)
+        states_per_s = T / (rec_ms / 1000.0)
+        achieved_tf = frec * states_per_s / 1e12
+        traffic = ncu_traffic(workload, T)
+        roofline = dict(bound="tensor", achieved=achieved_tf, peak=pk["tf_burst"], unit="TFLOP/s", frac=achieved_tf / pk["tf_burst"],
+                        traffic=traffic, traffic_source="ncu --set full capture committed under profiles/ (tower_fused_traffic.json)" if traffic else None,
+                        peak_source=pk["source"] + " (burst bf16: %d back-to-back launches, %.1f ms, timed alone)" % (rec_passes, rec_ms * rec_passes),
+                        frac_of_sustained_peak=achieved_tf / pk["tf_sustained"],
+                        kernel="tower_fused_kernel (one launch = recurrent_inference of all trees)" if rec_launches == 1 else "recurrent_inference towers",
+                        flops_per_state=frec, flops_per_launch=frec * T, launch_ms=rec_ms, states_per_s=states_per_s,
+                        launches_per_pass=rec_launches)
+        if extras:
+            # sustained: seconds of back-to-back tower launches and seconds of searches, with the clocks seen
+            sp = ClockSampler(local_rank)
+            sp.start()
+            n_pass = int(max(50, min(200000, round(1000.0 * seconds / max(rec_ms, 1e-3)))))
+            s_ms, _ = eng.bench_recurrent(T, n_pass)
+            ck = sp.stop()
+            s_tf = frec * T / (s_ms / 1000.0) / 1e12
+            roofline["sustained"] = dict(achieved=s_tf, peak=pk["tf_sustained"], frac=s_tf / pk["tf_sustained"], launches=n_pass,
+                                         seconds=s_ms * n_pass / 1000.0, launch_ms=s_ms, clocks=ck)
+            if dev_ms < 1000.0 * seconds * 0.8:
+                k2 = int(max(steps, round(1000.0 * seconds / (dev_ms / steps))))
+                sp = ClockSampler(local_rank)
+                sp.start()
+                d2, w2, _ = timed(run_dev, k2)
+                out["sustained"] = dict(value=world * T * nsim * k2 / (d2 / 1000.0), steps=k2, seconds=w2 / 1000.0, ms_per_step=d2 / k2, clocks=sp.stop())
+        if world > 1:
+            t = torch.tensor([states_per_s], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            roofline["states_per_s_all_gpus"] = float(t[0])
+        out["roofline"] = roofline
+        out["states_per_s"] = states_per_s
+        eng.close()
+        return out
 
-    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
-                ms_per_step=dev_ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
+    extras = not args.no_extras
+    m = measure(args.workload, T, args.steps, args.warmup, args.seconds, extras)
+    cfg, W, A = m["cfg"], m["W"], m["cfg"].num_actions
+    line = dict(metric=METRIC, value=m["value"], unit=UNIT, n_gpus=world, steps=m["steps"], warmup=args.warmup,
+                ms_per_step=m["ms_per_step"], higher_is_better=True, scaling="weak", vs_baseline=None,
                 dtype="bf16" if precision == mzb200.BF16 else "f32", data="synthetic",
-                config=dict(workload=wl["desc"], trees_per_gpu=T, sims_per_move=sims, weights="random-init",
-                            l2="working set (node pool %.2f GB per GPU) exceeds the 126 MB L2; no explicit flush" % (eng.get_shapes().node_pool_bytes / 1e9),
-                            timing="CUDA events around each search on the engine's stream; max over ranks"),
-                wall_ms_per_step=wall_ms / args.steps, clocks=clocks,
-                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=int(T * flat * 4 + T * (4 + 4 + 1)),
-                         d2h_bytes_per_step=int(T * (8 + 4 + 4 + A * (4 + 4 + 8 + 8))), ms_per_step=e2e_wall_ms / args.steps,
-                         device_ms_per_step=e2e_dev_ms / args.steps),
-                gpu_launches=int(launches), roofline=roofline, recurrent_states_per_s=states_per_s, step_split=step_split)
-    if sync_ms is not None:
-        line["weight_sync_ms"] = sync_ms
-        line["weight_sync_first_ms"] = sync_first_ms
-        line["weight_sync_bytes"] = int(eng.get_shapes().weight_blob_bytes)
-    eng.close()
+                config=workload_config(wl["desc"], T, sims),
+                timing="CUDA events around each search on the engine's stream; max over ranks; node pool %.2f GB per GPU" % m["node_pool_gb"],
+                wall_ms_per_step=m["wall_ms_per_step"], clocks=m["clocks"], e2e=m["e2e"],
+                gpu_launches=m["gpu_launches"], roofline=m["roofline"], recurrent_states_per_s=m["states_per_s"], step_split=m["step_split"])
+    for k in ("weight_sync_ms", "weight_sync_first_ms", "weight_sync_bytes", "sustained"):
+        if k in m:
+            line[k] = m[k]
 
     if rank == 0 and world == 1:
         # tree kernels alone (HBM bound): same search with the network stubbed by the SE evaluator, which still moves one hidden
         # state parent -> child per simulation.  At the workload's cohort the step is launch/latency bound (1024 warps); the
         # second figure uses a cohort large enough for HBM to be the limit.
-        S_h = 4 * eng.shapes.recurrent_flat_size
+        S_h = 4 * m["recurrent_flat_size"]
         d = 4
         b_sim = 2 * S_h + d * 28 * A + 32 * A + 36 * (d + 1) + (4 + 16 + 4 * A)   # SURVEY.md §8d
 
@@ -377,14 +431,14 @@ def main():
             scfg = mzb200.preset(preset_name, max_trees=Tt, evaluator=mzb200.EVAL_SYNTHETIC)
             seng = mzb200.Engine(scfg, local_rank)
             keys = (np.arange(Tt) + 1).astype(np.float32)
-            m = np.full(Tt, (1 << A) - 1, np.uint32)
+            mk = np.full(Tt, (1 << A) - 1, np.uint32)
             tp = (np.arange(Tt) % cfg.num_players).astype(np.int32)
             nz = np.ones(Tt, np.uint8)
             for _ in range(3):
-                seng.run(keys, m, tp, nz)
+                seng.run(keys, mk, tp, nz)
             ms = 0.0
             for _ in range(5):
-                seng.run(keys, m, tp, nz)
+                seng.run(keys, mk, tp, nz)
                 ms += seng.last_search_timing()["sim_loop_ms"]
             seng.close()
             sims_s = 5 * Tt * sims / (ms / 1000.0)
@@ -393,30 +447,46 @@ def main():
                         kernel="tree_step + SE stub (outputs + bulk-copy hidden-state move through shared memory)")
 
         # BASELINE metric M2: recurrent_inference states/s with device-resident inputs, by batch size
+        frec = m["roofline"]["flops_per_state"]
         by_batch = {}
         for B in (1024, 4096, 16384):
-            pool_bytes = B * (sims + 3) * eng.shapes.recurrent_flat_size * 2
+            pool_bytes = B * (sims + 3) * m["recurrent_flat_size"] * 2
             if pool_bytes > 60e9:
                 continue
             beng = mzb200.Engine(mzb200.preset(preset_name, max_trees=B, precision=precision), local_rank)
             beng.load_weights(W)
             b_ms, _ = beng.bench_recurrent(B, 20)
             by_batch[str(B)] = dict(states_per_s=B / (b_ms / 1000.0), ms_per_pass=b_ms, tflops=frec * B / (b_ms / 1000.0) / 1e12,
-                                    frac_of_sustained_peak=frec * B / (b_ms / 1000.0) / 1e12 / pk["tf_sustained"])
+                                    frac_of_burst_peak=frec * B / (b_ms / 1000.0) / 1e12 / pk["tf_burst"])
             beng.close()
         line["recurrent_states_per_s_by_batch"] = by_batch
         line["roofline_tree"] = tree_leg(T)
         T_big = 16384
         if T_big > T and T_big * (sims + 1) * S_h < 40e9:
             line["roofline_tree_large_cohort"] = tree_leg(T_big)
+        if extras:
+            # the other single-GPU configs of BASELINE.json as short driver-visible lines (3 warm-up + 3 timed steps each)
+            others = {}
+            for name in sorted(WORKLOADS):
+                if name == args.workload:
+                    continue
+                try:
+                    o = measure(name, WORKLOADS[name]["trees"], 3, 3, 0.0, False)
+                    others[name] = dict(value=o["value"], e2e=o["e2e"]["value"], unit=UNIT, trees=o["T"], sims_per_move=o["sims"], steps=3, warmup=3,
+                                        ms_per_step=o["ms_per_step"], tower_tflops=o["roofline"]["achieved"],
+                                        tower_frac_of_burst_peak=o["roofline"]["frac"], tower_launch_ms=o["roofline"]["launch_ms"],
+                                        tower_launches_per_pass=o["roofline"]["launches_per_pass"],
+                                        root_ms_per_step=o["step_split"]["root_ms_per_step"], traffic=o["roofline"]["traffic"])
+                except Exception as e:   # a side line must not take the headline down
+                    others[name] = dict(error=str(e)[:200])
+            line["workloads"] = others
         if not args.no_cpu_baseline:
-            res = run_reference_cpu(preset_name, args.cpu_seconds, sims)
+            res = run_reference_cpu(preset_name, args.cpu_seconds or 15.0, sims, steps=3, warmup=1)
             if res and "error" not in res:
                 line["cpu_baseline"] = dict(value=res["sims_per_s"], unit=UNIT, cores=res["cores"], kind="reference",
-                                            sample="%d actor threads x %d sims total, evaluator batch %d, 2 libtorch-CPU model replicas, %s torch threads" % (
-                                                res["actors"], res["sims"], res["batch"], res["torch_threads"]))
+                                            sample=reference_sample_text(res, sims))
             else:
-                res = run_port_cpu(preset_name, args.cpu_seconds, sims)
+                res = run_port_cpu(preset_name, args.cpu_seconds or 15.0, sims)
                 line["cpu_baseline"] = dict(value=res["sims_per_s"], unit=UNIT, cores=1, kind="port", sample=res["sample"])
     if rank == 0:
         emit(line)

@@ -1,0 +1,4 @@
+// include/compat/muzero-cpp/util.h — stands where the reference's muzero-cpp/util.h is included (e.g. tests/mcts_test.cpp,
+// self_play.cpp): compile with -I<repo>/include/compat and the reference's names resolve to the B200 engine's drop-in header.
+#pragma once
+#include "../../muzero_cpp_mzb200.hpp"

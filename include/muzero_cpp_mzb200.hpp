@@ -20,7 +20,8 @@
 //                                                             cohort; any other Evaluator subclass -> device tree kernels with
 //                                                             host callbacks per simulation (MZB_EVAL_HOST)
 //
-// What is NOT here: Learn / SaveCheckpoint (learner side).  LoadCheckpoint reads the reference's own files.
+// The reference's include paths resolve to this file through include/compat/muzero-cpp/*.h, so tests/mcts_test.cpp of the
+// reference compiles UNMODIFIED with -Iinclude/compat (tests/test_compat.py builds and runs it on the GPU).
 // MCTS::select_child / ucb_score / backpropogate take hand-built MCTSNode records like the reference's and run them through the
 // device step (mzb_debug_*): the arithmetic under test is the tree kernel's, not a host copy.
 #pragma once
@@ -29,6 +30,8 @@
 #include <cstring>
 #include <functional>
 #include <limits>
+#include <numeric>
+#include <random>
 #include <string>
 
 #include "mzb200_facade.hpp"
@@ -441,7 +444,39 @@ private:
     BatchPoint initial_, recurrent_;
 };
 
+namespace util {
+// util.cpp:28-43: N draws of Gamma(alpha, 1) from the caller's generator, normalised.  The arithmetic is libstdc++'s
+// std::gamma_distribution, as in the reference — the engine's own root noise (engine_search.cu) draws the same way on the tree
+// slot's generator state.
+inline std::vector<double> sample_dirichlet(double alpha, int num_samples, std::mt19937& rng) {
+    std::vector<double> samples;
+    samples.reserve(num_samples);
+    std::gamma_distribution<double> gamma_dist(alpha, 1.0);
+    for (int i = 0; i < num_samples; ++i) samples.push_back(gamma_dist(rng));
+    const double sum = std::reduce(samples.begin(), samples.end());
+    for (double& x : samples) x /= sum;
+    return samples;
+}
+}  // namespace util
+
 namespace algorithm {
+
+// mcts.h:79-112 (mcts.cpp:205-220): the running min/max a search normalises Q values with.  Inside MCTS::run the statistics live
+// in the tree slot on the device (tree.cu: updated by the backup half, read by pUCT); this is the same record for callers that
+// hold one themselves, as tests/mcts_test.cpp:156-188 does.
+class MinMaxStats {
+public:
+    MinMaxStats(double minimum, double maximum) : init_minimum_(minimum), init_maximum_(maximum), minimum_(minimum), maximum_(maximum) {}
+    MinMaxStats() : MinMaxStats(types::INF_D, types::NINF_D) {}
+    void reset() { maximum_ = init_maximum_; minimum_ = init_minimum_; }
+    void update(double value) { maximum_ = std::max(maximum_, value); minimum_ = std::min(minimum_, value); }
+    double normalize(double value) const { return (maximum_ > minimum_) ? (value - minimum_) / (maximum_ - minimum_) : value; }
+    double minimum() const { return minimum_; }
+    double maximum() const { return maximum_; }
+
+private:
+    double init_minimum_, init_maximum_, minimum_, maximum_;
+};
 
 // mcts.h:19-75 as a HOST record: what a caller (tests/mcts_test.cpp) assembles by hand and passes to the three public helpers
 // of MCTS below.  The search itself never builds these — its trees are structure-of-arrays pools in HBM — so only the
@@ -461,7 +496,27 @@ struct MCTSNode {
     void expand(const std::vector<types::Action>& actions, types::Player player, double r, const std::vector<double>& policy_probs,
                 const types::Observation& state) {                                      // mcts.cpp:157-167
         to_play = player; reward = r; encoded_state = state;
+        children.reserve(actions.size());
         for (types::Action a : actions) children.emplace_back(a, policy_probs[a]);
+    }
+    // mcts.cpp:170-176 on the caller's generator (inside MCTS::run: tree_root_kernel mixes the host-drawn noise in)
+    void add_exploration_noise(double dirichlet_alpha, double dirichlet_epsilon, std::mt19937& rng) {
+        const std::vector<double> noise = util::sample_dirichlet(dirichlet_alpha, (int)children.size(), rng);
+        for (size_t i = 0; i < children.size(); ++i) children[i].prior = children[i].prior * (1 - dirichlet_epsilon) + (noise[i] * dirichlet_epsilon);
+    }
+    // mcts.cpp:179-200 (inside MCTS::run: tree_stats_kernel)
+    void get_search_statistics(const std::vector<types::Action>& action_space, std::vector<types::Action>& child_actions,
+                               std::vector<double>& children_relative_visit, std::vector<double>& emperical_policy) const {
+        int sum_visits = 0;
+        emperical_policy = std::vector<double>(action_space.size(), 0);
+        for (const MCTSNode& c : children) {
+            child_actions.push_back(c.action);
+            children_relative_visit.push_back(c.visit_count);
+            emperical_policy[c.action] = c.visit_count;
+            sum_visits += c.visit_count;
+        }
+        for (double& v : children_relative_visit) v /= sum_visits;
+        for (double& v : emperical_policy) v /= sum_visits;
     }
 };
 
@@ -501,8 +556,7 @@ public:
                           types::Player to_play, bool add_exploration_noise) {
         if (device_search_) return device_search_->run(stacked_observation, legal_actions, to_play, add_exploration_noise);
         const int A = num_actions_;
-        uint32_t mask = 0;
-        for (types::Action a : legal_actions) mask |= 1u << a;
+        const uint32_t mask = mzb200::legal_mask_of(legal_actions, A);
         const int32_t tp = to_play;
         const uint8_t noise = add_exploration_noise ? 1 : 0;
         // the engine's row is initial_flat_size floats; a test evaluator may be handed any observation, so pad / trim a copy
@@ -733,7 +787,7 @@ public:
             std::vector<uint8_t> noise(m, is_evaluator ? 0 : 1);
             std::vector<double> root(m), rel((size_t)m * A_), pol((size_t)m * A_), temps(m, temperature);
             for (int k = 0; k < m; ++k) {
-                for (types::Action a : hist[srch[k]].legal_actions.back()) mask[k] |= 1u << a;
+                mask[k] = mzb200::legal_mask_of(hist[srch[k]].legal_actions.back(), A_);
                 to_play[k] = games_[srch[k]]->to_play();
             }
             mzb_search_result out{};
@@ -843,9 +897,7 @@ public:
                 live.push_back((int32_t)r);
                 led_by.push_back(h.action_history[i]);
                 frames.insert(frames.end(), h.observation_history[i].begin(), h.observation_history[i].end());
-                uint32_t m = 0;
-                for (types::Action a : h.legal_actions[i]) m |= 1u << a;
-                mask.push_back(m);
+                mask.push_back(mzb200::legal_mask_of(h.legal_actions[i], A_));
                 to_play.push_back(h.to_play_history[i]);
             }
             const int m = (int)live.size();

@@ -54,6 +54,32 @@ inline void check(int rc, const char* what) {
 #endif
 }
 
+inline void fail(const std::string& msg) {
+#ifdef MZB200_FACADE_THROW
+    throw std::runtime_error(msg);
+#else
+    std::fprintf(stderr, "mzb200: %s\n", msg.c_str());
+    std::abort();
+#endif
+}
+
+// legal_actions -> the engine's bit mask.  The engine creates the root's children in ascending action order; the reference
+// creates them in the order of the caller's vector (mcts.cpp:163-166), and that order feeds std::shuffle and the first-strict-
+// maximum tie rule.  The two agree exactly when the vector is strictly ascending — what every AbstractGame::legal_actions() of
+// the reference returns (connect4.h, tictactoe.h, the ALE wrapper) — so anything else is refused instead of silently searched
+// in another order; out-of-range actions would shift by a negative or too large amount.
+inline uint32_t legal_mask_of(const std::vector<Action>& legal_actions, int num_actions) {
+    uint32_t mask = 0;
+    Action prev = -1;
+    for (Action a : legal_actions) {
+        if (a < 0 || a >= num_actions || a >= 32) fail("legal action " + std::to_string(a) + " outside the action space [0, " + std::to_string(num_actions) + ")");
+        if (a <= prev) fail("legal_actions must be strictly ascending (the engine expands the root's children in action order)");
+        prev = a;
+        mask |= 1u << a;
+    }
+    return mask;
+}
+
 // One engine = one GPU = one resident model + max_trees tree slots (replaces VPRNetModel + DeviceManager + the MCTS
 // objects' storage for that device).
 class Engine {
@@ -130,7 +156,9 @@ private:
 class Cohort {
 public:
     Cohort(std::shared_ptr<Engine> engine, std::chrono::microseconds deadline = std::chrono::microseconds(1000))
-        : eng_(std::move(engine)), deadline_(deadline), used_(eng_->config().max_trees, 0) {}
+        : eng_(std::move(engine)), deadline_(deadline), used_(eng_->config().max_trees, 0) {
+        width_ = eng_->config().evaluator == MZB_EVAL_SYNTHETIC ? 1 : (size_t)eng_->shapes().initial_flat_size;
+    }
 
     std::shared_ptr<Engine> engine() const { return eng_; }
 
@@ -157,7 +185,10 @@ public:
     MCTSReturn search(int slot, const Observation& obs, const std::vector<Action>& legal_actions, Player to_play, bool add_noise) {
         Request rq;
         rq.slot = slot; rq.obs = &obs; rq.to_play = to_play; rq.noise = add_noise ? 1 : 0;
-        for (Action a : legal_actions) rq.mask |= 1u << a;
+        // the reference hands the observation to a torch tensor of the network's input shape and fails there on a wrong size
+        // (vprnet.cpp:84-90); here it would be read or written past its end, so it is checked before it is queued
+        if (obs.size() != width_) fail("MCTS::run: observation has " + std::to_string(obs.size()) + " values, the network input has " + std::to_string(width_));
+        rq.mask = legal_mask_of(legal_actions, eng_->config().num_actions);
         std::unique_lock<std::mutex> lk(mu_);
         cv_.wait(lk, [&] { return !running_; });        // a search is in flight: join the next cohort
         if (pending_.empty()) first_arrival_ = std::chrono::steady_clock::now();
@@ -189,7 +220,7 @@ private:
         running_ = true;
         lk.unlock();
         const int n = (int)batch.size(), A = eng_->config().num_actions;
-        const size_t width = batch[0]->obs->size();
+        const size_t width = width_;   // every queued observation has exactly this size (checked in search())
         std::vector<float> obs((size_t)n * width);
         std::vector<int32_t> slots(n), to_play(n), n_children(n), depth(n), actions((size_t)n * A);
         std::vector<uint32_t> masks(n);
@@ -223,6 +254,7 @@ private:
 
     std::shared_ptr<Engine> eng_;
     std::chrono::microseconds deadline_;
+    size_t width_ = 0;
     std::mutex mu_;
     std::condition_variable cv_;
     std::vector<char> used_;

@@ -74,7 +74,7 @@ struct mzb_engine {
     void* h_pin = nullptr;
     size_t h_pin_bytes = 0;
     // compat-path scratch
-    DevBuf c_hidden_in, c_hidden_out, c_action;
+    DevBuf c_hidden_in, c_hidden_out, c_action, bench_slots;
     mzb_search_timing timing;
     // device-resident observation history + actor generators (selfplay.cu)
     std::unique_ptr<mzb::ObsRing, ObsRingDeleter> ring;

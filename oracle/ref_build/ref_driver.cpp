@@ -441,19 +441,26 @@ static int mode_replay(const Args& a) {
 // The reference's own path: actor threads each own an MCTS (self_play.cpp:228-238) sharing one
 // VPRNetEvaluator (vprnet_evaluator.cpp:25-178) over a DeviceManager of libtorch-CPU VPRNetModels
 // (muzero.cpp:60-63,161-163) — i.e. --devices=cpu,cpu semantics.
-static int mode_bench(const Args& a) {
-    MuZeroConfig c = make_config(a);
-    int actors = a.i("actors", 4), moves = a.i("moves", 2), devices = a.i("devices", 2), seed = a.i("seed", 0);
-    int batch = a.i("batch", actors), eval_threads = a.i("eval_threads", 1);
-    if (a.has("torch_threads")) torch::set_num_threads(a.i("torch_threads", 1));
-    torch::manual_seed(seed);
+static std::vector<int> int_list(const std::string& s) {
+    std::vector<int> v;
+    size_t at = 0;
+    while (at < s.size()) {
+        size_t c = s.find(',', at);
+        if (c == std::string::npos) c = s.size();
+        if (c > at) v.push_back(std::stoi(s.substr(at, c - at)));
+        at = c + 1;
+    }
+    return v;
+}
+
+// One (actors, evaluator threads) arrangement: fresh DeviceManager + VPRNetEvaluator, `warmup` untimed and `steps` timed
+// steps of `moves` searches per actor thread.  Returns the seconds of every timed step.
+static std::vector<double> bench_combo(const MuZeroConfig& c, int actors, int eval_threads, int devices, int seed, int flat,
+                                       int moves, int warmup, int steps) {
     DeviceManager dm;
     for (int d = 0; d < devices; ++d) dm.AddDevice(VPRNetModel(c, "cpu"));
-    auto ev = std::make_shared<VPRNetEvaluator>(&dm, batch, eval_threads, batch, eval_threads);
-    model::MuzeroNetwork probe(c);
-    int flat = probe->get_initial_inference_channels() * c.observation_shape.h * c.observation_shape.w;
+    auto ev = std::make_shared<VPRNetEvaluator>(&dm, actors, eval_threads, actors, eval_threads);   // evaluator batch = actors (README.md:87)
     std::vector<Action> legal = c.action_space;
-    std::atomic<long> sims{0};
     auto body = [&](int id, int nmoves) {
         algorithm::MCTS mcts(c, seed + id, ev);
         std::mt19937 rng(seed + id);
@@ -463,26 +470,56 @@ static int mode_bench(const Args& a) {
             for (auto& x : obs) x = u(rng);
             MCTSReturn r = mcts.run(obs, legal, m % c.num_players, true);
             (void)r;
-            sims += c.num_simulations;
         }
     };
-    {   // warm-up (one move per actor), untimed
+    std::vector<double> secs;
+    for (int s = 0; s < warmup + steps; ++s) {
+        auto t0 = std::chrono::steady_clock::now();
         std::vector<std::thread> th;
-        for (int i = 0; i < actors; ++i) th.emplace_back(body, i, 1);
+        for (int i = 0; i < actors; ++i) th.emplace_back(body, i, s < warmup ? 1 : moves);
         for (auto& t : th) t.join();
+        if (s >= warmup) secs.push_back(std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
     }
-    sims = 0;
-    auto t0 = std::chrono::steady_clock::now();
-    {
-        std::vector<std::thread> th;
-        for (int i = 0; i < actors; ++i) th.emplace_back(body, i, moves);
-        for (auto& t : th) t.join();
+    return secs;
+}
+
+static int mode_bench(const Args& a) {
+    MuZeroConfig c = make_config(a);
+    int moves = a.i("moves", 2), devices = a.i("devices", 2), seed = a.i("seed", 0);
+    int steps = a.i("steps", 1), warmup = a.i("warmup", 1);
+    std::vector<int> actor_list = int_list(a.str("actors", "4")), et_list = int_list(a.str("eval_threads", "1"));
+    if (a.has("torch_threads")) torch::set_num_threads(a.i("torch_threads", 1));
+    torch::manual_seed(seed);
+    model::MuzeroNetwork probe(c);
+    int flat = probe->get_initial_inference_channels() * c.observation_shape.h * c.observation_shape.w;
+    // sweep (actors in {4, cores} with evaluator batch = actors; here also 1 or 2 evaluator threads): one short
+    // timed step per arrangement, the best one then runs the requested steps
+    int best_actors = actor_list[0], best_et = et_list[0];
+    double best_rate = -1;
+    std::string sweep = "[";
+    if (actor_list.size() * et_list.size() > 1) {
+        for (int ac : actor_list)
+            for (int et : et_list) {
+                std::vector<double> s = bench_combo(c, ac, et, devices, seed, flat, 1, 1, 1);
+                double rate = (double)ac * c.num_simulations / s[0];
+                char buf[160];
+                snprintf(buf, sizeof buf, "%s{\"actors\": %d, \"eval_threads\": %d, \"sims_per_s\": %.3f}", sweep.size() > 1 ? ", " : "", ac, et, rate);
+                sweep += buf;
+                if (rate > best_rate) { best_rate = rate; best_actors = ac; best_et = et; }
+            }
     }
-    double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    sweep += "]";
+    std::vector<double> secs = bench_combo(c, best_actors, best_et, devices, seed, flat, moves, warmup, steps);
+    double total = 0;
+    for (double x : secs) total += x;
+    long sims = (long)best_actors * moves * c.num_simulations * steps;
     printf("{\"mode\": \"bench\", \"game\": \"%s\", \"sims\": %ld, \"seconds\": %.6f, \"sims_per_s\": %.3f, \"actors\": %d, "
-           "\"batch\": %d, \"devices\": %d, \"torch_threads\": %d, \"hw_threads\": %u}\n",
-           a.str("game", "c4d").c_str(), sims.load(), sec, sims.load() / sec, actors, batch, devices,
-           torch::get_num_threads(), std::thread::hardware_concurrency());
+           "\"batch\": %d, \"eval_threads\": %d, \"devices\": %d, \"moves\": %d, \"steps\": %d, \"warmup\": %d, \"torch_threads\": %d, \"hw_threads\": %u, "
+           "\"sweep\": %s, \"step_seconds\": [",
+           a.str("game", "c4d").c_str(), sims, total, sims / total, best_actors, best_actors, best_et, devices, moves, steps, warmup,
+           torch::get_num_threads(), std::thread::hardware_concurrency(), sweep.c_str());
+    for (size_t i = 0; i < secs.size(); ++i) printf("%s%.6f", i ? ", " : "", secs[i]);
+    printf("]}\n");
     return 0;
 }
 

@@ -37,3 +37,38 @@ def test_reference_names_on_the_gpu():
     _build()
     out = subprocess.run([BIN, GOLDEN], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "compat_test: ok" in out.stdout, out.stdout + out.stderr
+
+
+# ---------------------------------------------------------------- the reference's OWN unit test, unmodified
+REF_TEST = "/root/reference/tests/mcts_test.cpp"
+REF_BIN = os.path.join(ROOT, "tests", "cpp", "ref_mcts_test")
+
+
+def build_reference_mcts_test():
+    """g++ of /root/reference/tests/mcts_test.cpp AS IT IS against include/compat (the reference's include paths forwarded to
+    muzero_cpp_mzb200.hpp) and libmzb200.so.  The source only exists in the build container; the binary travels to the GPU box."""
+    lib = os.path.join(ROOT, "muzero-cpp_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "include", "compat"), "-idirafter", "/root/reference",
+                           "-o", REF_BIN, REF_TEST, "-L", lib, "-lmzb200", "-Wl,-rpath," + lib, "-lpthread"])
+
+
+@pytest.mark.skipif(not os.path.exists(REF_TEST), reason="the reference tree is only present in the build container")
+def test_reference_mcts_test_compiles_unmodified_against_the_compat_headers():
+    import torch
+    build_reference_mcts_test()
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu test")
+    out = subprocess.run([REF_BIN], capture_output=True, text=True, timeout=120)
+    assert out.returncode != 0 and "mzb_engine_create" in out.stdout + out.stderr   # no CPU path: fails loudly at the first MCTS object
+
+
+@pytest.mark.gpu
+def test_reference_mcts_test_runs_green_on_the_gpu():
+    """tests/mcts_test.cpp of the reference (backpropogate for 2 and 1 players, select_child incl. the seeded all-tie pick,
+    ucb_score = 2.401782, MinMaxStats, MCTSNode + add_exploration_noise): exit code 0 = every REQUIRE held."""
+    if os.path.exists(REF_TEST):
+        build_reference_mcts_test()
+    if not os.path.exists(REF_BIN):
+        pytest.skip("tests/cpp/ref_mcts_test is built where /root/reference exists (build()); not in this checkout")
+    out = subprocess.run([REF_BIN], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr

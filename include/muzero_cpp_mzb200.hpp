@@ -10,7 +10,8 @@
 //   types::* (types.h:18-78)                                 muzero_cpp::types::* (aliases, ObservationShape, StepReturn, MCTSReturn)
 //   muzero_config::MuZeroConfig (config.h:15-117)            same fields and defaults (the learner / replay fields are carried, unused)
 //   AbstractGame (abstract_game.h:12-67)                     same eight virtuals
-//   VPRNetModel (vprnet.h:26-140)                            one resident engine per model; batch {Initial,Recurrent}Inference
+//   VPRNetModel (vprnet.h:26-140)                            one resident engine per model; batch {Initial,Recurrent}Inference,
+//                                                             LoadCheckpoint / SaveCheckpoint on the reference's own .pt files
 //   DeviceManager / DeviceLoan (device_manager.h:29-109)     least-outstanding-requests loans over the models
 //   Evaluator, VPRNetEvaluator (vprnet_evaluator.h:35-102)   blocking one-request calls coalesced into engine batches by the
 //                                                             callers themselves (leader/follower; no runner threads or promises)
@@ -28,6 +29,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <filesystem>
 #include <functional>
 #include <limits>
 #include <numeric>
@@ -244,6 +246,19 @@ public:
         mzb200::check(mzb_load_checkpoint(st_->engine->handle(), (path + ".pt").c_str()), "mzb_load_checkpoint");
     }
     void LoadCheckpoint(int step) { LoadCheckpoint(st_->path + "checkpoint-" + std::to_string(step)); }
+    // vprnet.cpp:58-63: writes "<config.path>/checkpoints/checkpoint-<step>.pt" in the format torch::save gives the module (so
+    // that a reference process, --resume or --test can torch::load it) and returns the path without the extension, like the
+    // reference.  What is written: the tensors this model was last loaded with (LoadCheckpoint / LoadWeights).  The
+    // "-optimizer.pt" file is the learner's (Adam state) and is not written here.
+    std::string SaveCheckpoint(int step) {
+        const std::string full_path = st_->path + "checkpoint-" + std::to_string(step);
+        std::error_code ec;
+        std::filesystem::create_directories(st_->path, ec);   // the reference's constructor creates the directory (vprnet.cpp:33)
+        if (ec) detail::fatal("SaveCheckpoint: cannot create " + st_->path + ": " + ec.message());
+        std::lock_guard<std::mutex> call(st_->engine->call_mutex());
+        mzb200::check(mzb_save_checkpoint(st_->engine->handle(), (full_path + ".pt").c_str()), "mzb_save_checkpoint");
+        return full_path;
+    }
     // The same hand-over without a file: the module's named fp32 tensors (a learner in the same process, tests).
     void LoadWeights(const std::vector<mzb_tensor_desc>& tensors) {
         std::lock_guard<std::mutex> call(st_->engine->call_mutex());

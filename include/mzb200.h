@@ -133,6 +133,20 @@ int mzb_checkpoint_count(const mzb_checkpoint* checkpoint);
 int mzb_checkpoint_tensor(const mzb_checkpoint* checkpoint, int index, mzb_tensor_desc* out);
 void mzb_checkpoint_close(mzb_checkpoint* checkpoint);
 int mzb_load_checkpoint(mzb_engine* e, const char* path);
+/* int64 scalars of the archive (BatchNorm num_batches_tracked; eval-mode inference never reads them, a faithful re-save does) */
+int mzb_checkpoint_long_count(const mzb_checkpoint* checkpoint);
+int mzb_checkpoint_long(const mzb_checkpoint* checkpoint, int index, const char** name, int64_t* value);
+
+/* Replaces: the write half, VPRNetModel::SaveCheckpoint(step) = torch::save(model_, "<path>.pt") (vprnet.cpp:58-63; SURVEY §8f
+ * rank 3).  Emits the same module archive natively — ZIP of stored members, protocol-2 pickle of the module tree rebuilt from the
+ * dotted tensor names, one TorchScript class definition per module — so that a reference process (torch::load, vprnet.cpp:71-74)
+ * or `--resume` reads what this engine holds.  mzb_checkpoint_write: any set of named float32 tensors (+ optional int64 scalars
+ * "....num_batches_tracked"; BatchNorm modules without one get 0), no GPU involved.  mzb_save_checkpoint: the tensors the engine
+ * was last loaded with (mzb_load_weights / mzb_load_checkpoint; NOT what a later mzb_broadcast_weights received into the packed
+ * blob).  The file appears atomically (written beside `path`, then renamed).  The optimiser file is the learner's. */
+int mzb_checkpoint_write(const char* path, const mzb_tensor_desc* tensors, int n_tensors, const char* const* long_names,
+                         const int64_t* long_values, int n_longs);
+int mzb_save_checkpoint(mzb_engine* e, const char* path);
 
 /* Replaces: the disk round trip SaveCheckpoint -> LoadCheckpoint of learner.cpp:93-101 / muzero.cpp:142-148.
  * One ncclBroadcast of the packed weight blob from `root` to all ranks.  id = 128-byte ncclUniqueId. */

@@ -250,8 +250,37 @@ int mzb_load_weights(mzb_engine* e, const mzb_tensor_desc* tensors, int n_tensor
         if (rc) return rc;
     }
     e->weights_loaded = true;
+    e->raw_weights.clear();
+    e->raw_longs.clear();
+    for (int i = 0; i < n_tensors; ++i) {
+        mzb_engine::RawTensor r;
+        r.name = tensors[i].name;
+        r.dims.assign(tensors[i].dims, tensors[i].dims + tensors[i].ndim);
+        size_t numel = 1;
+        for (int64_t d : r.dims) numel *= (size_t)d;
+        r.data.assign(tensors[i].data, tensors[i].data + numel);
+        e->raw_weights.push_back(std::move(r));
+    }
     return MZB_OK;
 }
+
+}  // extern "C" (checkpoint.cpp's view of the engine)
+namespace mzb {
+void engine_set_long_scalars(mzb_engine* e, const std::vector<std::pair<std::string, int64_t>>& longs) { e->raw_longs = longs; }
+int engine_named_tensors(mzb_engine* e, std::vector<mzb_tensor_desc>* tensors, std::vector<const char*>* long_names, std::vector<int64_t>* long_values) {
+    MZB_REQUIRE(e->weights_loaded && !e->raw_weights.empty(), "no weights loaded (mzb_load_weights / mzb_load_checkpoint): nothing to save");
+    for (const mzb_engine::RawTensor& r : e->raw_weights) {
+        mzb_tensor_desc d;
+        memset(&d, 0, sizeof(d));
+        d.name = r.name.c_str(); d.data = r.data.data(); d.ndim = (int32_t)r.dims.size();
+        for (size_t k = 0; k < r.dims.size(); ++k) d.dims[k] = r.dims[k];
+        tensors->push_back(d);
+    }
+    for (const auto& kv : e->raw_longs) { long_names->push_back(kv.first.c_str()); long_values->push_back(kv.second); }
+    return MZB_OK;
+}
+}  // namespace mzb
+extern "C" {
 
 int mzb_weights_checksum(mzb_engine* e, uint64_t* out) {
     MZB_REQUIRE(e && out && e->net && e->weights_loaded, "no weights loaded");

@@ -1,6 +1,8 @@
 // engine.h — the engine object behind the C ABI (include/mzb200.h).
 #pragma once
 #include <memory>
+#include <string>
+#include <utility>
 #include <vector>
 
 #include "net_backend.h"
@@ -45,6 +47,10 @@ struct mzb_engine {
     NetPlan plan;
     std::unique_ptr<NetBackend> net;
     bool weights_loaded = false;
+    // what mzb_load_weights / mzb_load_checkpoint last received, un-folded (VPRNetModel::SaveCheckpoint writes these back out)
+    struct RawTensor { std::string name; std::vector<int64_t> dims; std::vector<float> data; };
+    std::vector<RawTensor> raw_weights;
+    std::vector<std::pair<std::string, int64_t>> raw_longs;
     std::vector<float> action_planes;   // owned copy of cfg.action_planes
     static constexpr int MAX_PARTS = 4;
     cudaStream_t stream = nullptr, aux = nullptr;

@@ -163,6 +163,7 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_obs_ring_create", "mzb_obs_ring_reset", "mzb_obs_ring_push", "mzb_obs_ring_stacked", "mzb_search_batch_ring",
            "mzb_actor_seed", "mzb_select_actions", "mzb_actor_uniform_int", "mzb_set_host_evaluator",
            "mzb_checkpoint_open", "mzb_checkpoint_count", "mzb_checkpoint_tensor", "mzb_checkpoint_close", "mzb_load_checkpoint",
+           "mzb_checkpoint_long_count", "mzb_checkpoint_long", "mzb_checkpoint_write", "mzb_save_checkpoint",
            "mzb_debug_se_state", "mzb_debug_tree_write", "mzb_debug_tree_read", "mzb_debug_select_child", "mzb_debug_backpropagate"]
 
 
@@ -215,6 +216,10 @@ def load_library(path=None):
     lib.mzb_checkpoint_close.argtypes = [C.c_void_p]
     lib.mzb_checkpoint_close.restype = None
     lib.mzb_load_checkpoint.argtypes = [C.c_void_p, C.c_char_p]
+    lib.mzb_save_checkpoint.argtypes = [C.c_void_p, C.c_char_p]
+    lib.mzb_checkpoint_write.argtypes = [C.c_char_p, C.POINTER(_CTensorDesc), C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.c_int]
+    lib.mzb_checkpoint_long_count.argtypes = [C.c_void_p]
+    lib.mzb_checkpoint_long.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int64)]
     lib.mzb_set_host_evaluator.argtypes = [C.c_void_p, C.POINTER(_CHostEvaluator)]
     lib.mzb_value_encode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, fp]
     lib.mzb_value_decode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, C.c_int, fp]
@@ -242,6 +247,46 @@ def read_checkpoint(path):
             shape = tuple(int(d.dims[k]) for k in range(d.ndim))
             n = int(np.prod(shape)) if shape else 1
             out[d.name.decode(errors="replace")] = np.ctypeslib.as_array(d.data, (n,)).reshape(shape).copy()
+        return out
+    finally:
+        lib.mzb_checkpoint_close(h)
+
+
+def write_checkpoint(path, tensors: dict, longs: dict = None):
+    """VPRNetModel::SaveCheckpoint's write half (vprnet.cpp:58-63) without an engine: named float32 tensors (+ optional int64
+    scalars such as '...num_batches_tracked') -> the module archive torch::load reads (mzb_checkpoint_write)."""
+    lib = load_library()
+    keep = []
+    descs = (_CTensorDesc * len(tensors))()
+    for i, (name, arr) in enumerate(tensors.items()):
+        a = np.ascontiguousarray(arr, dtype=np.float32)
+        keep.append(a)
+        descs[i].name = name.encode()
+        descs[i].data = _ptr(a, C.c_float)
+        descs[i].ndim = a.ndim
+        for k in range(a.ndim):
+            descs[i].dims[k] = a.shape[k]
+    longs = longs or {}
+    names = (C.c_char_p * max(1, len(longs)))(*[k.encode() for k in longs])
+    values = (C.c_int64 * max(1, len(longs)))(*[int(v) for v in longs.values()])
+    rc = lib.mzb_checkpoint_write(os.fsencode(path), descs, len(tensors), names, values, len(longs))
+    if rc != 0:
+        raise MzbError("mzb200 error %d: %s" % (rc, lib.mzb_last_error().decode()))
+
+
+def read_checkpoint_longs(path):
+    """the int64 scalars of a checkpoint archive (BatchNorm num_batches_tracked) as {name: value}"""
+    lib = load_library()
+    h = C.c_void_p()
+    rc = lib.mzb_checkpoint_open(os.fsencode(path), C.byref(h))
+    if rc != 0:
+        raise MzbError("mzb200 error %d: %s" % (rc, lib.mzb_last_error().decode()))
+    try:
+        out = {}
+        for i in range(lib.mzb_checkpoint_long_count(h)):
+            name = C.c_char_p(); val = C.c_int64()
+            lib.mzb_checkpoint_long(h, i, C.byref(name), C.byref(val))
+            out[name.value.decode()] = val.value
         return out
     finally:
         lib.mzb_checkpoint_close(h)
@@ -413,6 +458,11 @@ class Engine:
     def load_checkpoint(self, path):
         """VPRNetModel::LoadCheckpoint's read half (vprnet.cpp:71-74): the reference's own .pt file, parsed without libtorch"""
         self._check(self.lib.mzb_load_checkpoint(self._h, os.fsencode(path)))
+
+    def save_checkpoint(self, path):
+        """VPRNetModel::SaveCheckpoint's write half (vprnet.cpp:58-63): the tensors this engine was last loaded with, as the
+        reference's own .pt archive"""
+        self._check(self.lib.mzb_save_checkpoint(self._h, os.fsencode(path)))
 
     def weights_checksum(self):
         out = C.c_uint64()

@@ -695,11 +695,33 @@ static void device_manager_policies(const std::string& golden_dir) {
     EXPECT(r.child_actions.size() == 5, "search while learning is malformed");
 }
 
+// (8) VPRNetModel::SaveCheckpoint(step) -> path (vprnet.cpp:58-63) and LoadCheckpoint(step) (vprnet.cpp:66-69) under the
+//     reference's names: what one model saves another loads, and both answer identically
+static void save_and_reload(const std::string& golden_dir) {
+    muzero_config::MuZeroConfig config = tiny_config(2);
+    char tmpl[] = "/tmp/mzb_compat_XXXXXX";
+    const char* dir = mkdtemp(tmpl);
+    EXPECT(dir != nullptr, "mkdtemp failed");
+    if (!dir) return;
+    config.path = dir;
+    VPRNetModel a(config, "cuda:0", MZB_FP32_CHECK);
+    a.LoadCheckpoint(golden_dir + "/checkpoint_tiny");
+    const std::string saved = a.SaveCheckpoint(12);
+    EXPECT(saved == std::string(dir) + "/checkpoints/checkpoint-12", "SaveCheckpoint returned %s", saved.c_str());
+    VPRNetModel b(config, "cuda:0", MZB_FP32_CHECK);
+    b.LoadCheckpoint(12);
+    std::vector<VPRNetModel::InitialInferenceInputs> in(3);
+    for (int i = 0; i < 3; ++i) { in[i].stacked_observation.assign(60, 0.f); for (int k = 0; k < 60; ++k) in[i].stacked_observation[k] = (float)((k * 7 + i * 13) % 11) / 11.f; }
+    auto oa = a.InitialInference(in), ob = b.InitialInference(in);
+    for (int i = 0; i < 3; ++i)
+        EXPECT(oa[i].value == ob[i].value && oa[i].policy == ob[i].policy && oa[i].encoded_state == ob[i].encoded_state, "reloaded model answers differently (sample %d)", i);
+}
+
 int main(int argc, char** argv) {
     try {
         reference_unit_tests();
         appendix_b();
-        if (argc > 1) { network_paths(argv[1]); self_play_cohort(argv[1]); device_manager_policies(argv[1]); }
+        if (argc > 1) { network_paths(argv[1]); self_play_cohort(argv[1]); device_manager_policies(argv[1]); save_and_reload(argv[1]); }
     } catch (const std::exception& e) {
         std::printf("compat_test: %s\n", e.what());
         return 1;

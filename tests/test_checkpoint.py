@@ -73,3 +73,82 @@ def test_engine_loaded_from_the_checkpoint_reproduces_the_reference(golden_dir):
     with pytest.raises(mzb200.MzbError):
         eng.load_checkpoint(os.path.join(golden_dir, "net_tiny.mzbt"))   # not a module archive
     eng.close()
+
+
+# ---------------------------------------------------------------- the writer (VPRNetModel::SaveCheckpoint, vprnet.cpp:58-63)
+def _same_tensors(a, b):
+    assert sorted(a) == sorted(b)
+    for k in a:
+        assert a[k].shape == b[k].shape and np.array_equal(a[k], b[k]), k
+
+
+@pytest.mark.parametrize("src", ["checkpoint_tiny.pt", "checkpoint_c4r_trained.pt"])
+def test_writer_round_trips_through_the_reader_and_through_torch(src, golden_dir, tmp_path):
+    """write what the reader parsed -> (a) the library's reader gives the same tensors back bit for bit, (b) torch.jit.load — the
+    code path torch::load(model_, path) takes in the reference (vprnet.cpp:71-74) — opens the archive and yields the same state,
+    num_batches_tracked included, denormal running_var included"""
+    import torch
+    import mzb200
+    path = os.path.join(golden_dir, src)
+    want = mzb200.read_checkpoint(path)
+    longs = mzb200.read_checkpoint_longs(path)
+    assert longs and all(k.endswith("num_batches_tracked") for k in longs)
+    out = str(tmp_path / "checkpoint-7.pt")
+    mzb200.write_checkpoint(out, want, longs)
+    _same_tensors(mzb200.read_checkpoint(out), want)
+    assert mzb200.read_checkpoint_longs(out) == longs
+    sd = torch.jit.load(out, map_location="cpu").state_dict()
+    ref = torch.jit.load(path, map_location="cpu").state_dict()
+    assert list(sd.keys()) == list(ref.keys())          # same modules, same attribute order as the reference's own file
+    for k in ref:
+        assert sd[k].dtype == ref[k].dtype and torch.equal(sd[k].cpu(), ref[k].cpu()), k
+
+
+def test_writer_supplies_the_modules_tensors_do_not_name(tmp_path, golden_dir):
+    """from float tensors alone: BatchNorm's num_batches_tracked (0) and the MLPs' parameter-less activation modules appear, so
+    that torch::load — which reads every registered child and buffer by name — accepts the file"""
+    import torch
+    import mzb200
+    want = mzb200.read_checkpoint(CKPT)
+    out = str(tmp_path / "bare.pt")
+    mzb200.write_checkpoint(out, want)
+    m = torch.jit.load(out, map_location="cpu")
+    sd = m.state_dict()
+    nbt = [k for k in sd if k.endswith("num_batches_tracked")]
+    assert len(nbt) == len([k for k in want if k.endswith("running_var")]) and all(int(sd[k]) == 0 for k in nbt)
+    names = [n for n, _ in m.named_modules()]
+    assert any(n.endswith("activation_0") for n in names)
+    with pytest.raises(mzb200.MzbError):
+        mzb200.write_checkpoint(str(tmp_path / "no" / "such" / "dir.pt"), want)
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/muzero-cpp"), reason="needs oracle/_ref/ref_driver (build container)")
+def test_reference_loads_what_the_writer_wrote(golden_dir, tmp_path):
+    """the UNMODIFIED reference (torch::load in C++, oracle/_ref/ref_driver net ckpt=...) loads the written archive and reproduces
+    the golden outputs it produced from its own file"""
+    import mzb200
+    if not O.have_ref():
+        pytest.skip("oracle/_ref not built")
+    src = os.path.join(golden_dir, "checkpoint_c4r_trained.pt")
+    out = str(tmp_path / "rewritten.pt")
+    mzb200.write_checkpoint(out, mzb200.read_checkpoint(src), mzb200.read_checkpoint_longs(src))
+    dump = str(tmp_path / "net.mzbt")
+    O.run_ref("net", "game=c4r", "batch=16", "seed=5", "binary_obs=1", "no_weights", "ckpt=" + out, "out=" + dump,
+              "path=" + str(tmp_path / "scratch"))
+    got, want = O.mzbt_load(dump), O.mzbt_load(os.path.join(golden_dir, "net_c4r_trained.mzbt"))
+    for k in want:
+        assert np.array_equal(got[k], want[k]), k
+
+
+@pytest.mark.gpu
+def test_engine_saves_what_it_loaded(golden_dir, tmp_path):
+    import mzb200
+    eng = mzb200.Engine(mzb200.preset("tiny", max_trees=8, precision=mzb200.FP32_CHECK), 0)
+    with pytest.raises(mzb200.MzbError):
+        eng.save_checkpoint(str(tmp_path / "empty.pt"))   # nothing loaded yet
+    eng.load_checkpoint(CKPT)
+    out = str(tmp_path / "checkpoint-3.pt")
+    eng.save_checkpoint(out)
+    _same_tensors(mzb200.read_checkpoint(out), mzb200.read_checkpoint(CKPT))
+    assert mzb200.read_checkpoint_longs(out) == mzb200.read_checkpoint_longs(CKPT)
+    eng.close()

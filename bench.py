@@ -27,7 +27,8 @@ UNIT = "sims/s"
 WORKLOADS = {  # BASELINE.json configs that fit one GPU; configs[1] is the headline
     "c4d": dict(desc="Connect4 example, 50 sims/move, ResNet tower 128ch x 4+4+4 blocks, 1024 concurrent games per GPU", trees=1024),
     "c4r": dict(desc="Connect4, README/shipped tower 64ch x 3 blocks, 50 sims, 1024 concurrent games per GPU", trees=1024),
-    "reanalyze": dict(desc="Connect4 reanalyze: batched re-search of 4096 replay positions per GPU, 50 sims", trees=4096, preset="c4d"),
+    "reanalyze": dict(desc="Connect4 reanalyze: batched re-search of 4096 replay positions per GPU (drawn from 128 stored games, "
+                           "legal sets and to_play from the history, through the observation ring), 50 sims", trees=4096, preset="c4d", ring=True),
     "ale": dict(desc="ALE/Pong-shaped synthetic 96x96 stacked frames, downsample ResNet, 50 sims, 18 actions, 1024 games per GPU", trees=1024),
     "ttt": dict(desc="TicTacToe, 25 sims/move (reference CPU-runnable case)", trees=1024),
 }
@@ -303,11 +304,24 @@ def main():
         A, nsim = cfg.num_actions, cfg.num_simulations
         flat = eng.shapes.initial_flat_size
         rng = np.random.default_rng(rank)
-        obs_host = torch.from_numpy(rng.random((T, flat), dtype=np.float32)).pin_memory()
-        obs_dev = obs_host.cuda()
-        masks = np.full(T, (1 << A) - 1, np.uint32)
-        to_play = (np.arange(T) % cfg.num_players).astype(np.int32)
         noise = np.ones(T, np.uint8)
+        ring = bool(w.get("ring"))
+        if ring:
+            # reanalyze (self_play.cpp:186-225) as BASELINE config 4 defines it: positions of stored games, each with the legal set
+            # and to_play its history recorded, exploration noise on; the frames travel through the device-resident observation ring
+            from mzb200 import positions as P
+            frames, masks, to_play, n_hist = P.sample_positions(T, seed=rank)
+            out["positions"] = "%d positions drawn with replacement from %d stored Connect4 games (tests/golden/selfplay_c4.txt)" % (T, n_hist)
+            slots = np.arange(T, dtype=np.int32)
+            led_by = np.zeros(T, np.int32)
+            eng.ring_create()
+            eng.ring_push(slots, frames, led_by)
+            obs_host = torch.from_numpy(frames).pin_memory()
+        else:
+            obs_host = torch.from_numpy(rng.random((T, flat), dtype=np.float32)).pin_memory()
+            obs_dev = obs_host.cuda()
+            masks = np.full(T, (1 << A) - 1, np.uint32)
+            to_play = (np.arange(T) % cfg.num_players).astype(np.int32)
         split = dict(root_ms=0.0, sim_loop_ms=0.0)   # rank-local split of the device time: root (initial inference + expansion) | simulations
 
         def timed(fn, k):
@@ -329,8 +343,15 @@ def main():
                 dev_ms, wall_ms = float(t[0]), float(t[1])
             return dev_ms, wall_ms, launches
 
-        run_dev = lambda: eng.run(None, masks, to_play, noise, device_obs_ptr=obs_dev.data_ptr())
-        run_host = lambda: eng.run(obs_host.numpy(), masks, to_play, noise)
+        if ring:
+            def run_host():   # one new frame per position from the host, then the ring-fed search
+                eng.ring_reset(slots)
+                eng.ring_push(slots, obs_host.numpy(), led_by)
+                return eng.run_ring(slots, masks, to_play, noise)
+            run_dev = lambda: eng.run_ring(slots, masks, to_play, noise)   # frames already in the ring (HBM)
+        else:
+            run_dev = lambda: eng.run(None, masks, to_play, noise, device_obs_ptr=obs_dev.data_ptr())
+            run_host = lambda: eng.run(obs_host.numpy(), masks, to_play, noise)
         for _ in range(warmup):
             run_dev()
         if steps is None:   # --seconds: derive K from one probe step (all ranks agree on the maximum)

@@ -742,7 +742,11 @@ public:
     // (the reference gives both `config.seed + actor_num`, self_play.cpp:232-233).
     SelfPlayCohort(const muzero_config::MuZeroConfig& config, VPRNetModel& model, std::vector<AbstractGame*> games,
                    const std::vector<int>& search_seeds, const std::vector<int>& actor_seeds)
-        : config_(config), engine_(model.engine()), games_(std::move(games)), A_((int)config.action_space.size()) {
+        : SelfPlayCohort(config, model.engine(), std::move(games), search_seeds, actor_seeds) {}
+    // the same over an engine the caller built itself (e.g. one with a synthetic evaluator, to compare drivers decision for decision)
+    SelfPlayCohort(const muzero_config::MuZeroConfig& config, std::shared_ptr<mzb200::Engine> engine, std::vector<AbstractGame*> games,
+                   const std::vector<int>& search_seeds, const std::vector<int>& actor_seeds)
+        : config_(config), engine_(std::move(engine)), games_(std::move(games)), A_((int)config.action_space.size()) {
         const int n = (int)games_.size();
         if (n < 1 || n > engine_->config().max_trees) detail::fatal("SelfPlayCohort: more games than tree slots (raise num_actors)");
         if ((int)search_seeds.size() != n || (int)actor_seeds.size() != n) detail::fatal("SelfPlayCohort: one seed pair per game");
@@ -875,7 +879,9 @@ private:
 class ReanalyzeCohort {
 public:
     ReanalyzeCohort(const muzero_config::MuZeroConfig& config, VPRNetModel& model, const std::vector<int>& search_seeds)
-        : config_(config), engine_(model.engine()), A_((int)config.action_space.size()), n_((int)search_seeds.size()) {
+        : ReanalyzeCohort(config, model.engine(), search_seeds) {}
+    ReanalyzeCohort(const muzero_config::MuZeroConfig& config, std::shared_ptr<mzb200::Engine> engine, const std::vector<int>& search_seeds)
+        : config_(config), engine_(std::move(engine)), A_((int)config.action_space.size()), n_((int)search_seeds.size()) {
         if (n_ < 1 || n_ > engine_->config().max_trees) detail::fatal("ReanalyzeCohort: more histories than tree slots");
         std::vector<float> planes;
         if (config.action_representation_initial)

@@ -34,9 +34,12 @@ typedef enum {
     MZB_EVAL_NETWORK = 0,   /* the VPRNet towers (vprnet.cpp / models.cpp / model_layers.cpp) */
     MZB_EVAL_SYNTHETIC = 1, /* deterministic hash evaluator "SE": pins the tree kernels bit-exactly and measures them
                                alone (the stub still moves one hidden state parent->child per simulation) */
-    MZB_EVAL_HOST = 2       /* a caller-supplied Evaluator subclass (e.g. tests/mcts_test.cpp:16-27 TestEvaluator): the tree
+    MZB_EVAL_HOST = 2,      /* a caller-supplied Evaluator subclass (e.g. tests/mcts_test.cpp:16-27 TestEvaluator): the tree
                                kernels run on the GPU, the two inference calls go to host callbacks once per cohort and
                                simulation (mzb_set_host_evaluator).  Compatibility / test path, not a throughput path. */
+    MZB_EVAL_SYNTHETIC_OBS = 3 /* "SE" keyed by a hash of the WHOLE stacked observation (rows of initial_flat_size floats, like
+                               the network's): lets real games — play_game / reanalyze over AbstractGame, the observation ring —
+                               be compared decision for decision with the reference driven by the same evaluator */
 } mzb_evaluator;
 
 /* POD mirror of muzero_config::MuZeroConfig + MuZeroNetworkConfig (muzero-cpp/config.h:15-117), restricted to the

@@ -158,7 +158,7 @@ int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out) {
         // i + 1 gets its few blocks onto the SMs between the mover's thousands of copy CTAs instead of queueing behind them
         int lowest = 0, greatest = 0;
         MZB_CUDA(cudaDeviceGetStreamPriorityRange(&lowest, &greatest));
-        MZB_CUDA(cudaStreamCreateWithPriority(&e->stream, cudaStreamNonBlocking, e->cfg.evaluator == MZB_EVAL_SYNTHETIC ? greatest : lowest));
+        MZB_CUDA(cudaStreamCreateWithPriority(&e->stream, cudaStreamNonBlocking, is_synthetic(e->cfg.evaluator) ? greatest : lowest));
     }
     MZB_CUDA(cudaStreamCreateWithFlags(&e->aux, cudaStreamNonBlocking));
     for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) MZB_CUDA(cudaStreamCreateWithFlags(&e->pipe[i], cudaStreamNonBlocking));
@@ -171,7 +171,7 @@ int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out) {
     rc = alloc_trees(e.get());
     if (rc) return rc;
     const int T = e->cfg.max_trees, n = e->cfg.num_simulations;
-    if (e->cfg.evaluator == MZB_EVAL_SYNTHETIC) {
+    if (is_synthetic(e->cfg.evaluator)) {
         e->se.slot_floats = e->dims.hidden_size();
         e->se.vlo = e->cfg.se_value_lo; e->se.vhi = e->cfg.se_value_hi;
         e->se.rlo = e->cfg.se_reward_lo; e->se.rhi = e->cfg.se_reward_hi;
@@ -185,7 +185,7 @@ int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out) {
             MZB_CUDA(cudaEventCreateWithFlags(&e->ev_se_out[k], cudaEventDisableTiming));
             MZB_CUDA(cudaEventCreateWithFlags(&e->ev_se_mv[k], cudaEventDisableTiming));
         }
-        MZB_CUDA(e->d_obs.alloc((size_t)T * sizeof(float)));
+        MZB_CUDA(e->d_obs.alloc((size_t)T * (e->cfg.evaluator == MZB_EVAL_SYNTHETIC_OBS ? e->dims.initial_flat() : 1) * sizeof(float)));
     } else if (e->cfg.evaluator == MZB_EVAL_HOST) {
         MZB_CUDA(e->d_obs.alloc((size_t)T * e->dims.initial_flat() * sizeof(float)));
     } else {
@@ -426,7 +426,7 @@ int mzb_debug_backpropagate(mzb_engine* e, int slot, const int32_t* path, int le
 int mzb_debug_se_state(mzb_engine* e, int tree, int node, float* out) {
     int rc = debug_slot_check(e, tree);
     if (rc) return rc;
-    MZB_REQUIRE(e->cfg.evaluator == MZB_EVAL_SYNTHETIC && e->se.pool, "engine was not created with the synthetic evaluator");
+    MZB_REQUIRE(is_synthetic(e->cfg.evaluator) && e->se.pool, "engine was not created with the synthetic evaluator");
     MZB_REQUIRE(out && node >= 0 && node <= e->cfg.num_simulations, "node %d outside [0, num_simulations]", node);
     MZB_CUDA(cudaStreamSynchronize(e->stream));
     const size_t slot = (size_t)tree * (e->cfg.num_simulations + 1) + node;

@@ -39,6 +39,8 @@ using namespace mzb;
 namespace mzb { struct ObsRing; void obs_ring_free(ObsRing*); }
 struct ObsRingDeleter { void operator()(mzb::ObsRing* r) const { mzb::obs_ring_free(r); } };
 
+inline bool is_synthetic(int evaluator) { return evaluator == MZB_EVAL_SYNTHETIC || evaluator == MZB_EVAL_SYNTHETIC_OBS; }
+
 struct mzb_engine {
     mzb_config cfg;
     int device = 0;

@@ -34,7 +34,7 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
     const mzb_config& c = e->cfg;
     const int A = c.num_actions, n = c.num_simulations;
     TreeDev& td = e->td;
-    const bool synthetic = c.evaluator == MZB_EVAL_SYNTHETIC;
+    const bool synthetic = is_synthetic(c.evaluator);
     const bool host = c.evaluator == MZB_EVAL_HOST;
     const uint32_t full = (A >= 32) ? 0xffffffffu : ((1u << A) - 1u);
     bool any_noise = false;

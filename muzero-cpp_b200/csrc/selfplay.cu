@@ -99,7 +99,8 @@ extern "C" {
 
 int mzb_obs_ring_create(mzb_engine* e, const float* action_planes_initial) {
     MZB_REQUIRE(e, "null argument");
-    MZB_REQUIRE(e->cfg.evaluator == MZB_EVAL_NETWORK, "the observation ring feeds the network evaluator");
+    MZB_REQUIRE(e->cfg.evaluator == MZB_EVAL_NETWORK || e->cfg.evaluator == MZB_EVAL_SYNTHETIC_OBS,
+                "the observation ring feeds evaluators that take whole observation rows (NETWORK, SYNTHETIC_OBS)");
     MZB_CUDA(cudaSetDevice(e->device));
     const mzb_config& c = e->cfg;
     std::unique_ptr<ObsRing, ObsRingDeleter> r(new ObsRing());

@@ -367,7 +367,15 @@ __global__ void se_initial_kernel(TreeDev td, SEDev se, int n_trees, const float
     const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (t >= n_trees) return;
-    const uint32_t key = (uint32_t)obs[(long)t * obs_stride];
+    uint32_t key;
+    if (obs_stride == 1) {
+        key = (uint32_t)obs[t];
+    } else {   // MZB_EVAL_SYNTHETIC_OBS: hash of the whole row (oracle/se_evaluator.h se_obs_key; a sum, so the order does not matter)
+        const float* row = obs + (long)t * obs_stride;
+        key = 0;
+        for (int i = lane; i < obs_stride; i += 32) key += se_mix(__float_as_uint(row[i]) + 0x9e3779b9U * (uint32_t)(i + 1));
+        for (int off = 16; off > 0; off >>= 1) key += __shfl_xor_sync(FULL, key, off);
+    }
     const uint32_t cid = se_mix(key ^ 0x9e3779b9U) & 0xFFFFFFU;
     if (lane == 0) se.node_cid[(long)t * (td.n_sims + 1)] = cid;
     se_outputs(td, se, t, cid, lane);
@@ -462,11 +470,9 @@ void launch_se_recurrent(const TreeDev& td, const SEDev& se, int n_trees, cudaSt
 bool se_move_available(int slot_floats) { return slot_floats % 4 == 0 && (size_t)slot_floats * 4 <= 200 * 1024; }
 void launch_se_move(const SEDev& se, int n_trees, cudaStream_t s) {
     const size_t bytes = (size_t)se.slot_floats * 4;
-    static bool attr_set = false;   // states above the 48 KB default need the opt-in (ALE: 18 KB, C4d: 21.5 KB do not)
-    if (!attr_set && bytes > 48 * 1024) {
-        cudaFuncSetAttribute(se_move_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
-    }
+    // states above the 48 KB default need the opt-in (ALE: 18 KB, C4d: 21.5 KB do not).  The attribute is per DEVICE (a
+    // DeviceManager may hold engines on several), so it is set on every such launch for the current one: a host-side store.
+    if (bytes > 48 * 1024) cudaFuncSetAttribute(se_move_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     se_move_kernel<<<n_trees, 32, bytes, s>>>(se, n_trees);
 }
 void launch_mt_move(uint32_t* d_mt_home, int* d_idx_home, uint32_t* d_mt_rows, int* d_idx_rows, const int* d_slots, int n,

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "libmzb200.so")
 MAX_ACTIONS = 32
 MAX_HEAD_LAYERS = 8
 FP32_CHECK, BF16 = 0, 1
-EVAL_NETWORK, EVAL_SYNTHETIC, EVAL_HOST = 0, 1, 2
+EVAL_NETWORK, EVAL_SYNTHETIC, EVAL_HOST, EVAL_SYNTHETIC_OBS = 0, 1, 2, 3
 INF_D = float(np.finfo(np.float64).max)    # types::INF_D  (types.h:78)
 NINF_D = -float(np.finfo(np.float64).max)  # types::NINF_D (types.h:77)
 

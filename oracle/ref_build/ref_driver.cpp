@@ -339,6 +339,15 @@ static int mode_net(const Args& a) {
     int flat = cin * c.observation_shape.h * c.observation_shape.w;
     torch::Tensor obs = torch::rand({B, flat});
     if (a.i("binary_obs", 0)) obs = (obs < 0.3).to(torch::kFloat);
+    if (a.has("obs_in")) {   // observations given by the caller (real game positions): MZBT file with a float tensor "in.obs" [B, flat]
+        std::vector<mzbt::Tensor> ts;
+        if (!mzbt::load(a.str("obs_in", ""), ts)) { std::cerr << "cannot read obs_in" << std::endl; return 1; }
+        const mzbt::Tensor* given = nullptr;
+        for (auto& t : ts) if (t.name == "in.obs") given = &t;
+        if (!given || given->dims.size() != 2 || given->dims[1] != flat) { std::cerr << "obs_in: no in.obs of width " << flat << std::endl; return 1; }
+        B = (int)given->dims[0];
+        obs = torch::from_blob((void*)given->as<float>(), {B, flat}, torch::kFloat).clone();
+    }
     std::vector<VPRNetModel::InitialInferenceInputs> in0(B);
     for (int b = 0; b < B; ++b) in0[b].stacked_observation = Observation(obs[b].data_ptr<float>(), obs[b].data_ptr<float>() + flat);
     auto o0 = vm.InitialInference(in0);

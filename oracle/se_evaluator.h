@@ -22,6 +22,17 @@ static inline uint32_t se_mix(uint32_t x) {
     x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
     return x;
 }
+/* key of a whole observation row (MZB_EVAL_SYNTHETIC_OBS): order-independent sum of per-position hashes of the float bit
+ * patterns, so that a warp can form it with a shuffle reduction and the host with a plain loop */
+static inline uint32_t se_obs_key(const float* obs, int n) {
+    uint32_t key = 0;
+    for (int i = 0; i < n; ++i) {
+        union { float f; uint32_t u; } b;
+        b.f = obs[i];
+        key += se_mix(b.u + 0x9e3779b9U * (uint32_t)(i + 1));
+    }
+    return key;
+}
 static inline uint32_t se_initial_cid(uint32_t key) { return se_mix(key ^ 0x9e3779b9U) & 0xFFFFFFU; }
 static inline uint32_t se_child_cid(uint32_t cid, uint32_t action) {
     return se_mix(cid * 31U + action + 0x85ebca6bU) & 0xFFFFFFU;

@@ -53,12 +53,17 @@ def main():
               "ckpt_out=" + os.path.join(HERE, "checkpoint_tiny.pt"))
     O.run_ref("net", "game=tinyds", "batch=2", "seed=4", "out=" + os.path.join(HERE, "net_tinyds.mzbt"))
     # TRAINED weights: the Connect4 checkpoint the reference ships (README.md:171,194), kept byte for byte as a data fixture;
-    # the expected outputs are the unmodified reference's on 16 Bernoulli(0.3) board-like inputs (weights stay in the .pt)
+    # the expected outputs are the unmodified reference's on 32 real Connect4 positions (weights stay in the .pt)
     shipped = "/root/reference/examples/connect4/reanalyze-00/checkpoints/checkpoint--1.pt"
     trained = os.path.join(HERE, "checkpoint_c4r_trained.pt")
     with open(shipped, "rb") as src, open(trained, "wb") as dst:
         dst.write(src.read())
-    O.run_ref("net", "game=c4r", "batch=16", "seed=5", "binary_obs=1", "no_weights", "ckpt=" + trained,
+    # inputs: 32 REAL Connect4 positions of the stored games (selfplay_c4.txt; make_golden_selfplay.py writes it first)
+    sys.path.insert(0, os.path.join(ROOT, "muzero-cpp_b200"))
+    from mzb200 import positions as P
+    obs, _, _, _ = P.sample_positions(32, seed=3)
+    O.mzbt_save("/tmp/mzb_c4_positions.mzbt", {"in.obs": obs})
+    O.run_ref("net", "game=c4r", "seed=5", "no_weights", "ckpt=" + trained, "obs_in=/tmp/mzb_c4_positions.mzbt",
               "out=" + os.path.join(HERE, "net_c4r_trained.mzbt"))
     enc = []
     for lo, hi, extra in [(-10, 10, []), (-22, 22, []), (-1, 1, []), (-21, 21, []), (-300, 300, []), (-5, 7, ["no_contractive"])]:

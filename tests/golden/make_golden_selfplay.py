@@ -1,6 +1,6 @@
 """Regenerate the self-play helper fixtures from the reference build (oracle/_ref/ref_driver, modes `stack` and `select`).
 Run in the build container only:   make -C oracle/ref_build && python tests/golden/make_golden_selfplay.py
-Outputs (committed): selfplay_stack.txt (GameHistory::get_stacked_observations, types.cpp:16-42, on synthetic games) and
+Outputs (committed): selfplay_c4.txt (whole games through the unmodified play_game / reanalyze, see main_c4), selfplay_stack.txt (GameHistory::get_stacked_observations, types.cpp:16-42, on synthetic games) and
 selfplay_select.txt (the self_play.cpp:21-39 selection rule over libstdc++'s std::discrete_distribution / std::mt19937)."""
 import os
 import subprocess
@@ -20,7 +20,17 @@ def run(mode, kw):
     return subprocess.run([DRV, mode] + ["%s=%s" % kv for kv in kw.items()], check=True, capture_output=True, text=True).stdout
 
 
+def main_c4():
+    """tests/golden/selfplay_c4.txt: 128 Connect4 games played by the UNMODIFIED play_game (self_play.cpp:84-183), each re-searched
+    by the UNMODIFIED reanalyze (self_play.cpp:186-225), plus 16 evaluator games against the Random opponent — all over the
+    observation-keyed synthetic evaluator (oracle/ref_build/ref_selfplay.cpp)."""
+    import subprocess
+    drv = os.path.join(ROOT, "oracle", "_ref", "ref_selfplay")
+    subprocess.check_call([drv, "games=128", "sims=50", "eval_games=16", "out=" + os.path.join(HERE, "selfplay_c4.txt")])
+
+
 if __name__ == "__main__":
+    main_c4()
     with open(os.path.join(HERE, "selfplay_stack.txt"), "w") as f:
         for kw in STACK_CASES:
             f.write(run("stack", kw))

@@ -132,10 +132,12 @@ def test_reference_loads_what_the_writer_wrote(golden_dir, tmp_path):
     src = os.path.join(golden_dir, "checkpoint_c4r_trained.pt")
     out = str(tmp_path / "rewritten.pt")
     mzb200.write_checkpoint(out, mzb200.read_checkpoint(src), mzb200.read_checkpoint_longs(src))
-    dump = str(tmp_path / "net.mzbt")
-    O.run_ref("net", "game=c4r", "batch=16", "seed=5", "binary_obs=1", "no_weights", "ckpt=" + out, "out=" + dump,
+    dump, obs_in = str(tmp_path / "net.mzbt"), str(tmp_path / "obs.mzbt")
+    want = O.mzbt_load(os.path.join(golden_dir, "net_c4r_trained.mzbt"))
+    O.mzbt_save(obs_in, {"in.obs": want["in.obs"]})
+    O.run_ref("net", "game=c4r", "seed=5", "no_weights", "ckpt=" + out, "obs_in=" + obs_in, "out=" + dump,
               "path=" + str(tmp_path / "scratch"))
-    got, want = O.mzbt_load(dump), O.mzbt_load(os.path.join(golden_dir, "net_c4r_trained.mzbt"))
+    got = O.mzbt_load(dump)
     for k in want:
         assert np.array_equal(got[k], want[k]), k
 

@@ -72,3 +72,27 @@ def test_reference_mcts_test_runs_green_on_the_gpu():
         pytest.skip("tests/cpp/ref_mcts_test is built where /root/reference exists (build()); not in this checkout")
     out = subprocess.run([REF_BIN], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
+
+
+# ---------------------------------------------------------------- cohort drivers vs the reference's play_game / reanalyze
+SP_SRC = os.path.join(ROOT, "tests", "cpp", "selfplay_c4_test.cpp")
+SP_BIN = os.path.join(ROOT, "tests", "cpp", "selfplay_c4_test")
+
+
+def _build_selfplay():
+    lib = os.path.join(ROOT, "muzero-cpp_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I", os.path.join(ROOT, "include"), "-o", SP_BIN, SP_SRC,
+                           "-L", lib, "-lmzb200", "-Wl,-rpath," + lib, "-lpthread"])
+
+
+def test_selfplay_driver_test_compiles():
+    _build_selfplay()
+
+
+@pytest.mark.gpu
+def test_cohort_drivers_reproduce_the_reference_self_play_layer():
+    """SelfPlayCohort / ReanalyzeCohort vs tests/golden/selfplay_c4.txt (the unmodified play_game / reanalyze over real Connect4,
+    128 actor games + their reanalysis + 16 evaluator games): identical histories, bit for bit"""
+    _build_selfplay()
+    out = subprocess.run([SP_BIN, GOLDEN], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "selfplay_c4_test: ok" in out.stdout, out.stdout[-3000:] + out.stderr[-2000:]

@@ -63,24 +63,26 @@ def net_errors(g, o, C):
     return out
 
 
-def positions(game, n, rng, binary):
+def positions(game, n, rng, real):
+    """(net config, observation rows, legal masks or None, to_play or None).  real: positions of the stored Connect4 games"""
     ncfg = V.preset(game)
     flat = ncfg.in_channels * ncfg.obs_shape[1] * ncfg.obs_shape[2]
-    obs = rng.random((n, flat), dtype=np.float32)
-    if binary:
-        obs = (obs < 0.3).astype(np.float32)
-    return ncfg, obs
+    if real:
+        from mzb200 import positions as P
+        obs, masks, to_play, _ = P.sample_positions(n, seed=int(rng.integers(0, 1 << 30)))
+        return ncfg, obs, masks, to_play
+    return ncfg, rng.random((n, flat), dtype=np.float32), None, None
 
 
 def run_config(name, game, weights, n_net, n_search, binary):
     t0 = time.time()
     rng = np.random.default_rng(7)
-    ncfg, obs = positions(game, n_net, rng, binary)
+    ncfg, obs, _, _ = positions(game, n_net, rng, binary)
     A = ncfg.num_actions
     W = weights(ncfg)
     net = V.VPRNetOracle(ncfg, W)
     res = dict(config=name, game=game, weights="trained (shipped checkpoint)" if name.endswith("trained") else "random-init seed 7",
-               net_positions=n_net, inputs="bernoulli(0.3) planes" if binary else "uniform[0,1)")
+               net_positions=n_net, inputs="real Connect4 positions of 128 stored games" if binary else "uniform[0,1)")
     eng = mzb200.Engine(mzb200.preset(game, max_trees=max(n_net, 64), precision=mzb200.BF16), 0)
     eng.load_weights(W)
     C = eng.shapes.enc_c
@@ -95,10 +97,10 @@ def run_config(name, game, weights, n_net, n_search, binary):
     eng.close()
     # decision impact: bf16 search vs fp32-check search, same positions / seeds / noise
     sims = 25 if game == "ttt" else 50
-    _, sobs = positions(game, n_search, np.random.default_rng(11), binary)
-    full = (1 << A) - 1
-    masks = np.full(n_search, full, np.uint32)
-    to_play = (np.arange(n_search) % (1 if game == "ale" else 2)).astype(np.int32)
+    _, sobs, masks, to_play = positions(game, n_search, np.random.default_rng(11), binary)
+    if masks is None:
+        masks = np.full(n_search, (1 << A) - 1, np.uint32)
+        to_play = (np.arange(n_search) % (1 if game == "ale" else 2)).astype(np.int32)
     noise = np.ones(n_search, np.uint8)
     out = {}
     for prec in (mzb200.FP32_CHECK, mzb200.BF16):
@@ -121,14 +123,15 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=os.path.join(ROOT, "profiles", "bf16_error_r02.json"))
     ap.add_argument("--positions", type=int, default=1024)
-    ap.add_argument("--configs", default="c4d,c4r,c4r_trained,ttt,ale")
+    ap.add_argument("--configs", default="c4d,c4r,c4r_real,c4r_trained,ttt,ale")
     a = ap.parse_args()
     rand = lambda ncfg: H.random_weights(ncfg, seed=7)
     trained = lambda ncfg: mzb200.read_checkpoint(os.path.join(ROOT, "tests", "golden", "checkpoint_c4r_trained.pt"))
     table = {
         "c4d": ("c4d", rand, 256, a.positions, False),
         "c4r": ("c4r", rand, 256, a.positions, False),
-        "c4r_trained": ("c4r", trained, 256, a.positions, True),
+        "c4r_trained": ("c4r", trained, 256, a.positions, True),       # TRAINED weights on REAL positions
+        "c4r_real": ("c4r", rand, 256, a.positions, True),             # random-init weights on the same positions
         "ttt": ("ttt", rand, 256, a.positions, False),
         "ale": ("ale", rand, 24, min(a.positions, 256), False),
     }

@@ -370,7 +370,7 @@ __global__ void se_initial_kernel(TreeDev td, SEDev se, int n_trees, const float
     uint32_t key;
     if (obs_stride == 1) {
         key = (uint32_t)obs[t];
-    } else {   // MZB_EVAL_SYNTHETIC_OBS: hash of the whole row (oracle/se_evaluator.h se_obs_key; a sum, so the order does not matter)
+    } else {   // MZB_EVAL_SYNTHETIC_OBS: hash of the whole row — an order-independent sum of per-position hashes of the float bit patterns
         const float* row = obs + (long)t * obs_stride;
         key = 0;
         for (int i = lane; i < obs_stride; i += 32) key += se_mix(__float_as_uint(row[i]) + 0x9e3779b9U * (uint32_t)(i + 1));

@@ -22,7 +22,7 @@ def _engine(game, T, precision, **over):
     return mzb200.Engine(cfg, 0)
 
 
-def _check_hidden(got, want, raw, precision, what, C):
+def _check_hidden(got, want, raw, precision, what, C, min_live=0.5):
     """Hidden states are min-max normalised per (sample, channel) (models.cpp:16-26): an absolute error e in the
     un-normalised tower output becomes e / (max - min) after normalisation.  fp32 mode: plain 1e-4.  bf16 mode: the 2e-2
     relative bound applies to the tower output (scale M = its largest magnitude), i.e. 2e-2 * M / (max - min) per channel;
@@ -37,7 +37,7 @@ def _check_hidden(got, want, raw, precision, what, C):
     tol = BF16_RTOL * M / np.maximum(rng_c, 1e-5)                  # [B, C]
     err = np.abs(got - want).reshape(B, C, -1).max(axis=2)
     live = tol < 0.5
-    assert live.mean() > 0.5, what + ": too few live channels to judge"
+    assert live.mean() > min_live, what + ": too few live channels to judge"
     bad = (err > np.maximum(tol, BF16_RTOL)) & live
     assert not bad.any(), "%s: %d channels above tolerance, worst err %g (tol %g)" % (
         what, int(bad.sum()), float(err[bad].max()), float(tol[bad][np.argmax(err[bad])]))
@@ -140,7 +140,12 @@ def test_trained_checkpoint_matches_reference_golden(precision, golden_dir):
             assert np.abs(_h(g.value) - _h(d[tag + ".value"])).max() <= 0.35, "trained %s value" % tag
             assert np.median(np.abs(_h(g.value) - _h(d[tag + ".value"]))) <= 2e-2, "trained %s value (median)" % tag
             assert np.abs(g.reward - d[tag + ".reward"]).max() <= 6e-2, "trained %s reward" % tag
-        _check_hidden(g.encoded_state, d[tag + ".hidden"], raw[tag] if raw else None, precision, "trained %s hidden" % tag, C)
+        # a trained tower concentrates its output in a few channels: most of the others span far less than 2 % of the sample's
+        # largest activation, so fewer channels are judged than with random weights (12 % on these positions); over ALL channels
+        # the measured normalised-state error is p99 3.4e-3 / max 3.6e-2 (profiles/bf16_error_r02.json, c4r_trained)
+        _check_hidden(g.encoded_state, d[tag + ".hidden"], raw[tag] if raw else None, precision, "trained %s hidden" % tag, C, min_live=0.05)
+        if precision == 1:
+            assert np.percentile(np.abs(g.encoded_state - d[tag + ".hidden"]), 99) <= 1e-2, "trained %s hidden (p99 over all channels)" % tag
     eng.close()
 
 

@@ -742,13 +742,19 @@ public:
     // (the reference gives both `config.seed + actor_num`, self_play.cpp:232-233).
     SelfPlayCohort(const muzero_config::MuZeroConfig& config, VPRNetModel& model, std::vector<AbstractGame*> games,
                    const std::vector<int>& search_seeds, const std::vector<int>& actor_seeds)
-        : SelfPlayCohort(config, model.engine(), std::move(games), search_seeds, actor_seeds) {}
+        : SelfPlayCohort(config, model.engine(), std::move(games), search_seeds, actor_seeds) {
+        // the cohort plays on tree slots 0 .. n-1 and re-seeds them: MCTS objects attached to the same model hold slots from 0 up too
+        if (model.cohort()->members() > 0) detail::fatal("SelfPlayCohort: the model's tree slots are in use by MCTS objects; give the cohort a model of its own");
+    }
     // the same over an engine the caller built itself (e.g. one with a synthetic evaluator, to compare drivers decision for decision)
     SelfPlayCohort(const muzero_config::MuZeroConfig& config, std::shared_ptr<mzb200::Engine> engine, std::vector<AbstractGame*> games,
                    const std::vector<int>& search_seeds, const std::vector<int>& actor_seeds)
         : config_(config), engine_(std::move(engine)), games_(std::move(games)), A_((int)config.action_space.size()) {
         const int n = (int)games_.size();
         if (n < 1 || n > engine_->config().max_trees) detail::fatal("SelfPlayCohort: more games than tree slots (raise num_actors)");
+        // play_game cuts a long game into slices of max_history_len moves for the trajectory queue (self_play.cpp:113-116,166-176);
+        // play() returns whole games, which is the same thing only without a limit
+        if (config.max_history_len > 0) detail::fatal("SelfPlayCohort: max_history_len > 0 (history slices) is not supported; play() returns whole games");
         if ((int)search_seeds.size() != n || (int)actor_seeds.size() != n) detail::fatal("SelfPlayCohort: one seed pair per game");
         std::vector<float> planes;   // action_representation_initial (types.h:43) pre-evaluated at observation resolution
         if (config.action_representation_initial)
@@ -879,7 +885,9 @@ private:
 class ReanalyzeCohort {
 public:
     ReanalyzeCohort(const muzero_config::MuZeroConfig& config, VPRNetModel& model, const std::vector<int>& search_seeds)
-        : ReanalyzeCohort(config, model.engine(), search_seeds) {}
+        : ReanalyzeCohort(config, model.engine(), search_seeds) {
+        if (model.cohort()->members() > 0) detail::fatal("ReanalyzeCohort: the model's tree slots are in use by MCTS objects; give the cohort a model of its own");
+    }
     ReanalyzeCohort(const muzero_config::MuZeroConfig& config, std::shared_ptr<mzb200::Engine> engine, const std::vector<int>& search_seeds)
         : config_(config), engine_(std::move(engine)), A_((int)config.action_space.size()), n_((int)search_seeds.size()) {
         if (n_ < 1 || n_ > engine_->config().max_trees) detail::fatal("ReanalyzeCohort: more histories than tree slots");

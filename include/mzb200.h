@@ -156,6 +156,12 @@ int mzb_save_checkpoint(mzb_engine* e, const char* path);
 int mzb_nccl_unique_id(char id_out[128]);
 int mzb_nccl_init(mzb_engine* e, const char id[128], int rank, int world_size);
 int mzb_broadcast_weights(mzb_engine* e, int root);
+/* The same hand-over in two phases, so that a learner's broadcast overlaps self-play.  _begin: the blob travels on a
+ * stream of its own into a SHADOW buffer (the root only sends; `rank` = this engine's rank in the communicator) while searches keep
+ * running on the live weights; returns without waiting.  mzb_weights_commit: enqueued on the search stream — waits for the receive
+ * and installs the shadow copy between two searches (stream order), never under one.  Commit without a pending _begin is a no-op. */
+int mzb_broadcast_weights_begin(mzb_engine* e, int root, int rank);
+int mzb_weights_commit(mzb_engine* e);
 /* checksum (FNV-1a over the packed blob, read back from the device) to verify a broadcast */
 int mzb_weights_checksum(mzb_engine* e, uint64_t* out);
 

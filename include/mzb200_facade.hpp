@@ -161,6 +161,8 @@ public:
     }
 
     std::shared_ptr<Engine> engine() const { return eng_; }
+    // MCTS objects currently holding a tree slot of this engine
+    int members() { std::lock_guard<std::mutex> lk(mu_); return members_; }
 
     // MCTS::MCTS: take a free tree slot and seed its std::mt19937 (mcts.cpp:26)
     int acquire_slot(int seed) {

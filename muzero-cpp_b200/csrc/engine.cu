@@ -128,6 +128,8 @@ int set_recording_buffers(mzb_engine* e, bool on) {
 
 }  // namespace
 
+extern "C" void mzb_nccl_release(mzb_engine* e);   // engine_nccl.cu
+
 extern "C" {
 
 const char* mzb_last_error(void) { return mzb::get_error(); }
@@ -137,7 +139,9 @@ int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out) {
     MZB_REQUIRE(config && out, "null argument");
     MZB_REQUIRE(config->max_trees >= 1, "max_trees must be >= 1");
     MZB_REQUIRE(config->num_simulations >= 0, "num_simulations must be >= 0");
-    std::unique_ptr<mzb_engine> e(new mzb_engine());
+    // every early return below hands the half-built engine to mzb_engine_destroy (streams, events, buffers, communicator)
+    struct Destroy { void operator()(mzb_engine* p) const { mzb_engine_destroy(p); } };
+    std::unique_ptr<mzb_engine, Destroy> e(new mzb_engine());
     e->cfg = *config;
     e->device = device;
     memset(&e->timing, 0, sizeof(e->timing));
@@ -210,6 +214,9 @@ void mzb_engine_destroy(mzb_engine* e) {
     if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) if (e->ev_join[i]) cudaEventDestroy(e->ev_join[i]);
     for (int k = 0; k < 2; ++k) { if (e->ev_se_out[k]) cudaEventDestroy(e->ev_se_out[k]); if (e->ev_se_mv[k]) cudaEventDestroy(e->ev_se_mv[k]); }
+    mzb_nccl_release(e);
+    if (e->sync_stream) cudaStreamDestroy(e->sync_stream);
+    if (e->ev_sync) cudaEventDestroy(e->ev_sync);
     e->net.reset();
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->aux) cudaStreamDestroy(e->aux);

@@ -89,6 +89,11 @@ struct mzb_engine {
     // nccl (dlopen'ed)
     void* nccl_lib = nullptr;
     void* nccl_comm = nullptr;
+    // two-phase weight hand-over (engine_nccl.cu): receive stream, shadow blob, 0 = nothing pending / 1 = sent (root) / 2 = received
+    cudaStream_t sync_stream = nullptr;
+    cudaEvent_t ev_sync = nullptr;
+    DevBuf shadow_blob;
+    int sync_pending = 0;
 };
 
 

@@ -145,11 +145,13 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
             }
         }
         e->net->set_pipelined(false);
-        if (rc) return rc;
+        // join the side streams into the search stream — also when a launch failed, so that no work is left running on them
+        // behind the caller's back
         for (int k = 1; k < K; ++k) {
             MZB_CUDA(cudaEventRecord(e->ev_join[k - 1], st[k]));
             MZB_CUDA(cudaStreamWaitEvent(s, e->ev_join[k - 1], 0));
         }
+        if (rc) { cudaStreamSynchronize(s); return rc; }
     } else if (synthetic) {
         // tree kernels alone.  The stub's hidden-state move of simulation i (se_move_kernel, HBM-bound) runs on its own stream
         // beside the tree step of simulation i + 1 (latency-bound, touches no hidden state): the outputs kernel snapshots the

@@ -156,7 +156,8 @@ class _CHostEvaluator(C.Structure):
 _lib = None
 
 EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_destroy", "mzb_load_weights",
-           "mzb_nccl_unique_id", "mzb_nccl_init", "mzb_broadcast_weights", "mzb_weights_checksum",
+           "mzb_nccl_unique_id", "mzb_nccl_init", "mzb_broadcast_weights", "mzb_broadcast_weights_begin", "mzb_weights_commit",
+           "mzb_weights_checksum",
            "mzb_initial_inference", "mzb_recurrent_inference", "mzb_bench_recurrent", "mzb_search_seed", "mzb_search_batch_slots",
            "mzb_search_batch", "mzb_search_batch_device_obs", "mzb_last_search_timing", "mzb_search_set_recording",
            "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes", "mzb_value_encode", "mzb_value_decode",
@@ -185,6 +186,8 @@ def load_library(path=None):
     lib.mzb_nccl_unique_id.argtypes = [C.c_char_p]
     lib.mzb_nccl_init.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int]
     lib.mzb_broadcast_weights.argtypes = [C.c_void_p, C.c_int]
+    lib.mzb_broadcast_weights_begin.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    lib.mzb_weights_commit.argtypes = [C.c_void_p]
     lib.mzb_weights_checksum.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
     dp, fp, ip = C.POINTER(C.c_double), C.POINTER(C.c_float), C.POINTER(C.c_int32)
     lib.mzb_initial_inference.argtypes = [C.c_void_p, fp, C.c_int, dp, dp, dp, fp]
@@ -484,6 +487,14 @@ class Engine:
 
     def broadcast_weights(self, root: int = 0):
         self._check(self.lib.mzb_broadcast_weights(self._h, root))
+
+    def broadcast_weights_begin(self, root: int, rank: int):
+        """phase 1 of the overlapped hand-over: receive into the shadow buffer on its own stream (searches keep running)"""
+        self._check(self.lib.mzb_broadcast_weights_begin(self._h, root, rank))
+
+    def weights_commit(self):
+        """phase 2: install the received weights between two searches (enqueued on the search stream)"""
+        self._check(self.lib.mzb_weights_commit(self._h))
 
     # VPRNetModel::InitialInference (vprnet.cpp:77-129)
     def initial_inference(self, stacked_observations) -> InferenceOutputs:

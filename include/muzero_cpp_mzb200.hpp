@@ -56,6 +56,14 @@ using SoftmaxTemperatureFunction = std::function<double(int)>;
 enum class OpponentTypes { Self, Random, Expert, Human };
 enum CheckpointStep { kMostRecentCheckpointStep = -1, kBestPerformanceCheckpointStep = -2 };
 struct StepReturn { Observation observation; double reward; bool done; };
+struct Batch {   // types.h:81-90: what PrioritizedReplayBuffer::sample hands to Learn
+    std::vector<double> priorities;
+    std::vector<int> indices;
+    std::vector<Action> actions;
+    Observation stacked_observations;
+    std::vector<double> target_rewards, target_values, target_policies, gradient_scale;
+    int num_samples = 0;
+};
 using MCTSReturn = mzb200::MCTSReturn;   // same five fields in the same order (types.h:70-76)
 constexpr double NINF_D = std::numeric_limits<double>::lowest();
 constexpr double INF_D = std::numeric_limits<double>::max();
@@ -263,6 +271,31 @@ public:
     void LoadWeights(const std::vector<mzb_tensor_desc>& tensors) {
         std::lock_guard<std::mutex> call(st_->engine->call_mutex());
         st_->engine->LoadWeights(tensors);
+    }
+    // vprnet.cpp:192-311, the forward half (first slice): the K + 1 unrolled TRAIN-mode network calls and the
+    // loss of Learn(batch) on the GPU, returned as the reference's LossInfo.  Named LearnForward because it stops there: no
+    // backward pass, no Adam step — the weights stay as they are (BatchNorm running statistics of the training state move).
+    struct LossInfo {   // vprnet.h:33-50
+        double total_loss = 0, value = 0, policy = 0, reward = 0;
+        std::vector<int> indices;
+        std::vector<double> errors;
+    };
+    template <class Batch>   // types::Batch (types.h:81-90) or any struct with its fields
+    LossInfo LearnForward(const Batch& inputs, int num_unroll_steps, double value_loss_weight) {
+        std::vector<int32_t> actions(inputs.actions.begin(), inputs.actions.end());
+        LossInfo li;
+        li.indices = inputs.indices;
+        li.errors.assign(inputs.num_samples, 0.0);
+        mzb_batch b{};
+        b.num_samples = inputs.num_samples; b.actions = actions.data(); b.stacked_observations = inputs.stacked_observations.data();
+        b.target_values = inputs.target_values.data(); b.target_rewards = inputs.target_rewards.data();
+        b.target_policies = inputs.target_policies.data(); b.gradient_scale = inputs.gradient_scale.data(); b.priorities = inputs.priorities.data();
+        mzb_loss_info out{};
+        out.errors = li.errors.data();
+        std::lock_guard<std::mutex> call(st_->engine->call_mutex());
+        mzb200::check(mzb_learn_forward(st_->engine->handle(), &b, num_unroll_steps, value_loss_weight, &out), "mzb_learn_forward");
+        li.total_loss = out.total_loss; li.value = out.value; li.policy = out.policy; li.reward = out.reward;
+        return li;
     }
     const std::string Device() const { return st_->device; }
 

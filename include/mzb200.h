@@ -151,6 +151,32 @@ int mzb_checkpoint_write(const char* path, const mzb_tensor_desc* tensors, int n
                          const int64_t* long_values, int n_longs);
 int mzb_save_checkpoint(mzb_engine* e, const char* path);
 
+/* Replaces (first slice, forward half): VPRNetModel::Learn (vprnet.cpp:192-311) up to the loss, SURVEY.md 8f rank 2.
+ * mzb_batch = types::Batch (types.h:81-90): B samples, each with K + 1 = num_unroll_steps + 1 steps.  mzb_learn_forward runs the
+ * K + 1 unrolled network calls in TRAIN mode (batch-statistics BatchNorm, eps 1e-4; the running statistics move by momentum 0.01 and
+ * persist across calls) on the tensors last loaded into the engine, encodes the value / reward targets (ValueEncoder::encode,
+ * util.cpp:59-76) and evaluates MuzeroNetworkImpl::loss (models.cpp:268-276) — fp32 on the GPU, whatever the engine's precision mode.
+ * mzb_loss_info = VPRNetModel::LossInfo (vprnet.h:33-50): total_loss = mean(priorities [B,1] * per-sample loss [B]) as the reference
+ * broadcasts it, value / policy / reward = batch means of the unscaled terms, errors[B] = decoded step-0 value - target_values[:,0]
+ * (may be NULL).  No backward pass and no optimiser step yet: weights are not changed.  gradient_scale is carried for that later
+ * half.  mzb_learn_get_tensor reads a tensor of the training state (e.g. a BatchNorm running_var after the call). */
+typedef struct {
+    int32_t num_samples;                 /* B */
+    const int32_t* actions;              /* [B][K+1] */
+    const float* stacked_observations;   /* [B][initial_flat_size] */
+    const double* target_values;         /* [B][K+1] */
+    const double* target_rewards;        /* [B][K+1] */
+    const double* target_policies;       /* [B][K+1][A] */
+    const double* gradient_scale;        /* [B]; backward only, may be NULL */
+    const double* priorities;            /* [B]: importance-sampling weights */
+} mzb_batch;
+typedef struct {
+    double total_loss, value, policy, reward;
+    double* errors;                      /* [B] or NULL */
+} mzb_loss_info;
+int mzb_learn_forward(mzb_engine* e, const mzb_batch* batch, int num_unroll_steps, double value_loss_weight, mzb_loss_info* out);
+int mzb_learn_get_tensor(mzb_engine* e, const char* name, float* out, int64_t numel);
+
 /* Replaces: the disk round trip SaveCheckpoint -> LoadCheckpoint of learner.cpp:93-101 / muzero.cpp:142-148.
  * One ncclBroadcast of the packed weight blob from `root` to all ranks.  id = 128-byte ncclUniqueId. */
 int mzb_nccl_unique_id(char id_out[128]);

@@ -23,6 +23,7 @@ SOURCES = [
     ("engine_nccl.cu", []),
     ("value_encoder.cu", ["-fmad=false"]),
     ("selfplay.cu", []),
+    ("learn.cu", []),
 ]
 
 

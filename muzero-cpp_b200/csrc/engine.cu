@@ -259,6 +259,7 @@ int mzb_load_weights(mzb_engine* e, const mzb_tensor_desc* tensors, int n_tensor
     e->weights_loaded = true;
     e->raw_weights.clear();
     e->raw_longs.clear();
+    ++e->weights_serial;
     for (int i = 0; i < n_tensors; ++i) {
         mzb_engine::RawTensor r;
         r.name = tensors[i].name;

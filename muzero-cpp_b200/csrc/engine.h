@@ -1,5 +1,6 @@
 // engine.h — the engine object behind the C ABI (include/mzb200.h).
 #pragma once
+#include <map>
 #include <memory>
 #include <string>
 #include <utility>
@@ -53,6 +54,10 @@ struct mzb_engine {
     struct RawTensor { std::string name; std::vector<int64_t> dims; std::vector<float> data; };
     std::vector<RawTensor> raw_weights;
     std::vector<std::pair<std::string, int64_t>> raw_longs;
+    int64_t weights_serial = 0;                               // bumped by every load
+    // training state of mzb_learn_forward (learn.cu): the module's tensors with BatchNorm running statistics as moved so far
+    std::map<std::string, std::vector<float>> learn_state;
+    int64_t learn_state_serial = -1;
     std::vector<float> action_planes;   // owned copy of cfg.action_planes
     static constexpr int MAX_PARTS = 4;
     cudaStream_t stream = nullptr, aux = nullptr;

@@ -64,6 +64,18 @@ class _CSearchResult(C.Structure):
                 ("emperical_policy", C.POINTER(C.c_double))]
 
 
+class _CBatch(C.Structure):   # mzb_batch = types::Batch (types.h:81-90)
+    _fields_ = [("num_samples", C.c_int32), ("actions", C.POINTER(C.c_int32)), ("stacked_observations", C.POINTER(C.c_float)),
+                ("target_values", C.POINTER(C.c_double)), ("target_rewards", C.POINTER(C.c_double)),
+                ("target_policies", C.POINTER(C.c_double)), ("gradient_scale", C.POINTER(C.c_double)),
+                ("priorities", C.POINTER(C.c_double))]
+
+
+class _CLossInfo(C.Structure):   # mzb_loss_info = VPRNetModel::LossInfo (vprnet.h:33-50)
+    _fields_ = [("total_loss", C.c_double), ("value", C.c_double), ("policy", C.c_double), ("reward", C.c_double),
+                ("errors", C.POINTER(C.c_double))]
+
+
 class _CSearchTiming(C.Structure):
     _fields_ = [("total_ms", C.c_float), ("root_ms", C.c_float), ("sim_loop_ms", C.c_float),
                 ("kernel_launches", C.c_int64), ("simulations", C.c_int64)]
@@ -165,6 +177,7 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_actor_seed", "mzb_select_actions", "mzb_actor_uniform_int", "mzb_set_host_evaluator",
            "mzb_checkpoint_open", "mzb_checkpoint_count", "mzb_checkpoint_tensor", "mzb_checkpoint_close", "mzb_load_checkpoint",
            "mzb_checkpoint_long_count", "mzb_checkpoint_long", "mzb_checkpoint_write", "mzb_save_checkpoint",
+           "mzb_learn_forward", "mzb_learn_get_tensor",
            "mzb_debug_se_state", "mzb_debug_tree_write", "mzb_debug_tree_read", "mzb_debug_select_child", "mzb_debug_backpropagate"]
 
 
@@ -220,6 +233,8 @@ def load_library(path=None):
     lib.mzb_checkpoint_close.restype = None
     lib.mzb_load_checkpoint.argtypes = [C.c_void_p, C.c_char_p]
     lib.mzb_save_checkpoint.argtypes = [C.c_void_p, C.c_char_p]
+    lib.mzb_learn_forward.argtypes = [C.c_void_p, C.POINTER(_CBatch), C.c_int, C.c_double, C.POINTER(_CLossInfo)]
+    lib.mzb_learn_get_tensor.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_float), C.c_int64]
     lib.mzb_checkpoint_write.argtypes = [C.c_char_p, C.POINTER(_CTensorDesc), C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.c_int]
     lib.mzb_checkpoint_long_count.argtypes = [C.c_void_p]
     lib.mzb_checkpoint_long.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int64)]
@@ -466,6 +481,31 @@ class Engine:
         """VPRNetModel::SaveCheckpoint's write half (vprnet.cpp:58-63): the tensors this engine was last loaded with, as the
         reference's own .pt archive"""
         self._check(self.lib.mzb_save_checkpoint(self._h, os.fsencode(path)))
+
+    def learn_forward(self, stacked_observations, actions, target_values, target_rewards, target_policies, priorities,
+                      gradient_scale=None, value_loss_weight=0.25):
+        """The forward half of VPRNetModel::Learn (vprnet.cpp:192-311): K + 1 unrolled train-mode network calls + the loss.
+        Returns dict(total_loss, value, policy, reward, errors[B]) = VPRNetModel::LossInfo.  K + 1 = actions.shape[1]."""
+        act = np.ascontiguousarray(actions, dtype=np.int32)
+        B, K1 = act.shape
+        obs = np.ascontiguousarray(stacked_observations, dtype=np.float32).reshape(B, self.shapes.initial_flat_size)
+        tv = np.ascontiguousarray(target_values, dtype=np.float64).reshape(B, K1)
+        tr = np.ascontiguousarray(target_rewards, dtype=np.float64).reshape(B, K1)
+        tp = np.ascontiguousarray(target_policies, dtype=np.float64).reshape(B, K1, self.config.num_actions)
+        pr = np.ascontiguousarray(priorities, dtype=np.float64).reshape(B)
+        gs = np.ascontiguousarray(gradient_scale if gradient_scale is not None else np.full(B, 1.0 / max(1, K1 - 1)), dtype=np.float64).reshape(B)
+        errors = np.empty(B, np.float64)
+        b = _CBatch(B, _ptr(act, C.c_int32), _ptr(obs, C.c_float), _ptr(tv, C.c_double), _ptr(tr, C.c_double), _ptr(tp, C.c_double),
+                    _ptr(gs, C.c_double), _ptr(pr, C.c_double))
+        li = _CLossInfo(0.0, 0.0, 0.0, 0.0, _ptr(errors, C.c_double))
+        self._check(self.lib.mzb_learn_forward(self._h, C.byref(b), K1 - 1, float(value_loss_weight), C.byref(li)))
+        return dict(total_loss=li.total_loss, value=li.value, policy=li.policy, reward=li.reward, errors=errors)
+
+    def learn_tensor(self, name, shape):
+        """a tensor of the training state (BatchNorm running statistics as moved by learn_forward calls)"""
+        out = np.empty(shape, np.float32)
+        self._check(self.lib.mzb_learn_get_tensor(self._h, name.encode(), _ptr(out, C.c_float), int(out.size)))
+        return out
 
     def weights_checksum(self):
         out = C.c_uint64()

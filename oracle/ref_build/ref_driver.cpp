@@ -388,6 +388,74 @@ static int mode_net(const Args& a) {
     return 0;
 }
 
+// ---------------------------------------------------------------- mode learn
+// One call of the UNMODIFIED VPRNetModel::Learn (vprnet.cpp:192-311) on a seeded types::Batch; dumps the batch, the LossInfo it
+// returns (losses are computed before the optimiser step) and the BatchNorm running statistics after the call (they are moved by
+// the forward passes alone: momentum 0.01, model_layers.cpp:36-42).  Weights: seeded random init (dumped) or ckpt=<module archive>.
+static int mode_learn(const Args& a) {
+    MuZeroConfig c = make_config(a);
+    const int B = a.i("batch", 6), seed = a.i("seed", 0);
+    c.num_unroll_steps = a.i("unroll", 5);
+    c.value_loss_weight = a.d("value_loss_weight", 0.25);
+    torch::manual_seed(seed);
+    model::MuzeroNetwork net(c);
+    if (a.has("ckpt")) { torch::load(net, a.str("ckpt", ""), torch::Device(torch::kCPU)); }
+    else { randomize_bn(net); }
+    VPRNetModel vm(c, "cpu");
+    std::string base = vm.SaveCheckpoint(-7);
+    torch::save(net, base + ".pt");
+    vm.LoadCheckpoint(-7);
+    mzbt::Writer w;
+    if (!a.has("no_weights")) dump_weights(w, net);
+    const int K1 = c.num_unroll_steps + 1, A = (int)c.action_space.size();
+    const int cin = net->get_initial_inference_channels();
+    const int flat = cin * c.observation_shape.h * c.observation_shape.w;
+    Batch batch;
+    batch.num_samples = B;
+    std::mt19937 rng(seed * 7919 + 3);
+    std::uniform_real_distribution<double> u(0.0, 1.0);
+    for (int b = 0; b < B; ++b) {
+        batch.indices.push_back(b);
+        batch.priorities.push_back(0.2 + 0.8 * u(rng));
+        batch.gradient_scale.push_back(1.0 / c.num_unroll_steps);
+        for (int i = 0; i < flat; ++i) batch.stacked_observations.push_back(a.i("binary_obs", 0) ? (u(rng) < 0.3 ? 1.f : 0.f) : (float)u(rng));
+        for (int k = 0; k < K1; ++k) {
+            batch.actions.push_back((int)(rng() % A));
+            batch.target_values.push_back(c.min_value + (c.max_value - c.min_value) * u(rng));
+            batch.target_rewards.push_back(c.min_reward + (c.max_reward - c.min_reward) * u(rng));
+            double sum = 0;
+            std::vector<double> p(A);
+            for (int i = 0; i < A; ++i) { p[i] = u(rng) < 0.3 ? 0.0 : u(rng); sum += p[i]; }
+            for (int i = 0; i < A; ++i) batch.target_policies.push_back(sum > 0 ? p[i] / sum : 1.0 / A);
+        }
+    }
+    std::vector<int32_t> acts(batch.actions.begin(), batch.actions.end());
+    w.add("in.obs", 0, {B, flat}, batch.stacked_observations.data());
+    w.add("in.actions", 2, {B, K1}, acts.data());
+    add_f64(w, "in.target_values", {B, K1}, batch.target_values);
+    add_f64(w, "in.target_rewards", {B, K1}, batch.target_rewards);
+    add_f64(w, "in.target_policies", {B, K1, A}, batch.target_policies);
+    add_f64(w, "in.gradient_scale", {B}, batch.gradient_scale);
+    add_f64(w, "in.priorities", {B}, batch.priorities);
+    VPRNetModel::LossInfo li = vm.Learn(batch);
+    add_f64(w, "out.losses", {4}, {li.total_loss, li.value, li.policy, li.reward});
+    add_f64(w, "out.errors", {(int64_t)li.errors.size()}, li.errors);
+    // BatchNorm buffers after the call: through the model's own checkpoint
+    std::string after = vm.SaveCheckpoint(-8);
+    model::MuzeroNetwork net2(c);
+    torch::load(net2, after + ".pt");
+    for (auto& kv : net2->named_buffers()) {
+        const std::string& k = kv.key();
+        if (k.find("running_") != std::string::npos && (!a.has("post_filter") || k.find(a.str("post_filter", "")) != std::string::npos))
+            add_tensor_f32(w, "post." + k, kv.value());
+    }
+    std::vector<int32_t> meta = {cin, c.observation_shape.h, c.observation_shape.w, A, c.num_unroll_steps};
+    w.add("meta", 2, {(int64_t)meta.size()}, meta.data());
+    if (!w.save(a.str("out", "/tmp/mzb_ref_learn.mzbt"))) { std::cerr << "cannot write output" << std::endl; return 1; }
+    printf("learn: total %.9g value %.9g policy %.9g reward %.9g\n", li.total_loss, li.value, li.policy, li.reward);
+    return 0;
+}
+
 // ---------------------------------------------------------------- mode replay
 // Replays network outputs recorded by the engine, so the reference's search runs on "identical network
 // outputs" (north star) and its decisions can be compared with the engine's, simulation by simulation.
@@ -648,6 +716,7 @@ int main(int argc, char** argv) {
     if (mode == "mcts") return mode_mcts(a);
     if (mode == "net") return mode_net(a);
     if (mode == "replay") return mode_replay(a);
+    if (mode == "learn") return mode_learn(a);
     if (mode == "bench") return mode_bench(a);
     if (mode == "bench_rec") return mode_bench_rec(a);
     if (mode == "encoder") return mode_encoder(a);

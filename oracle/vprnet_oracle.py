@@ -111,9 +111,12 @@ class ValueEncoder:
 
 
 # ------------------------------------------------------------------ layers (model_layers.cpp)
+TRAIN = [False]   # model_->train() (vprnet.cpp:246): batch statistics, running statistics moved in place by momentum 0.01
+
+
 def _bn(W, pre, x):
     return F.batch_norm(x, W[pre + ".running_mean"], W[pre + ".running_var"], W[pre + ".weight"], W[pre + ".bias"],
-                        False, 0.01, EPS_BN)
+                        TRAIN[0], 0.01, EPS_BN)
 
 
 def _resblock(W, pre, i, x):  # model_layers.cpp:81-88
@@ -232,3 +235,43 @@ class VPRNetOracle:
         nh, r = self.dynamics(h, act)
         p, v = self.prediction(nh)
         return self._finish(v, r, p, nh)
+
+    @torch.no_grad()
+    def learn_forward(self, obs_flat, actions, target_values, target_rewards, target_policies, priorities, value_loss_weight=0.25):
+        """The forward half of VPRNetModel::Learn (vprnet.cpp:192-311): K + 1 unrolled TRAIN-mode calls, targets through
+        ValueEncoder::encode, MuzeroNetworkImpl::loss (models.cpp:268-276), the reference's [B,1] x [B] broadcast of the
+        importance weights.  Moves this oracle's BatchNorm running statistics like the reference's.  Returns the LossInfo fields."""
+        c = self.cfg
+        eh, ew = c.enc_hw
+        actions = np.asarray(actions)
+        B, K1 = actions.shape
+        obs = torch.as_tensor(np.asarray(obs_flat), dtype=torch.float32).reshape(B, c.in_channels, c.obs_shape[1], c.obs_shape[2])
+        tv = torch.as_tensor(np.asarray(target_values, np.float64)).to(torch.float32).reshape(B, K1)
+        tr = torch.as_tensor(np.asarray(target_rewards, np.float64)).to(torch.float32).reshape(B, K1)
+        tp = torch.as_tensor(np.asarray(target_policies, np.float64)).to(torch.float32).reshape(B, K1, c.num_actions)
+        pri = torch.as_tensor(np.asarray(priorities, np.float64)).to(torch.float32).reshape(B, 1)
+        tve, tre = self.value_encoder.encode(tv), self.reward_encoder.encode(tr)
+
+        def loss(logits, target):
+            return torch.sum(-target * torch.log_softmax(logits, 1), -1)
+        TRAIN[0] = True
+        try:
+            h = self.representation(obs)
+            p, v = self.prediction(h)
+            value_loss, policy_loss = loss(v, tve[:, 0]), loss(p, tp[:, 0])
+            reward_loss = torch.zeros_like(value_loss)
+            errors = (self.value_encoder.decode(v) - tv[:, 0:1].to(torch.float64))[:, 0]
+            for step in range(1, K1):
+                act = torch.empty(B, c.action_channels, eh, ew)
+                for b in range(B):
+                    act[b].fill_(float(np.float32(float(int(actions[b, step])) / c.num_actions)))
+                h, r = self.dynamics(h, act)
+                p, v = self.prediction(h)
+                value_loss = value_loss + loss(v, tve[:, step])
+                reward_loss = reward_loss + loss(r, tre[:, step])
+                policy_loss = policy_loss + loss(p, tp[:, step])
+        finally:
+            TRAIN[0] = False
+        total = (pri * (value_loss * value_loss_weight + reward_loss + policy_loss)).mean()
+        return dict(total_loss=float(total), value=float(value_loss.mean()), policy=float(policy_loss.mean()),
+                    reward=float(reward_loss.mean()), errors=errors.numpy().astype(np.float64))

@@ -10,6 +10,7 @@ Outputs (committed):
   net_tinyds.mzbt same for the downsample head
   checkpoint_c4r_trained.pt / net_c4r_trained.mzbt  the shipped trained Connect4 checkpoint + the reference's outputs on it
   encoder.json    ValueEncoder support sizes and decode known answers
+  learn_{tiny,tinyds,c4r}.mzbt  one VPRNetModel::Learn call: batch, losses, per-sample errors, BatchNorm statistics afterwards
 """
 import json
 import os
@@ -65,6 +66,17 @@ def main():
     O.mzbt_save("/tmp/mzb_c4_positions.mzbt", {"in.obs": obs})
     O.run_ref("net", "game=c4r", "seed=5", "no_weights", "ckpt=" + trained, "obs_in=/tmp/mzb_c4_positions.mzbt",
               "out=" + os.path.join(HERE, "net_c4r_trained.mzbt"))
+    # VPRNetModel::Learn (vprnet.cpp:192-311): one call on a seeded batch -> batch, LossInfo, BatchNorm buffers after the call
+    O.run_ref("learn", "game=tiny", "batch=6", "seed=3", "out=" + os.path.join(HERE, "learn_tiny.mzbt"))
+    O.run_ref("learn", "game=tinyds", "batch=3", "seed=4", "out=" + os.path.join(HERE, "learn_tinyds.mzbt"))
+    # c4r: the weights are the product generator's (seed 5), handed to the reference through the product's checkpoint WRITER
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers as Hh
+    import mzb200
+    from oracle import vprnet_oracle as Vv
+    mzb200.write_checkpoint("/tmp/mzb_learn_c4r_w.pt", Hh.random_weights(Vv.preset("c4r"), seed=5))
+    O.run_ref("learn", "game=c4r", "batch=8", "seed=9", "binary_obs=1", "no_weights", "ckpt=/tmp/mzb_learn_c4r_w.pt",
+              "post_filter=representation_network.representation_head", "out=" + os.path.join(HERE, "learn_c4r.mzbt"))
     enc = []
     for lo, hi, extra in [(-10, 10, []), (-22, 22, []), (-1, 1, []), (-21, 21, []), (-300, 300, []), (-5, 7, ["no_contractive"])]:
         txt = O.run_ref("encoder", "min=%g" % lo, "max=%g" % hi, "rows=6", "seed=1", *extra)

@@ -32,6 +32,7 @@
 #include <filesystem>
 #include <functional>
 #include <limits>
+#include <map>
 #include <numeric>
 #include <random>
 #include <string>
@@ -768,6 +769,123 @@ struct GameHistory {   // types.h:110-118, the fields play_game fills
     }
 };
 }  // namespace types
+
+namespace buffer {
+// PrioritizedReplayBuffer (replay_buffer.h:212-300) on the engine's GPU: same constructor arguments plus the engine, same methods,
+// same batches for the same std::mt19937 state (mzb_replay_*, csrc/replay.cu: sum tree on the host, histories in HBM, one kernel
+// launch per batch).  save() / load() (libnop files) are not mirrored.  A host copy of each stored history is kept for sample_game,
+// which hands whole histories to reanalyze (self_play.cpp:198-200); it is dropped when the buffer evicts the history.
+class PrioritizedReplayBuffer {
+public:
+    PrioritizedReplayBuffer(const muzero_config::MuZeroConfig& config, int max_size, const std::string& name, std::shared_ptr<mzb200::Engine> engine)
+        : engine_(std::move(engine)), name_(name), A_((int)config.action_space.size()) {
+        std::vector<float> planes;
+        if (config.action_representation_initial)
+            for (types::Action a : config.action_space) {
+                const types::Observation pl = config.action_representation_initial(a);
+                planes.insert(planes.end(), pl.begin(), pl.end());
+            }
+        mzb_replay_config rc{};
+        rc.capacity = max_size; rc.min_sample_size = config.min_sample_size; rc.td_steps = config.td_steps; rc.num_unroll_steps = config.num_unroll_steps;
+        rc.per_alpha = config.per_alpha; rc.per_beta = config.per_beta; rc.per_epsilon = config.per_epsilon; rc.per_beta_increment = config.per_beta_increment;
+        rc.action_planes_initial = planes.empty() ? nullptr : planes.data();
+        K1_ = config.num_unroll_steps + 1;
+        alpha_ = config.per_alpha; epsilon_ = config.per_epsilon;
+        std::lock_guard<std::mutex> lk(engine_->call_mutex());
+        mzb200::check(mzb_replay_create(engine_->handle(), &rc, &r_), "mzb_replay_create");
+        flat_ = engine_->shapes().initial_flat_size;
+    }
+    PrioritizedReplayBuffer(const muzero_config::MuZeroConfig& config, int max_size, const std::string& name, VPRNetModel& model)
+        : PrioritizedReplayBuffer(config, max_size, name, model.engine()) {}
+    ~PrioritizedReplayBuffer() { mzb_replay_destroy(r_); }
+    PrioritizedReplayBuffer(const PrioritizedReplayBuffer&) = delete;
+    PrioritizedReplayBuffer& operator=(const PrioritizedReplayBuffer&) = delete;
+
+    bool can_sample() const { std::lock_guard<std::mutex> lk(m_); return mzb_replay_can_sample(r_) != 0; }
+    int size() const { std::lock_guard<std::mutex> lk(m_); return mzb_replay_size(r_); }
+
+    void save_game_history(const types::GameHistory& h) {
+        const int L = (int)h.root_values.size();
+        if (L < 1 || (int)h.observation_history.size() != L + 1 || (int)h.action_history.size() != L + 1 || (int)h.reward_history.size() != L + 1 ||
+            (int)h.to_play_history.size() != L + 1 || (int)h.child_visits.size() != L)
+            detail::fatal("PrioritizedReplayBuffer::save_game_history: a history of L searched positions holds L + 1 observations, actions, rewards and players");
+        std::vector<float> obs;
+        for (const auto& o : h.observation_history) obs.insert(obs.end(), o.begin(), o.end());
+        std::vector<double> cv;
+        for (const auto& v : h.child_visits) {
+            if ((int)v.size() != A_) detail::fatal("PrioritizedReplayBuffer::save_game_history: child_visits row is not one entry per action");
+            cv.insert(cv.end(), v.begin(), v.end());
+        }
+        mzb_game_history g{L, obs.data(), h.action_history.data(), h.reward_history.data(), h.to_play_history.data(), h.root_values.data(), cv.data()};
+        std::lock_guard<std::mutex> lk(m_);
+        {
+            std::lock_guard<std::mutex> el(engine_->call_mutex());
+            mzb200::check(mzb_replay_save_game_history(r_, &g), "mzb_replay_save_game_history");
+        }
+        host_[mzb_replay_num_histories(r_)] = h;
+        prune();
+    }
+
+    template <class Rng>
+    types::Batch sample(Rng& rng, int batch_size) {
+        types::Batch b;
+        b.priorities.resize(batch_size); b.indices.resize(batch_size); b.gradient_scale.resize(batch_size);
+        b.actions.resize((size_t)batch_size * K1_); b.target_rewards.resize((size_t)batch_size * K1_); b.target_values.resize((size_t)batch_size * K1_);
+        b.target_policies.resize((size_t)batch_size * K1_ * A_); b.stacked_observations.resize((size_t)batch_size * flat_);
+        mzb_batch_out o{0, b.priorities.data(), b.indices.data(), b.actions.data(), b.stacked_observations.data(), b.target_rewards.data(),
+                        b.target_values.data(), b.target_policies.data(), b.gradient_scale.data()};
+        std::lock_guard<std::mutex> lk(m_);
+        std::lock_guard<std::mutex> el(engine_->call_mutex());
+        mzb200::check(mzb_replay_sample(r_, &draw<Rng>, &rng, batch_size, &o), "mzb_replay_sample");
+        b.num_samples = o.num_samples;
+        return b;
+    }
+
+    void update_history_priorities(const std::vector<int>& indices, std::vector<double>& errors) {
+        if (indices.size() != errors.size()) detail::fatal("PrioritizedReplayBuffer::update_history_priorities: one error per index");
+        std::lock_guard<std::mutex> lk(m_);
+        mzb200::check(mzb_replay_update_priorities(r_, indices.data(), errors.data(), (int)indices.size()), "mzb_replay_update_priorities");
+        for (double& e : errors) e = std::pow(std::abs(e) + epsilon_, alpha_);   // the reference converts `errors` in place (replay_buffer.cpp:45-49,73)
+    }
+
+    template <class Rng>
+    std::tuple<int, types::GameHistory> sample_game(Rng& rng) {
+        std::lock_guard<std::mutex> lk(m_);
+        int32_t id = 0, len = 0;
+        mzb200::check(mzb_replay_sample_game(r_, &draw<Rng>, &rng, &id, &len), "mzb_replay_sample_game");
+        auto it = host_.find(id);
+        return {id, (len > 0 && it != host_.end()) ? it->second : types::GameHistory()};
+    }
+
+    void update_game_history(int history_id, const types::GameHistory& h) {
+        std::lock_guard<std::mutex> lk(m_);
+        auto it = host_.find(history_id);
+        if (it == host_.end()) return;   // lost meanwhile: nothing to do (replay_buffer.h:55-60)
+        std::vector<double> cv;
+        for (const auto& v : h.child_visits) cv.insert(cv.end(), v.begin(), v.end());
+        std::lock_guard<std::mutex> el(engine_->call_mutex());
+        mzb200::check(mzb_replay_update_game_history(r_, history_id, h.root_values.data(), cv.data(), (int)h.root_values.size()), "mzb_replay_update_game_history");
+        it->second = h;
+    }
+
+    mzb_replay* handle() const { return r_; }
+
+private:
+    template <class Rng>
+    static uint32_t draw(void* user) { return (uint32_t)(*static_cast<Rng*>(user))(); }
+    void prune() {
+        const int oldest = mzb_replay_oldest_history(r_);
+        for (auto it = host_.begin(); it != host_.end();) it = it->first < oldest ? host_.erase(it) : std::next(it);
+    }
+    std::shared_ptr<mzb200::Engine> engine_;
+    std::string name_;
+    int A_, K1_ = 1, flat_ = 0;
+    double alpha_ = 1, epsilon_ = 0.01;
+    mzb_replay* r_ = nullptr;
+    std::map<int, types::GameHistory> host_;
+    mutable std::mutex m_;
+};
+}  // namespace buffer
 
 class SelfPlayCohort {
 public:

@@ -177,6 +177,51 @@ typedef struct {
 int mzb_learn_forward(mzb_engine* e, const mzb_batch* batch, int num_unroll_steps, double value_loss_weight, mzb_loss_info* out);
 int mzb_learn_get_tensor(mzb_engine* e, const char* name, float* out, int64_t numel);
 
+/* Replaces: PrioritizedReplayBuffer (replay_buffer.cpp:15-141) over SumTree (replay_buffer.h:28-209) and the target construction of
+ * GameHistory (compute_target_value / make_target / get_stacked_observations, types.cpp:16-95) — SURVEY.md 8f rank 4.  The sum tree
+ * and the leaves' (step, history) stay on the host; the histories themselves (frames, actions, rewards, to_play, root values, visit
+ * distributions) are stored in HBM when a game is saved, and one kernel launch assembles a whole training batch from them.  Random
+ * draws come from the CALLER's generator (`next` returns its 32-bit outputs, e.g. std::mt19937::operator()) through libstdc++'s own
+ * distributions in the reference's order, so that the same generator state yields the same batch as the reference, bit for bit.
+ * mzb_game_history: length L = root_values.size(); observations [L+1][c*h*w], actions / rewards / to_play [L+1] (action_history[0]
+ * = 0 as play_game pushes it), root_values [L], child_visits [L][A].  mzb_batch_out = types::Batch with caller-allocated arrays:
+ * priorities (importance weights) / indices (tree leaves) / gradient_scale [B], actions / target_values / target_rewards [B][K+1],
+ * target_policies [B][K+1][A], stacked_observations [B][initial_flat_size]. */
+typedef uint32_t (*mzb_rng_fn)(void* user);
+typedef struct {
+    int32_t capacity;                    /* replay_buffer_size: stored positions */
+    int32_t min_sample_size, td_steps, num_unroll_steps;
+    double per_alpha, per_beta, per_epsilon, per_beta_increment;
+    const float* action_planes_initial;  /* action_representation_initial per action [A][ach*h*w]; NULL = constant plane a / A */
+} mzb_replay_config;
+typedef struct {
+    int32_t length;
+    const float* observations;
+    const int32_t* actions;
+    const double* rewards;
+    const int32_t* to_play;
+    const double* root_values;
+    const double* child_visits;
+} mzb_game_history;
+typedef struct {
+    int32_t num_samples;
+    double* priorities; int32_t* indices; int32_t* actions; float* stacked_observations;
+    double* target_rewards; double* target_values; double* target_policies; double* gradient_scale;
+} mzb_batch_out;
+typedef struct mzb_replay mzb_replay;
+int mzb_replay_create(mzb_engine* e, const mzb_replay_config* config, mzb_replay** out);
+void mzb_replay_destroy(mzb_replay* r);
+int mzb_replay_save_game_history(mzb_replay* r, const mzb_game_history* history);
+int mzb_replay_size(const mzb_replay* r);
+int mzb_replay_can_sample(const mzb_replay* r);
+int mzb_replay_num_histories(const mzb_replay* r);
+double mzb_replay_total_priority(const mzb_replay* r);
+int mzb_replay_oldest_history(const mzb_replay* r);   /* ids below it have been evicted (first in, first out) */
+int mzb_replay_sample(mzb_replay* r, mzb_rng_fn next, void* user, int batch_size, mzb_batch_out* out);
+int mzb_replay_update_priorities(mzb_replay* r, const int32_t* indices, const double* errors, int n);
+int mzb_replay_sample_game(mzb_replay* r, mzb_rng_fn next, void* user, int32_t* history_id, int32_t* length);
+int mzb_replay_update_game_history(mzb_replay* r, int history_id, const double* root_values, const double* child_visits, int length);
+
 /* Replaces: the disk round trip SaveCheckpoint -> LoadCheckpoint of learner.cpp:93-101 / muzero.cpp:142-148.
  * One ncclBroadcast of the packed weight blob from `root` to all ranks.  id = 128-byte ncclUniqueId. */
 int mzb_nccl_unique_id(char id_out[128]);

@@ -76,6 +76,28 @@ class _CLossInfo(C.Structure):   # mzb_loss_info = VPRNetModel::LossInfo (vprnet
                 ("errors", C.POINTER(C.c_double))]
 
 
+_RNG_FN = C.CFUNCTYPE(C.c_uint32, C.c_void_p)   # mzb_rng_fn: the caller's generator, 32 bits per draw (std::mt19937::operator())
+
+
+class _CReplayConfig(C.Structure):   # mzb_replay_config
+    _fields_ = [("capacity", C.c_int32), ("min_sample_size", C.c_int32), ("td_steps", C.c_int32), ("num_unroll_steps", C.c_int32),
+                ("per_alpha", C.c_double), ("per_beta", C.c_double), ("per_epsilon", C.c_double), ("per_beta_increment", C.c_double),
+                ("action_planes_initial", C.POINTER(C.c_float))]
+
+
+class _CGameHistory(C.Structure):    # mzb_game_history = the fields of types::GameHistory the buffer reads (types.h:43-78)
+    _fields_ = [("length", C.c_int32), ("observations", C.POINTER(C.c_float)), ("actions", C.POINTER(C.c_int32)),
+                ("rewards", C.POINTER(C.c_double)), ("to_play", C.POINTER(C.c_int32)), ("root_values", C.POINTER(C.c_double)),
+                ("child_visits", C.POINTER(C.c_double))]
+
+
+class _CBatchOut(C.Structure):       # mzb_batch_out = types::Batch (types.h:81-104)
+    _fields_ = [("num_samples", C.c_int32), ("priorities", C.POINTER(C.c_double)), ("indices", C.POINTER(C.c_int32)),
+                ("actions", C.POINTER(C.c_int32)), ("stacked_observations", C.POINTER(C.c_float)),
+                ("target_rewards", C.POINTER(C.c_double)), ("target_values", C.POINTER(C.c_double)),
+                ("target_policies", C.POINTER(C.c_double)), ("gradient_scale", C.POINTER(C.c_double))]
+
+
 class _CSearchTiming(C.Structure):
     _fields_ = [("total_ms", C.c_float), ("root_ms", C.c_float), ("sim_loop_ms", C.c_float),
                 ("kernel_launches", C.c_int64), ("simulations", C.c_int64)]
@@ -178,6 +200,9 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_checkpoint_open", "mzb_checkpoint_count", "mzb_checkpoint_tensor", "mzb_checkpoint_close", "mzb_load_checkpoint",
            "mzb_checkpoint_long_count", "mzb_checkpoint_long", "mzb_checkpoint_write", "mzb_save_checkpoint",
            "mzb_learn_forward", "mzb_learn_get_tensor",
+           "mzb_replay_create", "mzb_replay_destroy", "mzb_replay_save_game_history", "mzb_replay_size", "mzb_replay_can_sample",
+           "mzb_replay_num_histories", "mzb_replay_total_priority", "mzb_replay_oldest_history", "mzb_replay_sample", "mzb_replay_update_priorities",
+           "mzb_replay_sample_game", "mzb_replay_update_game_history",
            "mzb_debug_se_state", "mzb_debug_tree_write", "mzb_debug_tree_read", "mzb_debug_select_child", "mzb_debug_backpropagate"]
 
 
@@ -235,6 +260,18 @@ def load_library(path=None):
     lib.mzb_save_checkpoint.argtypes = [C.c_void_p, C.c_char_p]
     lib.mzb_learn_forward.argtypes = [C.c_void_p, C.POINTER(_CBatch), C.c_int, C.c_double, C.POINTER(_CLossInfo)]
     lib.mzb_learn_get_tensor.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_float), C.c_int64]
+    lib.mzb_replay_create.argtypes = [C.c_void_p, C.POINTER(_CReplayConfig), C.POINTER(C.c_void_p)]
+    lib.mzb_replay_destroy.argtypes = [C.c_void_p]
+    lib.mzb_replay_destroy.restype = None
+    lib.mzb_replay_save_game_history.argtypes = [C.c_void_p, C.POINTER(_CGameHistory)]
+    for f in ("mzb_replay_size", "mzb_replay_can_sample", "mzb_replay_num_histories", "mzb_replay_oldest_history"):
+        getattr(lib, f).argtypes = [C.c_void_p]
+    lib.mzb_replay_total_priority.argtypes = [C.c_void_p]
+    lib.mzb_replay_total_priority.restype = C.c_double
+    lib.mzb_replay_sample.argtypes = [C.c_void_p, _RNG_FN, C.c_void_p, C.c_int, C.POINTER(_CBatchOut)]
+    lib.mzb_replay_update_priorities.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_double), C.c_int]
+    lib.mzb_replay_sample_game.argtypes = [C.c_void_p, _RNG_FN, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.mzb_replay_update_game_history.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int]
     lib.mzb_checkpoint_write.argtypes = [C.c_char_p, C.POINTER(_CTensorDesc), C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.c_int]
     lib.mzb_checkpoint_long_count.argtypes = [C.c_void_p]
     lib.mzb_checkpoint_long.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int64)]
@@ -679,6 +716,110 @@ def legal_mask_from_actions(legal_actions, num_actions):
 
 
 # game presets = the shapes of BASELINE.json's configs
+class Mt19937:
+    """std::mt19937(seed) as a mzb_rng_fn source: numpy's MT19937 with the legacy (init_genrand) seeding is the same generator."""
+
+    def __init__(self, seed):
+        self._bg = np.random.RandomState(int(seed))._bit_generator
+        self.draws = 0
+
+    def __call__(self):
+        self.draws += 1
+        return int(self._bg.random_raw())
+
+
+class ReplayBuffer:
+    """PrioritizedReplayBuffer (replay_buffer.h:212-300) on one engine's GPU: the sum tree on the host, the histories in HBM, one
+    kernel launch per sampled batch (csrc/replay.cu).  `rng` arguments are callables returning std::mt19937's 32-bit draws."""
+
+    def __init__(self, engine, capacity, min_sample_size=1, td_steps=10, num_unroll_steps=5, per_alpha=1.0, per_beta=1.0,
+                 per_epsilon=0.01, per_beta_increment=0.001, action_planes_initial=None):
+        self.engine, self.lib = engine, engine.lib
+        self.K = int(num_unroll_steps)
+        planes = None
+        if action_planes_initial is not None:
+            planes = np.ascontiguousarray(action_planes_initial, dtype=np.float32)
+        rc = _CReplayConfig(int(capacity), int(min_sample_size), int(td_steps), self.K, float(per_alpha), float(per_beta),
+                            float(per_epsilon), float(per_beta_increment), _ptr(planes, C.c_float) if planes is not None else None)
+        h = C.c_void_p()
+        engine._check(self.lib.mzb_replay_create(engine._h, C.byref(rc), C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if self._h:
+            self.lib.mzb_replay_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def size(self):
+        return self.lib.mzb_replay_size(self._h)
+
+    def can_sample(self):
+        return bool(self.lib.mzb_replay_can_sample(self._h))
+
+    def num_histories(self):
+        return self.lib.mzb_replay_num_histories(self._h)
+
+    def total_priority(self):
+        return self.lib.mzb_replay_total_priority(self._h)
+
+    def oldest_history(self):
+        return self.lib.mzb_replay_oldest_history(self._h)
+
+    def save_game_history(self, observations, actions, rewards, to_play, root_values, child_visits):
+        """observations [L+1][c*h*w] (single frames), actions / rewards / to_play [L+1], root_values [L], child_visits [L][A]"""
+        rv = np.ascontiguousarray(root_values, dtype=np.float64)
+        L = rv.shape[0]
+        cfg = self.engine.config
+        c, h, w = cfg.observation_shape
+        obs = np.ascontiguousarray(observations, dtype=np.float32).reshape(L + 1, c * h * w)
+        act = np.ascontiguousarray(actions, dtype=np.int32).reshape(L + 1)
+        rew = np.ascontiguousarray(rewards, dtype=np.float64).reshape(L + 1)
+        tp = np.ascontiguousarray(to_play, dtype=np.int32).reshape(L + 1)
+        cv = np.ascontiguousarray(child_visits, dtype=np.float64).reshape(L, cfg.num_actions)
+        g = _CGameHistory(L, _ptr(obs, C.c_float), _ptr(act, C.c_int32), _ptr(rew, C.c_double), _ptr(tp, C.c_int32),
+                          _ptr(rv, C.c_double), _ptr(cv, C.c_double))
+        self.engine._check(self.lib.mzb_replay_save_game_history(self._h, C.byref(g)))
+
+    def sample(self, rng, batch_size):
+        """types::Batch as a dict of arrays (same field names)"""
+        B, K1, A = int(batch_size), self.K + 1, self.engine.config.num_actions
+        out = dict(priorities=np.empty(B, np.float64), indices=np.empty(B, np.int32), actions=np.empty((B, K1), np.int32),
+                   stacked_observations=np.empty((B, self.engine.shapes.initial_flat_size), np.float32),
+                   target_rewards=np.empty((B, K1), np.float64), target_values=np.empty((B, K1), np.float64),
+                   target_policies=np.empty((B, K1, A), np.float64), gradient_scale=np.empty(B, np.float64))
+        b = _CBatchOut(0, _ptr(out["priorities"], C.c_double), _ptr(out["indices"], C.c_int32), _ptr(out["actions"], C.c_int32),
+                       _ptr(out["stacked_observations"], C.c_float), _ptr(out["target_rewards"], C.c_double),
+                       _ptr(out["target_values"], C.c_double), _ptr(out["target_policies"], C.c_double),
+                       _ptr(out["gradient_scale"], C.c_double))
+        fn = _RNG_FN(lambda _u: rng())
+        self.engine._check(self.lib.mzb_replay_sample(self._h, fn, None, B, C.byref(b)))
+        out["num_samples"] = b.num_samples
+        return out
+
+    def update_history_priorities(self, indices, errors):
+        idx = np.ascontiguousarray(indices, dtype=np.int32)
+        err = np.ascontiguousarray(errors, dtype=np.float64)
+        self.engine._check(self.lib.mzb_replay_update_priorities(self._h, _ptr(idx, C.c_int32), _ptr(err, C.c_double), int(idx.size)))
+
+    def sample_game(self, rng):
+        """(history id, stored length or 0 if the buffer has lost it)"""
+        hid, ln = C.c_int32(), C.c_int32()
+        fn = _RNG_FN(lambda _u: rng())
+        self.engine._check(self.lib.mzb_replay_sample_game(self._h, fn, None, C.byref(hid), C.byref(ln)))
+        return hid.value, ln.value
+
+    def update_game_history(self, history_id, root_values, child_visits):
+        rv = np.ascontiguousarray(root_values, dtype=np.float64)
+        cv = np.ascontiguousarray(child_visits, dtype=np.float64)
+        self.engine._check(self.lib.mzb_replay_update_game_history(self._h, int(history_id), _ptr(rv, C.c_double), _ptr(cv, C.c_double), int(rv.shape[0])))
+
+
 def preset(name, **over):
     nc = MuZeroNetworkConfig()
     kw = {}

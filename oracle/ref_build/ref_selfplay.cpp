@@ -15,6 +15,11 @@
 //   * evaluator games (is_evaluator = true, opponent Random): temperature 0, no noise, the opponent's moves drawn from the SAME
 //     generator as select_action would use (self_play.cpp:41-56,128-143); only SharedStats sees their outcome.
 //
+//   * replay (replay_out=FILE): every played history also goes into ONE PrioritizedReplayBuffer (replay_buffer.cpp, unmodified) of a
+//     capacity small enough that old games are evicted; after every `replay_every` games one sample(rng, batch) is taken and dumped
+//     in full (types::Batch), its priorities are updated from synthetic errors, and one sample_game(rng) is drawn — all from one
+//     std::mt19937(replay_seed).  Golden for mzb_replay_* (csrc/replay.cu).
+//
 // Evaluator = "SE" keyed by the whole observation (oracle/se_evaluator.h, se_obs_key) — MZB_EVAL_SYNTHETIC_OBS on the engine side.
 #include <cinttypes>
 #include <cstdio>
@@ -125,6 +130,18 @@ static void dump_search(FILE* f, const char* tag, const GameHistory& h) {
     fprintf(f, "\n");
 }
 
+static void dump_batch(FILE* f, const Batch& b) {
+    fprintf(f, "indices"); for (int v : b.indices) fprintf(f, " %d", v); fprintf(f, "\n");
+    fprintf(f, "priorities"); for (double v : b.priorities) fprintf(f, " %a", v); fprintf(f, "\n");
+    fprintf(f, "actions"); for (int v : b.actions) fprintf(f, " %d", v); fprintf(f, "\n");
+    fprintf(f, "target_values"); for (double v : b.target_values) fprintf(f, " %a", v); fprintf(f, "\n");
+    fprintf(f, "target_rewards"); for (double v : b.target_rewards) fprintf(f, " %a", v); fprintf(f, "\n");
+    fprintf(f, "target_policies"); for (double v : b.target_policies) fprintf(f, " %a", v); fprintf(f, "\n");
+    fprintf(f, "gradient_scale"); for (double v : b.gradient_scale) fprintf(f, " %a", v); fprintf(f, "\n");
+    // observations are 0/1 planes and a/7 action planes: print the distinct values compactly (value index per cell)
+    fprintf(f, "stacked_observations"); for (float v : b.stacked_observations) fprintf(f, " %g", (double)v * 7); fprintf(f, "\n");
+}
+
 int main(int argc, char** argv) {
     std::map<std::string, std::string> kv;
     for (int i = 1; i < argc; ++i) { std::string s(argv[i]); auto p = s.find('='); if (p != std::string::npos) kv[s.substr(0, p)] = s.substr(p + 1); }
@@ -136,6 +153,24 @@ int main(int argc, char** argv) {
     MuZeroConfig config = connect4_config(sims, path);
     fprintf(f, "selfplay_c4 games %d sims %d seed %d rseed %d eval_games %d eseed %d\n", games, sims, seed, rseed, eval_games, eseed);
     auto stats = std::make_shared<SharedStats>();
+    // replay golden
+    FILE* rf = kv.count("replay_out") ? fopen(kv["replay_out"].c_str(), "w") : nullptr;
+    const int r_cap = geti("replay_capacity", 1000), r_batch = geti("replay_batch", 16), r_stack = geti("replay_stack", 2);
+    const int r_every = geti("replay_every", 8), r_seed = geti("replay_seed", 4242);
+    MuZeroConfig rbc = config;
+    rbc.path = path + "/replay";
+    rbc.stacked_observations = r_stack;
+    rbc.td_steps = geti("replay_td", 5); rbc.num_unroll_steps = geti("replay_unroll", 5);
+    rbc.per_alpha = 0.6; rbc.per_beta = 0.4; rbc.per_beta_increment = 0.05; rbc.per_epsilon = 0.01; rbc.discount = 0.997;
+    rbc.min_sample_size = 32;
+    std::unique_ptr<buffer::PrioritizedReplayBuffer> rb;
+    std::mt19937 replay_rng(r_seed);
+    if (rf) {
+        rb.reset(new buffer::PrioritizedReplayBuffer(rbc, r_cap, "replay"));
+        fprintf(rf, "replay_c4 games %d capacity %d batch %d stack %d every %d seed %d td %d unroll %d alpha %a beta %a beta_increment %a epsilon %a discount %a min_sample_size %d\n",
+                games, r_cap, r_batch, r_stack, r_every, r_seed, rbc.td_steps, rbc.num_unroll_steps, rbc.per_alpha, rbc.per_beta,
+                rbc.per_beta_increment, rbc.per_epsilon, rbc.discount, rbc.min_sample_size);
+    }
     for (int g = 0; g < games; ++g) {
         auto ev = std::make_shared<SEObsEvaluator>(7);
         util::StopToken stop;
@@ -150,6 +185,21 @@ int main(int argc, char** argv) {
         fprintf(f, "game %d positions %zu\n", g, h.root_values.size());
         dump_history(f, "play", h);
         dump_search(f, "play", h);
+        if (rf) {
+            rb->save_game_history(h);
+            fprintf(rf, "save %d size %d can_sample %d\n", g, rb->size(), (int)rb->can_sample());
+            if ((g + 1) % r_every == 0 && rb->can_sample()) {
+                Batch b = rb->sample(replay_rng, r_batch);
+                fprintf(rf, "sample %d\n", b.num_samples);
+                dump_batch(rf, b);
+                std::vector<double> errors;
+                for (int idx : b.indices) errors.push_back(((unsigned)idx * 2654435761u % 1000u) / 100.0 - 3.0);
+                fprintf(rf, "update"); for (double e : errors) fprintf(rf, " %a", e); fprintf(rf, "\n");
+                rb->update_history_priorities(b.indices, errors);
+                auto sg = rb->sample_game(replay_rng);
+                fprintf(rf, "sample_game %d %zu\n", std::get<0>(sg), std::get<1>(sg).root_values.size());
+            }
+        }
         // reanalyze: this history alone in a buffer, one full pass (see the header comment)
         MuZeroConfig rc = config;
         rc.path = path + "/re" + std::to_string(g);
@@ -180,6 +230,7 @@ int main(int argc, char** argv) {
         fprintf(f, "eval %d muzero_player %d length %a total_reward %a mean_value %a\n", g, ec.muzero_player, st.evaluator_episode_length,
                 st.evaluator_total_reward, st.evaluator_mean_value);
     }
+    if (rf) fclose(rf);
     if (f != stdout) fclose(f);
     return 0;
 }

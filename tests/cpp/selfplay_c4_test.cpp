@@ -228,6 +228,67 @@ int main(int argc, char** argv) {
             EXPECT(std::fabs(mean - w.mean_value) <= 1e-12, "evaluator game %d: mean root value %.17g vs %.17g", idx[k], mean, w.mean_value);
         }
     }
+    // ---- (4) replay: the played histories through buffer::PrioritizedReplayBuffer, event for event as the UNMODIFIED reference
+    // buffer handled them (tests/golden/replay_c4.txt) — here the generator is a real std::mt19937 behind the C-ABI callback
+    {
+        const std::string rpath = argc > 1 ? std::string(argv[1]) + "/replay_c4.txt" : "tests/golden/replay_c4.txt";
+        std::ifstream in(rpath);
+        std::string line;
+        if (!std::getline(in, line)) { std::printf("selfplay_c4_test: cannot read %s\n", rpath.c_str()); return 1; }
+        std::map<std::string, std::string> head;
+        { std::istringstream ls(line); std::string tag, k, v; ls >> tag; while (ls >> k >> v) head[k] = v; }
+        muzero_config::MuZeroConfig rc = config;
+        rc.stacked_observations = std::atoi(head["stack"].c_str());
+        rc.td_steps = std::atoi(head["td"].c_str()); rc.num_unroll_steps = std::atoi(head["unroll"].c_str());
+        rc.per_alpha = hexd(head["alpha"]); rc.per_beta = hexd(head["beta"]); rc.per_beta_increment = hexd(head["beta_increment"]);
+        rc.per_epsilon = hexd(head["epsilon"]); rc.discount = hexd(head["discount"]); rc.min_sample_size = std::atoi(head["min_sample_size"].c_str());
+        rc.action_representation_initial = [](Action a) { return Observation(42, (float)((double)a / 7)); };
+        auto engine = se_engine(rc, 8);
+        buffer::PrioritizedReplayBuffer rb(rc, std::atoi(head["capacity"].c_str()), "replay", engine);
+        std::mt19937 rng(std::atoi(head["seed"].c_str()));
+        Batch last;
+        int batches = 0;
+        auto ints = [](std::istringstream& ls) { std::vector<int> v; int x; while (ls >> x) v.push_back(x); return v; };
+        auto dbls = [](std::istringstream& ls) { std::vector<double> v; std::string t; while (ls >> t) v.push_back(hexd(t)); return v; };
+        while (std::getline(in, line)) {
+            std::istringstream ls(line);
+            std::string tag;
+            ls >> tag;
+            if (tag == "save") {
+                int g, size, can; std::string k;
+                ls >> g >> k >> size >> k >> can;
+                rb.save_game_history(played[g]);
+                EXPECT(rb.size() == size && (int)rb.can_sample() == can, "replay: size after game %d is %d, reference %d", g, rb.size(), size);
+            } else if (tag == "sample") {
+                int n; ls >> n;
+                last = rb.sample(rng, n);
+                ++batches;
+            } else if (tag == "indices") { EXPECT(last.indices == ints(ls), "replay batch %d: indices differ", batches);
+            } else if (tag == "actions") { EXPECT(last.actions == ints(ls), "replay batch %d: actions differ", batches);
+            } else if (tag == "priorities") { EXPECT(last.priorities == dbls(ls), "replay batch %d: importance weights differ", batches);
+            } else if (tag == "target_values") { EXPECT(last.target_values == dbls(ls), "replay batch %d: target values differ", batches);
+            } else if (tag == "target_rewards") { EXPECT(last.target_rewards == dbls(ls), "replay batch %d: target rewards differ", batches);
+            } else if (tag == "target_policies") { EXPECT(last.target_policies == dbls(ls), "replay batch %d: target policies differ", batches);
+            } else if (tag == "gradient_scale") { EXPECT(last.gradient_scale == dbls(ls), "replay batch %d: gradient scale differs", batches);
+            } else if (tag == "stacked_observations") {
+                std::vector<float> want; double x;
+                while (ls >> x) want.push_back((float)(x / 7.0));   // printed as value * 7: 0, 7 (a stone) or the action of an action plane
+                EXPECT(last.stacked_observations == want, "replay batch %d: stacked observations differ", batches);
+            } else if (tag == "update") {
+                std::vector<double> e = dbls(ls);
+                rb.update_history_priorities(last.indices, e);
+            } else if (tag == "sample_game") {
+                int id; size_t len;
+                ls >> id >> len;
+                auto sg = rb.sample_game(rng);
+                EXPECT(std::get<0>(sg) == id && std::get<1>(sg).root_values.size() == len, "replay: sample_game %d (%zu positions), reference %d (%zu)",
+                       std::get<0>(sg), std::get<1>(sg).root_values.size(), id, len);
+                if (len > 0) EXPECT(std::get<1>(sg).action_history == played[id - 1].action_history, "replay: sample_game returned another history");
+            }
+        }
+        EXPECT(batches == 16, "replay: %d batches compared", batches);
+        std::printf("selfplay_c4_test: %d replay batches\n", batches);
+    }
     if (failures) { std::printf("selfplay_c4_test: %d failure(s)\n", failures); return 1; }
     std::printf("selfplay_c4_test: ok\n");
     return 0;

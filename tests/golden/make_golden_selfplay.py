@@ -26,7 +26,10 @@ def main_c4():
     observation-keyed synthetic evaluator (oracle/ref_build/ref_selfplay.cpp)."""
     import subprocess
     drv = os.path.join(ROOT, "oracle", "_ref", "ref_selfplay")
-    subprocess.check_call([drv, "games=128", "sims=50", "eval_games=16", "out=" + os.path.join(HERE, "selfplay_c4.txt")])
+    subprocess.check_call([drv, "games=128", "sims=50", "eval_games=16", "out=" + os.path.join(HERE, "selfplay_c4.txt"),
+                           # replay_c4.txt: the same 128 histories through the unmodified PrioritizedReplayBuffer (capacity 1000 < stored
+                           # positions, so games are evicted), a sampled Batch every 8 games — golden for mzb_replay_* (csrc/replay.cu)
+                           "replay_out=" + os.path.join(HERE, "replay_c4.txt"), "replay_capacity=1000", "replay_batch=16", "replay_stack=2"])
 
 
 if __name__ == "__main__":

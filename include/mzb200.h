@@ -346,6 +346,15 @@ int mzb_actor_uniform_int(mzb_engine* e, const int32_t* slots, const int32_t* up
  * vprnet.cpp:240-243) and backs the reference's own round-trip tests (tests/util_test.cpp). */
 int mzb_value_encode(mzb_engine* e, int which, const float* x, int n, float* support /*[n][S]*/);
 int mzb_value_decode(mzb_engine* e, int which, const float* logits /*[n][S]*/, int n, int take_softmax, float* x /*[n]*/);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  mzb_value_decode with the same arguments, the same kernel and the same
+ * results, but it allocates nothing: its device staging (n rows of S logits + n decoded scalars) lives in a file-scope
+ * `static __device__` array of MZB_VALUE_DECODE_STATIC_MAX_FLOATS floats (4 MiB, held by every GPU that loads the library until the
+ * process exits).  n * (S + 1) beyond that is rejected with MZB_ERR_INVALID and a message naming both numbers.  The array is shared by
+ * every call on a device and keeps the last call's contents (nothing in it needs clearing: each call overwrites what it reads);
+ * calls that overlap on the same GPU race on it — serialise them. */
+#define MZB_VALUE_DECODE_STATIC_MAX_FLOATS (1 << 20)
+int mzb_value_decode_static(mzb_engine* e, int which, const float* logits /*[n][S]*/, int n, int take_softmax, float* x /*[n]*/);
 
 /* derived shapes (VPRNetModel ctor, vprnet.cpp:41-46; ValueEncoder::get_support_size, util.cpp:91-102) */
 typedef struct {

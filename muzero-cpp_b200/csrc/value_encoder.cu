@@ -3,8 +3,15 @@
 // directions are exported here for callers that hold logits or targets of their own (reanalyze targets, tests).
 // Arithmetic follows the reference's fp32 tensor ops step by step; -fmad=false keeps every product / sum separately rounded.
 #include <cmath>
+#include <mutex>
 
 #include "engine.h"
+
+// Scratch of mzb_value_decode_static: the staged logits followed by the decoded scalars.  File scope, so every GPU that loads the
+// library holds these 4 MiB until the process exits.  In host code the name is only a stand-in for the symbol: the device address
+// comes from cudaGetSymbolAddress (static_scratch_address below), once per device with that device current.
+#define MZB_STATIC_SCRATCH_FLOATS MZB_VALUE_DECODE_STATIC_MAX_FLOATS
+static __device__ __align__(256) float g_static_scratch[MZB_STATIC_SCRATCH_FLOATS];
 
 namespace mzb {
 namespace {
@@ -67,6 +74,22 @@ int encoder_args(mzb_engine* e, int which, const void* a, const void* b, int n, 
     return MZB_OK;
 }
 
+// device address of g_static_scratch on `device` (which must be current): looked up once per device, then cached
+int static_scratch_address(int device, float** out) {
+    static std::mutex mu;
+    static float* addr[64] = {};
+    MZB_REQUIRE(device >= 0 && device < 64, "device ordinal %d outside [0, 64)", device);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!addr[device]) {
+        float* p = nullptr;
+        MZB_CUDA(cudaGetSymbolAddress((void**)&p, g_static_scratch));
+        MZB_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address for the static scratch");
+        addr[device] = p;
+    }
+    *out = addr[device];
+    return MZB_OK;
+}
+
 }  // namespace
 }  // namespace mzb
 
@@ -106,6 +129,33 @@ int mzb_value_decode(mzb_engine* e, int which, const float* logits, int n, int t
                                                                    enc->contractive);
     MZB_CUDA(cudaGetLastError());
     MZB_CUDA(cudaMemcpyAsync(x, dx.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    MZB_CUDA(cudaStreamSynchronize(e->stream));
+    return MZB_OK;
+}
+
+// mzb_value_decode without any allocation: the same kernel on the same stream, its staging in g_static_scratch instead of two
+// cudaMalloc'ed buffers.  n * (support + 1) floats must fit MZB_STATIC_SCRATCH_FLOATS.  Nothing in the scratch has to start at
+// zero: the copy overwrites the n * support logits and the kernel writes every one of the n outputs before they are read back;
+// what a previous call left behind is never read.  All calls on a device share the one array: calls that overlap on the GPU
+// (two engines on the same device driven from two threads) race — serialise them.
+int mzb_value_decode_static(mzb_engine* e, int which, const float* logits, int n, int take_softmax, float* x) {
+    const EncoderConsts* enc = nullptr;
+    int rc = encoder_args(e, which, logits, x, n, &enc);
+    if (rc) return rc;
+    const int S = enc->support;
+    MZB_REQUIRE((long long)n * (S + 1) <= (long long)MZB_STATIC_SCRATCH_FLOATS,
+                "mzb_value_decode_static: %d rows of %d logits need %lld floats of scratch, the static array holds %d (use mzb_value_decode)", n, S,
+                (long long)n * (S + 1), (int)MZB_STATIC_SCRATCH_FLOATS);
+    MZB_CUDA(cudaSetDevice(e->device));
+    float* scratch = nullptr;
+    rc = static_scratch_address(e->device, &scratch);
+    if (rc) return rc;
+    float* dl = scratch;
+    float* dx = scratch + (size_t)n * S;
+    MZB_CUDA(cudaMemcpyAsync(dl, logits, (size_t)n * S * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    value_decode_kernel<<<(n * 32 + 127) / 128, 128, 0, e->stream>>>(dl, n, S, take_softmax, dx, (float)enc->min_value, (float)enc->step, enc->contractive);
+    MZB_CUDA(cudaGetLastError());
+    MZB_CUDA(cudaMemcpyAsync(x, dx, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
     MZB_CUDA(cudaStreamSynchronize(e->stream));
     return MZB_OK;
 }

@@ -195,6 +195,7 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_initial_inference", "mzb_recurrent_inference", "mzb_bench_recurrent", "mzb_search_seed", "mzb_search_batch_slots",
            "mzb_search_batch", "mzb_search_batch_device_obs", "mzb_last_search_timing", "mzb_search_set_recording",
            "mzb_search_get_trace", "mzb_search_get_records", "mzb_get_shapes", "mzb_value_encode", "mzb_value_decode",
+           "mzb_value_decode_static",
            "mzb_obs_ring_create", "mzb_obs_ring_reset", "mzb_obs_ring_push", "mzb_obs_ring_stacked", "mzb_search_batch_ring",
            "mzb_actor_seed", "mzb_select_actions", "mzb_actor_uniform_int", "mzb_set_host_evaluator",
            "mzb_checkpoint_open", "mzb_checkpoint_count", "mzb_checkpoint_tensor", "mzb_checkpoint_close", "mzb_load_checkpoint",
@@ -278,6 +279,7 @@ def load_library(path=None):
     lib.mzb_set_host_evaluator.argtypes = [C.c_void_p, C.POINTER(_CHostEvaluator)]
     lib.mzb_value_encode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, fp]
     lib.mzb_value_decode.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, C.c_int, fp]
+    lib.mzb_value_decode_static.argtypes = [C.c_void_p, C.c_int, fp, C.c_int, C.c_int, fp]
     _lib = lib
     return lib
 
@@ -494,6 +496,14 @@ class Engine:
         lg = np.ascontiguousarray(logits, dtype=np.float32).reshape(-1, S)
         out = np.empty(lg.shape[0], np.float32)
         self._check(self.lib.mzb_value_decode(self._h, which, _ptr(lg, C.c_float), lg.shape[0], int(bool(take_softmax)), _ptr(out, C.c_float)))
+        return out
+
+    def value_decode_static(self, logits, which=0, take_softmax=True):
+        """value_decode without any device allocation (static scratch, at most VALUE_DECODE_STATIC_MAX_FLOATS = n * (S + 1) floats)"""
+        S = self.shapes.value_support_size if which == 0 else self.shapes.reward_support_size
+        lg = np.ascontiguousarray(logits, dtype=np.float32).reshape(-1, S)
+        out = np.empty(lg.shape[0], np.float32)
+        self._check(self.lib.mzb_value_decode_static(self._h, which, _ptr(lg, C.c_float), lg.shape[0], int(bool(take_softmax)), _ptr(out, C.c_float)))
         return out
 
     # VPRNetModel::LoadCheckpoint (vprnet.cpp:66-74): named fp32 tensors of the module archive
@@ -716,6 +726,9 @@ def legal_mask_from_actions(legal_actions, num_actions):
 
 
 # game presets = the shapes of BASELINE.json's configs
+VALUE_DECODE_STATIC_MAX_FLOATS = 1 << 20   # MZB_VALUE_DECODE_STATIC_MAX_FLOATS
+
+
 class Mt19937:
     """std::mt19937(seed) as a mzb_rng_fn source: numpy's MT19937 with the legacy (init_genrand) seeding is the same generator."""
 

@@ -418,6 +418,28 @@ def main():
                 d2, w2, _ = timed(run_dev, k2)
                 out["sustained"] = dict(value=world * T * nsim * k2 / (d2 / 1000.0), steps=k2, seconds=w2 / 1000.0, ms_per_step=d2 / k2, clocks=sp.stop())
         if world > 1:
+            # the hand-over DURING self-play (learner.cpp:93-101 while actors search): rank 0 gets new weights, every rank receives
+            # them into its shadow blob on the side stream while a search runs, and installs them between two searches
+            before = eng.weights_checksum()
+            if rank == 0:
+                eng.load_weights(random_weights(cfg, seed=4321))
+            dist.barrier()
+            run_dev()
+            plain_ms, _, _ = timed(run_dev, 3)
+            t0 = time.time()
+            eng.broadcast_weights_begin(0, rank)
+            begin_host_ms = 1000 * (time.time() - t0)
+            over_ms, _, _ = timed(run_dev, 3)          # searches on the OLD weights while the broadcast is in flight
+            t0 = time.time()
+            eng.weights_commit()
+            run_dev()                                  # first search on the new weights
+            commit_ms = 1000 * (time.time() - t0)
+            sums = [None] * world
+            dist.all_gather_object(sums, eng.weights_checksum())
+            assert len(set(sums)) == 1, "overlapped weight hand-over left replicas different"
+            assert rank == 0 or sums[rank] != before, "overlapped weight hand-over did not install the new weights"
+            out["weight_sync_overlapped"] = dict(begin_call_ms=begin_host_ms, search_ms_per_step_plain=plain_ms / 3,
+                                                 search_ms_per_step_during_broadcast=over_ms / 3, commit_plus_one_search_ms=commit_ms)
             t = torch.tensor([states_per_s], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
             roofline["states_per_s_all_gpus"] = float(t[0])
@@ -436,7 +458,7 @@ def main():
                 timing="CUDA events around each search on the engine's stream; max over ranks; node pool %.2f GB per GPU" % m["node_pool_gb"],
                 wall_ms_per_step=m["wall_ms_per_step"], clocks=m["clocks"], e2e=m["e2e"],
                 gpu_launches=m["gpu_launches"], roofline=m["roofline"], recurrent_states_per_s=m["states_per_s"], step_split=m["step_split"])
-    for k in ("weight_sync_ms", "weight_sync_first_ms", "weight_sync_bytes", "sustained"):
+    for k in ("weight_sync_ms", "weight_sync_first_ms", "weight_sync_bytes", "weight_sync_overlapped", "sustained"):
         if k in m:
             line[k] = m[k]
 

@@ -294,6 +294,7 @@ int mzb_weights_checksum(mzb_engine* e, uint64_t* out) {
     MZB_REQUIRE(e && out && e->net && e->weights_loaded, "no weights loaded");
     MZB_CUDA(cudaSetDevice(e->device));
     std::vector<uint8_t> h(e->net->blob_bytes());
+    MZB_CUDA(cudaStreamSynchronize(e->stream));   // a commit or a load queued on the search stream lands first
     MZB_CUDA(cudaMemcpy(h.data(), e->net->blob_ptr(), h.size(), cudaMemcpyDeviceToHost));
     uint64_t x = 1469598103934665603ULL;
     for (uint8_t b : h) { x ^= b; x *= 1099511628211ULL; }

@@ -196,6 +196,8 @@ public:
         if (env && std::string(env) == "fp32") precision = MZB_FP32_CHECK;
         st_->device = device;
         st_->path = config.path + "/checkpoints/";   // vprnet.cpp:32
+        st_->num_unroll_steps = config.num_unroll_steps; st_->value_loss_weight = config.value_loss_weight;
+        st_->learning_rate = config.network_config.learning_rate; st_->l2_weight_decay = config.network_config.l2_weight_decay;
         const int trees = std::max({config.num_actors + config.num_reanalyze_actors + config.num_evaluators,
                                     config.initial_inference_batch_size, config.recurrent_inference_batch_size, 1});
         const mzb_config pod = detail::to_pod(config, trees, precision, MZB_EVAL_NETWORK, &st_->planes);
@@ -298,6 +300,33 @@ public:
         li.total_loss = out.total_loss; li.value = out.value; li.policy = out.policy; li.reward = out.reward;
         return li;
     }
+    // vprnet.cpp:192-311, all of it: forward, loss, backward with Learn's gradient hooks, one torch::optim::Adam step with
+    // config.network_config.learning_rate / l2_weight_decay (vprnet.cpp:35-36), fp32 on the GPU (mzb_learn_step).  Like the
+    // reference's model, this one answers inference with the trained tensors right after the call (`commit`, the default); a learner
+    // that only hands weights over every checkpoint_interval steps passes commit = false and calls CommitLearnedWeights() then.
+    template <class Batch>
+    LossInfo Learn(Batch& inputs, bool commit = true) {
+        std::vector<int32_t> actions(inputs.actions.begin(), inputs.actions.end());
+        LossInfo li;
+        li.indices = inputs.indices;
+        li.errors.assign(inputs.num_samples, 0.0);
+        mzb_batch b{};
+        b.num_samples = inputs.num_samples; b.actions = actions.data(); b.stacked_observations = inputs.stacked_observations.data();
+        b.target_values = inputs.target_values.data(); b.target_rewards = inputs.target_rewards.data();
+        b.target_policies = inputs.target_policies.data(); b.gradient_scale = inputs.gradient_scale.data(); b.priorities = inputs.priorities.data();
+        mzb_loss_info out{};
+        out.errors = li.errors.data();
+        std::lock_guard<std::mutex> call(st_->engine->call_mutex());
+        mzb200::check(mzb_learn_step(st_->engine->handle(), &b, st_->num_unroll_steps, st_->value_loss_weight, st_->learning_rate, st_->l2_weight_decay, &out),
+                      "mzb_learn_step");
+        if (commit) mzb200::check(mzb_learn_commit(st_->engine->handle()), "mzb_learn_commit");
+        li.total_loss = out.total_loss; li.value = out.value; li.policy = out.policy; li.reward = out.reward;
+        return li;
+    }
+    void CommitLearnedWeights() {
+        std::lock_guard<std::mutex> call(st_->engine->call_mutex());
+        mzb200::check(mzb_learn_commit(st_->engine->handle()), "mzb_learn_commit");
+    }
     const std::string Device() const { return st_->device; }
 
     // mzb200 side
@@ -327,6 +356,8 @@ private:
         std::shared_ptr<mzb200::Cohort> cohort;
         mzb_shapes shapes;
         int num_actions = 0;
+        int num_unroll_steps = 5;
+        double value_loss_weight = 1, learning_rate = 3e-4, l2_weight_decay = 1e-4;
     };
     std::unique_ptr<State> st_;
 };

@@ -176,6 +176,17 @@ typedef struct {
 } mzb_loss_info;
 int mzb_learn_forward(mzb_engine* e, const mzb_batch* batch, int num_unroll_steps, double value_loss_weight, mzb_loss_info* out);
 int mzb_learn_get_tensor(mzb_engine* e, const char* name, float* out, int64_t numel);
+/* Replaces: the whole of VPRNetModel::Learn (vprnet.cpp:192-311) — forward as mzb_learn_forward, then total_loss.backward() with
+ * Learn's gradient hooks (x0.5 on every recurrent hidden state, gradient_scale on the losses of unroll steps >= 1) and
+ * model_optimizer_.step() = torch::optim::Adam(lr, weight_decay = l2) (vprnet.cpp:35-36; betas 0.9 / 0.999, eps 1e-8), fp32 on the GPU.
+ * Parameters, gradients and Adam moments stay resident on the device between calls; a load (mzb_load_weights / _checkpoint) starts the
+ * optimizer over, like constructing a new VPRNetModel.  mzb_learn_get_tensor reads a trained tensor back, mzb_learn_get_gradient
+ * the gradient of the last step.  mzb_learn_commit = the learner -> actor hand-over on one GPU (learner.cpp:93-101): the trained
+ * tensors become the weights the engine searches with and mzb_save_checkpoint writes. */
+int mzb_learn_step(mzb_engine* e, const mzb_batch* batch, int num_unroll_steps, double value_loss_weight, double learning_rate,
+                   double l2_weight_decay, mzb_loss_info* out);
+int mzb_learn_get_gradient(mzb_engine* e, const char* name, float* out, int64_t numel);
+int mzb_learn_commit(mzb_engine* e);
 
 /* Replaces: PrioritizedReplayBuffer (replay_buffer.cpp:15-141) over SumTree (replay_buffer.h:28-209) and the target construction of
  * GameHistory (compute_target_value / make_target / get_stacked_observations, types.cpp:16-95) — SURVEY.md 8f rank 4.  The sum tree

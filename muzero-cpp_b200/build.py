@@ -24,6 +24,7 @@ SOURCES = [
     ("value_encoder.cu", ["-fmad=false"]),
     ("selfplay.cu", []),
     ("learn.cu", []),
+    ("learn_step.cu", []),
     ("replay.cu", ["-fmad=false"]),
 ]
 

@@ -214,6 +214,7 @@ void mzb_engine_destroy(mzb_engine* e) {
     if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) if (e->ev_join[i]) cudaEventDestroy(e->ev_join[i]);
     for (int k = 0; k < 2; ++k) { if (e->ev_se_out[k]) cudaEventDestroy(e->ev_se_out[k]); if (e->ev_se_mv[k]) cudaEventDestroy(e->ev_se_mv[k]); }
+    if (e->learn_step && e->learn_step_free) e->learn_step_free(e->learn_step);
     mzb_nccl_release(e);
     if (e->sync_stream) cudaStreamDestroy(e->sync_stream);
     if (e->ev_sync) cudaEventDestroy(e->ev_sync);

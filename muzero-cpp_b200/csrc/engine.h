@@ -58,6 +58,9 @@ struct mzb_engine {
     // training state of mzb_learn_forward (learn.cu): the module's tensors with BatchNorm running statistics as moved so far
     std::map<std::string, std::vector<float>> learn_state;
     int64_t learn_state_serial = -1;
+    bool learn_host_dirty = false;                            // mzb_learn_forward moved statistics the device training state has not seen
+    void* learn_step = nullptr;                               // device-resident training state of mzb_learn_step (learn_step.cu)
+    void (*learn_step_free)(void*) = nullptr;
     std::vector<float> action_planes;   // owned copy of cfg.action_planes
     static constexpr int MAX_PARTS = 4;
     cudaStream_t stream = nullptr, aux = nullptr;
@@ -103,5 +106,6 @@ struct mzb_engine {
 
 
 namespace mzb {
+int learn_sync_host(mzb_engine* e);   // learn_step.cu: device training state -> e->learn_state (no-op when nothing is newer there)
 int ensure_pinned(mzb_engine* e, size_t bytes);
 }

@@ -280,6 +280,10 @@ int mzb_learn_forward(mzb_engine* e, const mzb_batch* batch, int num_unroll_step
                 "null batch field");
     for (int i = 0; i < B * K1; ++i) MZB_REQUIRE(batch->actions[i] >= 0 && batch->actions[i] < A, "batch action %d outside the action space", batch->actions[i]);
     MZB_CUDA(cudaSetDevice(e->device));
+    {   // tensors trained by mzb_learn_step since the last look are the current ones
+        const int src = learn_sync_host(e);
+        if (src) return src;
+    }
     try {
         LearnNet net;
         net.e = e; net.s = e->stream;
@@ -359,6 +363,7 @@ int mzb_learn_forward(mzb_engine* e, const mzb_batch* batch, int num_unroll_step
             if (rs) MZB_CUDA(cudaMemcpyAsync(kv.second.data(), net.W[n].p, kv.second.size() * sizeof(float), cudaMemcpyDeviceToHost, net.s));
         }
         MZB_CUDA(cudaStreamSynchronize(net.s));
+        e->learn_host_dirty = true;
         // per-sample sums -> LossInfo (vprnet.cpp:293-310)
         double sv = 0, sr = 0, sp = 0, st = 0, spri = 0;
         for (int b = 0; b < B; ++b) {
@@ -384,6 +389,10 @@ int mzb_learn_forward(mzb_engine* e, const mzb_batch* batch, int num_unroll_step
 // a tensor of the training state (BatchNorm running statistics after mzb_learn_forward calls; everything else as loaded)
 int mzb_learn_get_tensor(mzb_engine* e, const char* name, float* out, int64_t numel) {
     MZB_REQUIRE(e && name && out, "null argument");
+    {
+        const int src = learn_sync_host(e);
+        if (src) return src;
+    }
     auto it = e->learn_state.find(name);
     MZB_REQUIRE(it != e->learn_state.end(), "no tensor %s in the training state (call mzb_learn_forward first)", name);
     MZB_REQUIRE((int64_t)it->second.size() == numel, "tensor %s has %zu elements, not %lld", name, it->second.size(), (long long)numel);

@@ -200,7 +200,7 @@ EXPORTS = ["mzb_last_error", "mzb_version", "mzb_engine_create", "mzb_engine_des
            "mzb_actor_seed", "mzb_select_actions", "mzb_actor_uniform_int", "mzb_set_host_evaluator",
            "mzb_checkpoint_open", "mzb_checkpoint_count", "mzb_checkpoint_tensor", "mzb_checkpoint_close", "mzb_load_checkpoint",
            "mzb_checkpoint_long_count", "mzb_checkpoint_long", "mzb_checkpoint_write", "mzb_save_checkpoint",
-           "mzb_learn_forward", "mzb_learn_get_tensor",
+           "mzb_learn_forward", "mzb_learn_get_tensor", "mzb_learn_step", "mzb_learn_get_gradient", "mzb_learn_commit",
            "mzb_replay_create", "mzb_replay_destroy", "mzb_replay_save_game_history", "mzb_replay_size", "mzb_replay_can_sample",
            "mzb_replay_num_histories", "mzb_replay_total_priority", "mzb_replay_oldest_history", "mzb_replay_sample", "mzb_replay_update_priorities",
            "mzb_replay_sample_game", "mzb_replay_update_game_history",
@@ -261,6 +261,9 @@ def load_library(path=None):
     lib.mzb_save_checkpoint.argtypes = [C.c_void_p, C.c_char_p]
     lib.mzb_learn_forward.argtypes = [C.c_void_p, C.POINTER(_CBatch), C.c_int, C.c_double, C.POINTER(_CLossInfo)]
     lib.mzb_learn_get_tensor.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_float), C.c_int64]
+    lib.mzb_learn_get_gradient.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_float), C.c_int64]
+    lib.mzb_learn_step.argtypes = [C.c_void_p, C.POINTER(_CBatch), C.c_int, C.c_double, C.c_double, C.c_double, C.POINTER(_CLossInfo)]
+    lib.mzb_learn_commit.argtypes = [C.c_void_p]
     lib.mzb_replay_create.argtypes = [C.c_void_p, C.POINTER(_CReplayConfig), C.POINTER(C.c_void_p)]
     lib.mzb_replay_destroy.argtypes = [C.c_void_p]
     lib.mzb_replay_destroy.restype = None
@@ -547,6 +550,35 @@ class Engine:
         li = _CLossInfo(0.0, 0.0, 0.0, 0.0, _ptr(errors, C.c_double))
         self._check(self.lib.mzb_learn_forward(self._h, C.byref(b), K1 - 1, float(value_loss_weight), C.byref(li)))
         return dict(total_loss=li.total_loss, value=li.value, policy=li.policy, reward=li.reward, errors=errors)
+
+    def learn_step(self, stacked_observations, actions, target_values, target_rewards, target_policies, priorities,
+                   gradient_scale=None, value_loss_weight=0.25, learning_rate=3e-4, l2_weight_decay=1e-4):
+        """VPRNetModel::Learn (vprnet.cpp:192-311): forward, loss, backward with Learn's gradient hooks, one Adam step.  Same
+        arguments and return value as learn_forward."""
+        act = np.ascontiguousarray(actions, dtype=np.int32)
+        B, K1 = act.shape
+        obs = np.ascontiguousarray(stacked_observations, dtype=np.float32).reshape(B, self.shapes.initial_flat_size)
+        tv = np.ascontiguousarray(target_values, dtype=np.float64).reshape(B, K1)
+        tr = np.ascontiguousarray(target_rewards, dtype=np.float64).reshape(B, K1)
+        tp = np.ascontiguousarray(target_policies, dtype=np.float64).reshape(B, K1, self.config.num_actions)
+        pr = np.ascontiguousarray(priorities, dtype=np.float64).reshape(B)
+        gs = np.ascontiguousarray(gradient_scale if gradient_scale is not None else np.full(B, 1.0 / max(1, K1 - 1)), dtype=np.float64).reshape(B)
+        errors = np.empty(B, np.float64)
+        b = _CBatch(B, _ptr(act, C.c_int32), _ptr(obs, C.c_float), _ptr(tv, C.c_double), _ptr(tr, C.c_double), _ptr(tp, C.c_double),
+                    _ptr(gs, C.c_double), _ptr(pr, C.c_double))
+        li = _CLossInfo(0.0, 0.0, 0.0, 0.0, _ptr(errors, C.c_double))
+        self._check(self.lib.mzb_learn_step(self._h, C.byref(b), K1 - 1, float(value_loss_weight), float(learning_rate), float(l2_weight_decay), C.byref(li)))
+        return dict(total_loss=li.total_loss, value=li.value, policy=li.policy, reward=li.reward, errors=errors)
+
+    def learn_gradient(self, name, shape):
+        """the gradient the last learn_step left on a parameter"""
+        out = np.empty(shape, np.float32)
+        self._check(self.lib.mzb_learn_get_gradient(self._h, name.encode(), _ptr(out, C.c_float), int(out.size)))
+        return out
+
+    def learn_commit(self):
+        """the trained tensors become the engine's search weights (and what save_checkpoint writes)"""
+        self._check(self.lib.mzb_learn_commit(self._h))
 
     def learn_tensor(self, name, shape):
         """a tensor of the training state (BatchNorm running statistics as moved by learn_forward calls)"""

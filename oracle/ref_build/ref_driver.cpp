@@ -31,6 +31,11 @@
 #include <thread>
 #include <vector>
 
+// learn mode reads the gradients Learn() leaves on the module's parameters: VPRNetModel keeps the module private, so this test
+// driver (and nothing else) opens the class up.  The reference sources stay unmodified; GCC lays the class out the same way.
+#define private public
+#include "muzero-cpp/vprnet.h"
+#undef private
 #include "muzero-cpp/config.h"
 #include "muzero-cpp/device_manager.h"
 #include "muzero-cpp/mcts.h"
@@ -397,6 +402,8 @@ static int mode_learn(const Args& a) {
     const int B = a.i("batch", 6), seed = a.i("seed", 0);
     c.num_unroll_steps = a.i("unroll", 5);
     c.value_loss_weight = a.d("value_loss_weight", 0.25);
+    c.network_config.learning_rate = a.d("lr", c.network_config.learning_rate);
+    c.network_config.l2_weight_decay = a.d("l2", c.network_config.l2_weight_decay);
     torch::manual_seed(seed);
     model::MuzeroNetwork net(c);
     if (a.has("ckpt")) { torch::load(net, a.str("ckpt", ""), torch::Device(torch::kCPU)); }
@@ -437,9 +444,41 @@ static int mode_learn(const Args& a) {
     add_f64(w, "in.target_policies", {B, K1, A}, batch.target_policies);
     add_f64(w, "in.gradient_scale", {B}, batch.gradient_scale);
     add_f64(w, "in.priorities", {B}, batch.priorities);
+    // steps=N: N Learn calls on the same batch (the optimizer's moments and the BatchNorm buffers move from call to call)
+    const int n_steps = a.i("steps", 1);
     VPRNetModel::LossInfo li = vm.Learn(batch);
+    std::vector<double> all_losses = {li.total_loss, li.value, li.policy, li.reward};
+    for (int it = 1; it < n_steps; ++it) {
+        li = vm.Learn(batch);
+        for (double v : {li.total_loss, li.value, li.policy, li.reward}) all_losses.push_back(v);
+    }
     add_f64(w, "out.losses", {4}, {li.total_loss, li.value, li.policy, li.reward});
+    add_f64(w, "out.all_losses", {n_steps, 4}, all_losses);
     add_f64(w, "out.errors", {(int64_t)li.errors.size()}, li.errors);
+    if (a.has("grads")) {
+        // what backward() left on the parameters in the LAST call, and the parameters after the last optimizer step.
+        // grads=full: every tensor; grads=digest: per tensor {sum g^2, sum g_i cos(0.731 i)} and {the same of the parameter}
+        const bool full = a.str("grads", "full") == "full";
+        for (auto& kv : vm.model_->named_parameters()) {
+            torch::Tensor g = kv.value().grad();
+            if (!g.defined()) continue;
+            torch::Tensor p = kv.value().detach();
+            if (full) {
+                add_tensor_f32(w, "grad." + kv.key(), g);
+                add_tensor_f32(w, "param." + kv.key(), p);
+            } else {
+                torch::Tensor probe = torch::cos(torch::arange(g.numel(), torch::kFloat64) * 0.731);
+                auto dig = [&](const torch::Tensor& t) {
+                    torch::Tensor f = t.contiguous().view({-1}).to(torch::kFloat64);
+                    return std::vector<double>{(f * f).sum().item<double>(), (f * probe).sum().item<double>()};
+                };
+                add_f64(w, "graddigest." + kv.key(), {2}, dig(g));
+                add_f64(w, "paramdigest." + kv.key(), {2}, dig(p));
+            }
+        }
+        std::vector<double> hp = {c.network_config.learning_rate, c.network_config.l2_weight_decay};
+        add_f64(w, "meta.optimizer", {2}, hp);
+    }
     // BatchNorm buffers after the call: through the model's own checkpoint
     std::string after = vm.SaveCheckpoint(-8);
     model::MuzeroNetwork net2(c);

@@ -275,3 +275,57 @@ class VPRNetOracle:
         total = (pri * (value_loss * value_loss_weight + reward_loss + policy_loss)).mean()
         return dict(total_loss=float(total), value=float(value_loss.mean()), policy=float(policy_loss.mean()),
                     reward=float(reward_loss.mean()), errors=errors.numpy().astype(np.float64))
+
+    def learn_step(self, obs_flat, actions, target_values, target_rewards, target_policies, priorities, gradient_scale,
+                   value_loss_weight=0.25, learning_rate=3e-4, l2_weight_decay=1e-4):
+        """The whole of VPRNetModel::Learn (vprnet.cpp:192-311) on torch autograd: the forward of learn_forward, the gradient hooks
+        (x0.5 on every recurrent hidden state :272, gradient_scale on the step losses :278-286), backward, and
+        torch::optim::Adam(lr).weight_decay(l2) (vprnet.cpp:35-36).  The optimizer persists across calls.  Returns the LossInfo
+        fields; self.grads holds what backward() left on every parameter."""
+        c = self.cfg
+        eh, ew = c.enc_hw
+        actions = np.asarray(actions)
+        B, K1 = actions.shape
+        names = [k for k in self.W if not (k.endswith("running_mean") or k.endswith("running_var"))]
+        if not hasattr(self, "_opt"):
+            for k in names:
+                self.W[k] = self.W[k].clone().requires_grad_(True)
+            self._opt = torch.optim.Adam([self.W[k] for k in names], lr=learning_rate, weight_decay=l2_weight_decay)
+        obs = torch.as_tensor(np.asarray(obs_flat), dtype=torch.float32).reshape(B, c.in_channels, c.obs_shape[1], c.obs_shape[2])
+        tv = torch.as_tensor(np.asarray(target_values, np.float64)).to(torch.float32).reshape(B, K1)
+        tr = torch.as_tensor(np.asarray(target_rewards, np.float64)).to(torch.float32).reshape(B, K1)
+        tp = torch.as_tensor(np.asarray(target_policies, np.float64)).to(torch.float32).reshape(B, K1, c.num_actions)
+        pri = torch.as_tensor(np.asarray(priorities, np.float64)).to(torch.float32).reshape(B, 1)
+        gs = torch.as_tensor(np.asarray(gradient_scale, np.float64)).to(torch.float32).reshape(B)
+        tve, tre = self.value_encoder.encode(tv), self.reward_encoder.encode(tr)
+
+        def loss(logits, target):
+            return torch.sum(-target * torch.log_softmax(logits, 1), -1)
+        TRAIN[0] = True
+        try:
+            with torch.enable_grad():
+                h = self.representation(obs)
+                p, v = self.prediction(h)
+                value_loss, policy_loss = loss(v, tve[:, 0]), loss(p, tp[:, 0])
+                reward_loss = torch.zeros_like(value_loss)
+                errors = (self.value_encoder.decode(v.detach()) - tv[:, 0:1].to(torch.float64))[:, 0]
+                for step in range(1, K1):
+                    act = torch.empty(B, c.action_channels, eh, ew)
+                    for b in range(B):
+                        act[b].fill_(float(np.float32(float(int(actions[b, step])) / c.num_actions)))
+                    h, r = self.dynamics(h, act)
+                    p, v = self.prediction(h)
+                    h.register_hook(lambda g: g * 0.5)
+                    lv, lr_, lp = loss(v, tve[:, step]), loss(r, tre[:, step]), loss(p, tp[:, step])
+                    for t in (lv, lr_, lp):
+                        t.register_hook(lambda g: g * gs)
+                    value_loss, reward_loss, policy_loss = value_loss + lv, reward_loss + lr_, policy_loss + lp
+                total = (pri * (value_loss * value_loss_weight + reward_loss + policy_loss)).mean()
+                self._opt.zero_grad()
+                total.backward()
+                self.grads = {k: self.W[k].grad.detach().clone() for k in names if self.W[k].grad is not None}
+                self._opt.step()
+        finally:
+            TRAIN[0] = False
+        return dict(total_loss=float(total.detach()), value=float(value_loss.detach().mean()), policy=float(policy_loss.detach().mean()),
+                    reward=float(reward_loss.detach().mean()), errors=errors.numpy().astype(np.float64))

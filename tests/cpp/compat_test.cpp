@@ -717,11 +717,62 @@ static void save_and_reload(const std::string& golden_dir) {
         EXPECT(oa[i].value == ob[i].value && oa[i].policy == ob[i].policy && oa[i].encoded_state == ob[i].encoded_state, "reloaded model answers differently (sample %d)", i);
 }
 
+// (9) VPRNetModel::Learn(batch) (vprnet.cpp:192-311) under the reference's name: repeated calls on one batch drive its loss down,
+//     the model answers inference with the trained tensors right away, and a checkpoint saved after training reloads to the same
+//     answers (the numerics of one step are checked against the unmodified reference in tests/test_learn.py)
+static void learn_under_the_reference_name(const std::string& golden_dir) {
+    muzero_config::MuZeroConfig config = tiny_config(2);
+    char tmpl[] = "/tmp/mzb_compat_learn_XXXXXX";
+    const char* dir = mkdtemp(tmpl);
+    if (!dir) { EXPECT(false, "mkdtemp failed"); return; }
+    config.path = dir;
+    config.num_unroll_steps = 3;
+    config.value_loss_weight = 0.25;
+    config.network_config.learning_rate = 3e-3;
+    VPRNetModel m(config, "cuda:0", MZB_FP32_CHECK);
+    m.LoadCheckpoint(golden_dir + "/checkpoint_tiny");
+    const int B = 8, K1 = 4, A = (int)config.action_space.size();
+    Batch batch;
+    batch.num_samples = B;
+    std::mt19937 rng(5);
+    std::uniform_real_distribution<double> u(0.0, 1.0);
+    for (int b = 0; b < B; ++b) {
+        batch.indices.push_back(b);
+        batch.priorities.push_back(0.5 + 0.5 * u(rng));
+        batch.gradient_scale.push_back(1.0 / config.num_unroll_steps);
+        for (int i = 0; i < 60; ++i) batch.stacked_observations.push_back((float)u(rng));
+        for (int k = 0; k < K1; ++k) {
+            batch.actions.push_back((int)(rng() % A));
+            batch.target_values.push_back(-4 + 8 * u(rng));
+            batch.target_rewards.push_back(-2 + 4 * u(rng));
+            std::vector<double> p(A);
+            double sum = 0;
+            for (double& x : p) { x = u(rng); sum += x; }
+            for (double x : p) batch.target_policies.push_back(x / sum);
+        }
+    }
+    std::vector<VPRNetModel::InitialInferenceInputs> in(1);
+    in[0].stacked_observation.assign(batch.stacked_observations.begin(), batch.stacked_observations.begin() + 60);
+    const auto before = m.InitialInference(in);
+    VPRNetModel::LossInfo first = m.Learn(batch), last = first;
+    EXPECT(first.errors.size() == (size_t)B && first.indices == batch.indices, "LossInfo fields");
+    for (int it = 0; it < 60; ++it) last = m.Learn(batch, /*commit=*/it == 59);
+    EXPECT(std::isfinite(last.total_loss) && last.total_loss < 0.8 * first.total_loss, "training did not reduce the loss: %g -> %g", first.total_loss, last.total_loss);
+    const auto after = m.InitialInference(in);
+    EXPECT(after[0].policy != before[0].policy, "inference still answers with the untrained weights");
+    const std::string saved = m.SaveCheckpoint(3);
+    VPRNetModel r(config, "cuda:0", MZB_FP32_CHECK);
+    r.LoadCheckpoint(3);
+    const auto again = r.InitialInference(in);
+    EXPECT(again[0].policy == after[0].policy && again[0].value == after[0].value, "a checkpoint saved after training reloads differently");
+    std::printf("compat_test: Learn x61 on one batch: total loss %.4f -> %.4f\n", first.total_loss, last.total_loss);
+}
+
 int main(int argc, char** argv) {
     try {
         reference_unit_tests();
         appendix_b();
-        if (argc > 1) { network_paths(argv[1]); self_play_cohort(argv[1]); device_manager_policies(argv[1]); save_and_reload(argv[1]); }
+        if (argc > 1) { network_paths(argv[1]); self_play_cohort(argv[1]); device_manager_policies(argv[1]); save_and_reload(argv[1]); learn_under_the_reference_name(argv[1]); }
     } catch (const std::exception& e) {
         std::printf("compat_test: %s\n", e.what());
         return 1;

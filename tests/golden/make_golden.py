@@ -10,6 +10,8 @@ Outputs (committed):
   net_tinyds.mzbt same for the downsample head
   checkpoint_c4r_trained.pt / net_c4r_trained.mzbt  the shipped trained Connect4 checkpoint + the reference's outputs on it
   encoder.json    ValueEncoder support sizes and decode known answers
+  learn_step_{tiny,tinyds,c4r}.mzbt  2-3 VPRNetModel::Learn calls on one batch: losses per call, gradients left by the last backward() and
+                                 parameters after the last Adam step (c4r: two digests per tensor instead of the tensors)
   learn_{tiny,tinyds,c4r}.mzbt  one VPRNetModel::Learn call: batch, losses, per-sample errors, BatchNorm statistics afterwards
 """
 import json
@@ -74,9 +76,14 @@ def main():
     import helpers as Hh
     import mzb200
     from oracle import vprnet_oracle as Vv
+    # the whole training step (forward, backward, Adam) twice on the same batch: gradients of the last call and parameters after it
+    O.run_ref("learn", "game=tiny", "batch=6", "seed=3", "steps=2", "grads=full", "lr=0.01", "l2=0.001", "out=" + os.path.join(HERE, "learn_step_tiny.mzbt"))
+    O.run_ref("learn", "game=tinyds", "batch=3", "seed=4", "steps=2", "grads=full", "out=" + os.path.join(HERE, "learn_step_tinyds.mzbt"))
     mzb200.write_checkpoint("/tmp/mzb_learn_c4r_w.pt", Hh.random_weights(Vv.preset("c4r"), seed=5))
     O.run_ref("learn", "game=c4r", "batch=8", "seed=9", "binary_obs=1", "no_weights", "ckpt=/tmp/mzb_learn_c4r_w.pt",
               "post_filter=representation_network.representation_head", "out=" + os.path.join(HERE, "learn_c4r.mzbt"))
+    O.run_ref("learn", "game=c4r", "batch=8", "seed=9", "binary_obs=1", "no_weights", "ckpt=/tmp/mzb_learn_c4r_w.pt", "steps=1", "grads=digest",
+              "post_filter=representation_network.representation_head", "out=" + os.path.join(HERE, "learn_step_c4r.mzbt"))
     enc = []
     for lo, hi, extra in [(-10, 10, []), (-22, 22, []), (-1, 1, []), (-21, 21, []), (-300, 300, []), (-5, 7, ["no_contractive"])]:
         txt = O.run_ref("encoder", "min=%g" % lo, "max=%g" % hi, "rows=6", "seed=1", *extra)

@@ -62,11 +62,11 @@ struct mzb_engine {
     void* learn_step = nullptr;                               // device-resident training state of mzb_learn_step (learn_step.cu)
     void (*learn_step_free)(void*) = nullptr;
     std::vector<float> action_planes;   // owned copy of cfg.action_planes
-    static constexpr int MAX_PARTS = 4;
+    static constexpr int MAX_PARTS = 8;
     cudaStream_t stream = nullptr, aux = nullptr;
-    cudaStream_t pipe[MAX_PARTS - 1] = {nullptr, nullptr, nullptr};   // streams of parts 1.. of the pipelined simulation loop (part 0 runs on `stream`)
+    cudaStream_t pipe[MAX_PARTS - 1] = {};   // streams of parts 1.. of the pipelined simulation loop (part 0 runs on `stream`)
     cudaEvent_t ev_start = nullptr, ev_root = nullptr, ev_end = nullptr, ev_aux = nullptr, ev_fork = nullptr;
-    cudaEvent_t ev_join[MAX_PARTS - 1] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev_join[MAX_PARTS - 1] = {};
     // trees
     TreeDev td;
     DevBuf meta, prior, value_sum, reward, mm_min, mm_max, root_to_play, n_legal, n_slots, max_depth, mt, mt_idx,

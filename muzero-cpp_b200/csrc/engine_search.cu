@@ -126,7 +126,7 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
         cudaStream_t st[mzb_engine::MAX_PARTS];
         int t0[mzb_engine::MAX_PARTS + 1];
         NetOutputs o[mzb_engine::MAX_PARTS];
-        for (int k = 0; k <= K; ++k) t0[k] = (int)((long)T * k / K);
+        e->net->pipeline_cut(T, K, t0);
         MZB_CUDA(cudaEventRecord(e->ev_fork, s));
         for (int k = 0; k < K; ++k) {
             st[k] = k == 0 ? s : e->pipe[k - 1];
@@ -135,16 +135,40 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
             o[k].value += t0[k]; o[k].reward += t0[k]; o[k].policy += (size_t)t0[k] * A;
         }
         e->net->set_pipelined(true);
+        // MZB_PIPELINE_TRACE=1: a timed event behind every launch, printed as a timeline after the search (diagnostic only)
+        static const bool trace = getenv("MZB_PIPELINE_TRACE") != nullptr;
+        std::vector<cudaEvent_t> tev;
+        auto mark = [&](cudaStream_t q) { if (trace) { cudaEvent_t ev; cudaEventCreate(&ev); cudaEventRecord(ev, q); tev.push_back(ev); } };
         for (int sim = 0; sim <= n && !rc; ++sim) {
             for (int k = 0; k < K && !rc; ++k) {
                 launch_tree_step_range(td, t0[k], t0[k + 1], sim, st[k]);
                 ++launches;
+                mark(st[k]);
                 if (sim == n) continue;
                 rc = e->net->recurrent(t0[k + 1] - t0[k], td.in_slot + t0[k], td.action + t0[k], td.out_slot + t0[k], o[k], st[k]);
                 launches += e->net->launches_recurrent();
+                mark(st[k]);
             }
         }
         e->net->set_pipelined(false);
+        if (trace) {
+            for (int k = 0; k < K; ++k) cudaStreamSynchronize(st[k]);
+            fprintf(stderr, "[pipeline] parts:");
+            for (int k = 0; k < K; ++k) fprintf(stderr, " %d", t0[k + 1] - t0[k]);
+            fprintf(stderr, " trees; end of (tree step | tower) per part, us since the root event\n");
+            size_t i = 0;
+            for (int sim = 0; sim <= n && sim < (getenv("MZB_PIPELINE_TRACE_ALL") ? n + 1 : 8); ++sim) {
+                fprintf(stderr, "[pipeline] sim %2d:", sim);
+                for (int k = 0; k < K; ++k) {
+                    float a = 0.f, b = 0.f;
+                    cudaEventElapsedTime(&a, e->ev_root, tev[i++]);
+                    if (sim < n) cudaEventElapsedTime(&b, e->ev_root, tev[i++]);
+                    fprintf(stderr, "  part %d: %8.1f | %8.1f", k, a * 1e3f, b * 1e3f);
+                }
+                fprintf(stderr, "\n");
+            }
+            for (cudaEvent_t ev : tev) cudaEventDestroy(ev);
+        }
         // join the side streams into the search stream — also when a launch failed, so that no work is left running on them
         // behind the caller's back
         for (int k = 1; k < K; ++k) {

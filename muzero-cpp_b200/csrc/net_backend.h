@@ -43,6 +43,9 @@ public:
     // hint: the following recurrent() calls are parts of a pipelined loop (the GPU always has another part's CTAs to run), so
     // tiles should be as full as possible rather than balanced over the SMs of one launch
     virtual void set_pipelined(bool) {}
+    // cut points t0[0..K] of a cohort of T trees into the K parts of a pipelined loop.  Default: equal parts.  A backend that
+    // knows its tile geometry cuts so that every part's launch is whole waves of tiles over the SMs (net_bf16.cu)
+    virtual void pipeline_cut(int T, int K, int* t0) const { for (int k = 0; k <= K; ++k) t0[k] = (int)((long)T * k / K); }
     virtual int launches_initial() const = 0;
     virtual int launches_recurrent() const = 0;
 };

@@ -695,9 +695,14 @@ protected:
             if (pipelined_) {
                 // part of a pipelined loop: full tiles (a tile costs nearly the same whatever it holds — the weight stream and the
                 // fixed phases do not shrink with it), the remainder spread over the last tiles
-                const int nt = (B + gmax - 1) / gmax;
+                // (MZB_PIPELINE_SM_CUT=1, experiment: smaller tiles on every SM instead — measured slower)
+                int nt = (B + gmax - 1) / gmax;
+                if (nt < S && getenv("MZB_PIPELINE_SM_CUT")) nt = std::min(S, B);
                 int g = 0;
-                for (int k = 0; k < nt; ++k) { const int part = B / nt + (k >= nt - B % nt ? 1 : 0); first.push_back(g); count.push_back(part); g += part; }
+                // the larger tiles FIRST: CTAs are handed out in index order, so the SMs that come free first take them and the
+                // SMs that run late get the smaller ones — a late SM catches up instead of falling further behind every simulation
+                // (the next launch of this part waits for the LAST tile, then for the tree step)
+                for (int k = 0; k < nt; ++k) { const int part = B / nt + (k < B % nt ? 1 : 0); first.push_back(g); count.push_back(part); g += part; }
             } else {
             const int per = (B + S - 1) / S;
             const int waves = (per + gmax - 1) / gmax;
@@ -764,6 +769,14 @@ protected:
             if (tim_.bytes < need) MZB_CUDA(tim_.alloc(need));
             MZB_CUDA(cudaMemsetAsync(tim_.p, 0, need, s));
             a.tim = tim_.as<long long>();
+        }
+        // MZB_TILE_TRACE=1 (diagnostic): every launch's tiles stamp their start / end; dump_tile_trace() prints them per launch
+        static const bool tile_trace = getenv("MZB_TILE_TRACE") != nullptr;
+        a.tile_trace = nullptr;
+        if (tile_trace && trace_launches_.size() < 256) {
+            if (!trace_.p) MZB_CUDA(trace_.alloc((size_t)256 * 1024 * 4 * sizeof(long long)));
+            a.tile_trace = trace_.as<long long>() + trace_launches_.size() * 1024 * 4;
+            trace_launches_.push_back(std::min(tt->n_tiles, 1024));
         }
         fused::tower_fused_kernel<<<tt->n_tiles, fused::F_THREADS, ch.smem, s>>>(a);
         MZB_CUDA(cudaGetLastError());
@@ -844,7 +857,46 @@ protected:
 
 public:
     // the one-launch fused recurrent pass keeps everything in shared memory / TMEM: no global scratch shared between calls
-    void set_pipelined(bool on) override { pipelined_ = on; }
+    void set_pipelined(bool on) override { pipelined_ = on; if (!on) dump_tile_trace(); }
+    void dump_tile_trace() {
+        if (trace_launches_.empty()) return;
+        cudaDeviceSynchronize();
+        std::vector<long long> h((size_t)trace_launches_.size() * 1024 * 4);
+        cudaMemcpy(h.data(), trace_.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
+        long long t_ref = h[0];
+        for (size_t l = 0; l < trace_launches_.size(); ++l) {
+            const long long* r = &h[l * 1024 * 4];
+            long long s0 = r[0], s1 = r[0], e0 = r[1], e1 = r[1];
+            double cyc = 0, ns = 0;
+            for (int t = 0; t < trace_launches_[l]; ++t) {
+                s0 = std::min(s0, r[t * 4]); s1 = std::max(s1, r[t * 4]); e0 = std::min(e0, r[t * 4 + 1]); e1 = std::max(e1, r[t * 4 + 1]);
+                cyc += (double)(r[t * 4 + 3] - r[t * 4 + 2]); ns += (double)(r[t * 4 + 1] - r[t * 4]);
+            }
+            const int n = trace_launches_[l];
+            fprintf(stderr, "[tiles] launch %3zu: %3d tiles; CTA starts %8.1f .. %8.1f us, ends %8.1f .. %8.1f us; per tile %7.0f cycles in %6.1f us (%.0f MHz)\n", l, n,
+                    (s0 - t_ref) * 1e-3, (s1 - t_ref) * 1e-3, (e0 - t_ref) * 1e-3, (e1 - t_ref) * 1e-3, cyc / n, ns / n * 1e-3, cyc / ns * 1e3);
+        }
+        trace_launches_.clear();
+    }
+    // EXPERIMENT (MZB_PIPELINE_SM_CUT=1; default = equal parts): two parts whose launches are whole waves over the SMs.
+    // q = games per SM and simulation.  One wave's worth or less (q <= gmax): the parts take ceil(q/2) and floor(q/2) games
+    // per SM.  More: part 0 takes floor(waves/2) waves of full tiles, part 1 the rest (C4d, T = 1024, 148 SMs: q = 7 -> 592
+    // trees as 148 tiles of 4, 432 trees as 148 tiles of 3).  Measured SLOWER than equal halves of full tiles (2 x 128 tiles
+    // of 4): with 256 tiles over 148 SMs the equal cut already rolls (a part's CTAs start wherever an SM comes free; 231 us
+    // per simulation against 249 for two tile times), while the SM-filling cut runs in lock step and every launch waits for
+    // its part's last tile plus the tree step (240 us against an ideal of 231).  DESIGN §4.5.
+    void pipeline_cut(int T, int K, int* t0) const override {
+        const int S = n_sm_ > 0 ? n_sm_ : 148, gmax = fused_rec_.gmax;
+        if (K != 2 || gmax <= 0 || T < 2 || !getenv("MZB_PIPELINE_SM_CUT")) { NetBackend::pipeline_cut(T, K, t0); return; }
+        const int q = (T + S - 1) / S, waves = (q + gmax - 1) / gmax;
+        long T1;
+        if (waves <= 1) T1 = ((long)T * ((q + 1) / 2) + q - 1) / q;
+        else T1 = (long)S * gmax * (waves / 2);
+        if (const char* ov = getenv("MZB_PIPELINE_CUT")) T1 = atol(ov);   // experiments
+        if (T1 < 1) T1 = 1;
+        if (T1 > T - 1) T1 = T - 1;
+        t0[0] = 0; t0[1] = (int)T1; t0[2] = T;
+    }
     bool recurrent_concurrent() const override {
         return uploaded_ && fused_final_ && fused_rec_.ok && fused_rec_.args.z_bytes > 0 && !getenv("MZB_FUSED_TIMING");
     }
@@ -908,6 +960,8 @@ protected:
     DevBuf red_[3];
     fused::MlpArgs mlp_;
     int mlp_mg_ = 16, n_sm_ = 0;
+    DevBuf trace_;
+    std::vector<int> trace_launches_;
     int* dbg_host_ = nullptr; int* dbg_dev_ = nullptr;
     DevBuf tim_;
     std::map<long, std::unique_ptr<TileTab>> tiles_;

@@ -108,6 +108,7 @@ struct FusedArgs {
     int dbg_flags;                                            // experiments: bit 0 = all taps unshifted (timing only, wrong results)
     int* dbg;                                                 // host-mapped diagnostics (barrier time-outs), may be null
     long long* tim;                                           // optional [tile][phase][4] clocks: mma start, mma issued, accum full, epilogue done
+    long long* tile_trace;                                    // optional [tile][4]: globaltimer ns at CTA start / end, clock64 at start / end (MZB_TILE_TRACE)
     int table_off;                                            // PH_TABLE: byte offset of the fp32 per-action table [A][HW][C]
     int z_bytes;                                              // > 0: head inputs stay in shared memory (Z) and the MLPs run in-kernel
     int z_rp;                                                 // channels per padded pixel row in Z's K order (multiple of 8)
@@ -202,13 +203,26 @@ __device__ __noinline__ void stage_table(const float* table_ch, const int* g_act
     tmem_st_wait();
 }
 
-__global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_constant__ FusedArgs a) {
+// Register budget: the register file is per SM sub-partition (16 K registers each) and this CTA's 10 warps sit 3 + 3 + 2 + 2 on
+// the four of them, so at the 168 registers ptxas takes a tree-step block (one warp per sub-partition, 56 registers) does NOT
+// fit beside a tower CTA (tools/coreside_probe.cu); it runs on the SMs a half-cohort launch leaves free.  -DMZB_TOWER_MAXNREG=152
+// makes the two co-resident at the cost of ~110 bytes of spills (tower +1 %); measured no faster in the search.
+// __maxnreg__ and __launch_bounds__ exclude each other.
+#ifndef MZB_TOWER_MAXNREG
+#define MZB_TOWER_MAXNREG 168
+#endif
+__global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_constant__ FusedArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     // warp index / tile size through a lane-0 shuffle: the compiler's uniformity analysis then knows they are warp-uniform,
     // so the role branches below are uniform branches and the MMA issuer's operands can live in uniform registers
     const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     const int game0 = __shfl_sync(0xffffffffu, a.tile_first[blockIdx.x], 0), G = __shfl_sync(0xffffffffu, a.tile_count[blockIdx.x], 0);
     if (a.tim && tid == 0) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 1) * 4 + 0] = clock64();   // CTA start (last row is free: n_phases < F_MAX_PHASES)
+    if (a.tile_trace && tid == 0) {
+        long long g;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+        a.tile_trace[(long)blockIdx.x * 4 + 0] = g; a.tile_trace[(long)blockIdx.x * 4 + 2] = clock64();
+    }
     const int P = a.P, R = a.R, HALO = a.HALO, C = a.C, KC = C >> 3, HW = a.HW, W1 = a.W + 1;
     const int N = (G * P + 15) & ~15;
     uint8_t* X = smem;
@@ -759,6 +773,11 @@ __global__ void __launch_bounds__(F_THREADS, 1) tower_fused_kernel(const __grid_
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem, F_TMEM_COLS);
     if (a.tim && tid == 0) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 1) * 4 + 1] = clock64();   // CTA end
+    if (a.tile_trace && tid == 0) {
+        long long g;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+        a.tile_trace[(long)blockIdx.x * 4 + 1] = g; a.tile_trace[(long)blockIdx.x * 4 + 3] = clock64();
+    }
 }
 
 // ------------------------------------------------------------------ head MLPs on the reduced activations

@@ -12,7 +12,7 @@ from typing import List, Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libmzb200.so")
+LIB_PATH = os.environ.get("MZB200_LIB") or os.path.join(os.path.dirname(_HERE), "libmzb200.so")   # MZB200_LIB: another build of the same library (kernel experiments)
 
 MAX_ACTIONS = 32
 MAX_HEAD_LAYERS = 8

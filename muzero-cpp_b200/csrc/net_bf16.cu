@@ -23,6 +23,7 @@
 #include <map>
 
 #include "conv_band.cuh"
+#include "conv_first.cuh"
 #include "net_direct.cuh"
 #include "tower_fused.cuh"
 #include "umma.cuh"
@@ -361,6 +362,41 @@ protected:
                 packed_[t][i] = p;
             }
         }
+        // first convolution of a downsample head (stride 2 on <= 16 observation planes): nine K = 16 tap images
+        // [2 K chunks][128 rows][8] for conv_first_kernel, which reads the fp32 NCHW observation itself
+        first_ok_ = false;
+        if (!plan.representation.convs.empty() && !plan.representation.steps.empty() && plan.representation.steps[0].kind == TowerStep::CONV &&
+            plan.representation.steps[0].conv0 == 0 && !getenv("MZB_NO_CONV_FIRST")) {
+            const Conv3Host& c = plan.representation.convs[0];
+            const int rbo = first::first_rows(c.out_w);
+            if (c.stride == 2 && c.cin <= 16 && c.cout <= UM && c.cout % 8 == 0 && c.act_table.empty() && c.out_h == (c.in_h - 1) / 2 + 1 &&
+                c.out_w == (c.in_w - 1) / 2 + 1 && rbo >= 1) {
+                while (extra->size() % 128) extra->push_back(0);
+                first_off_ = extra->size();
+                extra->resize(extra->size() + first::C1_W_BYTES, 0);
+                bf16* dst = reinterpret_cast<bf16*>(extra->data() + first_off_);
+                for (int tap = 0; tap < 9; ++tap)
+                    for (int kc = 0; kc < 2; ++kc)
+                        for (int row = 0; row < UM; ++row)
+                            for (int e = 0; e < 8; ++e) {
+                                const int k = kc * 8 + e;
+                                const float v = (row < c.cout && k < c.cin) ? c.w[((size_t)row * 9 + tap) * c.cin + k] : 0.f;
+                                dst[(((size_t)tap * 2 + kc) * UM + row) * 8 + e] = __float2bfloat16(v);
+                            }
+                first::FirstArgs& a = first_args_;
+                memset(&a, 0, sizeof(a));
+                a.cin = c.cin; a.cout = c.cout; a.H = c.in_h; a.W = c.in_w; a.Ho = c.out_h; a.Wo = c.out_w; a.relu = c.relu ? 1 : 0;
+                a.rbo = std::min(rbo, c.out_h);
+                a.bands = (c.out_h + a.rbo - 1) / a.rbo;
+                a.N = (a.rbo * (c.out_w + 1) + 15) / 16 * 16;
+                a.cls = first::first_cls(a.N, c.out_w);
+                const size_t smem = first::first_smem_bytes(a.cls, a.rbo, a.Wo, a.cout);
+                if (a.N <= 256 && smem <= 113 * 1024) {
+                    MZB_CUDA(cudaFuncSetAttribute(first::conv_first_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                    first_ok_ = true;
+                }
+            }
+        }
         if (!attr_set_) {
             MZB_CUDA(cudaFuncSetAttribute(umma_conv3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
             attr_set_ = true;
@@ -558,17 +594,34 @@ protected:
         return MZB_OK;
     }
 
-    bool rep_init_fusable(const NetPlan& plan, int C, int H, int W) const {
+    // The fused chain takes over the representation tower at the first step of its trailing run of residual blocks at the
+    // hidden-state shape (sets init_tail_): step 1 behind the thin head conv of a board game (ResidualHeadImpl), the step behind the
+    // last pooling of ResidualHeadDownsample.  What lies before runs layer by layer (conv_first / band kernels).
+    bool rep_init_fusable(const NetPlan& plan, int C, int H, int W) {
         const Tower& tw = plan.representation;
-        if (tw.steps.empty() || tw.steps[0].kind != TowerStep::CONV || tw.steps[0].conv0 != 0) return false;
-        for (size_t i = 1; i < tw.steps.size(); ++i) if (tw.steps[i].kind != TowerStep::BLOCK) return false;
-        const Conv3Host& c0 = tw.convs[0];
-        if (c0.cout != C || c0.out_h != H || c0.out_w != W) return false;
-        for (size_t k = 1; k < tw.convs.size(); ++k) {
-            const Conv3Host& c = tw.convs[k];
-            if (c.stride != 1 || c.cin != C || c.cout != C || c.in_h != H || c.in_w != W) return false;
-            if (!packed_[0][k].image) return false;
+        init_tail_ = 0;
+        if (tw.steps.empty()) return false;
+        size_t tail = tw.steps.size();
+        auto block_ok = [&](const TowerStep& st) {
+            if (st.kind != TowerStep::BLOCK) return false;
+            for (int k : {st.conv0, st.conv1}) {
+                const Conv3Host& c = tw.convs[k];
+                if (c.stride != 1 || c.cin != C || c.cout != C || c.in_h != H || c.in_w != W) return false;
+                if (!packed_[0][k].image) return false;
+            }
+            return true;
+        };
+        while (tail > 0 && block_ok(tw.steps[tail - 1])) --tail;
+        if (tail == 0 || tail == tw.steps.size()) return false;   // something must come before, and a block after (the skip preload)
+        // shape after the steps in front of the tail
+        int c = tw.in_c, h = tw.in_h, w = tw.in_w;
+        for (size_t i = 0; i < tail; ++i) {
+            const TowerStep& st = tw.steps[i];
+            if (st.kind == TowerStep::CONV) { const Conv3Host& cv = tw.convs[st.conv0]; c = cv.cout; h = cv.out_h; w = cv.out_w; }
+            else if (st.kind == TowerStep::POOL) { h = (h + 2 - 3) / 2 + 1; w = (w + 2 - 3) / 2 + 1; }
         }
+        if (c != C || h != H || w != W) return false;
+        init_tail_ = tail;
         return true;
     }
 
@@ -651,12 +704,12 @@ protected:
             add_conv1_phase(fa, 1, 0, C);
             add_mlp_phase(fa, 1);
         }
-        size_t phases_init = 2 * (steps_[0].size() - 1) + 1 + 2 * steps_[2].size() + 1 + 1;
+        size_t phases_init = 2 * (steps_[0].size() - init_tail_) + 1 + 2 * steps_[2].size() + 1 + 1;
         if (fused_init_.ok && phases_init > (size_t)fused::F_MAX_PHASES) fused_init_.ok = false;
         if (fused_init_.ok) {   // initial: (head conv on the direct kernel), representation blocks, normalise, prediction, heads
             fused::FusedArgs* fa = &fused_init_.args;
             fa->n_phases = 0; fa->preload = 1;
-            add_blocks(fa, 0, 1);
+            add_blocks(fa, 0, init_tail_);
             add_conv1_phase(fa, -1, fused::PH_NORM, C);
             add_blocks(fa, 2, 0);
             add_conv1_phase(fa, 1, 0, C);
@@ -925,20 +978,40 @@ public:
         const NetDims& d = plan_dims_;
         const direct::ConvDev& c0 = convs_[0][0];
         const size_t head_smem = ((size_t)c0.cin * (c0.in_h + 2) * (c0.in_w + 2) + (size_t)9 * c0.cin * c0.cout) * sizeof(float);
-        if (c0.stride == 1 && c0.cin <= 16 && !c0.has_table && c0.in_h == c0.out_h && c0.in_w == c0.out_w && head_smem <= 48 * 1024) {
+        const bf16* chain_in = bufB_.as<bf16>();
+        long chain_stride = (long)slot_elems_;
+        if (init_tail_ == 1 && c0.stride == 1 && c0.cin <= 16 && !c0.has_table && c0.in_h == c0.out_h && c0.in_w == c0.out_w && head_smem <= 48 * 1024) {
             const float* base = blob_.as<float>();
             head_conv_small_kernel<<<B, 128, head_smem, s>>>(d_obs, (long)d.initial_flat(), base + c0.w_off, base + c0.bias_off, bufB_.as<bf16>(),
                                                             (long)slot_elems_, c0.cin, c0.cout, c0.in_h, c0.in_w, c0.relu);
             MZB_CUDA(cudaGetLastError());
             launches_ = 1;
         } else {
-            long total = (long)B * d.initial_flat();
-            direct::nchw_to_nhwc_kernel<bf16><<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_obs, bufA_.as<bf16>(), nullptr, (long)d.initial_flat(), B, d.cin, d.in_h * d.in_w);
-            launches_ = 1;
-            rc = launch_conv(c0, B, bufA_.as<bf16>(), nullptr, (long)d.initial_flat(), bufB_.as<bf16>(), nullptr, nullptr, 0, nullptr, s);
+            // the steps in front of the fused chain, layer by layer: first conv (conv_first_kernel from the fp32 observation when
+            // it is a stride-2 head, else layout conversion + the generic path), then band / per-layer tensor kernels and pools
+            bf16* cur = nullptr;
+            launches_ = 0;
+            if (first_ok_) {
+                first::FirstArgs a = first_args_;
+                a.obs = d_obs; a.obs_stride = (long)d.initial_flat();
+                a.out = bufB_.as<bf16>();
+                a.wimg = reinterpret_cast<const uint8_t*>(blob_.p) + fp32_bytes_ + first_off_;
+                a.bias = blob_.as<float>() + c0.bias_off;
+                first::conv_first_kernel<<<B * a.bands, first::C1_THREADS, first::first_smem_bytes(a.cls, a.rbo, a.Wo, a.cout), s>>>(a);
+                MZB_CUDA(cudaGetLastError());
+                ++launches_;
+                rc = run_tower(0, B, bufB_.as<bf16>(), nullptr, 0, nullptr, s, &cur, 1, init_tail_);
+            } else {
+                long total = (long)B * d.initial_flat();
+                direct::nchw_to_nhwc_kernel<bf16><<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_obs, bufA_.as<bf16>(), nullptr, (long)d.initial_flat(), B, d.cin, d.in_h * d.in_w);
+                ++launches_;
+                rc = run_tower(0, B, bufA_.as<bf16>(), nullptr, 0, nullptr, s, &cur, 0, init_tail_);
+            }
             if (rc) return rc;
+            chain_in = cur;
+            chain_stride = (long)d.C * d.hw();
         }
-        rc = launch_fused(fused_init_, B, bufB_.as<bf16>(), nullptr, (long)slot_elems_, d_out_slot, nullptr, out, s);
+        rc = launch_fused(fused_init_, B, chain_in, nullptr, chain_stride, d_out_slot, nullptr, out, s);
         if (rc) return rc;
         if (!fused_init_.args.z_bytes) {
             rc = launch_mlp(B, 1, out, s);
@@ -954,6 +1027,8 @@ protected:
     FusedChain fused_rec_, fused_init_;
     bool fused_final_ = false;
     bool pipelined_ = false;
+    size_t init_tail_ = 0;            // first representation step of the fused initial chain
+    bool first_ok_ = false; size_t first_off_ = 0; first::FirstArgs first_args_;   // conv_first.cuh
     size_t conv1_rel_[2] = {0, 0}, conv1_bias_rel_[2] = {0, 0}, w0t_rel_[3] = {0, 0, 0};
     size_t mlp0_rel_[2] = {0, 0}, mlp0_bias_rel_[2] = {0, 0};
     int mlp0_nkb_[2] = {0, 0};
@@ -1006,6 +1081,15 @@ protected:
         }
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("umma_conv3_kernel launch failed: %s", cudaGetErrorString(e)); return MZB_ERR_CUDA; }
+        return 1;
+    }
+
+    int fast_pool(const bf16* in, bf16* out, int B, int C, int in_h, int in_w, int out_h, int out_w, cudaStream_t s) override {
+        if (C % 8 != 0) return 0;
+        const long total = (long)B * out_h * out_w * (C / 8);
+        first::avgpool3_vec_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(in, out, B, C / 8, in_h, in_w, out_h, out_w);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("avgpool3_vec_kernel launch failed: %s", cudaGetErrorString(e)); return MZB_ERR_CUDA; }
         return 1;
     }
 

@@ -382,6 +382,8 @@ protected:
     virtual int pack_extra(const NetPlan&, std::vector<uint8_t>*) { return MZB_OK; }
     // return 1 when the call was executed by a specialised kernel, 0 to fall through to the direct kernel, <0 on error
     virtual int fast_conv(const ConvCall<T>&, cudaStream_t) { return 0; }
+    // same contract for AvgPool2d(3, 2, 1) on a compact NHWC activation
+    virtual int fast_pool(const T*, T*, int, int, int, int, int, int, cudaStream_t) { return 0; }
 
     static int conv_smem(int stride) { int PW = TILE * stride + 2; return (CK * PW * PW + 9 * CK * TC) * (int)sizeof(float); }
     int head_smem(int h) const { return (int)head_smem_bytes(heads_[h], head_maxw_[h], head_maxw2_[h]); }
@@ -416,7 +418,9 @@ protected:
 
     // Runs tower t.  Input: `in` (slot-addressed when in_slot != nullptr).  Scratch ping-pong: bufA/bufB/bufC.
     // On return *cur_out points at the final activation (compact [B][...]).
-    int run_tower(int t, int B, T* in, const int* in_slot, long in_stride, const int* action, cudaStream_t s, T** cur_out) {
+    // Steps [step_begin, step_end) only when given: `in` is then the activation the step before step_begin produced.
+    int run_tower(int t, int B, T* in, const int* in_slot, long in_stride, const int* action, cudaStream_t s, T** cur_out,
+                  size_t step_begin = 0, size_t step_end = (size_t)-1) {
         T* bufs[3] = {bufA_.as<T>(), bufB_.as<T>(), bufC_.as<T>()};
         const T* cur = in;
         const int* cur_slot = in_slot;
@@ -426,7 +430,13 @@ protected:
             for (int i = 0; i < 3; ++i) if (bufs[i] != a && bufs[i] != b) return bufs[i];
             return nullptr;
         };
-        for (const TowerStep& st : steps_[t]) {
+        for (size_t si = 0; si < steps_[t].size() && si < step_end; ++si) {
+            const TowerStep& st = steps_[t][si];
+            if (si < step_begin) {   // shape bookkeeping only
+                if (st.kind == TowerStep::CONV) { const ConvDev& c = convs_[t][st.conv0]; cur_c = c.cout; cur_h = c.out_h; cur_w = c.out_w; }
+                else if (st.kind == TowerStep::POOL) { cur_h = (cur_h + 2 - 3) / 2 + 1; cur_w = (cur_w + 2 - 3) / 2 + 1; }
+                continue;
+            }
             const long compact = (long)cur_c * cur_h * cur_w;
             const long istride = cur_slot ? cur_stride : compact;
             if (st.kind == TowerStep::CONV) {
@@ -450,8 +460,12 @@ protected:
                 if (cur_slot) { set_error("pooling a slot-addressed activation is not supported"); return MZB_ERR_STATE; }
                 int oh = (cur_h + 2 - 3) / 2 + 1, ow = (cur_w + 2 - 3) / 2 + 1;
                 T* o = pick(cur, nullptr);
-                long total = (long)B * oh * ow * cur_c;
-                avgpool3_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, s>>>(cur, o, B, cur_c, cur_h, cur_w, oh, ow);
+                int fr = fast_pool(cur, o, B, cur_c, cur_h, cur_w, oh, ow, s);
+                if (fr < 0) return fr;
+                if (fr == 0) {
+                    long total = (long)B * oh * ow * cur_c;
+                    avgpool3_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, s>>>(cur, o, B, cur_c, cur_h, cur_w, oh, ow);
+                }
                 ++launches_;
                 cur = o; cur_h = oh; cur_w = ow;
             }

@@ -115,7 +115,11 @@ public:
     std::vector<InferenceOutputs> InitialInference(const std::vector<Observation>& stacked_observations) {
         const int B = (int)stacked_observations.size(), A = eng_->config().num_actions;
         std::vector<float> obs((size_t)B * sh_.initial_flat_size);
-        for (int b = 0; b < B; ++b) std::copy(stacked_observations[b].begin(), stacked_observations[b].end(), obs.begin() + (size_t)b * sh_.initial_flat_size);
+        for (int b = 0; b < B; ++b) {
+            if (stacked_observations[b].size() != (size_t)sh_.initial_flat_size)
+                fail("InitialInference: observation " + std::to_string(b) + " has " + std::to_string(stacked_observations[b].size()) + " values, the network input has " + std::to_string(sh_.initial_flat_size));
+            std::copy(stacked_observations[b].begin(), stacked_observations[b].end(), obs.begin() + (size_t)b * sh_.initial_flat_size);
+        }
         std::vector<double> v(B), r(B), p((size_t)B * A);
         std::vector<float> h((size_t)B * sh_.recurrent_flat_size);
         std::lock_guard<std::mutex> call(eng_->call_mutex());
@@ -125,7 +129,12 @@ public:
     std::vector<InferenceOutputs> RecurrentInference(const std::vector<Observation>& hidden_states, const std::vector<Action>& actions) {
         const int B = (int)hidden_states.size(), A = eng_->config().num_actions;
         std::vector<float> hin((size_t)B * sh_.recurrent_flat_size);
-        for (int b = 0; b < B; ++b) std::copy(hidden_states[b].begin(), hidden_states[b].end(), hin.begin() + (size_t)b * sh_.recurrent_flat_size);
+        if (actions.size() != hidden_states.size()) fail("RecurrentInference: " + std::to_string(hidden_states.size()) + " hidden states, " + std::to_string(actions.size()) + " actions");
+        for (int b = 0; b < B; ++b) {
+            if (hidden_states[b].size() != (size_t)sh_.recurrent_flat_size)
+                fail("RecurrentInference: hidden state " + std::to_string(b) + " has " + std::to_string(hidden_states[b].size()) + " values, expected " + std::to_string(sh_.recurrent_flat_size));
+            std::copy(hidden_states[b].begin(), hidden_states[b].end(), hin.begin() + (size_t)b * sh_.recurrent_flat_size);
+        }
         std::vector<int32_t> act(actions.begin(), actions.end());
         std::vector<double> v(B), r(B), p((size_t)B * A);
         std::vector<float> h((size_t)B * sh_.recurrent_flat_size);

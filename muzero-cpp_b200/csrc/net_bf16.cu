@@ -356,7 +356,10 @@ protected:
                             for (int row = 0; row < UM; ++row)
                                 for (int e = 0; e < 8; ++e) {
                                     const int k = cc * KB + kc * 8 + e;
-                                    const float v = row < c.cout ? c.w[((size_t)row * 9 + tap) * c.cin + k] : 0.f;
+                                    // cout <= 64: rows 64-127 repeat rows 0-63 (the fused chain's epilogue then uses all four
+                                    // TMEM lane quarters, tower_fused.cuh `dup`; the per-layer kernels ignore rows >= cout)
+                                    const int wr = (c.cout <= 64 && row >= 64) ? row - 64 : row;
+                                    const float v = wr < c.cout ? c.w[((size_t)wr * 9 + tap) * c.cin + k] : 0.f;
                                     dst[(((size_t)(tap * kb_per_tap + cc) * 8 + kc) * UM + row) * 8 + e] = __float2bfloat16(v);
                                 }
                 packed_[t][i] = p;
@@ -583,6 +586,7 @@ protected:
         base.z_bytes = z_bytes; base.z_rp = z_rp;
         base.C = C; base.H = H; base.W = W; base.P = P; base.HALO = halo; base.R = R; base.HW = H * W; base.x_bytes = x_bytes;
         base.normalize = plan.normalize ? 1 : 0;
+        base.dup = (C <= 64 && !getenv("MZB_FUSED_NO_DUP")) ? 1 : 0;
         base.red_rows[0] = plan.reward_head.red; base.red_rows[1] = plan.policy_head.red; base.red_rows[2] = plan.value_head.red;
         fused_rec_.args = base; fused_rec_.gmax = gmax; fused_rec_.smem = smem;
         fused_rec_.ok = true;    // phases are laid out by finalize_fused() once the blob offsets are known

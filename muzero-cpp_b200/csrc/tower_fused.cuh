@@ -105,6 +105,7 @@ struct FusedArgs {
     const int* tile_first; const int* tile_count;             // tile -> first game, number of games
     int C, H, W, P, HALO, R, HW, x_bytes;
     int n_phases, preload, normalize;
+    int dup;                                                  // C <= 64: weight-image rows 64-127 repeat rows 0-63, so lane quarters 2, 3 hold the same channels as 0, 1 and the four warp pairs split the GAMES four ways
     int dbg_flags;                                            // experiments: bit 0 = all taps unshifted (timing only, wrong results)
     int* dbg;                                                 // host-mapped diagnostics (barrier time-outs), may be null
     long long* tim;                                           // optional [tile][phase][4] clocks: mma start, mma issued, accum full, epilogue done
@@ -181,8 +182,8 @@ __device__ __forceinline__ void epi_store16(uint32_t* v, float bias, uint32_t m,
 // Per-action table of the dynamics head -> R2 (fp32), for the games of one epilogue warp.  All of a game's loads are issued
 // before the first is used: the L2 latency is paid once per 64 columns, not once per 8-column chunk.  Kept out of line so that its
 // 64 staging registers do not weigh on the register allocation of the per-layer epilogue.
-__device__ __noinline__ void stage_table(const float* table_ch, const int* g_act, uint32_t pt, uint32_t t_r2, int P, int G, int hsel, long a_stride, int C, bool ch_ok) {
-    for (int g = hsel; g < G; g += F_EPI_SPLIT) {
+__device__ __noinline__ void stage_table(const float* table_ch, const int* g_act, uint32_t pt, uint32_t t_r2, int P, int G, int sel, int nsplit, long a_stride, int C, bool ch_ok) {
+    for (int g = sel; g < G; g += nsplit) {
         const float* tg = table_ch + (long)g_act[g] * a_stride;
         for (int cb = 0; cb < P; cb += 64) {
             uint32_t tv[64];
@@ -387,13 +388,18 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
         // predicated on their stores.  The pixel map of a chunk is fetched BEFORE its stores (two 16-byte shared loads),
         // so the eight bf16 stores of a chunk issue back to back instead of alternating with dependent table look-ups.
         const int q = warp & 3, hsel = (warp - 2) >> 2;   // hsel in [0, F_EPI_SPLIT)
-        const int ch = 32 * q + lane;
+        // `row` = accumulator lane = weight-image row.  For the 3x3 phases it is the output channel, except with duplicated rows
+        // (a.dup, C <= 64): there quarters 2, 3 repeat the channels of quarters 0, 1 and take other games — all eight warps
+        // work on a 64-channel layer instead of four (its epilogue halves).  `sel` / `nsplit` = which games this warp owns.
+        const int row = 32 * q + lane;
+        const int ch = a.dup ? 32 * (q & 1) + lane : row;
+        const int sel = a.dup ? hsel + 2 * (q >> 1) : hsel, nsplit = a.dup ? 4 : F_EPI_SPLIT;
         const bool ch_ok = ch < C;
         const uint32_t t_lane = tmem + ((uint32_t)(32 * q) << 16);
         const uint32_t xs = smem_u32(X) + (uint32_t)(((ch >> 3) * R + HALO) * 16 + (ch & 7) * 2);   // + row * 16
         const uint32_t pt = smem_u32(pixtab), pm = smem_u32(pixmask);
         if (a.preload) {   // the chain starts with a residual block: its skip input = the chain input, fp32 into R2
-            for (int g = hsel; g < G; g += F_EPI_SPLIT) {
+            for (int g = sel; g < G; g += nsplit) {
                 const int cbase = g * P;
                 for (int c0 = 0; c0 < P; c0 += 8) {
                     int pix[8];
@@ -418,9 +424,9 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
             const Phase& ph = a.ph[p];
             const int flags = ph.flags;
             // the per-channel bias is fetched BEFORE waiting for the accumulator: its L2 latency hides behind the MMAs
-            const float bias_pf = (ph.bias_off >= 0) ? __ldg(reinterpret_cast<const float*>(a.blob + ph.bias_off) + ch) : 0.f;
+            const float bias_pf = (ph.bias_off >= 0) ? __ldg(reinterpret_cast<const float*>(a.blob + ph.bias_off) + ((flags & (PH_RED | PH_MLP)) ? row : ch)) : 0.f;
             if (flags & PH_TABLE)   // dynamics head: per-action table -> R2 (fp32) while the MMAs of this phase run into R1
-                stage_table(reinterpret_cast<const float*>(a.blob + a.table_off) + ch, g_act, pt, t_lane + (uint32_t)F_R2_COL, P, G, hsel, (long)HW * C, C, ch_ok);
+                stage_table(reinterpret_cast<const float*>(a.blob + a.table_off) + ch, g_act, pt, t_lane + (uint32_t)F_R2_COL, P, G, sel, nsplit, (long)HW * C, C, ch_ok);
             mbar_wait_dbg(accum_full, p & 1, a.dbg, 4, p);
             tc_fence_after();
             if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 2] = clock64();
@@ -455,9 +461,9 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                         }
                     }
                 } else if (32 * q < nred) {   // warp-uniform; lanes beyond nred only skip the stores
-                    const bool row_ok = ch < nred;
-                    const bool second = ch >= ph.red_n0;
-                    const int rr = second ? ch - ph.red_n0 : ch;
+                    const bool row_ok = row < nred;
+                    const bool second = row >= ph.red_n0;
+                    const int rr = second ? row - ph.red_n0 : row;
                     const float bias = row_ok ? bias_pf : 0.f;
                     if (a.z_bytes) {
                         // in-kernel heads.  Z is the B operand of the first MLP layer: [K / 8][16 rows][8] bf16, rows 0-7 = head0's
@@ -505,7 +511,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
             if (flags & PH_NORM) {
                 // normalize_hidden_state (models.cpp:16-26): a thread owns one channel, its columns are the pixels
                 const int nskip = (W1 >> 3) << 3;   // the pad row of a game: no real pixel, nothing to normalise (its R2 columns are never read)
-                for (int g = hsel; g < G; g += F_EPI_SPLIT) {
+                for (int g = sel; g < G; g += nsplit) {
                     const int cbase = g * P;
                     float mn = 3.402823466e38f, mx = -3.402823466e38f;
                     if (a.normalize) {
@@ -556,7 +562,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                 const float bias = ch_ok ? bias_pf : 0.f;
                 const bool relu = (flags & PH_RELU) != 0, stash = (flags & PH_STASH) != 0, wx = (flags & PH_WRITE_X) != 0 && ch_ok;
                 if (flags & PH_TABLE) {   // accumulator (R1) + staged per-action table (R2), 16 columns at a time
-                    for (int g = hsel; g < G; g += F_EPI_SPLIT) {
+                    for (int g = sel; g < G; g += nsplit) {
                         const int cbase = g * P;
                         for (int c0 = (W1 >> 3) << 3; c0 < P; c0 += 16) {   // (from the first real row on, as below)
                             uint32_t v[16], w[16];
@@ -585,10 +591,10 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                     static_assert(F_EPI_SPLIT == 2, "the column split below assumes two warp halves");
                     const int G2 = G & ~1;
                     const int mid = skip + ((((P - skip) >> 1) + 7) & ~7);
-                    const int n_mine = (G2 > hsel ? (G2 - hsel + 1) >> 1 : 0) + (G & 1);
+                    const int n_mine = a.dup ? (G > sel ? (G - sel + 3) >> 2 : 0) : (G2 > hsel ? (G2 - hsel + 1) >> 1 : 0) + (G & 1);
                     for (int i = 0; i < n_mine; ++i) {
-                        int g = hsel + 2 * i, c_lo = skip, c_hi = P;
-                        if (g >= G2) { g = G - 1; if (hsel == 0) c_hi = mid; else c_lo = mid; }
+                        int g = a.dup ? sel + 4 * i : hsel + 2 * i, c_lo = skip, c_hi = P;
+                        if (!a.dup && g >= G2) { g = G - 1; if (hsel == 0) c_hi = mid; else c_lo = mid; }
                         const int cbase = g * P;
                         for (int c0 = c_lo; c0 < c_hi; c0 += 32) {
                             const int left = c_hi - c0;
@@ -621,8 +627,8 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                     uint32_t v[16];   // columns 0-7: head0's games, 8-15: head1's games (Z rows 8-15)
                     tmem_ld16(t_lane, v);
                     tmem_ld_wait();
-                    if (ch < ph.red_n0 + ph.red_n1) {
-                        const bool second = ch >= ph.red_n0;
+                    if (row < ph.red_n0 + ph.red_n1) {
+                        const bool second = row >= ph.red_n0;
                         const HeadTail& hd = a.head[second ? ph.red_head1 : ph.red_head0];
                         const float b0 = bias_pf;
                         const bool relu0 = hd.n_layers > 1;
@@ -630,7 +636,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                         for (int j = 0; j < 8; ++j) {
                             float y = __uint_as_float(second ? v[8 + j] : v[j]) + b0;
                             if (relu0) y = fmaxf(y, 0.f);
-                            Hs[j * 128 + ch] = y;
+                            Hs[j * 128 + row] = y;
                         }
                     }
                 }

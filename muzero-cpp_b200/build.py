@@ -54,7 +54,7 @@ def build(verbose=False, force=False):
     if failed:
         raise RuntimeError("nvcc failed")
     if procs or not os.path.exists(OUT):
-        subprocess.check_call(["nvcc", "-shared", "-o", OUT] + objs + ["-lcudart", "-ldl", "-gencode", "arch=compute_100a,code=sm_100a"])
+        subprocess.check_call(["nvcc", "-shared", "-o", OUT] + objs + ["-lcudart", "-ldl", "-lpthread", "-gencode", "arch=compute_100a,code=sm_100a"])
     return OUT
 
 

@@ -146,10 +146,14 @@ __global__ void __launch_bounds__(B_THREADS, 1) conv_band_kernel(const __grid_co
         __syncwarp();
     } else {
         // ===== epilogue: lane quarter q = output channels 32q..32q+31, the two warps of a quarter split the tile rows =====
-        const int q = warp & 3, hsel = (warp - 2) >> 2;
+        // cout <= 64: the weight images repeat rows 0-63 in rows 64-127 (net_bf16.cu pack_extra), so quarters 2, 3 hold the same
+        // channels as 0, 1 and the four warp pairs split the band's rows four ways
+        const bool dup = a.cout <= 64;
+        const int q = dup ? (warp & 1) : (warp & 3), hsel = dup ? ((warp - 2) >> 2) + 2 * ((warp & 3) >> 1) : (warp - 2) >> 2;
+        const int rstep = dup ? 4 : 2;
         const int co = 32 * q + lane;
         const bool co_ok = co < a.cout;
-        const uint32_t t_lane = tmem + ((uint32_t)(32 * q) << 16);
+        const uint32_t t_lane = tmem + ((uint32_t)(32 * (warp & 3)) << 16);
         const float bias = co_ok ? __ldg(a.bias + co) : 0.f;
         const long out_base = (long)(a.out_slot ? a.out_slot[img] : img) * a.out_stride;
         const long res_base = a.res ? (long)(a.res_slot ? a.res_slot[img] : img) * a.res_stride : 0;
@@ -160,7 +164,7 @@ __global__ void __launch_bounds__(B_THREADS, 1) conv_band_kernel(const __grid_co
         //    store (the direct lane = channel stores were 2 bytes per thread: 4x slower than the MMAs they followed).
         float* S = reinterpret_cast<float*>(stages);
         if (32 * q < a.cout) {   // warp-uniform: quarters beyond cout hold zero rows
-            for (int i = 1 + hsel; i <= a.rb; i += 2) {
+            for (int i = 1 + hsel; i <= a.rb; i += rstep) {
                 if (y0 - 1 + i >= a.H) break;   // (warp-uniform) last band of an image whose height is not a multiple of rb
                 for (int x0 = 0; x0 < a.W; x0 += 16) {
                     uint32_t v[16];

@@ -5,6 +5,7 @@
 #include <cstring>
 #include <numeric>
 #include <random>
+#include <thread>
 
 #include "engine.h"
 
@@ -98,10 +99,23 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
         MZB_CUDA(cudaMemcpyAsync(h_mt, td.mt, (size_t)T * 624 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ax));
         MZB_CUDA(cudaMemcpyAsync(h_idx, td.mt_idx, T * sizeof(int), cudaMemcpyDeviceToHost, ax));
         MZB_CUDA(cudaStreamSynchronize(ax));
-        for (int t = 0; t < T; ++t) {
-            if (!add_noise[t]) continue;
-            HostMt rng{h_mt + (size_t)t * 624, h_idx + t};
-            sample_dirichlet(rng, c.dirichlet_alpha, popcount32(legal_mask[t]), h_noise + (size_t)t * A);
+        // every tree draws from its own generator, so the trees split over a few host threads (1024 C4 trees: ~0.5 ms of
+        // gamma draws on one core, longer than the initial inference they are meant to hide behind)
+        auto draw = [&](int t_lo, int t_hi) {
+            for (int t = t_lo; t < t_hi; ++t) {
+                if (!add_noise[t]) continue;
+                HostMt rng{h_mt + (size_t)t * 624, h_idx + t};
+                sample_dirichlet(rng, c.dirichlet_alpha, popcount32(legal_mask[t]), h_noise + (size_t)t * A);
+            }
+        };
+        static const int noise_threads = getenv("MZB_NOISE_THREADS") ? std::max(1, atoi(getenv("MZB_NOISE_THREADS"))) : 4;
+        const int nthr = std::min(noise_threads, std::max(1, T / 128));
+        if (nthr <= 1) draw(0, T);
+        else {
+            std::vector<std::thread> pool;
+            for (int k = 1; k < nthr; ++k) pool.emplace_back(draw, (int)((long)T * k / nthr), (int)((long)T * (k + 1) / nthr));
+            draw(0, T / nthr);
+            for (std::thread& th : pool) th.join();
         }
         MZB_CUDA(cudaMemcpyAsync(td.mt, h_mt, (size_t)T * 624 * sizeof(uint32_t), cudaMemcpyHostToDevice, ax));
         MZB_CUDA(cudaMemcpyAsync(td.mt_idx, h_idx, T * sizeof(int), cudaMemcpyHostToDevice, ax));

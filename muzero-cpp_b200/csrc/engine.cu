@@ -59,7 +59,7 @@ int alloc_trees(mzb_engine* e) {
     MZB_CUDA(e->value.alloc(T * sizeof(double)));
     MZB_CUDA(e->reward_out.alloc(T * sizeof(double)));
     MZB_CUDA(e->policy.alloc((size_t)T * A * sizeof(double)));
-    MZB_CUDA(e->pbc_table.alloc((n + 2) * sizeof(double)));
+    MZB_CUDA(e->pbc_table.alloc(2 * (n + 2) * sizeof(double)));
     td.meta = e->meta.as<int4>(); td.prior = e->prior.as<double>(); td.value_sum = e->value_sum.as<double>();
     td.reward = e->reward.as<double>(); td.mm_min = e->mm_min.as<double>(); td.mm_max = e->mm_max.as<double>();
     td.root_to_play = e->root_to_play.as<int>(); td.n_legal = e->n_legal.as<int>(); td.n_slots = e->n_slots.as<int>();
@@ -72,8 +72,10 @@ int alloc_trees(mzb_engine* e) {
     td.init_max = c.value_upperbound;
     td.dirichlet_epsilon = c.dirichlet_epsilon;
     // pb_c table: std::log is glibc's on the reference side, so evaluate it on the host with the same libm
-    std::vector<double> tab(n + 2);
+    // second half: std::sqrt(N) (mcts.cpp:130), correctly rounded on host and device alike
+    std::vector<double> tab(2 * (n + 2));
     for (int N = 0; N < n + 2; ++N) tab[N] = std::log((N + c.pb_c_base + 1) / c.pb_c_base) + c.pb_c_init;  // mcts.cpp:129
+    for (int N = 0; N < n + 2; ++N) tab[n + 2 + N] = std::sqrt((double)N);
     MZB_CUDA(cudaMemcpy(e->pbc_table.p, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice));
     td.pbc_table = e->pbc_table.as<double>();
     // inputs / results

@@ -84,6 +84,11 @@ struct WarpRng {
     }
 };
 
+// ceil(65536 / b) for b = 0 .. 33: x / b == (x * kRecip16[b]) >> 16 exactly for x * (b - 1) < 65536 — std::shuffle's paired
+// draw is x < (i + 1)(i + 2) <= 1056 with b = i + 2 <= 33.  Replaces two runtime integer divisions (~240 warp instructions per
+// tree and step, the largest single item in the ncu source view).
+__constant__ uint32_t kRecip16[34] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042, 4682, 4370,
+                                      4096, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115, 2048, 1986};
 // std::shuffle (stl_algo.h:3741-3800) on a permutation distributed over lanes: lane j holds perm[j]
 __device__ __forceinline__ int swap_lanes(int perm, int a, int b, int lane) {
     int va = __shfl_sync(FULL, perm, a);
@@ -104,7 +109,9 @@ __device__ int shuffle_perm(WarpRng& rng, int n, int lane) {
         uint32_t swap_range = (uint32_t)i + 1u;
         uint32_t b1 = swap_range + 1u;
         uint32_t x = rng.below(swap_range * b1);
-        int p0 = (int)(x / b1), p1 = (int)(x % b1);
+        int p0, p1;
+        if (b1 <= 33u) { p0 = (int)((x * kRecip16[b1]) >> 16); p1 = (int)(x - (uint32_t)p0 * b1); }
+        else { p0 = (int)(x / b1); p1 = (int)(x % b1); }
         perm = swap_lanes(perm, i, p0, lane); ++i;
         perm = swap_lanes(perm, i, p1, lane); ++i;
     }
@@ -209,7 +216,8 @@ __global__ void __launch_bounds__(128) tree_step_kernel(TreeDev td, int t_first,
                 const double vs_l = shfl_d(vs, l);
                 const double r_l = shfl_d(r, l);
                 const int vc_l = __shfl_sync(FULL, m.x, l);
-                const bool same = ((root_tp + kk) % players) == vtp;
+                const int tp_k = players == 2 ? ((root_tp + kk) & 1) : (players == 1 ? 0 : (root_tp + kk) % players);
+                const bool same = tp_k == vtp;
                 const double nvs = vs_l + (same ? value : -value);
                 const int nvc = vc_l + 1;
                 const double nodeval = nvs / nvc;
@@ -251,6 +259,9 @@ __global__ void __launch_bounds__(128) tree_step_kernel(TreeDev td, int t_first,
         int4 cm = make_int4(0, 0, -1, -1); double cp = 0.0, cvs = 0.0, cr = 0.0;
         if (lane < n) { cm = meta[cb + lane]; cp = prior[cb + lane]; cvs = value_sum[cb + lane]; cr = reward[cb + lane]; }
         const double pbc_n = __ldg(td.pbc_table + N);   // in flight with the child loads, consumed after the shuffle
+        // sqrt(parent visits): correctly rounded on both sides, so the host-built table is bit-identical to the software fp64
+        // sqrt it replaces (hand-built trees of the unit-test hooks may exceed the table)
+        const double sqrt_n = (N <= td.n_sims + 1) ? __ldg(td.pbc_table + (td.n_sims + 2) + N) : sqrt((double)N);
         // std::shuffle(children) — physically permutes the child records
         const int perm = shuffle_perm(rng, n, lane);
         int4 pm;
@@ -262,7 +273,7 @@ __global__ void __launch_bounds__(128) tree_step_kernel(TreeDev td, int t_first,
         double score = 0.0;
         if (lane < n) {
             double pb_c = pbc_n;
-            const double ratio = sqrt((double)N) / (double)(pm.x + 1);
+            const double ratio = sqrt_n / (double)(pm.x + 1);
             pb_c = pb_c * ratio;
             const double prior_score = pb_c * pp;
             double value_score = 0.0;
@@ -277,16 +288,16 @@ __global__ void __launch_bounds__(128) tree_step_kernel(TreeDev td, int t_first,
         }
         if (td.dbg_score && len == 1) td.dbg_score[lane] = score;
         // first strict arg-max over children 0..n-1 (mcts.cpp:115-121)
-        int best = lane;
-        bool valid = lane < n;
+        // (an index >= 64 marks a lane without a child; the butterfly only spans the lanes that can hold one)
+        int best = lane < n ? lane : 64 + lane;
         double bs = score;
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
+        const int off0 = n <= 8 ? 4 : (n <= 16 ? 8 : 16);   // warp-uniform
+        for (int off = off0; off > 0; off >>= 1) {
             const double os = __shfl_xor_sync(FULL, bs, off);
             const int oi = __shfl_xor_sync(FULL, best, off);
-            const bool ov = __shfl_xor_sync(FULL, (int)valid, off) != 0;
-            if (ov && (!valid || os > bs || (os == bs && oi < best))) { bs = os; best = oi; valid = true; }
+            if (oi < 64 && (best >= 64 || os > bs || (os == bs && oi < best))) { bs = os; best = oi; }
         }
+        best = __shfl_sync(FULL, best, 0);   // lanes beyond the butterfly's span take lane 0's result
         cur.x = __shfl_sync(FULL, pm.x, best); cur.y = __shfl_sync(FULL, pm.y, best);
         cur.z = __shfl_sync(FULL, pm.z, best); cur.w = __shfl_sync(FULL, pm.w, best);
         slot = cb + best;

@@ -27,7 +27,7 @@ struct TreeDev {
     int* in_slot; int* out_slot; int* action;      // [T] pool slots (parent state, child state) and action
     double* value; double* reward_out; double* policy;   // [T], [T], [T][A]
     // constants
-    const double* pbc_table;            // [n_sims + 2]: log((N + pb_c_base + 1) / pb_c_base) + pb_c_init, glibc-evaluated
+    const double* pbc_table;            // [2][n_sims + 2]: log((N + pb_c_base + 1) / pb_c_base) + pb_c_init, then sqrt(N); host (glibc) evaluated
     double discount, init_min, init_max, dirichlet_epsilon;
     // optional recording (parity hooks); null when disabled
     int* trace_parent; int* trace_action;                  // [T][n_sims]

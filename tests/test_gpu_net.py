@@ -63,9 +63,15 @@ def _check(got, want, precision, what):
     if precision == 0:
         np.testing.assert_allclose(got, want, rtol=0, atol=FP32_ATOL, err_msg=what)
     else:
-        scale = max(1.0, float(np.abs(want).max()))
-        err = float(np.abs(got - want).max())
-        assert err <= BF16_RTOL * scale, "%s: max err %g above %g" % (what, err, BF16_RTOL * scale)
+        # bf16 mode: 2e-2 relative PER ELEMENT, with a floor on the magnitude it is relative to — 0.1 for a probability
+        # (bound >= 2e-3), 0.5 for a decoded value / reward (bound >= 1e-2).  Measured on random-init weights
+        # (profiles/bf16_error_r02.json, all configs): policy <= 8.5e-4, value <= 6.5e-3, reward <= 1.4e-3.
+        floor = 0.1 if "policy" in what else 0.5
+        got = np.asarray(got, np.float64); want = np.asarray(want, np.float64)
+        tol = BF16_RTOL * np.maximum(floor, np.abs(want))
+        err = np.abs(got - want)
+        assert (err <= tol).all(), "%s: %d elements above the per-element bound, worst err %g (bound %g)" % (
+            what, int((err > tol).sum()), float(err.max()), float(tol.flat[int(np.argmax(err - tol))]))
 
 
 def _run_chain(eng, net, obs, a1, a2, precision, tag):

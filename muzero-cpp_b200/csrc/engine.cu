@@ -174,6 +174,7 @@ int mzb_engine_create(const mzb_config* config, int device, mzb_engine** out) {
     MZB_CUDA(cudaEventCreateWithFlags(&e->ev_aux, cudaEventDisableTiming));
     MZB_CUDA(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
     for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) MZB_CUDA(cudaEventCreateWithFlags(&e->ev_join[i], cudaEventDisableTiming));
+    for (int i = 0; i < mzb_engine::MAX_PARTS; ++i) MZB_CUDA(cudaEventCreateWithFlags(&e->ev_tower[i], cudaEventDisableTiming));
     rc = alloc_trees(e.get());
     if (rc) return rc;
     const int T = e->cfg.max_trees, n = e->cfg.num_simulations;
@@ -215,6 +216,7 @@ void mzb_engine_destroy(mzb_engine* e) {
     if (e->ev_aux) cudaEventDestroy(e->ev_aux);
     if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) if (e->ev_join[i]) cudaEventDestroy(e->ev_join[i]);
+    for (int i = 0; i < mzb_engine::MAX_PARTS; ++i) if (e->ev_tower[i]) cudaEventDestroy(e->ev_tower[i]);
     for (int k = 0; k < 2; ++k) { if (e->ev_se_out[k]) cudaEventDestroy(e->ev_se_out[k]); if (e->ev_se_mv[k]) cudaEventDestroy(e->ev_se_mv[k]); }
     if (e->learn_step && e->learn_step_free) e->learn_step_free(e->learn_step);
     mzb_nccl_release(e);

@@ -67,6 +67,7 @@ struct mzb_engine {
     cudaStream_t pipe[MAX_PARTS - 1] = {};   // streams of parts 1.. of the pipelined simulation loop (part 0 runs on `stream`)
     cudaEvent_t ev_start = nullptr, ev_root = nullptr, ev_end = nullptr, ev_aux = nullptr, ev_fork = nullptr;
     cudaEvent_t ev_join[MAX_PARTS - 1] = {};
+    cudaEvent_t ev_tower[MAX_PARTS] = {};   // end of each part's latest tower kernel (alternating pipeline)
     // trees
     TreeDev td;
     DevBuf meta, prior, value_sum, reward, mm_min, mm_max, root_to_play, n_legal, n_slots, max_depth, mt, mt_idx,

@@ -149,6 +149,8 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
             o[k].value += t0[k]; o[k].reward += t0[k]; o[k].policy += (size_t)t0[k] * A;
         }
         e->net->set_pipelined(true);
+        static const int alt_env = getenv("MZB_PIPELINE_ALTERNATE") ? atoi(getenv("MZB_PIPELINE_ALTERNATE")) : -1;
+        const bool alternate = alt_env > 0;
         // MZB_PIPELINE_TRACE=1: a timed event behind every launch, printed as a timeline after the search (diagnostic only)
         static const bool trace = getenv("MZB_PIPELINE_TRACE") != nullptr;
         std::vector<cudaEvent_t> tev;
@@ -159,6 +161,11 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
                 ++launches;
                 mark(st[k]);
                 if (sim == n) continue;
+                // EXPERIMENT (MZB_PIPELINE_ALTERNATE=1, off by default): this part's tower starts only when the previous part's tower
+                // has ended, so that the kernels behind a tower (head MLPs of a wide-head network, the next tree step) run beside the
+                // other part's tower.  Measured slower everywhere (ALE 17.4 -> 21.6 ms, c4d 11.5 -> 14.4 ms per search): serialised
+                // towers expose every launch's ramp-up and drain (~20 us), which freely overlapping launches hide.
+                if (alternate) e->net->set_tower_events((sim > 0 || k > 0) ? e->ev_tower[(k + K - 1) % K] : nullptr, e->ev_tower[k]);
                 rc = e->net->recurrent(t0[k + 1] - t0[k], td.in_slot + t0[k], td.action + t0[k], td.out_slot + t0[k], o[k], st[k]);
                 launches += e->net->launches_recurrent();
                 mark(st[k]);

@@ -46,6 +46,12 @@ public:
     // cut points t0[0..K] of a cohort of T trees into the K parts of a pipelined loop.  Default: equal parts.  A backend that
     // knows its tile geometry cuts so that every part's launch is whole waves of tiles over the SMs (net_bf16.cu)
     virtual void pipeline_cut(int T, int K, int* t0) const { for (int k = 0; k <= K; ++k) t0[k] = (int)((long)T * k / K); }
+    // pipelined loop, alternating parts: the NEXT recurrent() call waits for `wait_before` (may be null) ahead of its tower
+    // kernel and records `record_after` right behind it — i.e. before any follow-up kernel of the same pass (head MLPs of a
+    // wide-head network), which is the work that should overlap the other part's tower
+    virtual void set_tower_events(cudaEvent_t /*wait_before*/, cudaEvent_t /*record_after*/) {}
+    // true when a recurrent pass launches further kernels behind its tower kernel
+    virtual bool recurrent_has_followup() const { return false; }
     virtual int launches_initial() const = 0;
     virtual int launches_recurrent() const = 0;
 };

@@ -722,12 +722,12 @@ protected:
         for (fused::FusedArgs* fa : {&fused_rec_.args, &fused_init_.args})
             for (int p = 0; p < fa->n_phases; ++p) fused::derive_issue_fields(fa->ph[p], fa->R, fa->W);
         // reduced head inputs and MLP descriptors
-        for (int h = 0; h < 3; ++h) MZB_CUDA(red_[h].alloc((size_t)max_batch_ * heads_[h].red * hw * sizeof(float)));
+        red_sets_.clear();   // reduced head inputs: one set of buffers per stream (red_for), so that the parts of a pipelined loop do not share them
         const uint8_t* blob = reinterpret_cast<const uint8_t*>(blob_.p);
         memset(&mlp_, 0, sizeof(mlp_));
         for (int h = 0; h < 3; ++h) {
             fused::MlpHead& m = mlp_.h[h];
-            m.x = red_[h].as<float>();
+            m.x = nullptr;   // per launch: the calling stream's buffers
             m.w0t = reinterpret_cast<const float*>(blob + fp32_bytes_ + w0t_rel_[h]);
             m.n_layers = heads_[h].n_layers;
             for (int l = 0; l <= m.n_layers; ++l) m.sizes[l] = heads_[h].sizes[l];
@@ -797,7 +797,10 @@ protected:
         a.pool = pool_.as<bf16>(); a.out_slot = out_slot; a.pool_stride = (long)slot_elems_;
         a.action = action;
         a.blob = reinterpret_cast<const uint8_t*>(blob_.p);
-        for (int h = 0; h < 3; ++h) a.red[h] = red_[h].as<float>();
+        RedSet* rs = nullptr;
+        rc = red_for(s, &rs);
+        if (rc) return rc;
+        for (int h = 0; h < 3; ++h) a.red[h] = rs->r[h].as<float>();
         if (a.z_bytes) {
             double* outs[3] = {out.reward, out.policy, out.value};
             const int strides[3] = {1, plan_dims_.A, 1};
@@ -898,8 +901,11 @@ protected:
         double* outs[3] = {out.reward, out.policy, out.value};
         const int strides[3] = {1, plan_dims_.A, 1};
         int n = 0, n0max = 0;
+        RedSet* rs = nullptr;
+        int rrc = red_for(s, &rs);
+        if (rrc) return rrc;
         for (int h = first_head; h < 3; ++h) {
-            m.h[n] = mlp_.h[h]; m.h[n].out = outs[h]; m.h[n].out_stride = strides[h];
+            m.h[n] = mlp_.h[h]; m.h[n].x = rs->r[h].as<float>(); m.h[n].out = outs[h]; m.h[n].out_stride = strides[h];
             n0max = std::max(n0max, m.h[n].sizes[0]);
             ++n;
         }
@@ -914,7 +920,9 @@ protected:
 
 public:
     // the one-launch fused recurrent pass keeps everything in shared memory / TMEM: no global scratch shared between calls
-    void set_pipelined(bool on) override { pipelined_ = on; if (!on) dump_tile_trace(); }
+    void set_pipelined(bool on) override { pipelined_ = on; if (!on) { ev_wait_ = nullptr; ev_record_ = nullptr; dump_tile_trace(); } }
+    void set_tower_events(cudaEvent_t wait_before, cudaEvent_t record_after) override { ev_wait_ = wait_before; ev_record_ = record_after; }
+    bool recurrent_has_followup() const override { return fused_rec_.ok && fused_rec_.args.z_bytes == 0; }
     void dump_tile_trace() {
         if (trace_launches_.empty()) return;
         cudaDeviceSynchronize();
@@ -955,7 +963,8 @@ public:
         t0[0] = 0; t0[1] = (int)T1; t0[2] = T;
     }
     bool recurrent_concurrent() const override {
-        return uploaded_ && fused_final_ && fused_rec_.ok && fused_rec_.args.z_bytes > 0 && !getenv("MZB_FUSED_TIMING");
+        // (wide heads run a second kernel, mlp_heads_kernel, on the reduced activations: those buffers are per stream)
+        return uploaded_ && fused_final_ && fused_rec_.ok && (fused_rec_.args.z_bytes > 0 || !getenv("MZB_NO_PIPELINE_WIDE")) && !getenv("MZB_FUSED_TIMING");
     }
     int recurrent(int B, const int* d_in_slot, const int* d_action, const int* d_out_slot, const NetOutputs& out, cudaStream_t s) override {
         MZB_REQUIRE(uploaded_, "weights not loaded (mzb_load_weights)");
@@ -963,8 +972,11 @@ public:
         if (rc) return rc;
         if (!fused_rec_.ok) return direct::DirectBackend<bf16>::recurrent(B, d_in_slot, d_action, d_out_slot, out, s);
         MZB_REQUIRE(B <= max_batch_, "batch %d above engine capacity %d", B, max_batch_);
+        if (ev_wait_) MZB_CUDA(cudaStreamWaitEvent(s, ev_wait_, 0));
         rc = launch_fused(fused_rec_, B, pool_.as<bf16>(), d_in_slot, (long)slot_elems_, d_out_slot, d_action, out, s);
         if (rc) return rc;
+        if (ev_record_) MZB_CUDA(cudaEventRecord(ev_record_, s));
+        ev_wait_ = nullptr; ev_record_ = nullptr;
         launches_recurrent_ = 1;
         if (!fused_rec_.args.z_bytes) {
             rc = launch_mlp(B, 0, out, s);
@@ -1031,12 +1043,25 @@ protected:
     FusedChain fused_rec_, fused_init_;
     bool fused_final_ = false;
     bool pipelined_ = false;
+    cudaEvent_t ev_wait_ = nullptr, ev_record_ = nullptr;
     size_t init_tail_ = 0;            // first representation step of the fused initial chain
     bool first_ok_ = false; size_t first_off_ = 0; first::FirstArgs first_args_;   // conv_first.cuh
     size_t conv1_rel_[2] = {0, 0}, conv1_bias_rel_[2] = {0, 0}, w0t_rel_[3] = {0, 0, 0};
     size_t mlp0_rel_[2] = {0, 0}, mlp0_bias_rel_[2] = {0, 0};
     int mlp0_nkb_[2] = {0, 0};
-    DevBuf red_[3];
+    struct RedSet { DevBuf r[3]; };
+    std::map<cudaStream_t, std::unique_ptr<RedSet>> red_sets_;
+    int red_for(cudaStream_t s, RedSet** out) {
+        auto it = red_sets_.find(s);
+        if (it == red_sets_.end()) {
+            std::unique_ptr<RedSet> rs(new RedSet());
+            const int hw = plan_dims_.hw();
+            for (int h = 0; h < 3; ++h) MZB_CUDA(rs->r[h].alloc((size_t)max_batch_ * heads_[h].red * hw * sizeof(float)));
+            it = red_sets_.emplace(s, std::move(rs)).first;
+        }
+        *out = it->second.get();
+        return MZB_OK;
+    }
     fused::MlpArgs mlp_;
     int mlp_mg_ = 16, n_sm_ = 0;
     DevBuf trace_;

@@ -53,7 +53,7 @@ def _run(tmp_path, tag, env_value, game, T, sims):
     return np.load(out)
 
 
-@pytest.mark.parametrize("game,T,sims", [("c4d", 97, 12), ("c4r", 300, 8)])
+@pytest.mark.parametrize("game,T,sims", [("c4d", 97, 12), ("c4r", 300, 8), ("ale", 40, 6)])
 def test_pipelined_loop_is_bit_identical_to_single_stream(tmp_path, game, T, sims):
     single = _run(tmp_path, "single", 0, game, T, sims)       # 0 disables the pipeline
     piped = _run(tmp_path, "piped", 2, game, T, sims)         # every cohort of >= 2 trees is split

@@ -910,9 +910,14 @@ protected:
             ++n;
         }
         m.n_heads = n; m.B = B; m.mg = mlp_mg_;
+        // split the first layer's K range over several CTAs when it is long (ALE shape: 2304 inputs = 72 K tiles, a latency
+        // chain of ~1.3 us per tile on one CTA); a fixed function of the layer size, so results do not depend on the batch
+        static const int split_env = getenv("MZB_MLP_SPLITS") ? atoi(getenv("MZB_MLP_SPLITS")) : 0;
+        m.splits = split_env > 0 ? std::min(split_env, MLP_SPLITS_MAX) : (n0max >= 1024 ? 4 : 1);
+        m.part = rs->part.as<float>(); m.part_head_stride = (long)MLP_SPLITS_MAX * max_batch_ * 256; m.counter = rs->counter.as<int>();
         const size_t smem = ((size_t)mlp_mg_ * 512 + 16 * (fused::MLP_KT + 4) + fused::MLP_KT * 64 + fused::MLP_WT) * sizeof(float);
         (void)n0max;
-        dim3 grid((B + mlp_mg_ - 1) / mlp_mg_, n);
+        dim3 grid((B + mlp_mg_ - 1) / mlp_mg_, n, m.splits);
         fused::mlp_heads_kernel<<<grid, fused::MLP_THREADS, smem, s>>>(m);
         MZB_CUDA(cudaGetLastError());
         return MZB_OK;
@@ -1049,7 +1054,8 @@ protected:
     size_t conv1_rel_[2] = {0, 0}, conv1_bias_rel_[2] = {0, 0}, w0t_rel_[3] = {0, 0, 0};
     size_t mlp0_rel_[2] = {0, 0}, mlp0_bias_rel_[2] = {0, 0};
     int mlp0_nkb_[2] = {0, 0};
-    struct RedSet { DevBuf r[3]; };
+    static constexpr int MLP_SPLITS_MAX = 8;
+    struct RedSet { DevBuf r[3], part, counter; };   // + split-K scratch of mlp_heads_kernel
     std::map<cudaStream_t, std::unique_ptr<RedSet>> red_sets_;
     int red_for(cudaStream_t s, RedSet** out) {
         auto it = red_sets_.find(s);
@@ -1057,6 +1063,9 @@ protected:
             std::unique_ptr<RedSet> rs(new RedSet());
             const int hw = plan_dims_.hw();
             for (int h = 0; h < 3; ++h) MZB_CUDA(rs->r[h].alloc((size_t)max_batch_ * heads_[h].red * hw * sizeof(float)));
+            MZB_CUDA(rs->part.alloc((size_t)3 * MLP_SPLITS_MAX * max_batch_ * 256 * sizeof(float)));
+            MZB_CUDA(rs->counter.alloc((size_t)3 * (max_batch_ + 1) * sizeof(int)));
+            MZB_CUDA(cudaMemset(rs->counter.p, 0, rs->counter.bytes));
             it = red_sets_.emplace(s, std::move(rs)).first;
         }
         *out = it->second.get();

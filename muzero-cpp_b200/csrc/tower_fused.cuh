@@ -803,7 +803,12 @@ struct MlpHead {
     float step, min_value; int contractive;
     double* out; int out_stride;
 };
-struct MlpArgs { MlpHead h[3]; int n_heads, B, mg; };
+struct MlpArgs {
+    MlpHead h[3]; int n_heads, B, mg;
+    // split-K of the first layer (gridDim.z = splits > 1): partial sums [head][split][B][n1] in global memory, one arrival
+    // counter per (head, game group); the last CTA to arrive adds the partials in split order (deterministic) and carries on
+    int splits; float* part; long part_head_stride; int* counter;
+};
 
 constexpr int MLP_KT = 32;    // K tile of the first layer
 constexpr int MLP_WT = 64 * 65;   // floats of the transposed tail-layer weight buffer
@@ -817,6 +822,10 @@ __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_con
     const int b0 = blockIdx.x * a.mg;
     const int nb = min(a.mg, a.B - b0);
     const int n0 = hd.sizes[0], n1 = hd.sizes[1];
+    const int S = a.splits > 1 ? a.splits : 1, split = blockIdx.z;
+    const int n_kt = (n0 + MLP_KT - 1) / MLP_KT;
+    const int k_lo = (int)((long)n_kt * split / S) * MLP_KT, k_hi = min(n0, (int)((long)n_kt * (split + 1) / S) * MLP_KT);
+    float* part = a.part + blockIdx.y * a.part_head_stride;
     float* bufA = msm;                    // [mg][256]
     float* bufB = bufA + a.mg * 256;      // [mg][256]
     float* xs = bufB + a.mg * 256;        // [16][KT + 4]
@@ -845,8 +854,8 @@ __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_con
                     wq[r] = (k < kt && j0 + jj < n1) ? __ldg(hd.w0t + (long)(k0 + k) * n1 + j0 + jj) : 0.f;
                 }
             };
-            gload(0);
-            for (int k0 = 0; k0 < n0; k0 += MLP_KT) {
+            gload(k_lo);
+            for (int k0 = k_lo; k0 < k_hi; k0 += MLP_KT) {
                 __syncthreads();
 #pragma unroll
                 for (int r = 0; r < XR; ++r) {
@@ -856,7 +865,7 @@ __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_con
 #pragma unroll
                 for (int r = 0; r < WR; ++r) ws[tid + r * MLP_THREADS] = wq[r];
                 __syncthreads();
-                if (k0 + MLP_KT < n0) gload(k0 + MLP_KT);
+                if (k0 + MLP_KT < k_hi) gload(k0 + MLP_KT);
                 const float* xr = xs + (ty * 4) * (MLP_KT + 4);
 #pragma unroll
                 for (int k = 0; k < MLP_KT; k += 4) {
@@ -873,6 +882,7 @@ __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_con
                 for (int g = 0; g < 4; ++g) {
                     const int gg = ty * 4 + g;
                     if (gg < nb) {
+                        if (S > 1) { part[((long)split * a.B + b0 + gg) * n1 + j] = acc[g]; continue; }
                         float v = acc[g] + hd.b[0][j];
                         if (hd.n_layers > 1) v = fmaxf(v, 0.f);
                         bufA[gg * 256 + j] = v;
@@ -881,6 +891,28 @@ __global__ void __launch_bounds__(MLP_THREADS) mlp_heads_kernel(const __grid_con
             }
         }
         (void)groups;
+    }
+    if (S > 1) {
+        __shared__ int s_last;
+        __threadfence();
+        __syncthreads();
+        int* cnt = a.counter + blockIdx.y * gridDim.x + blockIdx.x;
+        if (tid == 0) {
+            const int old = atomicAdd(cnt, 1);
+            s_last = (old == S - 1);
+            if (s_last) *cnt = 0;   // ready for the next launch on this stream
+        }
+        __syncthreads();
+        if (!s_last) return;
+        __threadfence();
+        for (int i = tid; i < nb * n1; i += MLP_THREADS) {
+            const int g = i / n1, j = i - g * n1;
+            float v = 0.f;
+            for (int sp = 0; sp < S; ++sp) v += __ldcg(part + ((long)sp * a.B + b0 + g) * n1 + j);   // split order: run-to-run identical
+            v += hd.b[0][j];
+            if (hd.n_layers > 1) v = fmaxf(v, 0.f);
+            bufA[g * 256 + j] = v;
+        }
     }
     __syncthreads();
     float* cur = bufA; float* nxt = bufB;

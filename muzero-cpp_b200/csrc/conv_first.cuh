@@ -35,6 +35,7 @@ struct FirstArgs {
     const uint8_t* wimg;                    // C1_W_BYTES
     const float* bias;                      // [cout]
     int cin, cout, H, W, Ho, Wo, relu;
+    int pkm;                                // 1: the output is a PKM tensor [cout / 8][Ho + 2][Wo + 1][8] (conv_band.cuh), else NHWC
     int rbo, bands, N, cls;                 // output rows per band, bands per image, MMA columns, entries per parity class
 };
 
@@ -46,7 +47,7 @@ inline int first_rows(int Wo) {   // rbo * Wp <= 256 and the epilogue's last 16-
 }
 inline int first_cls(int N, int Wo) { return N + (Wo + 1) + 8; }
 inline size_t first_smem_bytes(int cls, int rbo, int Wo, int cout) {
-    size_t in_b = (size_t)2 * 4 * cls * 16, out_b = (size_t)rbo * Wo * cout * 2;
+    size_t in_b = (size_t)2 * 4 * cls * 16, out_b = (size_t)rbo * (Wo + 1) * cout * 2;
     return (((in_b > out_b ? in_b : out_b) + 127) & ~(size_t)127) + C1_W_BYTES + 64;
 }
 
@@ -57,7 +58,7 @@ __global__ void __launch_bounds__(C1_THREADS) conv_first_kernel(const __grid_con
     const int oy0 = band * a.rbo;
     const int rows_here = min(a.rbo, a.Ho - oy0);
     const int Wp = a.Wo + 1, CLS = a.cls;
-    const size_t in_b = (size_t)2 * 4 * CLS * 16, out_b = (size_t)a.rbo * a.Wo * a.cout * 2;
+    const size_t in_b = (size_t)2 * 4 * CLS * 16, out_b = (size_t)a.rbo * (a.Wo + 1) * a.cout * 2;
     uint8_t* S = smem;                                   // staged band, later the bf16 output rows
     uint8_t* Wt = smem + (((in_b > out_b ? in_b : out_b) + 127) & ~(size_t)127);  // weight images
     uint64_t* w_full = reinterpret_cast<uint64_t*>(Wt + C1_W_BYTES);
@@ -76,34 +77,47 @@ __global__ void __launch_bounds__(C1_THREADS) conv_first_kernel(const __grid_con
     __syncthreads();
     if (warp == 0) tmem_alloc(tmem_ptr, 256);
     {
-        // input rows iy = 2 oy0 - 1 .. 2 (oy0 + rows_here - 1) + 1; a work item = (plane, row, 4 consecutive columns)
+        // input rows iy = 2 oy0 - 1 .. 2 (oy0 + rows_here - 1) + 1.  A work item = (plane half, row, column): the thread reads its
+        // pixel from up to 8 planes (each read coalesced across the warp: consecutive lanes = consecutive columns), packs them to
+        // bf16 and writes ONE 16-byte entry.  (First version: one plane x 4 columns per thread and 2-byte scatter stores — 70 % of
+        // the shared-store wavefronts were bank conflicts, ncu.)
         const int iy0 = 2 * oy0 - 1, nrows = 2 * rows_here + 1;
-        const int wq = (a.W + 3) >> 2;
-        const int items = a.cin * nrows * wq;
+        const int halves = (a.cin + 7) >> 3;
+        const int items = halves * nrows * a.W;
         const float* ob = a.obs + (long)img * a.obs_stride;
-        const bool vec_ok = (a.W & 3) == 0 && ((a.obs_stride & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.obs) & 15) == 0);
-        for (int e = tid; e < items; e += C1_THREADS) {
-            const int xq = e % wq, t = e / wq, r = t % nrows, p = t / nrows;
-            const int iy = iy0 + r;
-            if (iy < 0 || iy >= a.H) continue;
-            const float* src = ob + ((long)p * a.H + iy) * a.W + xq * 4;
-            float v[4];
-            if (vec_ok) {
-                const float4 f = __ldg(reinterpret_cast<const float4*>(src));
-                v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
-            } else {
+        const long plane = (long)a.H * a.W;
+        // four items per pass: all 32 loads of a pass are in flight before the first is used (one item at a time was a chain of
+        // ~8 DRAM round trips per thread — most of the kernel's time)
+        constexpr int U = 4;
+        for (int e0 = tid; e0 < items; e0 += U * C1_THREADS) {
+            float v[U][8];
+            uint32_t dst[U];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) v[j] = (xq * 4 + j < a.W) ? __ldg(src + j) : 0.f;
-            }
-            const int rp = iy & 1;                                   // even rows: r2 = iy / 2 - oy0; odd: (iy + 1) / 2 - oy0
-            const int r2 = ((iy + rp) >> 1) - oy0;
-            uint8_t* base = S + ((size_t)((p >> 3) * 4 + rp * 2) * CLS + (size_t)r2 * Wp) * 16 + (p & 7) * 2;
+            for (int u = 0; u < U; ++u) {
+                const int e = e0 + u * C1_THREADS;
+                dst[u] = 0xffffffffu;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int ix = xq * 4 + j;
-                if (ix >= a.W) break;
+                for (int p = 0; p < 8; ++p) v[u][p] = 0.f;
+                if (e >= items) continue;
+                const int ix = e % a.W, t = e / a.W, r = t % nrows, h = t / nrows;
+                const int iy = iy0 + r;
+                if (iy < 0 || iy >= a.H) continue;
+                const float* src = ob + (long)(8 * h) * plane + (long)iy * a.W + ix;
+                const int np = min(8, a.cin - 8 * h);
+#pragma unroll
+                for (int p = 0; p < 8; ++p) if (p < np) v[u][p] = __ldg(src + p * plane);
+                const int rp = iy & 1, r2 = ((iy + rp) >> 1) - oy0;      // even rows: r2 = iy / 2 - oy0; odd: (iy + 1) / 2 - oy0
                 const int cp = ix & 1, c2 = (ix + cp) >> 1;
-                *reinterpret_cast<bf16*>(base + ((size_t)cp * CLS + c2) * 16) = __float2bfloat16(v[j]);
+                dst[u] = (uint32_t)((((size_t)(h * 4 + rp * 2 + cp) * CLS + (size_t)r2 * Wp + c2) * 16));
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (dst[u] == 0xffffffffu) continue;
+                uint4 pk;
+                __nv_bfloat162* p2 = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                for (int p = 0; p < 4; ++p) p2[p] = __floats2bfloat162_rn(v[u][2 * p], v[u][2 * p + 1]);
+                *reinterpret_cast<uint4*>(S + dst[u]) = pk;
             }
         }
     }
@@ -150,14 +164,17 @@ __global__ void __launch_bounds__(C1_THREADS) conv_first_kernel(const __grid_con
                     uint32_t v[16];
                     tmem_ld16(t_lane + (uint32_t)(r * Wp + x0), v);   // may run past the row: only x < Wo is used
                     tmem_ld_wait();
-                    bf16* sp = So + (long)(r * a.Wo + x0) * a.cout + co;
+                    // NHWC staging [row][x][cout], or PKM staging [K chunk][row][x incl. pad column][8]
+                    bf16* sp = a.pkm ? So + ((long)((co >> 3) * a.rbo + r) * Wp + x0) * 8 + (co & 7) : So + (long)(r * a.Wo + x0) * a.cout + co;
+                    const long sj = a.pkm ? 8 : a.cout;
 #pragma unroll
                     for (int j = 0; j < 16; ++j)
                         if (x0 + j < a.Wo && co_ok) {
                             float y = __uint_as_float(v[j]) + bias;
                             if (a.relu) y = fmaxf(y, 0.f);
-                            sp[(long)j * a.cout] = __float2bfloat16(y);
+                            sp[(long)j * sj] = __float2bfloat16(y);
                         }
+                    if (a.pkm && co_ok && x0 + 16 >= a.Wo) sp[(long)(a.Wo - x0) * 8] = __float2bfloat16(0.f);   // the pad column
                 }
             }
         }
@@ -166,10 +183,25 @@ __global__ void __launch_bounds__(C1_THREADS) conv_first_kernel(const __grid_con
     __syncthreads();
     {
         // the band's output rows are contiguous in the NHWC tensor: 16-byte coalesced stores
-        const long n16 = (long)rows_here * a.Wo * a.cout * 2 / 16;
-        uint4* dst = reinterpret_cast<uint4*>(a.out + ((long)img * a.Ho + oy0) * a.Wo * a.cout);
         const uint4* src = reinterpret_cast<const uint4*>(S);
-        for (long i = tid; i < n16; i += C1_THREADS) dst[i] = src[i];
+        if (!a.pkm) {
+            const long n16 = (long)rows_here * a.Wo * a.cout * 2 / 16;
+            uint4* dst = reinterpret_cast<uint4*>(a.out + ((long)img * a.Ho + oy0) * a.Wo * a.cout);
+            for (long i = tid; i < n16; i += C1_THREADS) dst[i] = src[i];
+        } else {
+            // per K chunk the band's rows (pad column included) are one contiguous run of the PKM tensor
+            const int KCo = a.cout >> 3, per = rows_here * Wp;
+            uint4* dst = reinterpret_cast<uint4*>(a.out + (long)img * KCo * (a.Ho + 2) * Wp * 8);
+            for (int i = tid; i < KCo * per; i += C1_THREADS) {
+                const int kc = i / per, rem = i - kc * per;
+                dst[((long)kc * (a.Ho + 2) + oy0 + 1) * Wp + rem] = src[(long)kc * a.rbo * Wp + rem];
+            }
+            // zero border rows of the tensor: row 0 by the first band, row Ho + 1 by the last
+            if (oy0 == 0)
+                for (int i = tid; i < KCo * Wp; i += C1_THREADS) dst[(long)(i / Wp) * (a.Ho + 2) * Wp + i % Wp] = make_uint4(0u, 0u, 0u, 0u);
+            if (oy0 + rows_here == a.Ho)
+                for (int i = tid; i < KCo * Wp; i += C1_THREADS) dst[((long)(i / Wp) * (a.Ho + 2) + a.Ho + 1) * Wp + i % Wp] = make_uint4(0u, 0u, 0u, 0u);
+        }
     }
     if (warp == 0) tmem_dealloc(tmem, 256);
 }
@@ -178,7 +210,7 @@ __global__ void __launch_bounds__(C1_THREADS) conv_first_kernel(const __grid_con
 // 8 channels of one output pixel: nine 16-byte loads, one 16-byte store (HBM-bound: reads the input once, 2.25 taps per element
 // from L1/L2)
 __global__ void __launch_bounds__(256) avgpool3_vec_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int B, int C8, int in_h, int in_w,
-                                                           int out_h, int out_w) {
+                                                           int out_h, int out_w, int pkm_in) {
     const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const long total = (long)B * out_h * out_w * C8;
     if (i >= total) return;
@@ -196,7 +228,8 @@ __global__ void __launch_bounds__(256) avgpool3_vec_kernel(const bf16* __restric
         for (int kx = 0; kx < 3; ++kx) {
             const int ix = ox * 2 + kx - 1;
             if (ix < 0 || ix >= in_w) continue;
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(in + ((((long)b * in_h + iy) * in_w + ix) * C8 + c8) * 8));
+            const long idx = pkm_in ? (((long)b * C8 + c8) * (in_h + 2) + iy + 1) * (in_w + 1) + ix : (((long)b * in_h + iy) * in_w + ix) * C8 + c8;
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(in + idx * 8));
             const bf16* p = reinterpret_cast<const bf16*>(&v);
 #pragma unroll
             for (int k = 0; k < 8; ++k) acc[k] += __bfloat162float(p[k]);

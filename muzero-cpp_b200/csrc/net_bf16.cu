@@ -400,6 +400,27 @@ protected:
                 }
             }
         }
+        // PKM segment (conv_band.cuh): first conv -> every convolution up to the first pooling step, when all of them fit
+        // conv_band2_kernel.  The activations between those kernels then stay in the padded K-major layout.
+        pkm_chain_ = false; pkm_max_elems_ = 0;
+        if (first_ok_ && !getenv("MZB_BAND_V1")) {
+            const Tower& tw = plan.representation;
+            size_t pool_at = 0;
+            for (size_t i = 1; i < tw.steps.size(); ++i) if (tw.steps[i].kind == TowerStep::POOL) { pool_at = i; break; }
+            bool ok = pool_at > 1;
+            size_t mxe = (size_t)band::pkm_elems(tw.convs[0].cout, tw.convs[0].out_h, tw.convs[0].out_w);
+            for (size_t i = 1; ok && i < pool_at; ++i) {
+                const TowerStep& st = tw.steps[i];
+                for (int k : {st.conv0, st.kind == TowerStep::BLOCK ? st.conv1 : st.conv0}) {
+                    const Conv3Host& c = tw.convs[k];
+                    band::Band2Args g2;
+                    memset(&g2, 0, sizeof(g2));
+                    ok = ok && packed_[0][k].image && !packed_[0][k].ok && c.act_table.empty() && band2_geometry(c.cin, c.cout, c.stride, c.in_h, c.in_w, &g2);
+                    mxe = std::max(mxe, (size_t)band::pkm_elems(c.cout, c.out_h, c.out_w));
+                }
+            }
+            if (ok) { pkm_chain_ = true; pkm_max_elems_ = mxe; pkm_last_conv_ = 0; for (size_t i = 1; i < pool_at; ++i) pkm_last_conv_ = std::max(pkm_last_conv_, std::max(tw.steps[i].conv0, tw.steps[i].kind == TowerStep::BLOCK ? tw.steps[i].conv1 : tw.steps[i].conv0)); }
+        }
         if (!attr_set_) {
             MZB_CUDA(cudaFuncSetAttribute(umma_conv3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
             attr_set_ = true;
@@ -1018,6 +1039,8 @@ public:
                 a.out = bufB_.as<bf16>();
                 a.wimg = reinterpret_cast<const uint8_t*>(blob_.p) + fp32_bytes_ + first_off_;
                 a.bias = blob_.as<float>() + c0.bias_off;
+                a.pkm = pkm_chain_ ? 1 : 0;
+                cur_pkm_ = pkm_chain_;
                 first::conv_first_kernel<<<B * a.bands, first::C1_THREADS, first::first_smem_bytes(a.cls, a.rbo, a.Wo, a.cout), s>>>(a);
                 MZB_CUDA(cudaGetLastError());
                 ++launches_;
@@ -1051,6 +1074,7 @@ protected:
     cudaEvent_t ev_wait_ = nullptr, ev_record_ = nullptr;
     size_t init_tail_ = 0;            // first representation step of the fused initial chain
     bool first_ok_ = false; size_t first_off_ = 0; first::FirstArgs first_args_;   // conv_first.cuh
+    bool pkm_chain_ = false, cur_pkm_ = false; size_t pkm_max_elems_ = 0; int pkm_last_conv_ = 0;   // PKM segment of the downsample head
     size_t conv1_rel_[2] = {0, 0}, conv1_bias_rel_[2] = {0, 0}, w0t_rel_[3] = {0, 0, 0};
     size_t mlp0_rel_[2] = {0, 0}, mlp0_bias_rel_[2] = {0, 0};
     int mlp0_nkb_[2] = {0, 0};
@@ -1122,10 +1146,40 @@ protected:
         return 1;
     }
 
+    // geometry of conv_band2_kernel for one convolution; false when it does not fit
+    static bool band2_geometry(int cin, int cout, int stride, int H, int W, band::Band2Args* g2) {
+        if (cin % 64 != 0 || cout > 128 || cout % 8 != 0 || (stride != 1 && stride != 2)) return false;
+        band::BandArgs& a = g2->b;
+        a.stride = stride;
+        a.rb = band::band_rows(H, W);
+        if (stride == 2) a.rb = a.rb / 2 * 2;
+        if (a.rb < 1) return false;
+        a.bands = (H + a.rb - 1) / a.rb;
+        a.N = ((a.rb + 2) * (W + 1) + 15) / 16 * 16;
+        a.HALO = W + 2;
+        a.R = a.HALO + a.N + a.HALO;
+        a.x_bytes = (int)((((size_t)(cin / 8) * a.R * 16) + 127) / 128 * 128);
+        a.H = H; a.W = W; a.cin = cin; a.cout = cout;
+        // fp32 staging [K chunk][pixel][8] with 8 floats of padding per plane; its own buffer for the whole band when that fits
+        // beside two X buffers and >= 4 ring slots (the 64-channel stage), else aliased on X[j % 2] in row chunks
+        const size_t kco = cout / 8;
+        auto stage_bytes = [&](int rows) { return kco * ((size_t)rows * W * 8 + 8) * sizeof(float); };
+        long avail = 227L * 1024 - 2L * a.x_bytes - 256;
+        g2->sep = (avail - (long)stage_bytes(a.rb) >= 4L * band::B_KB_BYTES && !getenv("MZB_BAND_NO_SEP")) ? 1 : 0;
+        if (g2->sep) { avail -= (long)stage_bytes(a.rb); g2->rc = a.rb; }
+        else { g2->rc = a.rb; while (g2->rc >= 1 && stage_bytes(g2->rc) > (size_t)a.x_bytes) --g2->rc; }
+        g2->ns = (int)std::min<long>(8, avail / band::B_KB_BYTES);
+        g2->ps = g2->rc * W * 8 + 8;
+        return a.N <= 256 && g2->ns >= 2 && g2->rc >= 1;
+    }
+    size_t act_elems(size_t mx) const override { return std::max(mx, pkm_max_elems_); }
+
     int fast_pool(const bf16* in, bf16* out, int B, int C, int in_h, int in_w, int out_h, int out_w, cudaStream_t s) override {
         if (C % 8 != 0) return 0;
         const long total = (long)B * out_h * out_w * (C / 8);
-        first::avgpool3_vec_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(in, out, B, C / 8, in_h, in_w, out_h, out_w);
+        const int pkm_in = cur_pkm_ ? 1 : 0;
+        cur_pkm_ = false;   // pools write NHWC
+        first::avgpool3_vec_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(in, out, B, C / 8, in_h, in_w, out_h, out_w, pkm_in);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("avgpool3_vec_kernel launch failed: %s", cudaGetErrorString(e)); return MZB_ERR_CUDA; }
         return 1;
@@ -1150,6 +1204,39 @@ protected:
         const size_t stage_need = (size_t)a.rb * c.in_w * c.cout * sizeof(float);
         a.nstage = (band::band_smem_bytes(a.x_bytes, 2) <= 113 * 1024 && stage_need <= 2 * (size_t)band::B_STAGE_BYTES) ? 2 : 4;
         const size_t smem = band::band_smem_bytes(a.x_bytes, a.nstage);
+        a.in = call.in; a.in_slot = call.in_slot; a.in_stride = call.in_stride;
+        a.out = call.out; a.out_slot = call.out_slot; a.out_stride = call.out_stride;
+        a.res = call.res; a.res_slot = call.res_slot; a.res_stride = call.res_stride;
+        a.wimg = reinterpret_cast<const uint8_t*>(blob_.p) + fp32_bytes_ + p.off;
+        a.bias = blob_.as<float>() + c.bias_off;
+        a.H = c.in_h; a.W = c.in_w; a.cin = c.cin; a.cout = c.cout; a.relu = c.relu;
+        if (cur_pkm_) {
+            // inside the PKM segment: persistent, double-buffered kernel over padded K-major activations (conv_band2_kernel)
+            if (!(pkm_chain_ && c.tower == 0 && c.index <= pkm_last_conv_)) { set_error("convolution %d of tower %d got a PKM activation outside the PKM segment", c.index, c.tower); return MZB_ERR_STATE; }
+            band::Band2Args g2;
+            memset(&g2, 0, sizeof(g2));
+            if (!band2_geometry(c.cin, c.cout, c.stride, c.in_h, c.in_w, &g2)) { set_error("conv_band2_kernel geometry"); return MZB_ERR_STATE; }
+            band::BandArgs& b = g2.b;
+            b.in = call.in; b.out = call.out; b.res = call.res;
+            b.in_slot = nullptr; b.out_slot = nullptr; b.res_slot = nullptr;
+            b.in_stride = band::pkm_elems(c.cin, c.in_h, c.in_w);
+            b.out_stride = band::pkm_elems(c.cout, c.out_h, c.out_w);
+            b.res_stride = b.out_stride;
+            b.wimg = a.wimg; b.bias = a.bias; b.relu = c.relu;
+            static const int band_dbg = getenv("MZB_BAND_DBG") ? atoi(getenv("MZB_BAND_DBG")) : 0;
+            g2.dbg = band_dbg;
+            g2.total = call.B * b.bands;
+            if (n_sm_ <= 0) { int dev = 0; MZB_CUDA(cudaGetDevice(&dev)); MZB_CUDA(cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, dev)); }
+            if (!band2_attr_set_) {
+                MZB_CUDA(cudaFuncSetAttribute(band::conv_band2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                band2_attr_set_ = true;
+            }
+            const size_t stage = g2.sep ? (size_t)(c.cout / 8) * g2.ps * sizeof(float) : 0;
+            band::conv_band2_kernel<<<std::min(n_sm_, g2.total), band::B_THREADS, band::band2_smem_bytes(b.x_bytes, g2.ns, stage), s>>>(g2);
+            cudaError_t e2 = cudaGetLastError();
+            if (e2 != cudaSuccess) { set_error("conv_band2_kernel launch failed: %s", cudaGetErrorString(e2)); return MZB_ERR_CUDA; }
+            return 1;
+        }
         if (a.N > 256 || smem > 227 * 1024 || stage_need > (size_t)a.nstage * band::B_STAGE_BYTES) return 0;
         if (!band_attr_set_) {
             MZB_CUDA(cudaFuncSetAttribute(band::conv_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -1168,7 +1255,7 @@ protected:
     }
 
     std::vector<Packed> packed_[3];
-    bool band_attr_set_ = false;
+    bool band_attr_set_ = false, band2_attr_set_ = false;
     DevBuf dbg_;
     bool attr_set_ = false;
 };

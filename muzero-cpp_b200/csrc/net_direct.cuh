@@ -310,6 +310,7 @@ public:
         max_batch_ = max_batch;
         size_t mx = 0;
         for (int t = 0; t < 3; ++t) if ((size_t)max_act_[t] > mx) mx = max_act_[t];
+        mx = act_elems(mx);
         MZB_CUDA(bufA_.alloc((size_t)max_batch * mx * sizeof(T)));
         MZB_CUDA(bufB_.alloc((size_t)max_batch * mx * sizeof(T)));
         MZB_CUDA(bufC_.alloc((size_t)max_batch * mx * sizeof(T)));
@@ -382,6 +383,8 @@ protected:
     virtual int pack_extra(const NetPlan&, std::vector<uint8_t>*) { return MZB_OK; }
     // return 1 when the call was executed by a specialised kernel, 0 to fall through to the direct kernel, <0 on error
     virtual int fast_conv(const ConvCall<T>&, cudaStream_t) { return 0; }
+    // elements per sample of the activation scratch buffers (a backend may keep activations in a padded layout)
+    virtual size_t act_elems(size_t largest_activation) const { return largest_activation; }
     // same contract for AvgPool2d(3, 2, 1) on a compact NHWC activation
     virtual int fast_pool(const T*, T*, int, int, int, int, int, int, cudaStream_t) { return 0; }
 

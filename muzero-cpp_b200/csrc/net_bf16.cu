@@ -419,6 +419,7 @@ protected:
                     mxe = std::max(mxe, (size_t)band::pkm_elems(c.cout, c.out_h, c.out_w));
                 }
             }
+            if (getenv("MZB_VERBOSE")) fprintf(stderr, "[bf16] downsample head: conv_first %s, PKM segment (conv_band2_kernel) %s\n", first_ok_ ? "yes" : "no", ok ? "yes" : "no");
             if (ok) { pkm_chain_ = true; pkm_max_elems_ = mxe; pkm_last_conv_ = 0; for (size_t i = 1; i < pool_at; ++i) pkm_last_conv_ = std::max(pkm_last_conv_, std::max(tw.steps[i].conv0, tw.steps[i].kind == TowerStep::BLOCK ? tw.steps[i].conv1 : tw.steps[i].conv0)); }
         }
         if (!attr_set_) {

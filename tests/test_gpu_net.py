@@ -231,6 +231,28 @@ def test_bf16_matches_oracle_random_weights(game, B):
     eng.close()
 
 
+def test_bf16_downsample_head_with_ragged_bands():
+    """the downsample head's tensor kernels (conv_first, PKM band kernel, pools) on a 76 x 88 observation: 38 x 44 and 19 x 22
+    stages whose bands do not divide the height (last band 2 rows / 1 row), odd pooled sizes (10 x 11 -> 5 x 6)"""
+    import mzb200
+    over = dict(obs_shape=(1, 76, 88), stacked_observations=2, rep_blocks=1, dyn_blocks=1, pred_blocks=1)
+    ncfg = V.preset("ale", **over)
+    W = H.random_weights(ncfg, seed=11)
+    net = V.VPRNetOracle(ncfg, W)
+    nc = mzb200.MuZeroNetworkConfig(downsample=True, representation_blocks=1, dynamics_blocks=1, prediction_blocks=1,
+                                    reward_reduced_channels=64, policy_reduced_channels=64, value_reduced_channels=64,
+                                    reward_head_layers=[64, 64], policy_head_layers=[64, 64], value_head_layers=[64, 64])
+    eng = _engine("ale", 8, 1, observation_shape=(1, 76, 88), stacked_observations=2, network_config=nc)
+    eng.load_weights(W)
+    rng = np.random.default_rng(5)
+    B = 3
+    obs = rng.random((B, ncfg.in_channels * 76 * 88), dtype=np.float32)
+    a1 = rng.integers(0, ncfg.num_actions, B).astype(np.int32)
+    a2 = rng.integers(0, ncfg.num_actions, B).astype(np.int32)
+    _run_chain(eng, net, obs, a1, a2, 1, "ale 76x88 bf16")
+    eng.close()
+
+
 def test_bf16_odd_shapes_use_direct_kernels():
     """channel counts the tensor path cannot take (16) still run in bf16 storage on the direct kernels"""
     ncfg = V.preset("tiny")

@@ -67,7 +67,9 @@ struct mzb_engine {
     cudaStream_t pipe[MAX_PARTS - 1] = {};   // streams of parts 1.. of the pipelined simulation loop (part 0 runs on `stream`)
     cudaEvent_t ev_start = nullptr, ev_root = nullptr, ev_end = nullptr, ev_aux = nullptr, ev_fork = nullptr;
     cudaEvent_t ev_join[MAX_PARTS - 1] = {};
-    cudaEvent_t ev_tower[MAX_PARTS] = {};   // end of each part's latest tower kernel (alternating pipeline)
+    cudaEvent_t ev_tower[MAX_PARTS] = {};
+    // CUDA graph of the pipelined simulation loop (engine_search.cu)
+    cudaGraphExec_t sim_graph = nullptr; uint64_t sim_graph_key = 0, sim_graph_warm_key = 0; int64_t sim_graph_launches = 0; bool graph_failed = false;   // end of each part's latest tower kernel (alternating pipeline)
     // trees
     TreeDev td;
     DevBuf meta, prior, value_sum, reward, mm_min, mm_max, root_to_play, n_legal, n_slots, max_depth, mt, mt_idx,

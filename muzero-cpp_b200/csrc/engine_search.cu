@@ -141,60 +141,109 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
         int t0[mzb_engine::MAX_PARTS + 1];
         NetOutputs o[mzb_engine::MAX_PARTS];
         e->net->pipeline_cut(T, K, t0);
-        MZB_CUDA(cudaEventRecord(e->ev_fork, s));
-        for (int k = 0; k < K; ++k) {
-            st[k] = k == 0 ? s : e->pipe[k - 1];
-            if (k > 0) MZB_CUDA(cudaStreamWaitEvent(st[k], e->ev_fork, 0));
-            o[k] = tree_outputs(e);
-            o[k].value += t0[k]; o[k].reward += t0[k]; o[k].policy += (size_t)t0[k] * A;
-        }
-        e->net->set_pipelined(true);
         static const int alt_env = getenv("MZB_PIPELINE_ALTERNATE") ? atoi(getenv("MZB_PIPELINE_ALTERNATE")) : -1;
         const bool alternate = alt_env > 0;
         // MZB_PIPELINE_TRACE=1: a timed event behind every launch, printed as a timeline after the search (diagnostic only)
         static const bool trace = getenv("MZB_PIPELINE_TRACE") != nullptr;
-        std::vector<cudaEvent_t> tev;
-        auto mark = [&](cudaStream_t q) { if (trace) { cudaEvent_t ev; cudaEventCreate(&ev); cudaEventRecord(ev, q); tev.push_back(ev); } };
-        for (int sim = 0; sim <= n && !rc; ++sim) {
-            for (int k = 0; k < K && !rc; ++k) {
-                launch_tree_step_range(td, t0[k], t0[k + 1], sim, st[k]);
-                ++launches;
-                mark(st[k]);
-                if (sim == n) continue;
-                // EXPERIMENT (MZB_PIPELINE_ALTERNATE=1, off by default): this part's tower starts only when the previous part's tower
-                // has ended, so that the kernels behind a tower (head MLPs of a wide-head network, the next tree step) run beside the
-                // other part's tower.  Measured slower everywhere (ALE 17.4 -> 21.6 ms, c4d 11.5 -> 14.4 ms per search): serialised
-                // towers expose every launch's ramp-up and drain (~20 us), which freely overlapping launches hide.
-                if (alternate) e->net->set_tower_events((sim > 0 || k > 0) ? e->ev_tower[(k + K - 1) % K] : nullptr, e->ev_tower[k]);
-                rc = e->net->recurrent(t0[k + 1] - t0[k], td.in_slot + t0[k], td.action + t0[k], td.out_slot + t0[k], o[k], st[k]);
-                launches += e->net->launches_recurrent();
-                mark(st[k]);
-            }
+        for (int k = 0; k < K; ++k) {
+            st[k] = k == 0 ? s : e->pipe[k - 1];
+            o[k] = tree_outputs(e);
+            o[k].value += t0[k]; o[k].reward += t0[k]; o[k].policy += (size_t)t0[k] * A;
         }
-        e->net->set_pipelined(false);
-        if (trace) {
-            for (int k = 0; k < K; ++k) cudaStreamSynchronize(st[k]);
-            fprintf(stderr, "[pipeline] parts:");
-            for (int k = 0; k < K; ++k) fprintf(stderr, " %d", t0[k + 1] - t0[k]);
-            fprintf(stderr, " trees; end of (tree step | tower) per part, us since the root event\n");
-            size_t i = 0;
-            for (int sim = 0; sim <= n && sim < (getenv("MZB_PIPELINE_TRACE_ALL") ? n + 1 : 8); ++sim) {
-                fprintf(stderr, "[pipeline] sim %2d:", sim);
-                for (int k = 0; k < K; ++k) {
-                    float a = 0.f, b = 0.f;
-                    cudaEventElapsedTime(&a, e->ev_root, tev[i++]);
-                    if (sim < n) cudaEventElapsedTime(&b, e->ev_root, tev[i++]);
-                    fprintf(stderr, "  part %d: %8.1f | %8.1f", k, a * 1e3f, b * 1e3f);
+        int64_t loop_launches = 0;
+        // fork -> every simulation's launches on the parts' streams -> join, as one enqueue: run eagerly, or captured into a CUDA graph
+        auto enqueue = [&]() -> int {
+            int lrc = MZB_OK;
+            loop_launches = 0;
+            MZB_CUDA(cudaEventRecord(e->ev_fork, s));
+            for (int k = 1; k < K; ++k) MZB_CUDA(cudaStreamWaitEvent(st[k], e->ev_fork, 0));
+            e->net->set_pipelined(true);
+            std::vector<cudaEvent_t> tev;
+            auto mark = [&](cudaStream_t q) { if (trace) { cudaEvent_t ev; cudaEventCreate(&ev); cudaEventRecord(ev, q); tev.push_back(ev); } };
+            for (int sim = 0; sim <= n && !lrc; ++sim) {
+                for (int k = 0; k < K && !lrc; ++k) {
+                    launch_tree_step_range(td, t0[k], t0[k + 1], sim, st[k]);
+                    ++loop_launches;
+                    mark(st[k]);
+                    if (sim == n) continue;
+                    // EXPERIMENT (MZB_PIPELINE_ALTERNATE=1, off by default): this part's tower starts only when the previous part's tower
+                    // has ended, so that the kernels behind a tower (head MLPs of a wide-head network, the next tree step) run beside the
+                    // other part's tower.  Measured slower everywhere (ALE 17.4 -> 21.6 ms, c4d 11.5 -> 14.4 ms per search): serialised
+                    // towers expose every launch's ramp-up and drain (~20 us), which freely overlapping launches hide.
+                    if (alternate) e->net->set_tower_events((sim > 0 || k > 0) ? e->ev_tower[(k + K - 1) % K] : nullptr, e->ev_tower[k]);
+                    lrc = e->net->recurrent(t0[k + 1] - t0[k], td.in_slot + t0[k], td.action + t0[k], td.out_slot + t0[k], o[k], st[k]);
+                    loop_launches += e->net->launches_recurrent();
+                    mark(st[k]);
                 }
-                fprintf(stderr, "\n");
             }
-            for (cudaEvent_t ev : tev) cudaEventDestroy(ev);
+            e->net->set_pipelined(false);
+            if (trace) {
+                for (int k = 0; k < K; ++k) cudaStreamSynchronize(st[k]);
+                fprintf(stderr, "[pipeline] parts:");
+                for (int k = 0; k < K; ++k) fprintf(stderr, " %d", t0[k + 1] - t0[k]);
+                fprintf(stderr, " trees; end of (tree step | tower) per part, us since the root event\n");
+                size_t i = 0;
+                for (int sim = 0; sim <= n && sim < (getenv("MZB_PIPELINE_TRACE_ALL") ? n + 1 : 8); ++sim) {
+                    fprintf(stderr, "[pipeline] sim %2d:", sim);
+                    for (int k = 0; k < K; ++k) {
+                        float a = 0.f, b = 0.f;
+                        cudaEventElapsedTime(&a, e->ev_root, tev[i++]);
+                        if (sim < n) cudaEventElapsedTime(&b, e->ev_root, tev[i++]);
+                        fprintf(stderr, "  part %d: %8.1f | %8.1f", k, a * 1e3f, b * 1e3f);
+                    }
+                    fprintf(stderr, "\n");
+                }
+                for (cudaEvent_t ev : tev) cudaEventDestroy(ev);
+            }
+            // join the side streams into the search stream — also when a launch failed, so that no work is left running on them
+            // behind the caller's back
+            for (int k = 1; k < K; ++k) {
+                MZB_CUDA(cudaEventRecord(e->ev_join[k - 1], st[k]));
+                MZB_CUDA(cudaStreamWaitEvent(s, e->ev_join[k - 1], 0));
+            }
+            return lrc;
+        };
+        // CUDA graph of the loop: the launch sequence of a search depends only on the cohort size, the cut and
+        // the pointers baked into the kernels' arguments.  The first search with a given key runs eagerly (it also creates the
+        // backend's per-batch tables), the second is captured, later ones replay the instantiated graph: ~4 n launches + 2 n
+        // event operations per search leave the host thread.  MZB_NO_GRAPH=1 keeps the eager loop.
+        static const bool no_graph = getenv("MZB_NO_GRAPH") != nullptr;
+        const bool graphable = !no_graph && !trace && !alternate && !getenv("MZB_TILE_TRACE") && !e->graph_failed;
+        uint64_t key = 1469598103934665603ull;
+        auto mix = [&](const void* p, size_t nb) { const uint8_t* b = (const uint8_t*)p; for (size_t i = 0; i < nb; ++i) { key ^= b[i]; key *= 1099511628211ull; } };
+        if (graphable) {
+            const void* blob = e->net->blob_ptr();
+            mix(&td, sizeof(td)); mix(&T, sizeof(T)); mix(&K, sizeof(K)); mix(t0, sizeof(int) * (K + 1)); mix(&blob, sizeof(blob));
+            mix(&e->weights_serial, sizeof(e->weights_serial));
         }
-        // join the side streams into the search stream — also when a launch failed, so that no work is left running on them
-        // behind the caller's back
-        for (int k = 1; k < K; ++k) {
-            MZB_CUDA(cudaEventRecord(e->ev_join[k - 1], st[k]));
-            MZB_CUDA(cudaStreamWaitEvent(s, e->ev_join[k - 1], 0));
+        if (graphable && e->sim_graph && e->sim_graph_key == key) {
+            MZB_CUDA(cudaGraphLaunch(e->sim_graph, s));
+            launches += e->sim_graph_launches;
+        } else if (graphable && e->sim_graph_warm_key == key) {
+            if (e->sim_graph) { cudaGraphExecDestroy(e->sim_graph); e->sim_graph = nullptr; }
+            cudaGraph_t g = nullptr;
+            cudaError_t ce = cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
+            if (ce == cudaSuccess) {
+                rc = enqueue();
+                ce = cudaStreamEndCapture(s, &g);
+                if (ce == cudaSuccess && !rc) ce = cudaGraphInstantiate(&e->sim_graph, g, 0);
+                if (g) cudaGraphDestroy(g);
+            }
+            if (ce != cudaSuccess || rc || !e->sim_graph) {
+                // capture is an optimisation: fall back to the eager loop for good
+                cudaGetLastError();
+                e->graph_failed = true; e->sim_graph = nullptr; rc = MZB_OK;
+                rc = enqueue();
+                launches += loop_launches;
+            } else {
+                e->sim_graph_key = key; e->sim_graph_launches = loop_launches;
+                MZB_CUDA(cudaGraphLaunch(e->sim_graph, s));
+                launches += loop_launches;
+            }
+        } else {
+            rc = enqueue();
+            launches += loop_launches;
+            e->sim_graph_warm_key = key;
         }
         if (rc) { cudaStreamSynchronize(s); return rc; }
     } else if (synthetic) {

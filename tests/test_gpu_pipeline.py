@@ -28,7 +28,7 @@ eng.set_recording(True)
 rng = np.random.default_rng(1)
 A = cfg.num_actions
 keep = {}
-for move in range(2):
+for move in range(4):   # move 0 eager, move 1 captured into a CUDA graph, moves 2-3 replay it (the single-stream run has no graph)
     obs = rng.random((T, eng.shapes.initial_flat_size), dtype=np.float32)
     masks = H.se_legal_masks(H.se_keys(T, move), A, 1)
     to_play = rng.integers(0, cfg.num_players, T).astype(np.int32)

@@ -218,6 +218,7 @@ void mzb_engine_destroy(mzb_engine* e) {
     for (int i = 0; i < mzb_engine::MAX_PARTS - 1; ++i) if (e->ev_join[i]) cudaEventDestroy(e->ev_join[i]);
     for (int i = 0; i < mzb_engine::MAX_PARTS; ++i) if (e->ev_tower[i]) cudaEventDestroy(e->ev_tower[i]);
     if (e->sim_graph) cudaGraphExecDestroy(e->sim_graph);
+    for (int i = 0; i < mzb_engine::MAX_PARTS; ++i) { if (e->hi[i]) cudaStreamDestroy(e->hi[i]); if (e->ev_tree[i]) cudaEventDestroy(e->ev_tree[i]); }
     for (int k = 0; k < 2; ++k) { if (e->ev_se_out[k]) cudaEventDestroy(e->ev_se_out[k]); if (e->ev_se_mv[k]) cudaEventDestroy(e->ev_se_mv[k]); }
     if (e->learn_step && e->learn_step_free) e->learn_step_free(e->learn_step);
     mzb_nccl_release(e);

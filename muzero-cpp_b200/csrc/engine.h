@@ -68,6 +68,8 @@ struct mzb_engine {
     cudaEvent_t ev_start = nullptr, ev_root = nullptr, ev_end = nullptr, ev_aux = nullptr, ev_fork = nullptr;
     cudaEvent_t ev_join[MAX_PARTS - 1] = {};
     cudaEvent_t ev_tower[MAX_PARTS] = {};
+    cudaStream_t hi[MAX_PARTS] = {};          // high-priority streams of the parts' tree steps (MZB_TREE_PRIORITY, created on first use)
+    cudaEvent_t ev_tree[MAX_PARTS] = {};
     // CUDA graph of the pipelined simulation loop (engine_search.cu)
     cudaGraphExec_t sim_graph = nullptr; uint64_t sim_graph_key = 0, sim_graph_warm_key = 0; int64_t sim_graph_launches = 0; bool graph_failed = false;   // end of each part's latest tower kernel (alternating pipeline)
     // trees

@@ -151,6 +151,15 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
             o[k].value += t0[k]; o[k].reward += t0[k]; o[k].policy += (size_t)t0[k] * A;
         }
         int64_t loop_launches = 0;
+        static const bool tree_prio = getenv("MZB_TREE_PRIORITY") != nullptr;
+        if (tree_prio && !e->hi[0]) {
+            int lowest = 0, greatest = 0;
+            MZB_CUDA(cudaDeviceGetStreamPriorityRange(&lowest, &greatest));
+            for (int k = 0; k < mzb_engine::MAX_PARTS; ++k) {
+                MZB_CUDA(cudaStreamCreateWithPriority(&e->hi[k], cudaStreamNonBlocking, greatest));
+                MZB_CUDA(cudaEventCreateWithFlags(&e->ev_tree[k], cudaEventDisableTiming));
+            }
+        }
         // fork -> every simulation's launches on the parts' streams -> join, as one enqueue: run eagerly, or captured into a CUDA graph
         auto enqueue = [&]() -> int {
             int lrc = MZB_OK;
@@ -162,6 +171,15 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
             auto mark = [&](cudaStream_t q) { if (trace) { cudaEvent_t ev; cudaEventCreate(&ev); cudaEventRecord(ev, q); tev.push_back(ev); } };
             for (int sim = 0; sim <= n && !lrc; ++sim) {
                 for (int k = 0; k < K && !lrc; ++k) {
+                    if (tree_prio) {
+                        // EXPERIMENT (MZB_TREE_PRIORITY=1): the part's tree step on a high-priority stream of its own, chained to the
+                        // part's towers by events — its few blocks get the first SM that comes free instead of queueing behind the
+                        // other parts' pending tower CTAs
+                        MZB_CUDA(cudaStreamWaitEvent(e->hi[k], sim == 0 ? e->ev_fork : e->ev_tower[k], 0));
+                        launch_tree_step_range(td, t0[k], t0[k + 1], sim, e->hi[k]);
+                        MZB_CUDA(cudaEventRecord(e->ev_tree[k], e->hi[k]));
+                        MZB_CUDA(cudaStreamWaitEvent(st[k], e->ev_tree[k], 0));
+                    } else
                     launch_tree_step_range(td, t0[k], t0[k + 1], sim, st[k]);
                     ++loop_launches;
                     mark(st[k]);
@@ -173,6 +191,7 @@ int search_impl(mzb_engine* e, const float* d_obs, int obs_stride, const uint32_
                     if (alternate) e->net->set_tower_events((sim > 0 || k > 0) ? e->ev_tower[(k + K - 1) % K] : nullptr, e->ev_tower[k]);
                     lrc = e->net->recurrent(t0[k + 1] - t0[k], td.in_slot + t0[k], td.action + t0[k], td.out_slot + t0[k], o[k], st[k]);
                     loop_launches += e->net->launches_recurrent();
+                    if (tree_prio) MZB_CUDA(cudaEventRecord(e->ev_tower[k], st[k]));
                     mark(st[k]);
                 }
             }

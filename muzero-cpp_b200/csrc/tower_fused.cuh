@@ -259,13 +259,10 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
         const int yy = r / W1, xx = r - yy * W1;
         pixtab[r] = (r < P && yy >= 1 && yy <= a.H && xx < a.W) ? (yy - 1) * a.W + xx : -1;
     }
-    if (tid < 8) {
-        uint32_t m = 0;
-        for (int j = 0; j < 32; ++j) {
-            const int r = tid * 32 + j, yy = r / W1, xx = r - yy * W1;
-            if (r < P && yy >= 1 && yy <= a.H && xx < a.W) m |= 1u << j;
-        }
-        pixmask[tid] = m;
+    if (tid < 256) {   // one row per thread, a ballot per warp (was: 8 threads x 32 rows with two divisions each, ~1.3 k cycles in front of the first barrier)
+        const int r = tid, yy = r / W1, xx = r - yy * W1;
+        const uint32_t m = __ballot_sync(0xffffffffu, r < P && yy >= 1 && yy <= a.H && xx < a.W);
+        if (lane == 0) pixmask[tid >> 5] = m;
     }
     for (int i = tid; i < a.z_bytes / 16; i += F_THREADS) reinterpret_cast<uint4*>(Z)[i] = make_uint4(0u, 0u, 0u, 0u);
     tc_fence_before();

@@ -263,7 +263,11 @@ int mzb_search_seed(mzb_engine* e, int first_slot, int n, const int32_t* seeds);
 
 /* Replaces: T concurrent MCTS::run calls (mcts.cpp:34-87; callers self_play.cpp:130,208), tree slot t <- row t.
  * obs [T][Cin*H*W] host (SYNTHETIC evaluator: obs row = one float, the position key), legal_mask[T] bit a = action a
- * legal, to_play[T], add_noise[T].  Blocks until all T searches finished. */
+ * legal, to_play[T], add_noise[T].  Blocks until all T searches finished.
+ * The root's children are created in ASCENDING action order.  The reference creates them in the order of the caller's
+ * legal_actions vector (mcts.cpp:163-166), and that order feeds std::shuffle and the first-strict-maximum tie rule: the two agree
+ * bit for bit when the vector is strictly ascending and duplicate-free — what every AbstractGame::legal_actions() of the reference's
+ * examples returns; the C++ headers above this ABI (legal_mask_of) refuse any other vector. */
 int mzb_search_batch(mzb_engine* e, const float* obs, const uint32_t* legal_mask, const int32_t* to_play,
                      const uint8_t* add_noise, int n_trees, mzb_search_result* out);
 /* Same search with observations already resident in HBM (device pointer, engine layout = row-major fp32). */

@@ -639,6 +639,7 @@ protected:
         // the representation head conv (index 0) has its own input channel count and stays on the direct kernel
         fused_init_.args = base; fused_init_.gmax = gmax; fused_init_.smem = smem;
         fused_init_.ok = rep_init_fusable(plan, C, H, W);
+        plan_mid_chain(plan, C);
         MZB_CUDA(cudaFuncSetAttribute(fused::tower_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         MZB_CUDA(cudaFuncSetAttribute(fused::mlp_heads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         return MZB_OK;
@@ -647,6 +648,47 @@ protected:
     // The fused chain takes over the representation tower at the first step of its trailing run of residual blocks at the
     // hidden-state shape (sets init_tail_): step 1 behind the thin head conv of a board game (ResidualHeadImpl), the step behind the
     // last pooling of ResidualHeadDownsample.  What lies before runs layer by layer (conv_first / band kernels).
+    // A run of residual blocks INSIDE the representation tower (not its tail) at a shape that fits a whole-game tile — the 12x12
+    // stage of the ALE-shaped downsample head between the two poolings — runs as one fused chain as well: blocks, then a plain copy
+    // phase (PH_NORM with normalize = 0) that writes the result as a compact NHWC activation.  One launch instead of two per block.
+    void plan_mid_chain(const NetPlan& plan, int C) {
+        fused_mid_ = FusedChain(); mid_first_ = mid_end_ = 0;
+        if (getenv("MZB_NO_MID_CHAIN")) return;
+        const Tower& tw = plan.representation;
+        const size_t tail = init_tail_ ? init_tail_ : tw.steps.size();
+        for (size_t i = 1; i < tail; ++i) {
+            if (tw.steps[i].kind != TowerStep::BLOCK) continue;
+            const Conv3Host& c0 = tw.convs[tw.steps[i].conv0];
+            const int h = c0.in_h, w = c0.in_w, P = (h + 1) * (w + 1);
+            if (c0.cin != C || P > 256) continue;
+            size_t j = i;
+            auto ok = [&](const TowerStep& st) {
+                if (st.kind != TowerStep::BLOCK) return false;
+                for (int k : {st.conv0, st.conv1}) {
+                    const Conv3Host& c = tw.convs[k];
+                    if (c.stride != 1 || c.cin != C || c.cout != C || c.in_h != h || c.in_w != w || !packed_[0][k].image) return false;
+                }
+                return true;
+            };
+            while (j < tail && ok(tw.steps[j])) ++j;
+            if (j - i < 1 || 2 * (j - i) + 1 > (size_t)fused::F_MAX_PHASES) { i = j; continue; }
+            const int halo = w + 2, gmax = std::min(256 / P, fused::F_MAX_G), nmax = (gmax * P + 15) / 16 * 16;
+            int R = halo + nmax + halo;
+            if ((R & 1) == 0) ++R;
+            const int x_bytes = (int)((((size_t)(C / 8) * R * 16) + 127) / 128 * 128);
+            const size_t smem = fused::fused_smem_bytes(x_bytes, 0, P);
+            if (smem > 227 * 1024 || (fused_rec_.smem && smem > fused_rec_.smem)) return;   // (the kernel's shared-memory attribute is the main chain's)
+            fused::FusedArgs base;
+            memset(&base, 0, sizeof(base));
+            base.C = C; base.H = h; base.W = w; base.P = P; base.HALO = halo; base.R = R; base.HW = h * w; base.x_bytes = x_bytes;
+            base.normalize = 0;
+            base.dup = (C <= 64 && !getenv("MZB_FUSED_NO_DUP")) ? 1 : 0;
+            fused_mid_.args = base; fused_mid_.gmax = gmax; fused_mid_.smem = smem; fused_mid_.ok = true;
+            mid_first_ = i; mid_end_ = j;
+            return;
+        }
+    }
+
     bool rep_init_fusable(const NetPlan& plan, int C, int H, int W) {
         const Tower& tw = plan.representation;
         init_tail_ = 0;
@@ -692,8 +734,8 @@ protected:
             ph.flags |= fused::PH_TABLE;
         }
     }
-    void add_blocks(fused::FusedArgs* fa, int tower, size_t first_step) {
-        for (size_t i = first_step; i < steps_[tower].size(); ++i) {
+    void add_blocks(fused::FusedArgs* fa, int tower, size_t first_step, size_t end_step = (size_t)-1) {
+        for (size_t i = first_step; i < steps_[tower].size() && i < end_step; ++i) {
             add_conv_phase(fa, tower, steps_[tower][i].conv0, fused::PH_WRITE_X);
             add_conv_phase(fa, tower, steps_[tower][i].conv1, fused::PH_WRITE_X | fused::PH_ACC_R2 | fused::PH_STASH);
         }
@@ -765,6 +807,13 @@ protected:
             add_conv1_phase(fa, 1, 0, C);
             add_mlp_phase(fa, 1);
         }
+        if (fused_mid_.ok) {
+            fused::FusedArgs* fa = &fused_mid_.args;
+            fa->n_phases = 0; fa->preload = 1;
+            add_blocks(fa, 0, mid_first_, mid_end_);
+            add_conv1_phase(fa, -1, fused::PH_NORM, C);
+            for (int p = 0; p < fa->n_phases; ++p) fused::derive_issue_fields(fa->ph[p], fa->R, fa->W);
+        }
         for (fused::FusedArgs* fa : {&fused_rec_.args, &fused_init_.args})
             for (int p = 0; p < fa->n_phases; ++p) fused::derive_issue_fields(fa->ph[p], fa->R, fa->W);
         // reduced head inputs and MLP descriptors
@@ -790,7 +839,7 @@ protected:
     // balanced tiles: every SM gets ceil-or-floor(B / SMs) games, cut into as few tiles of <= gmax games as possible,
     // emitted wave by wave (the hardware scheduler hands out CTAs in index order)
     int tiles_for(int B, int gmax, const TileTab** out) {
-        const long key = (long)B * 2 + (pipelined_ ? 1 : 0);
+        const long key = ((long)B * 2 + (pipelined_ ? 1 : 0)) * 32 + gmax;
         auto it = tiles_.find(key);
         if (it == tiles_.end()) {
             std::vector<int> first, count;
@@ -834,13 +883,13 @@ protected:
     }
 
     int launch_fused(FusedChain& ch, int B, const bf16* in, const int* in_slot, long in_stride, const int* out_slot,
-                     const int* action, const NetOutputs& out, cudaStream_t s) {
+                     const int* action, const NetOutputs& out, cudaStream_t s, bf16* out_buf = nullptr, long out_stride = 0) {
         const TileTab* tt = nullptr;
         int rc = tiles_for(B, ch.gmax, &tt);
         if (rc) return rc;
         fused::FusedArgs a = ch.args;
         a.in = in; a.in_slot = in_slot; a.in_stride = in_stride;
-        a.pool = pool_.as<bf16>(); a.out_slot = out_slot; a.pool_stride = (long)slot_elems_;
+        a.pool = out_buf ? out_buf : pool_.as<bf16>(); a.out_slot = out_slot; a.pool_stride = out_buf ? out_stride : (long)slot_elems_;
         a.action = action;
         a.blob = reinterpret_cast<const uint8_t*>(blob_.p);
         RedSet* rs = nullptr;
@@ -1093,7 +1142,8 @@ public:
     }
 
 protected:
-    FusedChain fused_rec_, fused_init_;
+    FusedChain fused_rec_, fused_init_, fused_mid_;
+    size_t mid_first_ = 0, mid_end_ = 0;   // representation steps [mid_first_, mid_end_) run as fused_mid_
     bool fused_final_ = false;
     bool pipelined_ = false;
     cudaEvent_t ev_wait_ = nullptr, ev_record_ = nullptr;
@@ -1198,6 +1248,17 @@ protected:
         return a.N <= 256 && g2->ns >= 2 && g2->rc >= 1;
     }
     size_t act_elems(size_t mx) const override { return std::max(mx, pkm_max_elems_); }
+
+    int fast_steps(int tower, size_t si, int B, const bf16* in, bf16* out, cudaStream_t s, size_t* used) override {
+        *used = 0;
+        if (tower != 0 || !fused_mid_.ok || si != mid_first_ || cur_pkm_ || !fused_final_ || fused_mid_.args.n_phases == 0) return 0;
+        const long stride = (long)fused_mid_.args.C * fused_mid_.args.HW;
+        NetOutputs none;
+        int rc = launch_fused(fused_mid_, B, in, nullptr, stride, nullptr, nullptr, none, s, out, stride);
+        if (rc) return rc;
+        *used = mid_end_ - mid_first_;
+        return 1;
+    }
 
     int fast_pool(const bf16* in, bf16* out, int B, int C, int in_h, int in_w, int out_h, int out_w, cudaStream_t s) override {
         if (C % 8 != 0) return 0;

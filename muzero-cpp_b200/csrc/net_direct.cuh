@@ -387,6 +387,9 @@ protected:
     virtual size_t act_elems(size_t largest_activation) const { return largest_activation; }
     // same contract for AvgPool2d(3, 2, 1) on a compact NHWC activation
     virtual int fast_pool(const T*, T*, int, int, int, int, int, int, cudaStream_t) { return 0; }
+    // a run of tower steps starting at step `si` taken by one specialised launch: compact activation in -> compact activation
+    // out; *used = steps consumed (0 = not taken)
+    virtual int fast_steps(int /*tower*/, size_t /*si*/, int /*B*/, const T* /*in*/, T* /*out*/, cudaStream_t, size_t* used) { *used = 0; return 0; }
 
     static int conv_smem(int stride) { int PW = TILE * stride + 2; return (CK * PW * PW + 9 * CK * TC) * (int)sizeof(float); }
     int head_smem(int h) const { return (int)head_smem_bytes(heads_[h], head_maxw_[h], head_maxw2_[h]); }
@@ -442,6 +445,23 @@ protected:
             }
             const long compact = (long)cur_c * cur_h * cur_w;
             const long istride = cur_slot ? cur_stride : compact;
+            if (!cur_slot) {
+                size_t used = 0;
+                T* o = pick(cur, nullptr);
+                int fr = fast_steps(t, si, B, cur, o, s, &used);
+                if (fr < 0) return fr;
+                if (used > 0) {
+                    for (size_t k = si; k < si + used; ++k) {
+                        const TowerStep& sk = steps_[t][k];
+                        if (sk.kind == TowerStep::CONV) { const ConvDev& c = convs_[t][sk.conv0]; cur_c = c.cout; cur_h = c.out_h; cur_w = c.out_w; }
+                        else if (sk.kind == TowerStep::POOL) { cur_h = (cur_h + 2 - 3) / 2 + 1; cur_w = (cur_w + 2 - 3) / 2 + 1; }
+                    }
+                    ++launches_;
+                    cur = o;
+                    si += used - 1;
+                    continue;
+                }
+            }
             if (st.kind == TowerStep::CONV) {
                 const ConvDev& c = convs_[t][st.conv0];
                 T* o = pick(cur, nullptr);

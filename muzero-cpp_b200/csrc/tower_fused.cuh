@@ -491,15 +491,20 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                         for (int g = hsel; g < G; g += F_EPI_SPLIT) {
                             float* dst = dst0 + (long)(game0 + g) * gstride;
                             const int cbase = g * P;
-                            for (int c0 = 0; c0 < P; c0 += 8) {
-                                int pix[8];
-                                lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4);
-                                uint32_t v[8];
-                                tmem_ld8(t_lane + cbase + c0, v);
+                            // 16 columns per pass, the pixel map fetched while the TMEM load is in flight; 32-bit offsets (the 8-column
+                            // version was a chain of TMEM round trips with 64-bit address arithmetic per store: 8.3 k cycles per phase on
+                            // the ALE shape)
+                            const int rows4 = rows * 4;
+                            char* dstb = reinterpret_cast<char*>(dst);
+                            for (int c0 = 0; c0 < P; c0 += 16) {
+                                uint32_t v[16];
+                                tmem_ld16(t_lane + cbase + c0, v);
+                                int pix[16];
+                                lds_v4(pt + c0 * 4, pix); lds_v4(pt + c0 * 4 + 16, pix + 4); lds_v4(pt + c0 * 4 + 32, pix + 8); lds_v4(pt + c0 * 4 + 48, pix + 12);
                                 tmem_ld_wait();
 #pragma unroll
-                                for (int j = 0; j < 8; ++j)
-                                    if (pix[j] >= 0 && row_ok) dst[(long)pix[j] * rows] = __uint_as_float(v[j]) + bias;
+                                for (int j = 0; j < 16; ++j)
+                                    if (pix[j] >= 0 && row_ok) *reinterpret_cast<float*>(dstb + pix[j] * rows4) = __uint_as_float(v[j]) + bias;
                             }
                         }
                     }

@@ -768,6 +768,28 @@ protected:
         else { ph.red_head0 = 1; ph.red_n0 = heads_[1].sizes[1]; ph.red_head1 = 2; ph.red_n1 = heads_[2].sizes[1]; }
     }
 
+    // Staggered half tiles (tower_fused.cuh): a plain 3x3 layer (result -> X, no table / reduction / normalisation) ends per half
+    // tile, and the 3x3 layer behind a plain one starts per half tile.  MZB_TOWER_SPLIT="nh,nt" sets the ring slots issued per half
+    // at the head / tail of a layer ("0,0" switches the scheme off).
+    void mark_split(fused::FusedArgs* fa) {
+        static const char* env = getenv("MZB_TOWER_SPLIT");
+        int nh = 1, nt = 1;   // measured best (c4d, 4-game tiles): 1,1 0.139 ms | 2,2 0.140 | 3,3 0.141 | off 0.143 per 592 states
+        if (env) sscanf(env, "%d,%d", &nh, &nt);
+        nh = std::max(0, std::min(nh, 3)); nt = std::max(0, std::min(nt, 3));   // a half's slots stay in the ring (4 slots) until the other half has used them
+        fa->split_nh = nh; fa->split_nt = nt;
+        auto plain = [&](const fused::Phase& ph) {
+            return ph.taps == 9 && (ph.flags & fused::PH_WRITE_X) && !(ph.flags & (fused::PH_RED | fused::PH_NORM | fused::PH_MLP | fused::PH_TABLE));
+        };
+        for (int p = 0; p < fa->n_phases; ++p) {
+            fused::Phase& ph = fa->ph[p];
+            ph.flags &= ~(fused::PH_SPLIT_HEAD | fused::PH_SPLIT_TAIL);
+            const int nslots = (ph.nkb + 1) / 2;
+            if (nt == 0 || ph.taps != 9 || nslots < nh + nt + 1) continue;
+            if (plain(ph)) ph.flags |= fused::PH_SPLIT_TAIL;
+            if (nh > 0 && p > 0 && plain(fa->ph[p - 1]) && plain(ph)) ph.flags |= fused::PH_SPLIT_HEAD;
+        }
+    }
+
     int finalize_fused() {
         if (fused_final_) return MZB_OK;
         fused_final_ = true;
@@ -816,6 +838,7 @@ protected:
         }
         for (fused::FusedArgs* fa : {&fused_rec_.args, &fused_init_.args})
             for (int p = 0; p < fa->n_phases; ++p) fused::derive_issue_fields(fa->ph[p], fa->R, fa->W);
+        for (fused::FusedArgs* fa : {&fused_rec_.args, &fused_init_.args, &fused_mid_.args}) mark_split(fa);
         // reduced head inputs and MLP descriptors
         red_sets_.clear();   // reduced head inputs: one set of buffers per stream (red_for), so that the parts of a pipelined loop do not share them
         const uint8_t* blob = reinterpret_cast<const uint8_t*>(blob_.p);

@@ -54,6 +54,8 @@ enum : int {
     PH_RED = 32,      // 1x1 head convolution: rows of R1 -> red[] buffers (no activation)
     PH_NORM = 64,     // normalize_hidden_state on R2 -> X, node pool slot, R2
     PH_EARLY = 256,   // (with PH_NORM) the next phase does not read this one's output: release the MMA warp before the epilogue work
+    PH_SPLIT_HEAD = 512,   // (host-derived) the phase's first K stages may run per half tile: the previous phase's epilogue hands over games [0, G/2) early
+    PH_SPLIT_TAIL = 1024,  // (host-derived) the phase's last K stages run per half tile, so that the epilogue of games [0, G/2) starts under the other half's MMAs
     PH_MLP = 128,     // head MLPs: first layer on the tensor core (A = stacked W0 images, B = Z), later layers + output transform on CUDA cores
 };
 
@@ -105,6 +107,7 @@ struct FusedArgs {
     const int* tile_first; const int* tile_count;             // tile -> first game, number of games
     int C, H, W, P, HALO, R, HW, x_bytes;
     int n_phases, preload, normalize;
+    int split_nh, split_nt;                                   // staggered half tiles: ring slots issued per half at the head / tail of a 3x3 phase (0 = off)
     int dup;                                                  // C <= 64: weight-image rows 64-127 repeat rows 0-63, so lane quarters 2, 3 hold the same channels as 0, 1 and the four warp pairs split the GAMES four ways
     int dbg_flags;                                            // experiments: bit 0 = all taps unshifted (timing only, wrong results)
     int* dbg;                                                 // host-mapped diagnostics (barrier time-outs), may be null
@@ -232,7 +235,16 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
     uint64_t* empty = full + F_NSTAGE;
     uint64_t* accum_full = empty + F_NSTAGE;
     uint64_t* act_ready = accum_full + 1;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(act_ready + 1);
+    uint64_t* acc_half = act_ready + 1;
+    uint64_t* act_half = acc_half + 1;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(act_half + 1);
+    // Staggered half tiles (4-game tiles): the epilogue of a 3x3 layer is strictly behind its MMAs and in front of the next layer's —
+    // unless the tile is treated as two halves at the layer boundaries.  The last split_nt ring slots of a layer are issued twice, as
+    // N/2-column MMAs over games [0, G/2) and then over [G/2, G), and the first split_nh slots of the next layer likewise: the first
+    // half's epilogue runs under the second half's last MMAs, the second half's under the first half's first MMAs of the next layer.
+    // A half's MMAs read rows of the other half only for output columns that are padding (masked in every epilogue).
+    const int Nh = (G >> 1) * P;
+    const bool split = a.split_nt > 0 && !a.dup && (G & 3) == 0 && (Nh & 15) == 0 && Nh >= 112;
     int* pixtab = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(full) + 256);   // [P] row within a game -> pixel or -1
     const int PT = fused_ptab_entries(P);
     int* g_in = pixtab + PT;
@@ -246,6 +258,8 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
         for (int s = 0; s < F_NSTAGE; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         mbar_init(accum_full, 1);
         mbar_init(act_ready, F_EPI_WARPS);
+        mbar_init(acc_half, 1);
+        mbar_init(act_half, F_EPI_WARPS);
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(tmem_ptr, F_TMEM_COLS);
@@ -324,9 +338,12 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
             const uint64_t dz0 = smem_desc_kmajor_noswizzle((smem_u32(pixmask + 8) + 127u) & ~127u, 256, 128);   // = Z, in 32-bit shared-space arithmetic (uniform datapath)
             const uint32_t a_hi = (uint32_t)(da0 >> 32), x_hi = (uint32_t)(db0 >> 32), z_hi = (uint32_t)(dz0 >> 32);
             const uint32_t a_lo0 = (uint32_t)da0, b_lo0 = (uint32_t)db0, z_lo0 = (uint32_t)dz0;
-            uint32_t it = 0, ar = 0;
+            const uint32_t idescH = idesc_bf16_f32(128u, (uint32_t)(split ? Nh : N));
+            uint32_t it = 0, ar = 0, hr = 0;
             for (int p = 0; p < a.n_phases; ++p) {
-                if (p > 0 || a.preload) { mbar_wait_dbg(act_ready, ar & 1, a.dbg, 2, p); ++ar; tc_fence_after(); }
+                const bool head = split && (a.ph[p].flags & PH_SPLIT_HEAD), tail = split && (a.ph[p].flags & PH_SPLIT_TAIL);
+                if (head) { mbar_wait_dbg(act_half, hr & 1, a.dbg, 5, p); ++hr; tc_fence_after(); }
+                else if (p > 0 || a.preload) { mbar_wait_dbg(act_ready, ar & 1, a.dbg, 2, p); ++ar; tc_fence_after(); }
                 const long long t_ph = a.tim ? clock64() : 0;
                 long long w_full = 0;   // dbg_flags bit 0: the "issue" column reports the cycles spent waiting for weight slots
                 if (a.tim && leader) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 0] = t_ph;
@@ -338,8 +355,22 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                 const uint32_t kk_b = a.ph[p].kk_b;    // two 8-element K chunks per MMA, in 16-byte units
                 const uint32_t cc_b = a.ph[p].cc_b;    // eight K chunks per weight image
                 uint32_t b_cur = b_lo0 + is_mlp * (z_lo0 - b_lo0) + (uint32_t)a.ph[p].tap_off0;   // B start of the current K stage
-                int cc = 0, tx = 0;
-                for (int kb = 0; kb < nkb; ++it) {
+                int cc = 0, tx = 0, kb = 0;
+                const int nslots = (nkb + 1) >> 1, nh = head ? a.split_nh : 0, nt = tail ? a.split_nt : 0;
+                int s_cc = 0, s_tx = 0, s_kb = 0;
+                uint32_t s_b = 0, s_it = 0;
+                // segments: 0 / 1 = the first nh slots for the first / second half tile, 2 = full width, 3 / 4 = the last nt slots per half
+                for (int seg = 0; seg < 5; ++seg) {
+                const int nseg = seg < 2 ? nh : (seg == 2 ? nslots - nh - nt : nt);
+                if (nseg == 0) continue;
+                const bool first = (seg == 0) | (seg == 3), second = (seg == 1) | (seg == 4);
+                if (first) { s_cc = cc; s_tx = tx; s_kb = kb; s_b = b_cur; s_it = it; }
+                if (second) { cc = s_cc; tx = s_tx; kb = s_kb; b_cur = s_b; it = s_it; }
+                if (seg == 1) { mbar_wait_dbg(act_ready, ar & 1, a.dbg, 2, p); ++ar; tc_fence_after(); }
+                const uint32_t half_off = second ? (uint32_t)Nh : 0u;
+                const uint32_t d_seg = d_tmem + half_off;
+                const uint32_t idesc_seg = (seg == 2) ? idesc : idescH;
+                for (int js = 0; js < nseg; ++js, ++it) {
                     const uint32_t s = it % F_NSTAGE;
                     const uint32_t a_lo = a_lo0 + s * (F_STAGE_BYTES >> 4);
                     if (a.tim && (a.dbg_flags & 1)) { const long long t = clock64(); mbar_wait_dbg(&full[s], (it / F_NSTAGE) & 1, a.dbg, 3, (int)it); w_full += clock64() - t; }
@@ -353,12 +384,12 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                             // ptxas keeps the loop-carried b_cur in a vector register; an opaque lane-0 shuffle (which it knows to be
                             // warp-uniform) moves it to the uniform file ONCE per K stage instead of once per MMA
                             uint32_t ub;
-                            asm volatile("shfl.sync.idx.b32 %0, %1, 0, 0x1f, 0xffffffff;" : "=r"(ub) : "r"(b_cur));
+                            asm volatile("shfl.sync.idx.b32 %0, %1, 0, 0x1f, 0xffffffff;" : "=r"(ub) : "r"(b_cur + half_off));
                             if (leader) {
-                                mma_bf16_lohi_rt(d_tmem, ah, a_hi, ub, b_hi, idesc, acc0);
-                                mma_bf16_lohi<1>(d_tmem, ah + 256u, a_hi, ub + kk_b, b_hi, idesc);
-                                mma_bf16_lohi<1>(d_tmem, ah + 512u, a_hi, ub + 2u * kk_b, b_hi, idesc);
-                                mma_bf16_lohi<1>(d_tmem, ah + 768u, a_hi, ub + 3u * kk_b, b_hi, idesc);
+                                mma_bf16_lohi_rt(d_seg, ah, a_hi, ub, b_hi, idesc_seg, acc0);
+                                mma_bf16_lohi<1>(d_seg, ah + 256u, a_hi, ub + kk_b, b_hi, idesc_seg);
+                                mma_bf16_lohi<1>(d_seg, ah + 512u, a_hi, ub + 2u * kk_b, b_hi, idesc_seg);
+                                mma_bf16_lohi<1>(d_seg, ah + 768u, a_hi, ub + 3u * kk_b, b_hi, idesc_seg);
                             }
                             ++kb;
                             b_cur += cc_b;
@@ -369,8 +400,10 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                             }
                         }
                     }
-                    if (leader) mma_commit(&empty[s]);
+                    if (leader && !first) mma_commit(&empty[s]);
                     __syncwarp();
+                }
+                if (seg == 3 && leader) mma_commit(acc_half);
                 }
                 if (leader) {
                     if (nkb > 0) mma_commit(accum_full); else mbar_arrive(accum_full);
@@ -417,6 +450,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
             if (lane == 0) mbar_arrive(act_ready);
         }
         bool pool_pending = false;
+        uint32_t qh = 0;
         for (int p = 0; p < a.n_phases; ++p) {
             const Phase& ph = a.ph[p];
             const int flags = ph.flags;
@@ -424,7 +458,10 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
             const float bias_pf = (ph.bias_off >= 0) ? __ldg(reinterpret_cast<const float*>(a.blob + ph.bias_off) + ((flags & (PH_RED | PH_MLP)) ? row : ch)) : 0.f;
             if (flags & PH_TABLE)   // dynamics head: per-action table -> R2 (fp32) while the MMAs of this phase run into R1
                 stage_table(reinterpret_cast<const float*>(a.blob + a.table_off) + ch, g_act, pt, t_lane + (uint32_t)F_R2_COL, P, G, sel, nsplit, (long)HW * C, C, ch_ok);
-            mbar_wait_dbg(accum_full, p & 1, a.dbg, 4, p);
+            const bool tail = split && (flags & PH_SPLIT_TAIL);
+            const bool sig_half = split && p + 1 < a.n_phases && (a.ph[p + 1].flags & PH_SPLIT_HEAD);
+            if (tail) { mbar_wait_dbg(acc_half, qh & 1, a.dbg, 6, p); ++qh; }
+            else mbar_wait_dbg(accum_full, p & 1, a.dbg, 4, p);
             tc_fence_after();
             if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 2] = clock64();
             if (flags & PH_EARLY) {   // nothing the next phase reads is produced here (its inputs were fenced by the previous arrive)
@@ -594,7 +631,18 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                     const int G2 = G & ~1;
                     const int mid = skip + ((((P - skip) >> 1) + 7) & ~7);
                     const int n_mine = a.dup ? (G > sel ? (G - sel + 3) >> 2 : 0) : (G2 > hsel ? (G2 - hsel + 1) >> 1 : 0) + (G & 1);
+                    const int i_half = (tail || sig_half) ? (n_mine >> 1) : -1;
                     for (int i = 0; i < n_mine; ++i) {
+                        if (i == i_half) {   // games [0, G/2) are done: hand them to the next layer's first MMAs, then wait for the second half's accumulator
+                            if (a.tim && tid == 64 && (a.dbg_flags & 4)) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();   // diagnostic: first half done
+                            if (sig_half) {
+                                fence_proxy_async_smem();
+                                tc_fence_before();
+                                __syncwarp();
+                                if (lane == 0) mbar_arrive(act_half);
+                            }
+                            if (tail) { mbar_wait_dbg(accum_full, p & 1, a.dbg, 4, p); tc_fence_after(); }
+                        }
                         int g = a.dup ? sel + 4 * i : hsel + 2 * i, c_lo = skip, c_hi = P;
                         if (!a.dup && g >= G2) { g = G - 1; if (hsel == 0) c_hi = mid; else c_lo = mid; }
                         const int cbase = g * P;
@@ -774,7 +822,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");   // nobody overwrites X (next epilogue) before the copy is done
             }
-            if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();
+            if (a.tim && tid == 64 && !((a.dbg_flags & 4) && (tail || sig_half))) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();
         }
     }
     tc_fence_before();

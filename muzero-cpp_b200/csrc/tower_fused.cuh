@@ -599,7 +599,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
             if (!(flags & (PH_RED | PH_NORM | PH_MLP))) {
                 const uint32_t src_col = (flags & PH_ACC_R2) ? (uint32_t)F_R2_COL : 0u;
                 const float bias = ch_ok ? bias_pf : 0.f;
-                const bool relu = (flags & PH_RELU) != 0, stash = (flags & PH_STASH) != 0, wx = (flags & PH_WRITE_X) != 0 && ch_ok;
+                const bool relu = (flags & PH_RELU) != 0, stash = (flags & PH_STASH) != 0, wx = (flags & PH_WRITE_X) != 0 && ch_ok && !(a.dbg_flags & 8);   // bit 3: timing experiment, no stores into X (wrong results)
                 if (flags & PH_TABLE) {   // accumulator (R1) + staged per-action table (R2), 16 columns at a time
                     for (int g = sel; g < G; g += nsplit) {
                         const int cbase = g * P;

@@ -45,9 +45,9 @@ eng.close()
 """
 
 
-def _run(tmp_path, tag, env_value, game, T, sims):
+def _run(tmp_path, tag, env_value, game, T, sims, **extra_env):
     out = str(tmp_path / ("%s.npz" % tag))
-    env = dict(os.environ, MZB_PIPELINE_MIN_TREES=str(env_value))
+    env = dict(os.environ, MZB_PIPELINE_MIN_TREES=str(env_value), **extra_env)
     proc = subprocess.run([sys.executable, "-c", SCRIPT, ROOT, out, game, str(T), str(sims)], env=env, capture_output=True, text=True, timeout=600)
     assert proc.returncode == 0, proc.stderr[-2000:]
     return np.load(out)
@@ -63,3 +63,15 @@ def test_pipelined_loop_is_bit_identical_to_single_stream(tmp_path, game, T, sim
             continue
         assert np.array_equal(single[k], piped[k]), "pipelined search differs from the single-stream search in %s" % k
     assert (piped["visits1"].sum(axis=1) == sims).all()
+
+
+@pytest.mark.parametrize("game,T,sims", [("c4d", 64, 10), ("ale", 40, 6)])
+def test_staggered_half_tiles_are_bit_identical_to_the_unsplit_tower(tmp_path, game, T, sims):
+    """tower_fused_kernel issues the first / last ring slots of a 3x3 layer per half tile (games {0,1}, then {2,3}) so that a half's
+    epilogue runs under the other half's MMAs.  The per-column accumulation order is untouched, so whole searches — recorded network
+    outputs included — must not change by a bit, whatever the number of slots per half (pipelined cohorts: every tile holds 4 games)."""
+    off = _run(tmp_path, "off", 2, game, T, sims, MZB_TOWER_SPLIT="0,0")
+    for spec in ("1,1", "3,2"):
+        on = _run(tmp_path, "on" + spec.replace(",", "_"), 2, game, T, sims, MZB_TOWER_SPLIT=spec)
+        for k in off.files:
+            assert np.array_equal(off[k], on[k]), "split %s differs from the unsplit kernel in %s" % (spec, k)

@@ -36,7 +36,16 @@ using namespace umma;
 constexpr int F_EPI_WARPS = 8;        // 2 per TMEM lane quarter (16 measured no faster: the epilogue is issue-bound); a warp owns games g = e (mod 2)
 constexpr int F_EPI_THREADS = 32 * F_EPI_WARPS;
 constexpr int F_EPI_SPLIT = F_EPI_WARPS / 4;
-constexpr int F_THREADS = 64 + F_EPI_THREADS;   // warp 0: weight producer, warp 1: MMA issuer + TMEM owner, the rest: epilogue
+// Three warpgroups: warps 0-3 = service (0: weight producer, 1: MMA issuer + TMEM owner, 2-3 idle), warps 4-11 = epilogue.  The CTA is
+// launched at 168 registers per thread (384 x 168 = the whole register file) and redistributes them with setmaxnreg: the service
+// group shrinks to F_SVC_REGS, the two epilogue groups grow to F_EPI_REGS (per SM sub-partition: 72 + 2 x 216 = 504 <= 512).
+// With 10 warps (3 on one sub-partition) every warp was held at 168 registers, which every deeper epilogue variant overflowed.
+constexpr int F_SVC_THREADS = 128;
+#ifndef MZB_SVC_REGS
+#define MZB_SVC_REGS 72
+#endif
+constexpr int F_SVC_REGS = MZB_SVC_REGS, F_EPI_REGS = (512 - 8 - MZB_SVC_REGS) / 2 / 8 * 8;
+constexpr int F_THREADS = F_SVC_THREADS + F_EPI_THREADS;
 constexpr int F_NSTAGE = 4;                   // ring slots of two 64-K weight images each
 constexpr int F_KB_BYTES = 64 * 128 * 2;      // one weight image: 64 K x 128 cout, bf16 (16 KB)
 constexpr int F_STAGE_BYTES = 2 * F_KB_BYTES; // a ring slot = 128 K: halves the issuer's wait/commit overhead per MMA
@@ -185,7 +194,12 @@ __device__ __forceinline__ void epi_store16(uint32_t* v, float bias, uint32_t m,
 // Per-action table of the dynamics head -> R2 (fp32), for the games of one epilogue warp.  All of a game's loads are issued
 // before the first is used: the L2 latency is paid once per 64 columns, not once per 8-column chunk.  Kept out of line so that its
 // 64 staging registers do not weigh on the register allocation of the per-layer epilogue.
-__device__ __noinline__ void stage_table(const float* table_ch, const int* g_act, uint32_t pt, uint32_t t_r2, int P, int G, int sel, int nsplit, long a_stride, int C, bool ch_ok) {
+#ifdef MZB_TABLE_INLINE
+__device__ __forceinline__
+#else
+__device__ __noinline__
+#endif
+void stage_table(const float* table_ch, const int* g_act, uint32_t pt, uint32_t t_r2, int P, int G, int sel, int nsplit, long a_stride, int C, bool ch_ok) {
     for (int g = sel; g < G; g += nsplit) {
         const float* tg = table_ch + (long)g_act[g] * a_stride;
         for (int cb = 0; cb < P; cb += 64) {
@@ -308,6 +322,9 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
     tc_fence_after();
     if (a.tim && tid == 0) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 1) * 4 + 3] = clock64();   // chain input (and table) resident
 
+    // (each role's code is dominated by its own setmaxnreg: ptxas allocates registers per region only then)
+    if (warp < F_SVC_THREADS / 32) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(F_SVC_REGS));
     if (warp == 0) {
         if (lane == 0) {   // ===== weight producer: every stage of every phase, in order, as far ahead as the ring allows =====
             uint32_t it = 0;
@@ -414,12 +431,14 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                 __syncwarp();
             }
         }
+    }
     } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(F_EPI_REGS));
         // ===== epilogue warps: lane quarter q (hardware rule: warp id % 4), games of parity hsel =====
         // Every TMEM access below is a warp-collective: all control flow around it is warp-uniform, lanes are only
         // predicated on their stores.  The pixel map of a chunk is fetched BEFORE its stores (two 16-byte shared loads),
         // so the eight bf16 stores of a chunk issue back to back instead of alternating with dependent table look-ups.
-        const int q = warp & 3, hsel = (warp - 2) >> 2;   // hsel in [0, F_EPI_SPLIT)
+        const int q = warp & 3, hsel = (warp - F_SVC_THREADS / 32) >> 2;   // hsel in [0, F_EPI_SPLIT)
         // `row` = accumulator lane = weight-image row.  For the 3x3 phases it is the output channel, except with duplicated rows
         // (a.dup, C <= 64): there quarters 2, 3 repeat the channels of quarters 0, 1 and take other games — all eight warps
         // work on a 64-channel layer instead of four (its epilogue halves).  `sel` / `nsplit` = which games this warp owns.
@@ -465,7 +484,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
             if (tail) { mbar_wait_dbg(acc_half, qh & 1, a.dbg, 6, p); ++qh; }
             else mbar_wait_dbg(accum_full, p & 1, a.dbg, 4, p);
             tc_fence_after();
-            if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 2] = clock64();
+            if (a.tim && tid == F_SVC_THREADS) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 2] = clock64();
             if (flags & PH_EARLY) {   // nothing the next phase reads is produced here (its inputs were fenced by the previous arrive)
                 tc_fence_before();
                 __syncwarp();
@@ -642,7 +661,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                         int g = a.dup ? sel + 4 * i : hsel + 2 * i, c_lo = skip, c_hi = P;
                         if (!crossed && (i == n_mine || g >= g_half)) {
                             crossed = true;
-                            if (a.tim && tid == 64 && (a.dbg_flags & 4)) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();   // diagnostic: first half done
+                            if (a.tim && tid == F_SVC_THREADS && (a.dbg_flags & 4)) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();   // diagnostic: first half done
                             if (sig_half) {
                                 fence_proxy_async_smem();
                                 tc_fence_before();
@@ -709,8 +728,8 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                 // remaining layers (model_layers.cpp:46-65) and the output transform on CUDA cores, overlapped with the next
                 // phase's MMAs: policy softmax (vprnet.cpp:118-119,178-179) / ValueEncoder::decode (util.cpp:80-87)
                 asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");
-                if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 2) * 4 + 0] = clock64();
-                const int et = tid - 64;
+                if (a.tim && tid == F_SVC_THREADS) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 2) * 4 + 0] = clock64();
+                const int et = tid - F_SVC_THREADS;
                 const int nh = ph.red_n1 > 0 ? 2 : 1;
                 float* cur = Hs;
                 float* nxt = Hs + 8 * 128;
@@ -750,11 +769,11 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                     asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");
                     float* t = cur; cur = nxt; nxt = t;
                 }
-                if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 2) * 4 + 1] = clock64();
+                if (a.tim && tid == F_SVC_THREADS) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 2) * 4 + 1] = clock64();
                 // output transform, one warp per (game, head), lane = logit: softmax by warp reductions (vprnet.cpp:118-119,
                 // 178-179) / expected support value + inverse contractive map (util.cpp:80-87).  Heads wider than a warp take the
                 // serial form on one lane.
-                for (int item = (tid - 64) >> 5; item < G * nh; item += F_EPI_WARPS) {   // warp-uniform
+                for (int item = (tid - F_SVC_THREADS) >> 5; item < G * nh; item += F_EPI_WARPS) {   // warp-uniform
                     const int g = item / nh, hh = item - g * nh;
                     const HeadTail& hd = a.head[hh ? ph.red_head1 : ph.red_head0];
                     const int n = hd.sizes[n_layers];
@@ -811,7 +830,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                         }
                     }
                 }
-                if (a.tim && tid == 64) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 2) * 4 + 2] = clock64();
+                if (a.tim && tid == F_SVC_THREADS) a.tim[((long)blockIdx.x * F_MAX_PHASES + F_MAX_PHASES - 2) * 4 + 2] = clock64();
                 asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");   // Hs is free again
             }
             if (flags & PH_EARLY) pool_pending = true;   // the copy below would sit on the critical path: do it after the next arrive
@@ -820,7 +839,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                 // child hidden state -> node pool, straight from X (bf16, already normalised): 16-byte coalesced stores,
                 // overlapped with the next phase's MMAs (which only read X)
                 asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");   // every epilogue warp has finished writing X
-                const int et = tid - 64;
+                const int et = tid - F_SVC_THREADS;
                 const int kc = et % KC, rsub = et / KC, rstep = F_EPI_THREADS / KC;   // a thread keeps its 8-channel chunk; rows stride
                 const uint32_t xk = smem_u32(X) + (uint32_t)((kc * R + HALO) * 16);
                 for (int g = 0; g < G; ++g) {
@@ -832,7 +851,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(F_EPI_THREADS) : "memory");   // nobody overwrites X (next epilogue) before the copy is done
             }
-            if (a.tim && tid == 64 && !((a.dbg_flags & 4) && (tail || sig_half))) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();
+            if (a.tim && tid == F_SVC_THREADS && !((a.dbg_flags & 4) && (tail || sig_half))) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();
         }
     }
     tc_fence_before();

@@ -221,10 +221,9 @@ void stage_table(const float* table_ch, const int* g_act, uint32_t pt, uint32_t 
     tmem_st_wait();
 }
 
-// Register budget: the register file is per SM sub-partition (16 K registers each) and this CTA's 10 warps sit 3 + 3 + 2 + 2 on
-// the four of them, so at the 168 registers ptxas takes a tree-step block (one warp per sub-partition, 56 registers) does NOT
-// fit beside a tower CTA (tools/coreside_probe.cu); it runs on the SMs a half-cohort launch leaves free.  -DMZB_TOWER_MAXNREG=152
-// makes the two co-resident at the cost of ~110 bytes of spills (tower +1 %); measured no faster in the search.
+// Register budget: 384 threads x 168 registers = the SM's whole register file (the launch allocation; setmaxnreg then moves
+// registers from the service warpgroup to the epilogue warpgroups).  A tree-step block therefore never fits beside a tower CTA
+// (tools/coreside_probe.cu): it runs on the SMs a half-cohort launch leaves free.
 // __maxnreg__ and __launch_bounds__ exclude each other.
 #ifndef MZB_TOWER_MAXNREG
 #define MZB_TOWER_MAXNREG 168

@@ -575,13 +575,14 @@ protected:
         // geometry: as many games per tile as 256 accumulator columns hold; the in-kernel head MLPs (first layer on the tensor
         // core, one launch per inference) need <= 8 games per tile and stacked widths <= 128, and are preferred over wider tiles
         const HeadHost& hR = plan.reward_head; const HeadHost& hP = plan.policy_head; const HeadHost& hV = plan.value_head;
-        const int halo = W + 2;
+        static const bool align8 = getenv("MZB_X_ALIGN8") != nullptr;   // experiment: 128-byte aligned K-chunk planes and game blocks (what a tensor-map copy of the chain input would need)
+        const int halo = align8 ? (W + 2 + 7) / 8 * 8 : W + 2;
         int gmax = 0, R = 0, x_bytes = 0, z_bytes = 0, z_rp = 0;
         auto geometry = [&](int g) {
             gmax = g;
             const int nmax = (gmax * P + 15) / 16 * 16;
-            R = halo + nmax + halo;
-            if ((R & 1) == 0) ++R;
+            R = halo + nmax + (align8 ? (W + 1 + 7) / 8 * 8 : halo);
+            if (!align8 && (R & 1) == 0) ++R;
             x_bytes = (int)((((size_t)(C / 8) * R * 16) + 127) / 128 * 128);
         };
         {

@@ -1,10 +1,13 @@
 #!/bin/bash
-# three warpgroups + setmaxnreg (service 72 / epilogue 216 registers): parity tests, pass times
-timeout 900 python -m pytest tests/test_gpu_net.py tests/test_gpu_pipeline.py tests/test_gpu_e2e.py -x -q 2>&1 | tail -3
+# experiment: X with 128-byte aligned planes (R multiple of 8): what do the epilogue's bank conflicts cost?
 for rep in 1 2; do
-for spec in "c4d 592" "c4d 1024" "ale 1024" "c4r 1024" "ttt 1024"; do set -- $spec
-  timeout 300 python tools/profile_recurrent.py $1 $2 300 2>&1 | grep recurrent | sed "s/^/dblbuf   $1 T=$2 /"
-  MZB200_LIB=$PWD/tools/bin/libmzb200_base.so timeout 300 python tools/profile_recurrent.py $1 $2 300 2>&1 | grep recurrent | sed "s/^/base     $1 T=$2 /"
+for al in 0 1; do
+  if [ $al = 1 ]; then export MZB_X_ALIGN8=1; else unset MZB_X_ALIGN8; fi
+  for spec in "c4d 592" "c4d 1024"; do set -- $spec
+    timeout 300 python tools/profile_recurrent.py $1 $2 300 2>&1 | grep -E "recurrent|rror" | sed "s/^/align8=$al $1 T=$2 /"
+  done
 done
 done
-MZB_FUSED_TIMING=1 timeout 300 python tools/profile_recurrent.py c4d 592 2 2>&1 | grep "fused" | tail -24 | head -9
+export MZB_X_ALIGN8=1
+MZB_FUSED_TIMING=1 timeout 300 python tools/profile_recurrent.py c4d 592 2 2>&1 | grep "fused" | tail -24 | head -6
+timeout 600 python -m pytest tests/test_gpu_net.py -x -q -k "c4d or c4r" 2>&1 | tail -2

@@ -1032,7 +1032,7 @@ protected:
         // split the first layer's K range over several CTAs when it is long (ALE shape: 2304 inputs = 72 K tiles, a latency
         // chain of ~1.3 us per tile on one CTA); a fixed function of the layer size, so results do not depend on the batch
         static const int split_env = getenv("MZB_MLP_SPLITS") ? atoi(getenv("MZB_MLP_SPLITS")) : 0;
-        m.splits = split_env > 0 ? std::min(split_env, MLP_SPLITS_MAX) : (n0max >= 1024 ? 4 : 1);
+        m.splits = split_env > 0 ? std::min(split_env, MLP_SPLITS_MAX) : (n0max >= 1024 ? 8 : 1);   // 2 / 4 / 6 / 8 splits: 0.328 / 0.329 / 0.322 / 0.322 ms per ALE-shaped recurrent pass of 1024 states
         m.part = rs->part.as<float>(); m.part_head_stride = (long)MLP_SPLITS_MAX * max_batch_ * 256; m.counter = rs->counter.as<int>();
         const size_t smem = ((size_t)mlp_mg_ * 512 + 16 * (fused::MLP_KT + 4) + fused::MLP_KT * 64 + fused::MLP_WT) * sizeof(float);
         (void)n0max;

@@ -649,7 +649,10 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                     // boundary and shared, so that a 3-game tile's epilogue costs 1.5 games per warp, not 2.
                     static_assert(F_EPI_SPLIT == 2, "the column split below assumes two warp halves");
                     const int G2 = G & ~1;
-                    const int mid = skip + ((((P - skip) >> 1) + 7) & ~7);
+                    // ... and nothing behind a game's last real pixel either (6x6 board: 7 x 7 = 49 rows padded to P = 56, last pixel at
+                    // row 47 -> 48 of 56 columns)
+                    const int c_end = min(P, (a.H * W1 + a.W + 7) & ~7);
+                    const int mid = skip + ((((c_end - skip) >> 1) + 7) & ~7);
                     const int n_mine = a.dup ? (G > sel ? (G - sel + 3) >> 2 : 0) : (G2 > hsel ? (G2 - hsel + 1) >> 1 : 0) + (G & 1);
                     // staggered half tiles: a warp takes its games in ascending order; before its first game of the second half
                     // (or after its last game, if it has none there) it hands the first half to the next layer's MMAs, then waits
@@ -657,7 +660,7 @@ __global__ void __maxnreg__(MZB_TOWER_MAXNREG) tower_fused_kernel(const __grid_c
                     bool crossed = !(tail || sig_half);
                     const int g_half = G >> 1;
                     for (int i = 0; i <= n_mine; ++i) {
-                        int g = a.dup ? sel + 4 * i : hsel + 2 * i, c_lo = skip, c_hi = P;
+                        int g = a.dup ? sel + 4 * i : hsel + 2 * i, c_lo = skip, c_hi = c_end;
                         if (!crossed && (i == n_mine || g >= g_half)) {
                             crossed = true;
                             if (a.tim && tid == F_SVC_THREADS && (a.dbg_flags & 4)) a.tim[((long)blockIdx.x * F_MAX_PHASES + p) * 4 + 3] = clock64();   // diagnostic: first half done
